@@ -1,0 +1,204 @@
+/*
+ * strus_pattern_b200.h -- C ABI of the B200-native strusPattern hot path.
+ *
+ * This is the drop-in boundary: plain C, plain pointers and sizes, int return codes
+ * (0 = ok, <0 = error, message via sp_*_last_error). The C++ strus interface classes
+ * (PatternLexer*Interface / PatternMatcher*Interface, struspattern_b200/csrc/strus_iface.cpp)
+ * and the python harness (struspattern_b200/capi.py) are thin layers over these calls.
+ * Every entry point names the reference interface (file:line under the strusPattern
+ * source tree) it replaces.
+ *
+ * There is no CPU fallback behind this ABI: every scan/run call launches sm_100a kernels
+ * and fails with SP_ERR_CUDA when no device is usable.
+ */
+#ifndef STRUS_PATTERN_B200_H_INCLUDED
+#define STRUS_PATTERN_B200_H_INCLUDED
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SP_OK            0
+#define SP_ERR_ARGUMENT -1   /* bad argument / call in wrong state (reference: runtime_error -> report) */
+#define SP_ERR_SYNTAX   -2   /* regex not compilable (reference: hyperscanErrorCode(HS_COMPILER_ERROR)) */
+#define SP_ERR_NOMEM    -3
+#define SP_ERR_CUDA     -4   /* no device, launch failure */
+#define SP_ERR_RUNTIME  -5   /* per-document runtime error (e.g. token >= 65535 bytes, arena overflow) */
+#define SP_ERR_UNSUPPORTED -6
+
+/* analyzer::PositionBind (strus/analyzer/positionBind.hpp) */
+#define SP_BIND_CONTENT     0
+#define SP_BIND_SUCCESSOR   1
+#define SP_BIND_PREDECESSOR 2
+#define SP_BIND_UNIQUE      3
+
+/* PatternMatcherInstanceInterface::JoinOperation */
+#define SP_OP_SEQUENCE        0
+#define SP_OP_SEQUENCE_IMM    1
+#define SP_OP_SEQUENCE_STRUCT 2
+#define SP_OP_WITHIN          3
+#define SP_OP_WITHIN_STRUCT   4
+#define SP_OP_ANY             5
+#define SP_OP_AND             6
+
+/* One lexem = analyzer::PatternLexem(id, ordpos, Position(seg, origpos), origsize).
+ * The lexer always emits segment 0 (src/patternLexer.cpp:908); callers that feed several
+ * segments to the matcher pass the segment numbers in a parallel array. 16 bytes, so a
+ * warp reads/writes lexem records with 16-byte vector accesses. */
+typedef struct sp_lexem
+{
+	uint32_t id;
+	uint32_t ordpos;
+	uint32_t origpos;
+	uint32_t origsize;
+} sp_lexem;
+
+/* One result = analyzer::PatternMatcherResult (src/patternMatcher.cpp:248-269). */
+typedef struct sp_result
+{
+	uint32_t name;        /* pattern handle: sp_matcher_pattern_name(m, name) */
+	uint32_t format;      /* format handle (0 = none) */
+	uint32_t ordpos;
+	uint32_t ordend;
+	uint32_t origseg;
+	uint32_t origpos;
+	uint32_t endseg;
+	uint32_t endpos;
+	uint32_t item_begin;  /* index of the first item, relative to the document's item range */
+	uint32_t item_count;
+} sp_result;
+
+/* One result item = analyzer::PatternMatcherResultItem (src/patternMatcher.cpp:164-190). */
+typedef struct sp_item
+{
+	uint32_t variable;    /* variable handle: sp_matcher_variable_name(m, variable) */
+	uint32_t format;
+	uint32_t ordpos;
+	uint32_t ordend;
+	uint32_t origseg;
+	uint32_t origpos;
+	uint32_t endseg;
+	uint32_t endpos;
+} sp_item;
+
+/* Per-document statistics = PatternMatcherContext::getStatistics (src/patternMatcher.cpp:303-318). */
+typedef struct sp_matcher_stats
+{
+	uint64_t nof_programs_installed;
+	uint64_t nof_altkey_programs_installed;
+	uint64_t nof_signals_fired;
+	uint64_t nof_open_patterns;   /* sum over events of live triggers (reference: double accumulator) */
+	uint64_t nof_events;          /* number of putInput calls */
+} sp_matcher_stats;
+
+/* ---------------------------------------------------------------------------------------
+ * Level 1: regex lexer.  Replaces PatternLexerInstance / PatternLexerContext
+ * (src/patternLexer.cpp:961-1151, 681-959) and the Hyperscan database behind them.
+ * ------------------------------------------------------------------------------------- */
+typedef struct sp_lexer sp_lexer;          /* = PatternLexerInstanceInterface */
+typedef struct sp_lexer_ctx sp_lexer_ctx;  /* = PatternLexerContextInterface, batched */
+
+/* PatternLexer::createInstance, src/patternLexer.cpp:1165 */
+sp_lexer* sp_lexer_create(void);
+void sp_lexer_destroy( sp_lexer* lx);
+const char* sp_lexer_last_error( const sp_lexer* lx);
+/* PatternLexerInstance::defineOption, src/patternLexer.cpp:1031 (CASELESS DOTALL MULTILINE ALLOWEMPTY UCP BYTECHAR) */
+int sp_lexer_define_option( sp_lexer* lx, const char* name, double value);
+/* PatternLexerInstance::defineLexem, src/patternLexer.cpp:990 -> PatternTable::definePattern :245 */
+int sp_lexer_define_lexem( sp_lexer* lx, uint32_t id, const char* expression, size_t expression_len,
+			   uint32_t result_index, uint32_t level, uint32_t posbind);
+/* PatternLexerInstance::defineSymbol, src/patternLexer.cpp:1008 -> PatternTable::defineSymbol :264 */
+int sp_lexer_define_symbol( sp_lexer* lx, uint32_t symbolid, uint32_t lexemid, const char* name, size_t name_len);
+/* PatternLexerInstance::getSymbol, src/patternLexer.cpp:1020 (0 = not defined) */
+uint32_t sp_lexer_get_symbol( const sp_lexer* lx, uint32_t lexemid, const char* name, size_t name_len);
+/* PatternLexerInstance::compile, src/patternLexer.cpp:1068 (replaces hs_compile_ext_multi :1083);
+ * builds the transition tables on the host and uploads them to the current CUDA device. */
+int sp_lexer_compile( sp_lexer* lx);
+/* Introspection of the compiled tables (DESIGN.md "lexer tables"); values by key name, -1 if unknown. */
+int64_t sp_lexer_table_info( const sp_lexer* lx, const char* key);
+
+/* PatternLexerInstance::createContext, src/patternLexer.cpp:1120: scratch + output buffers of one
+ * in-flight batch. cuda_stream is a cudaStream_t (NULL = default stream). */
+sp_lexer_ctx* sp_lexer_ctx_create( const sp_lexer* lx, void* cuda_stream);
+void sp_lexer_ctx_destroy( sp_lexer_ctx* ctx);
+const char* sp_lexer_ctx_last_error( const sp_lexer_ctx* ctx);
+
+/* PatternLexerContext::match (src/patternLexer.cpp:858) for a batch of documents laid out
+ * back to back: document d is text[doc_offsets[d] .. doc_offsets[d+1]). doc_offsets is a host
+ * array of ndocs+1 entries. text_on_device != 0: text is a device pointer (inputs resident in
+ * HBM); else a host pointer that is copied to the device inside the call.
+ * Asynchronous on the context's stream; results stay on the device until fetched. */
+int sp_lexer_scan( sp_lexer_ctx* ctx, const uint8_t* text, int text_on_device,
+		   const uint64_t* doc_offsets, uint32_t ndocs);
+/* Blocks until the scan finished; returns total number of lexems (or <0 on error). */
+int64_t sp_lexer_result_count( sp_lexer_ctx* ctx);
+/* Device views of the last scan's output (valid until the next scan on this context). */
+const sp_lexem* sp_lexer_result_lexems_device( sp_lexer_ctx* ctx);
+const uint64_t* sp_lexer_result_offsets_device( sp_lexer_ctx* ctx);   /* ndocs+1 */
+const uint32_t* sp_lexer_result_status_device( sp_lexer_ctx* ctx);    /* ndocs, 0 = ok else SP_ERR_* (positive) */
+/* Copy results to host arrays: lexems[count], offsets[ndocs+1], status[ndocs] (each may be NULL). */
+int sp_lexer_fetch( sp_lexer_ctx* ctx, sp_lexem* lexems, uint64_t* offsets, uint32_t* status);
+/* Counters of the last scan (for roofline accounting): "raw_events", "lexems", "chunks",
+ * "fixup_chunks", "text_bytes". */
+int64_t sp_lexer_ctx_counter( sp_lexer_ctx* ctx, const char* key);
+
+/* ---------------------------------------------------------------------------------------
+ * Level 2: token pattern matcher.  Replaces PatternMatcherInstance / PatternMatcherContext
+ * (src/patternMatcher.cpp:345-704, 107-341) and ProgramTable / StateMachine
+ * (src/ruleMatcherAutomaton.cpp:259-586, 589-1334).
+ * ------------------------------------------------------------------------------------- */
+typedef struct sp_matcher sp_matcher;          /* = PatternMatcherInstanceInterface */
+typedef struct sp_matcher_ctx sp_matcher_ctx;  /* = PatternMatcherContextInterface, batched */
+
+sp_matcher* sp_matcher_create(void);                                          /* src/patternMatcher.cpp:718 */
+void sp_matcher_destroy( sp_matcher* m);
+const char* sp_matcher_last_error( const sp_matcher* m);
+int sp_matcher_define_option( sp_matcher* m, const char* name, double value);  /* :614 */
+int sp_matcher_define_term_frequency( sp_matcher* m, uint32_t termid, double df); /* :361 */
+int sp_matcher_push_term( sp_matcher* m, uint32_t termid);                    /* :366 */
+int sp_matcher_push_expression( sp_matcher* m, int joinop, size_t argc, uint32_t range, uint32_t cardinality); /* :377 */
+int sp_matcher_push_pattern( sp_matcher* m, const char* name);                /* :510 */
+int sp_matcher_attach_variable( sp_matcher* m, const char* name);             /* :522 */
+int sp_matcher_define_pattern( sp_matcher* m, const char* name, const char* formatstring, int visible); /* :545 */
+/* PatternMatcherInstance::compile (:646): ProgramTable::optimize (src/ruleMatcherAutomaton.cpp:512). */
+int sp_matcher_compile( sp_matcher* m);
+/* Flatten the rule graph into device tables and upload them to the current device. Called
+ * implicitly by sp_matcher_ctx_create; explicit call allowed (idempotent until the next define). */
+int sp_matcher_upload( sp_matcher* m);
+const char* sp_matcher_pattern_name( const sp_matcher* m, uint32_t handle);    /* patternMap.key, :250 */
+const char* sp_matcher_variable_name( const sp_matcher* m, uint32_t handle);   /* variableMap.key, :170 */
+int64_t sp_matcher_table_info( const sp_matcher* m, const char* key);
+
+sp_matcher_ctx* sp_matcher_ctx_create( sp_matcher* m, void* cuda_stream);      /* :586 */
+void sp_matcher_ctx_destroy( sp_matcher_ctx* ctx);
+const char* sp_matcher_ctx_last_error( const sp_matcher_ctx* ctx);
+/* putInput for every token of every document + fetchResults (:131, :271). Document d owns
+ * tokens[tok_offsets[d] .. tok_offsets[d+1]); tokens must be in non-decreasing ordpos order per
+ * document (violations give status SP_ERR_RUNTIME for that document, like the reference's
+ * "term events not fed in ascending order"). origsegs may be NULL (all zero).
+ * on_device != 0: tokens/origsegs/tok_offsets are device pointers, else host pointers. */
+int sp_matcher_run( sp_matcher_ctx* ctx, const sp_lexem* tokens, const uint32_t* origsegs,
+		    const uint64_t* tok_offsets, uint32_t ndocs, int on_device);
+/* Blocks; total results / items of the last run. */
+int64_t sp_matcher_result_count( sp_matcher_ctx* ctx);
+int64_t sp_matcher_item_count( sp_matcher_ctx* ctx);
+const sp_result* sp_matcher_results_device( sp_matcher_ctx* ctx);
+const sp_item* sp_matcher_items_device( sp_matcher_ctx* ctx);
+/* Copy to host: results[nres], result_offsets[ndocs+1], items[nitems], item_offsets[ndocs+1],
+ * stats[ndocs], status[ndocs]; each may be NULL. */
+int sp_matcher_fetch( sp_matcher_ctx* ctx, sp_result* results, uint64_t* result_offsets,
+		      sp_item* items, uint64_t* item_offsets, sp_matcher_stats* stats, uint32_t* status);
+
+/* Fused pipeline: lexems of a finished sp_lexer_scan are fed to the matcher without leaving the device. */
+int sp_matcher_run_lexer_output( sp_matcher_ctx* ctx, sp_lexer_ctx* lexer_ctx);
+
+/* Library identification. */
+const char* sp_version(void);
+int sp_device_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

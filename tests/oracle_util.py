@@ -1,0 +1,136 @@
+"""ctypes bindings of the ORACLE libraries (oracle/_ref/*.so). Test infrastructure only:
+nothing under struspattern_b200/ may import this module."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+REF_DIR = os.path.join(ORACLE_DIR, "_ref")
+
+LEXEM_DT = np.dtype([("id", "<u4"), ("ordpos", "<u4"), ("origpos", "<u4"), ("origsize", "<u4")])
+RESULT_DT = np.dtype([(n, "<u4") for n in ("name", "format", "ordpos", "ordend", "origseg", "origpos",
+                                            "endseg", "endpos", "item_begin", "item_count")])
+ITEM_DT = np.dtype([(n, "<u4") for n in ("variable", "format", "ordpos", "ordend", "origseg", "origpos",
+                                          "endseg", "endpos")])
+STATS_DT = np.dtype([(n, "<u8") for n in ("nof_programs_installed", "nof_altkey_programs_installed",
+                                           "nof_signals_fired", "nof_open_patterns", "nof_events")])
+
+
+def build_oracle():
+    """Build the oracle libraries when a compiler is around (no-op if they are up to date)."""
+    subprocess.run(["make", "-s", "-C", ORACLE_DIR, "all"], check=True, stdout=subprocess.DEVNULL)
+
+
+def _ptr(a, t=C.c_void_p):
+    return a.ctypes.data_as(t) if a is not None else None
+
+
+class RefMatcher:
+    """The reference's own PatternMatcher (libsp_ref_matcher.so), driven like its tests do."""
+
+    _lib = None
+
+    @classmethod
+    def lib(cls):
+        if cls._lib is None:
+            path = os.path.join(REF_DIR, "libsp_ref_matcher.so")
+            if not os.path.exists(path):
+                build_oracle()
+            L = C.CDLL(path)
+            L.refm_create.restype = C.c_void_p
+            L.refm_last_error.restype = C.c_char_p
+            L.refm_name.restype = C.c_char_p
+            L.refm_result_count.restype = C.c_uint64
+            L.refm_item_count.restype = C.c_uint64
+            for f in ("refm_destroy", "refm_last_error", "refm_define_option", "refm_define_term_frequency",
+                      "refm_push_term", "refm_push_expression", "refm_push_pattern", "refm_attach_variable",
+                      "refm_define_pattern", "refm_compile", "refm_run_batch", "refm_result_count",
+                      "refm_item_count", "refm_fetch", "refm_name"):
+                getattr(L, f).argtypes = None
+            cls._lib = L
+        return cls._lib
+
+    def __init__(self):
+        self.L = self.lib()
+        self.h = C.c_void_p(self.L.refm_create())
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.refm_destroy(self.h)
+            self.h = None
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise RuntimeError(self.L.refm_last_error(self.h).decode())
+
+    def define_option(self, name, value=0.0):
+        self._ck(self.L.refm_define_option(self.h, name.encode(), C.c_double(value)))
+
+    def define_term_frequency(self, termid, df):
+        self._ck(self.L.refm_define_term_frequency(self.h, C.c_uint32(termid), C.c_double(df)))
+
+    def push_term(self, termid):
+        self._ck(self.L.refm_push_term(self.h, C.c_uint32(termid)))
+
+    def push_expression(self, op, argc, rng, card):
+        self._ck(self.L.refm_push_expression(self.h, C.c_int(op), C.c_size_t(argc), C.c_uint32(rng), C.c_uint32(card)))
+
+    def push_pattern(self, name):
+        self._ck(self.L.refm_push_pattern(self.h, name.encode()))
+
+    def attach_variable(self, name):
+        self._ck(self.L.refm_attach_variable(self.h, name.encode()))
+
+    def define_pattern(self, name, fmt="", visible=True):
+        self._ck(self.L.refm_define_pattern(self.h, name.encode(), fmt.encode(), C.c_int(1 if visible else 0)))
+
+    def compile(self):
+        self._ck(self.L.refm_compile(self.h))
+
+    def run(self, tokens, tok_offsets, origsegs=None, nthreads=1, with_results=True):
+        tokens = np.ascontiguousarray(tokens, dtype=LEXEM_DT)
+        tok_offsets = np.ascontiguousarray(tok_offsets, dtype=np.uint64)
+        ndocs = len(tok_offsets) - 1
+        if origsegs is not None:
+            origsegs = np.ascontiguousarray(origsegs, dtype=np.uint32)
+        self._ck(self.L.refm_run_batch(self.h, _ptr(tokens), _ptr(origsegs), _ptr(tok_offsets), C.c_uint32(ndocs),
+                                       C.c_int(nthreads), C.c_int(1 if with_results else 0)))
+        nres = int(self.L.refm_result_count(self.h))
+        nitems = int(self.L.refm_item_count(self.h))
+        out = {
+            "results": np.zeros(nres if with_results else 0, dtype=RESULT_DT),
+            "result_offsets": np.zeros(ndocs + 1, dtype=np.uint64),
+            "items": np.zeros(nitems, dtype=ITEM_DT),
+            "item_offsets": np.zeros(ndocs + 1, dtype=np.uint64),
+            "stats": np.zeros(ndocs, dtype=STATS_DT),
+            "status": np.zeros(ndocs, dtype=np.uint32),
+        }
+        self.L.refm_fetch(self.h, _ptr(out["results"]) if with_results and nres else None, _ptr(out["result_offsets"]),
+                          _ptr(out["items"]) if nitems else None, _ptr(out["item_offsets"]), _ptr(out["stats"]),
+                          _ptr(out["status"]))
+        return out
+
+    def name(self, idx):
+        return self.L.refm_name(self.h, C.c_uint32(int(idx))).decode()
+
+
+def canonical_results(out, result_name, item_name):
+    """Per document: sorted list of (name, ordpos, ordend, origseg, origpos, endseg, endpos, (items...))
+    with items in emission order -- the multiset the parity contract compares."""
+    docs = []
+    ro, io = out["result_offsets"], out["item_offsets"]
+    for d in range(len(ro) - 1):
+        recs = []
+        items = out["items"][int(io[d]):int(io[d + 1])]
+        for r in out["results"][int(ro[d]):int(ro[d + 1])]:
+            its = tuple((item_name(i["variable"]), int(i["ordpos"]), int(i["ordend"]), int(i["origseg"]), int(i["origpos"]),
+                         int(i["endseg"]), int(i["endpos"]))
+                        for i in items[int(r["item_begin"]):int(r["item_begin"]) + int(r["item_count"])])
+            recs.append((result_name(r["name"]), int(r["ordpos"]), int(r["ordend"]), int(r["origseg"]), int(r["origpos"]),
+                         int(r["endseg"]), int(r["endpos"]), its))
+        recs.sort()
+        docs.append(recs)
+    return docs
