@@ -134,3 +134,75 @@ def canonical_results(out, result_name, item_name):
         recs.sort()
         docs.append(recs)
     return docs
+
+
+class OracleLexer:
+    """CPU restatement of level 1 (oracle/lexer_oracle.cpp -> libsp_oracle_lexer.so)."""
+
+    _lib = None
+
+    @classmethod
+    def lib(cls):
+        if cls._lib is None:
+            path = os.path.join(REF_DIR, "libsp_oracle_lexer.so")
+            if not os.path.exists(path):
+                build_oracle()
+            L = C.CDLL(path)
+            L.lxo_create.restype = C.c_void_p
+            L.lxo_last_error.restype = C.c_char_p
+            L.lxo_result_count.restype = C.c_uint64
+            L.lxo_raw_event_count.restype = C.c_uint64
+            cls._lib = L
+        return cls._lib
+
+    def __init__(self):
+        self.L = self.lib()
+        self.h = C.c_void_p(self.L.lxo_create())
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.lxo_destroy(self.h)
+            self.h = None
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise RuntimeError(self.L.lxo_last_error(self.h).decode(errors="replace"))
+
+    def define_option(self, name, value=0.0):
+        self._ck(self.L.lxo_define_option(self.h, name.encode(), C.c_double(value)))
+
+    def define_lexem(self, id, expr, result_index=0, level=0, posbind=0):
+        e = expr if isinstance(expr, bytes) else expr.encode()
+        self._ck(self.L.lxo_define_lexem(self.h, C.c_uint32(id), e, C.c_size_t(len(e)), C.c_uint32(result_index),
+                                         C.c_uint32(level), C.c_uint32(posbind)))
+
+    def define_symbol(self, symbolid, lexemid, name):
+        n = name if isinstance(name, bytes) else name.encode()
+        self._ck(self.L.lxo_define_symbol(self.h, C.c_uint32(symbolid), C.c_uint32(lexemid), n, C.c_size_t(len(n))))
+
+    def compile(self):
+        self._ck(self.L.lxo_compile(self.h))
+
+    def scan(self, text, doc_offsets, nthreads=1, keep_raw=False):
+        """text: bytes/np.uint8 array; doc_offsets: ndocs+1 byte offsets."""
+        buf = np.frombuffer(text, dtype=np.uint8) if isinstance(text, (bytes, bytearray)) else np.ascontiguousarray(text, dtype=np.uint8)
+        offs = np.ascontiguousarray(doc_offsets, dtype=np.uint64)
+        ndocs = len(offs) - 1
+        self._ck(self.L.lxo_scan_batch(self.h, _ptr(buf), _ptr(offs), C.c_uint32(ndocs), C.c_int(nthreads),
+                                       C.c_int(1 if keep_raw else 0)))
+        n = int(self.L.lxo_result_count(self.h))
+        out = {"lexems": np.zeros(n, dtype=LEXEM_DT), "offsets": np.zeros(ndocs + 1, dtype=np.uint64),
+               "status": np.zeros(ndocs, dtype=np.uint32), "raw_event_count": int(self.L.lxo_raw_event_count(self.h))}
+        self.L.lxo_fetch(self.h, _ptr(out["lexems"]) if n else None, _ptr(out["offsets"]), _ptr(out["status"]))
+        if keep_raw:
+            nr = out["raw_event_count"]
+            out["raw"] = np.zeros((nr, 3), dtype=np.uint32)
+            out["raw_offsets"] = np.zeros(ndocs + 1, dtype=np.uint64)
+            self.L.lxo_fetch_raw(self.h, _ptr(out["raw"]) if nr else None, _ptr(out["raw_offsets"]))
+        return out
+
+    def match(self, src):
+        """PatternLexerContext::match of one document -> list of (id, ordpos, origpos, origsize)."""
+        b = src if isinstance(src, bytes) else src.encode()
+        out = self.scan(b, [0, len(b)])
+        return [tuple(int(x) for x in r) for r in out["lexems"]]
