@@ -1,0 +1,342 @@
+// Host side lexer compiler: lexem definitions -> flat tables (lexer_tables.h) ready for upload to HBM.
+//
+// Mirrors the definition phase of the reference's PatternLexerInstance:
+//   PatternTable::definePattern   src/patternLexer.cpp:245-262  (" ~N" suffix :605-626, range checks :76-99)
+//   PatternTable::defineSymbol    src/patternLexer.cpp:264-311
+//   PatternTable::complete        src/patternLexer.cpp:333-412  (engine id = definition index)
+//   PatternLexerInstance::compile src/patternLexer.cpp:1068-1118
+#ifndef SP_LEXER_COMPILE_HPP_INCLUDED
+#define SP_LEXER_COMPILE_HPP_INCLUDED
+#include "automaton.hpp"
+#include "lexer_tables.h"
+#include <cstdlib>
+
+namespace sp {
+
+struct LexemDefinition
+{
+	std::string expression;
+	uint32_t id;
+	uint8_t level, posbind, resultidx, editdist, symtab;
+};
+
+// All table arrays as host vectors; `view` points into them (or into their device copies after upload).
+struct LexerTablesHost
+{
+	std::vector<uint16_t> fwd_next;
+	std::vector<uint8_t> fwd_class;
+	std::vector<uint32_t> fwd_acc_off;
+	std::vector<uint16_t> fwd_acc_pat;
+	std::vector<uint32_t> rev_next;
+	std::vector<uint8_t> rev_classes;
+	std::vector<uint32_t> cap_next;
+	std::vector<uint8_t> cap_classes;
+	std::vector<SpAnchoredDfa> cap;
+	std::vector<SpPatternInfo> pat;
+	std::vector<SpSymbolSlot> sym_slots;
+	std::vector<uint8_t> sym_pool;
+	SpLexerTables view;
+
+	void pointToHost()
+	{
+		view.fwd_next = fwd_next.data(); view.fwd_class = fwd_class.data();
+		view.fwd_acc_off = fwd_acc_off.data(); view.fwd_acc_pat = fwd_acc_pat.data();
+		view.rev_next = rev_next.data(); view.rev_classes = rev_classes.data();
+		view.cap_next = cap_next.data(); view.cap_classes = cap_classes.data(); view.cap = cap.data();
+		view.pat = pat.data(); view.sym_slots = sym_slots.data(); view.sym_pool = sym_pool.data();
+	}
+};
+
+class LexerProgram
+{
+public:
+	enum {MaxPatternId = (1<<30)-1};
+
+	LexerProgram() :m_flags(0),m_bytechar(false),m_compiled(false),m_fwdStates(0),m_revStates(0){}
+
+	bool compiled() const {return m_compiled;}
+	unsigned int flags() const {return m_flags;}
+	const std::vector<LexemDefinition>& definitions() const {return m_defs;}
+	const LexerTablesHost& tables() const {return m_tables;}
+	LexerTablesHost& tables() {return m_tables;}
+	uint32_t forwardStates() const {return m_fwdStates;}
+	uint32_t reverseStates() const {return m_revStates;}
+
+	// PatternLexerInstance::defineOption, src/patternLexer.cpp:1031-1066
+	void defineOption( const std::string& name)
+	{
+		if (m_compiled) throw std::runtime_error( "called define option after calling 'compile'");
+		std::string n( name);
+		for (char& c: n) c = (char)toupper( (unsigned char)c);
+		if (n == "CASELESS") m_flags |= RX_CASELESS;
+		else if (n == "DOTALL") m_flags |= RX_DOTALL;
+		else if (n == "MULTILINE") m_flags |= RX_MULTILINE;
+		else if (n == "ALLOWEMPTY") m_flags |= RX_ALLOWEMPTY;
+		else if (n == "UCP") m_flags |= RX_UCP;
+		else if (n == "BYTECHAR") m_bytechar = true;
+		else throw std::runtime_error( "unknown option '" + name + "'");
+	}
+
+	void defineLexem( uint32_t id, const std::string& expression_, unsigned int resultIndex, unsigned int level, unsigned int posbind)
+	{
+		if (m_compiled) throw std::runtime_error( "called define pattern after calling 'compile'");
+		LexemDefinition def;
+		def.expression = expression_;
+		unsigned int editdist = stripEditDistance( def.expression);
+		if (id > MaxPatternId) throw std::runtime_error( "pattern id out of range");
+		if (level > 255) throw std::runtime_error( "level out of range");
+		if (resultIndex > 255) throw std::runtime_error( "result index out of range");
+		if (editdist > 255) throw std::runtime_error( "edit distance out of range");
+		if (posbind > 3) throw std::runtime_error( "unknown position bind value");
+		def.id = id; def.level = (uint8_t)level; def.posbind = (uint8_t)posbind;
+		def.resultidx = (uint8_t)resultIndex; def.editdist = (uint8_t)editdist; def.symtab = 0;
+		m_defs.push_back( def);
+	}
+
+	void defineSymbol( uint32_t symbolid, uint32_t lexemid, const std::string& name)
+	{
+		if (m_compiled) throw std::runtime_error( "called define symbol after calling 'compile'");
+		if (lexemid > MaxPatternId) throw std::runtime_error( "pattern id out of range");
+		if (symbolid > MaxPatternId) throw std::runtime_error( "symbol id out of range");
+		if (name.size() > 0xFFFF) throw std::runtime_error( "symbol too long");
+		uint8_t table = tableOf( lexemid, true);
+		std::pair<uint32_t,std::string> key( table, name);
+		if (m_symbols.find( key) != m_symbols.end()) throw std::runtime_error( "symbol defined twice: '" + name + "'");
+		m_symbols[ key] = symbolid;
+	}
+
+	uint32_t getSymbol( uint32_t lexemid, const std::string& name) const
+	{
+		std::map<uint32_t,uint8_t>::const_iterator ti = m_symtabOfLexem.find( lexemid);
+		if (ti == m_symtabOfLexem.end()) return 0;
+		std::map<std::pair<uint32_t,std::string>,uint32_t>::const_iterator si = m_symbols.find( std::make_pair( (uint32_t)ti->second, name));
+		return si == m_symbols.end() ? 0 : si->second;
+	}
+
+	// Throws SyntaxError / UnsupportedError / std::runtime_error; the message names the offending expression
+	// like the reference does (src/patternLexer.cpp:1087-1113).
+	void compile()
+	{
+		if (m_bytechar) throw UnsupportedError( "option BYTECHAR (one byte character map) is not supported");
+		ClassGraphCache cache;
+		ByteNfa fwd;
+		std::vector<int> entries;
+		std::vector<RxRef> trees;
+		m_tables = LexerTablesHost();
+		m_tables.pat.resize( m_defs.size());
+		for (std::size_t di=0; di<m_defs.size(); ++di)
+		{
+			LexemDefinition& def = m_defs[di];
+			std::map<uint32_t,uint8_t>::const_iterator ti = m_symtabOfLexem.find( def.id);
+			def.symtab = (ti == m_symtabOfLexem.end()) ? 0 : ti->second;
+			try
+			{
+				if (def.editdist) throw UnsupportedError( "approximate matching (~N) is not supported");
+				RegexParser parser( def.expression, m_flags);
+				RxRef tree = parser.parse();
+				if ((m_flags & RX_UCP) && containsWordAssertion( tree)) throw UnsupportedError( "\\b and \\B with option UCP are not supported");
+				trees.push_back( tree);
+				NfaBuilder builder( fwd, cache, false);
+				int entry = builder.addPattern( tree, (int)di);
+				if (!(m_flags & RX_ALLOWEMPTY) && nfaNullable( fwd, entry)) throw SyntaxError( "pattern matches empty buffer; use option ALLOWEMPTY");
+				entries.push_back( entry);
+				buildReverse( di, tree, cache);
+				SpPatternInfo& P = m_tables.pat[di];
+				P.id = def.id; P.level = def.level; P.posbind = def.posbind; P.symtab = def.symtab; P.resultidx = def.resultidx;
+				P.cap_first = 0;
+				if (def.resultidx) buildCapture( di, cache);
+			}
+			catch (const UnsupportedError& e)
+			{
+				throw UnsupportedError( "failed to compile pattern \"" + def.expression + "\": " + e.what());
+			}
+			catch (const std::runtime_error& e)
+			{
+				throw SyntaxError( "failed to compile pattern \"" + def.expression + "\": " + e.what());
+			}
+		}
+		if (m_defs.size() > 65535) throw UnsupportedError( "too many lexem definitions");
+		buildForward( fwd, entries);
+		buildSymbols();
+		m_tables.view.npat = (uint32_t)m_defs.size();
+		m_tables.pointToHost();
+		m_compiled = true;
+	}
+
+private:
+	// restates extractEditDistFromExpression, src/patternLexer.cpp:605-626
+	static unsigned int stripEditDistance( std::string& expr)
+	{
+		long se = (long)expr.size() - 1;
+		while (se >= 0 && (unsigned char)expr[se] <= 32) --se;
+		long de = se;
+		while (se >= 0 && expr[se] >= '0' && expr[se] <= '9') --se;
+		if (de == se) return 0;
+		std::string digits = expr.substr( se+1, de-se);
+		while (se >= 0 && (unsigned char)expr[se] <= 32) --se;
+		if (se < 0 || expr[se] != '~') return 0;
+		while (se > 0 && (unsigned char)expr[se-1] <= 32) --se;
+		expr.resize( se);
+		return (unsigned int)std::atoi( digits.c_str());
+	}
+	uint8_t tableOf( uint32_t lexemid, bool create)
+	{
+		std::map<uint32_t,uint8_t>::const_iterator ti = m_symtabOfLexem.find( lexemid);
+		if (ti != m_symtabOfLexem.end()) return ti->second;
+		if (!create) return 0;
+		if (m_symtabOfLexem.size() >= 255) throw std::runtime_error( "too many pattern symbol tables defined");
+		uint8_t rt = (uint8_t)(m_symtabOfLexem.size() + 1);
+		m_symtabOfLexem[ lexemid] = rt;
+		return rt;
+	}
+
+	// appends an anchored automaton to `next`/`classes` in the row|flags entry format; returns init rows and stride
+	static void appendAnchored( const Dfa& dfa, std::vector<uint32_t>& next, std::vector<uint8_t>& classes,
+				    uint32_t init[4], uint32_t& stride, uint32_t& classOffset)
+	{
+		stride = dfa.stride();
+		classOffset = (uint32_t)classes.size();
+		classes.insert( classes.end(), dfa.byteclass, dfa.byteclass + 256);
+		std::size_t base = next.size();
+		if (base + (std::size_t)dfa.nstates * stride >= SP_REV_ROWMASK) throw UnsupportedError( "automata too large");
+		std::vector<char> dying( dfa.nstates, 0);
+		for (uint32_t s=0; s<dfa.nstates; ++s)
+		{
+			bool allDead = true;
+			for (uint32_t c=0; c<stride && allDead; ++c) allDead = dfa.next[ (std::size_t)s*stride + c] == dfa.dead;
+			dying[s] = allDead;
+		}
+		next.resize( base + (std::size_t)dfa.nstates * stride);
+		for (uint32_t s=0; s<dfa.nstates; ++s)
+		{
+			for (uint32_t c=0; c<stride; ++c)
+			{
+				uint32_t t = dfa.next[ (std::size_t)s*stride + c];
+				uint32_t e = (uint32_t)(base + (std::size_t)t * stride);
+				if (!dfa.accepts[t].empty()) e |= SP_REV_ACCEPT;
+				if (dying[t]) e |= SP_REV_STOP;
+				next[ base + (std::size_t)s*stride + c] = e;
+			}
+		}
+		for (int k=0; k<4; ++k) init[k] = (uint32_t)(base + (std::size_t)dfa.init[k] * stride);
+	}
+
+	void buildReverse( std::size_t di, const RxRef& tree, ClassGraphCache& cache)
+	{
+		ByteNfa nfa;
+		NfaBuilder builder( nfa, cache, true);
+		std::vector<int> entry( 1, builder.addPattern( tree, 0));
+		DfaOptions opt; opt.unanchored = false; opt.allowEmpty = false;
+		Dfa dfa = DfaBuilder( nfa, entry, opt).build();
+		SpPatternInfo& P = m_tables.pat[di];
+		appendAnchored( dfa, m_tables.rev_next, m_tables.rev_classes, P.rev_init, P.rev_stride, P.rev_class);
+		m_revStates += dfa.nstates;
+	}
+
+	// The selected sub expression must be a top level group: expression = A (G) B. The helper automata are
+	// compiled without the instance options, as the reference hands the bare expression to libtre
+	// (REG_EXTENDED only, src/patternLexer.cpp:474); '.' includes newline there.
+	void buildCapture( std::size_t di, ClassGraphCache& cache)
+	{
+		const LexemDefinition& def = m_defs[di];
+		RegexParser parser( def.expression, RX_DOTALL);
+		RxRef tree = parser.parse();
+		if ((int)def.resultidx > parser.captureCount()) throw SyntaxError( "sub expression selection index out of range");
+		std::vector<RxRef> parts;
+		if (tree->kind == RxConcat) parts = tree->sub; else parts.push_back( tree);
+		std::size_t gi = 0;
+		for (; gi<parts.size(); ++gi) if (parts[gi]->kind == RxGroup && parts[gi]->capture == (int)def.resultidx) break;
+		if (gi == parts.size()) throw UnsupportedError( "the selected sub expression must be a top level group of the expression");
+		RxRef pieces[5] = {tree, Rx::concatOf( parts, 0, gi), Rx::concatOf( parts, gi, parts.size()),
+				   Rx::concatOf( parts, gi, gi+1), Rx::concatOf( parts, gi+1, parts.size())};
+		m_tables.pat[di].cap_first = (uint32_t)m_tables.cap.size();
+		for (int k=0; k<5; ++k)
+		{
+			ByteNfa nfa;
+			NfaBuilder builder( nfa, cache, false);
+			std::vector<int> entry( 1, builder.addPattern( pieces[k], 0));
+			DfaOptions opt; opt.unanchored = false; opt.allowEmpty = true;
+			Dfa dfa = DfaBuilder( nfa, entry, opt).build();
+			SpAnchoredDfa A; A.accept_on_entry = 0;
+			appendAnchored( dfa, m_tables.cap_next, m_tables.cap_classes, A.init, A.stride, A.classes);
+			m_tables.cap.push_back( A);
+		}
+	}
+
+	void buildForward( const ByteNfa& nfa, const std::vector<int>& entries)
+	{
+		DfaOptions opt; opt.unanchored = true; opt.allowEmpty = false; opt.maxStates = 65000;
+		Dfa dfa = DfaBuilder( nfa, entries, opt).build();
+		// renumber: states that report matches last, so that the scan loop tests `state >= fwd_acc_base`
+		std::vector<uint32_t> newid( dfa.nstates);
+		uint32_t nplain = 0;
+		for (uint32_t s=0; s<dfa.nstates; ++s) if (dfa.accepts[s].empty()) newid[s] = nplain++;
+		uint32_t nextid = nplain;
+		for (uint32_t s=0; s<dfa.nstates; ++s) if (!dfa.accepts[s].empty()) newid[s] = nextid++;
+		uint32_t stride = dfa.stride();
+		LexerTablesHost& T = m_tables;
+		T.fwd_next.resize( (std::size_t)dfa.nstates * stride);
+		T.fwd_acc_off.assign( dfa.nstates - nplain + 1, 0);
+		for (uint32_t s=0; s<dfa.nstates; ++s)
+		{
+			for (uint32_t c=0; c<stride; ++c) T.fwd_next[ (std::size_t)newid[s]*stride + c] = (uint16_t)newid[ dfa.next[ (std::size_t)s*stride + c]];
+		}
+		std::vector<std::vector<uint32_t> > acc( dfa.nstates - nplain);
+		for (uint32_t s=0; s<dfa.nstates; ++s) if (!dfa.accepts[s].empty()) acc[ newid[s]-nplain] = dfa.accepts[s];
+		for (std::size_t a=0; a<acc.size(); ++a)
+		{
+			T.fwd_acc_off[a] = (uint32_t)T.fwd_acc_pat.size();
+			for (uint32_t p: acc[a]) T.fwd_acc_pat.push_back( (uint16_t)p);	// ascending definition index = canonical event order
+		}
+		T.fwd_acc_off[ acc.size()] = (uint32_t)T.fwd_acc_pat.size();
+		T.fwd_class.assign( dfa.byteclass, dfa.byteclass + 256);
+		T.view.fwd_states = dfa.nstates;
+		T.view.fwd_stride = stride;
+		T.view.fwd_init = newid[ dfa.init[ KindEdge]];
+		T.view.fwd_acc_base = nplain;
+		m_fwdStates = dfa.nstates;
+	}
+
+	void buildSymbols()
+	{
+		LexerTablesHost& T = m_tables;
+		T.view.has_symbols = m_symbols.empty() ? 0 : 1;
+		T.view.sym_mask = 0;
+		if (m_symbols.empty()) {T.sym_slots.assign( 1, SpSymbolSlot()); std::memset( &T.sym_slots[0], 0, sizeof(SpSymbolSlot)); T.sym_pool.assign( 1, 0); return;}
+		std::size_t nslots = 16;
+		while (nslots < m_symbols.size() * 2) nslots <<= 1;
+		SpSymbolSlot empty; std::memset( &empty, 0, sizeof(empty));
+		T.sym_slots.assign( nslots, empty);
+		T.view.sym_mask = (uint32_t)nslots - 1;
+		for (const auto& kv: m_symbols)
+		{
+			const std::string& name = kv.first.second;
+			uint32_t h = symbolHash( (const uint8_t*)name.data(), (uint32_t)name.size(), kv.first.first);
+			std::size_t slot = h & T.view.sym_mask;
+			while (T.sym_slots[ slot].hash) slot = (slot + 1) & T.view.sym_mask;
+			SpSymbolSlot& e = T.sym_slots[ slot];
+			e.hash = h; e.symid = kv.second; e.str = (uint32_t)T.sym_pool.size(); e.len = (uint16_t)name.size(); e.symtab = (uint16_t)kv.first.first;
+			T.sym_pool.insert( T.sym_pool.end(), name.begin(), name.end());
+		}
+		if (T.sym_pool.empty()) T.sym_pool.push_back( 0);
+	}
+	static uint32_t symbolHash( const uint8_t* s, uint32_t len, uint32_t symtab)
+	{
+		// must equal sp_symbol_hash (lexer_device.cuh)
+		uint32_t h = 2166136261u ^ (symtab * 0x9E3779B1u);
+		for (uint32_t i=0; i<len; ++i) {h ^= s[i]; h *= 16777619u;}
+		return h ? h : 1;
+	}
+
+	std::vector<LexemDefinition> m_defs;
+	std::map<uint32_t,uint8_t> m_symtabOfLexem;
+	std::map<std::pair<uint32_t,std::string>,uint32_t> m_symbols;
+	unsigned int m_flags;
+	bool m_bytechar;
+	bool m_compiled;
+	LexerTablesHost m_tables;
+	uint32_t m_fwdStates, m_revStates;
+};
+
+} // namespace sp
+#endif

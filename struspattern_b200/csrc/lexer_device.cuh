@@ -1,0 +1,498 @@
+// Per-thread building blocks of the lexer kernels (lexer_kernels.cu). Written as host+device inline
+// functions so that tests/hostsim can run the very same table walks on the CPU against the oracle while no
+// GPU is around; the product (libstrus_pattern_b200.so) only ever calls them from CUDA kernels.
+//
+// Reference behaviour restated here (file:line under the strusPattern tree):
+//   scan contract of hs_scan with HS_FLAG_SOM_LEFTMOST          src/patternLexer.cpp:875-879, 403
+//   match_event_handler (supersede logic, symbols, size check)  src/patternLexer.cpp:717-826
+//   sub expression selection                                    src/patternLexer.cpp:414-426, 488-507
+//   ordinal position assignment                                 src/patternLexer.cpp:893-945
+#ifndef SP_LEXER_DEVICE_CUH_INCLUDED
+#define SP_LEXER_DEVICE_CUH_INCLUDED
+#include "lexer_tables.h"
+#include "strus_pattern_b200.h"
+
+#ifdef __CUDACC__
+#define SP_HD __host__ __device__ __forceinline__
+#define SP_LDG(p) __ldg(p)
+#else
+#define SP_HD inline
+#define SP_LDG(p) (*(p))
+#endif
+
+#define SP_PAT_DROPPED   0xFFFFFFFFu	/* event removed by the sub expression selection */
+#define SP_PAT_SIZEERROR 0xFFFFFFFEu	/* matched term of 65535 bytes or more: error of the document */
+
+typedef struct SpRawEvent
+{
+	uint32_t pat;		/* 0-based definition index (reference: 1-based hyperscan id, src/patternLexer.cpp:390) */
+	uint32_t from;		/* byte offsets relative to the document */
+	uint32_t to;
+	uint32_t aux;		/* document index until the start is resolved, then symbol id (0 = none) */
+} SpRawEvent;
+
+typedef struct SpMatchEvent	/* = MatchEvent, src/patternLexer.cpp:665-679 */
+{
+	uint32_t id;
+	uint32_t origpos;
+	uint32_t origsize;
+	uint32_t meta;		/* level | posbind << 8 */
+} SpMatchEvent;
+
+SP_HD uint32_t sp_kind_of_byte( uint32_t b)
+{
+	if (b == '\n') return 2;
+	return ((b - '0') < 10u || ((b | 0x20) - 'a') < 26u || b == '_') ? 1 : 0;
+}
+
+// index of the non empty document that contains the byte at global offset `pos` (pos < total)
+SP_HD uint32_t sp_find_doc( const uint64_t* doc_off, uint32_t ndocs, uint64_t pos)
+{
+	uint32_t lo = 0, hi = ndocs;	// invariant: doc_off[lo] <= pos < doc_off[hi]
+	while (hi - lo > 1)
+	{
+		uint32_t mid = lo + ((hi - lo) >> 1);
+		if (SP_LDG( doc_off + mid) <= pos) lo = mid; else hi = mid;
+	}
+	return lo;
+}
+
+struct SpCountSink
+{
+	const SpLexerTables* T;
+	uint32_t count;
+	SP_HD void accept( uint32_t state, uint32_t, uint32_t)
+	{
+		uint32_t a = state - T->fwd_acc_base;
+		count += SP_LDG( T->fwd_acc_off + a + 1) - SP_LDG( T->fwd_acc_off + a);
+	}
+	SP_HD void docBegin( uint32_t) {}
+};
+
+struct SpEmitSink
+{
+	const SpLexerTables* T;
+	SpRawEvent* events;
+	uint64_t cursor;
+	uint64_t* doc_ev_begin;
+	SP_HD void accept( uint32_t state, uint32_t to, uint32_t doc)
+	{
+		uint32_t a = state - T->fwd_acc_base;
+		uint32_t pi = SP_LDG( T->fwd_acc_off + a), pe = SP_LDG( T->fwd_acc_off + a + 1);
+		for (; pi < pe; ++pi)
+		{
+			SpRawEvent ev; ev.pat = SP_LDG( T->fwd_acc_pat + pi); ev.from = SP_NO_POS; ev.to = to; ev.aux = doc;
+			events[ cursor++] = ev;
+		}
+	}
+	SP_HD void docBegin( uint32_t doc) {doc_ev_begin[ doc] = cursor;}
+};
+
+// Forward scan of the global byte range [begin,end) of the concatenated documents starting in `state`
+// (ignored when `begin` is the first byte of a document). Returns the state behind the last byte.
+template <class Sink>
+SP_HD uint32_t sp_scan_range( const SpLexerTables& T, const uint8_t* text, const uint64_t* doc_off, uint32_t ndocs,
+				uint64_t begin, uint64_t end, uint32_t state, Sink& sink)
+{
+	const uint32_t stride = T.fwd_stride, accbase = T.fwd_acc_base;
+	uint32_t d = sp_find_doc( doc_off, ndocs, begin);
+	uint64_t dstart = SP_LDG( doc_off + d), dend = SP_LDG( doc_off + d + 1);
+	if (dstart == begin) state = T.fwd_init;
+	uint64_t pos = begin;
+	while (pos < end)
+	{
+		uint64_t stop = dend < end ? dend : end;
+		while (pos < stop)
+		{
+			if ((((uintptr_t)(text + pos)) & 15) == 0 && pos + 16 <= stop)
+			{
+				uint4 v = *reinterpret_cast<const uint4*>( text + pos);
+				uint32_t w[4] = {v.x, v.y, v.z, v.w};
+				#pragma unroll
+				for (int wi=0; wi<4; ++wi)
+				{
+					#pragma unroll
+					for (int bi=0; bi<4; ++bi)
+					{
+						uint32_t b = (w[wi] >> (8*bi)) & 0xFF;
+						state = SP_LDG( T.fwd_next + state * stride + SP_LDG( T.fwd_class + b));
+						if (state >= accbase) sink.accept( state, (uint32_t)(pos - dstart), d);
+						++pos;
+					}
+				}
+			}
+			else
+			{
+				uint32_t b = SP_LDG( text + pos);
+				state = SP_LDG( T.fwd_next + state * stride + SP_LDG( T.fwd_class + b));
+				if (state >= accbase) sink.accept( state, (uint32_t)(pos - dstart), d);
+				++pos;
+			}
+		}
+		if (pos == dend)
+		{
+			// end of the document: the virtual end-of-text symbol reports the matches that end here
+			state = SP_LDG( T.fwd_next + state * stride + (stride-1));
+			if (state >= accbase) sink.accept( state, (uint32_t)(dend - dstart), d);
+			state = T.fwd_init;
+			for (++d; d < ndocs; ++d)
+			{
+				sink.docBegin( d);
+				if (SP_LDG( doc_off + d + 1) > pos) break;	// next non empty document
+			}
+			if (d >= ndocs) break;
+			dstart = pos; dend = SP_LDG( doc_off + d + 1);
+		}
+	}
+	return state;
+}
+
+// Leftmost start of a match of definition `pat` that ends at `to` (document relative); doc = text of the
+// document, doclen its size. SP_NO_POS if the reverse automaton finds none (table inconsistency).
+SP_HD uint32_t sp_leftmost_start( const SpLexerTables& T, const SpPatternInfo& P, const uint8_t* doc, uint32_t doclen, uint32_t to)
+{
+	uint32_t pk = (to < doclen) ? sp_kind_of_byte( SP_LDG( doc + to)) : 3;
+	uint32_t row = P.rev_init[ pk];
+	const uint8_t* cls = T.rev_classes + P.rev_class;
+	uint32_t from = SP_NO_POS;
+	for (uint32_t i=to; i>0; --i)
+	{
+		uint32_t e = SP_LDG( T.rev_next + row + SP_LDG( cls + SP_LDG( doc + i - 1)));
+		if (e & SP_REV_ACCEPT) from = i;
+		if (e & SP_REV_STOP) return from;
+		row = e & SP_REV_ROWMASK;
+	}
+	uint32_t e = SP_LDG( T.rev_next + row + (P.rev_stride-1));
+	if (e & SP_REV_ACCEPT) from = 0;
+	return from;
+}
+
+// ---- capture selection (libtre re-match of the reference restated with anchored automata)
+// true if the automaton matches exactly doc[a,b) with the real neighbours visible to assertions
+SP_HD bool sp_cap_span( const SpLexerTables& T, const SpAnchoredDfa& A, const uint8_t* doc, uint32_t doclen, uint32_t a, uint32_t b)
+{
+	uint32_t pk = a ? sp_kind_of_byte( SP_LDG( doc + a - 1)) : 3;
+	uint32_t row = A.init[ pk];
+	const uint8_t* cls = T.cap_classes + A.classes;
+	for (uint32_t i=a; i<b; ++i)
+	{
+		uint32_t e = SP_LDG( T.cap_next + row + SP_LDG( cls + SP_LDG( doc + i)));
+		if (e & SP_REV_STOP) return false;
+		row = e & SP_REV_ROWMASK;
+	}
+	uint32_t e = (b < doclen) ? SP_LDG( T.cap_next + row + SP_LDG( cls + SP_LDG( doc + b))) : SP_LDG( T.cap_next + row + (A.stride-1));
+	return (e & SP_REV_ACCEPT) != 0;
+}
+
+// PatternTable::matchSubExpression (src/patternLexer.cpp:414-426) + SubExpressionDef::match (:488-507):
+// POSIX leftmost-longest overall match from `from`, then the selected group as early and as long as possible.
+SP_HD bool sp_select_subexpression( const SpLexerTables& T, const SpPatternInfo& P, const uint8_t* doc, uint32_t doclen, uint32_t& from, uint32_t& to)
+{
+	const SpAnchoredDfa* C = T.cap + P.cap_first;	// whole, A, GB, G, B
+	uint32_t best = SP_NO_POS;
+	{
+		uint32_t pk = from ? sp_kind_of_byte( SP_LDG( doc + from - 1)) : 3;
+		uint32_t row = C[0].init[ pk];
+		const uint8_t* cls = T.cap_classes + C[0].classes;
+		uint32_t i = from;
+		for (;; ++i)
+		{
+			if (i == doclen)
+			{
+				if (SP_LDG( T.cap_next + row + (C[0].stride-1)) & SP_REV_ACCEPT) best = i;
+				break;
+			}
+			uint32_t b = SP_LDG( doc + i);
+			uint32_t e = SP_LDG( T.cap_next + row + SP_LDG( cls + b));
+			if (e & SP_REV_ACCEPT) best = i;
+			if (b == 0 || (e & SP_REV_STOP)) break;		// the subject of the re-match is a C string
+			row = e & SP_REV_ROWMASK;
+		}
+	}
+	if (best == SP_NO_POS) return false;
+	uint32_t gs = SP_NO_POS, ge = SP_NO_POS;
+	for (uint32_t s=from; s<=best; ++s)
+	{
+		if (sp_cap_span( T, C[1], doc, doclen, from, s) && sp_cap_span( T, C[2], doc, doclen, s, best)) {gs = s; break;}
+	}
+	if (gs == SP_NO_POS) return false;
+	for (uint32_t e=best+1; e>gs; --e)
+	{
+		if (sp_cap_span( T, C[3], doc, doclen, gs, e-1) && sp_cap_span( T, C[4], doc, doclen, e-1, best)) {ge = e-1; break;}
+	}
+	if (ge == SP_NO_POS) return false;
+	if (ge > to) return false;	// mt.rm_eo > to - from (:503)
+	from = gs; to = ge;
+	return true;
+}
+
+SP_HD uint32_t sp_symbol_hash( const uint8_t* s, uint32_t len, uint32_t symtab)
+{
+	uint32_t h = 2166136261u ^ (symtab * 0x9E3779B1u);
+	for (uint32_t i=0; i<len; ++i) {h ^= SP_LDG( s + i); h *= 16777619u;}
+	return h ? h : 1;
+}
+
+// SymbolTable lookup of the matched bytes (src/patternLexer.cpp:312-317, 740-744); 0 = no symbol
+SP_HD uint32_t sp_symbol_lookup( const SpLexerTables& T, uint32_t symtab, const uint8_t* s, uint32_t len)
+{
+	if (!T.sym_mask || len > 0xFFFF) return 0;
+	uint32_t h = sp_symbol_hash( s, len, symtab);
+	for (uint32_t slot = h & T.sym_mask;; slot = (slot + 1) & T.sym_mask)
+	{
+		SpSymbolSlot e = T.sym_slots[ slot];
+		if (e.hash == 0) return 0;
+		if (e.hash == h && e.len == len && e.symtab == symtab)
+		{
+			uint32_t i = 0;
+			while (i < len && SP_LDG( T.sym_pool + e.str + i) == SP_LDG( s + i)) ++i;
+			if (i == len) return e.symid;
+		}
+	}
+}
+
+// Completes one raw event: leftmost start, size check, sub expression selection, symbol.
+SP_HD void sp_finish_event( const SpLexerTables& T, SpRawEvent& ev, const uint8_t* doc, uint32_t doclen)
+{
+	const SpPatternInfo P = T.pat[ ev.pat];
+	uint32_t from = sp_leftmost_start( T, P, doc, doclen, ev.to), to = ev.to;
+	ev.aux = 0;
+	if (from == SP_NO_POS || to - from >= 65535) {ev.pat = SP_PAT_SIZEERROR; ev.from = 0; return;}	// src/patternLexer.cpp:727-730
+	if (P.resultidx && !sp_select_subexpression( T, P, doc, doclen, from, to)) {ev.pat = SP_PAT_DROPPED; ev.from = from; return;}
+	ev.from = from; ev.to = to;
+	if (P.symtab) ev.aux = sp_symbol_lookup( T, P.symtab, doc + from, to - from);
+}
+
+SP_HD SpMatchEvent sp_make_match_event( uint32_t id, const SpPatternInfo& P, uint32_t from, uint32_t to)
+{
+	SpMatchEvent m; m.id = id; m.origpos = from; m.origsize = to - from; m.meta = (uint32_t)P.level | ((uint32_t)P.posbind << 8);
+	return m;
+}
+
+// match_event_handler (src/patternLexer.cpp:746-822) for one completed event on the array ar[0..n).
+SP_HD void sp_supersede( const SpLexerTables& T, const SpRawEvent& rev, SpMatchEvent* ar, uint32_t& n)
+{
+	const SpPatternInfo P = T.pat[ rev.pat];
+	SpMatchEvent ev = sp_make_match_event( P.id, P, rev.from, rev.to);
+	bool withSymbol = rev.aux != 0 && rev.aux != P.id;
+	SpMatchEvent symev = ev; symev.id = rev.aux;
+	if (n == 0)
+	{
+		ar[ n++] = ev;
+		if (withSymbol) ar[ n++] = symev;
+		return;
+	}
+	const uint32_t evLevel = ev.meta & 0xFF, evEnd = ev.origpos + ev.origsize;
+	// elements replaced by the new one (same lexem at the same place) or covered by it with a lower level
+	uint32_t deleted = 0;
+	for (uint32_t k=n; k>0; --k)
+	{
+		SpMatchEvent old = ar[ k-1];
+		if (old.origpos < ev.origpos) break;
+		uint32_t oldLevel = old.meta & 0xFF;
+		if ((old.id == ev.id && old.origpos == ev.origpos && oldLevel == evLevel)
+		||  (oldLevel < evLevel && old.origpos + old.origsize <= evEnd))
+		{
+			for (uint32_t m=k; m<n; ++m) ar[ m-1] = ar[ m];
+			--n; ++deleted;
+		}
+	}
+	if (!deleted)
+	{
+		// the new element is dropped if an element of higher level at the tail covers it
+		for (uint32_t k=n; k>0; --k)
+		{
+			SpMatchEvent old = ar[ k-1];
+			if (old.origpos + old.origsize < evEnd) break;
+			if ((old.meta & 0xFF) > evLevel && old.origpos <= ev.origpos) return;
+		}
+	}
+	if (!withSymbol)
+	{
+		uint32_t k = n;
+		for (; k>0 && ar[ k-1].origpos > ev.origpos; --k) ar[ k] = ar[ k-1];
+		ar[ k] = ev;
+		++n;
+	}
+	else
+	{
+		// two elements are inserted; as in the reference (:809-820) the first later-starting element moves
+		// by two places and every further one by one only, which loses an element and leaves a zeroed one
+		SpMatchEvent zero; zero.id = 0; zero.origpos = 0; zero.origsize = 0; zero.meta = 0;
+		ar[ n] = zero; ar[ n+1] = zero;
+		uint32_t dst = n + 1, k = n;
+		for (; k>0 && ar[ k-1].origpos > ev.origpos; --k) {ar[ dst] = ar[ k-1]; dst = k-1;}
+		ar[ k] = ev;
+		ar[ k+1] = symev;
+		n += 2;
+	}
+}
+
+// Ordinal position assignment (src/patternLexer.cpp:893-945). out == 0: only count.
+SP_HD uint32_t sp_assign_ordpos( const SpMatchEvent* ar, uint32_t n, sp_lexem* out)
+{
+	uint32_t nout = 0, mi = 0, ordpos = 0, origpos = 0, lastbind = SP_BIND_CONTENT;
+	for (; mi < n; ++mi)
+	{
+		SpMatchEvent e = ar[ mi];
+		uint32_t bind = (e.meta >> 8) & 0xFF;
+		lastbind = bind;
+		if (bind == SP_BIND_UNIQUE || bind == SP_BIND_CONTENT)
+		{
+			ordpos = 1; origpos = e.origpos;
+			if (out) {sp_lexem lx; lx.id = e.id; lx.ordpos = 1; lx.origpos = e.origpos; lx.origsize = e.origsize; out[ nout] = lx;}
+			++nout; ++mi;
+			break;
+		}
+		else if (bind == SP_BIND_SUCCESSOR)
+		{
+			if (out) {sp_lexem lx; lx.id = e.id; lx.ordpos = 1; lx.origpos = e.origpos; lx.origsize = e.origsize; out[ nout] = lx;}
+			++nout;
+		}
+	}
+	if (ordpos == 0) return 0;	// no content element: empty result (:919-922)
+	for (; mi < n; ++mi)
+	{
+		SpMatchEvent e = ar[ mi];
+		uint32_t bind = (e.meta >> 8) & 0xFF;
+		uint32_t pos = 0; bool emit = true;
+		if (bind == SP_BIND_UNIQUE && lastbind == SP_BIND_UNIQUE) emit = false;
+		else if (bind == SP_BIND_UNIQUE || bind == SP_BIND_CONTENT)
+		{
+			if (e.origpos > origpos) {origpos = e.origpos; ++ordpos;}
+			pos = ordpos;
+		}
+		else if (bind == SP_BIND_SUCCESSOR) pos = ordpos + 1;
+		else pos = ordpos;
+		if (emit)
+		{
+			if (out) {sp_lexem lx; lx.id = e.id; lx.ordpos = pos; lx.origpos = e.origpos; lx.origsize = e.origsize; out[ nout] = lx;}
+			++nout;
+		}
+		lastbind = bind;
+	}
+	return nout;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Kernel bodies: one call = the work of one CUDA thread (lexer_kernels.cu) or one loop iteration (tests/hostsim).
+// Pipeline of one batch (DESIGN.md "lexer pipeline"):
+//   count (speculative start states) -> verify/fix-up rounds -> prefix sum -> emit -> finish events
+//   -> resolve per document -> prefix sum -> write lexems
+typedef struct SpScanParams
+{
+	SpLexerTables T;
+	const uint8_t* text;		/* concatenated documents */
+	const uint64_t* doc_off;	/* [ndocs+1] */
+	uint32_t ndocs;
+	uint64_t total;			/* = doc_off[ndocs] */
+	uint32_t chunk;			/* bytes per scan thread */
+	uint32_t warmup;		/* bytes scanned ahead of a chunk to guess its start state */
+	uint64_t nchunks;
+	uint32_t* start_state;		/* [nchunks] */
+	uint32_t* end_state;		/* [nchunks] */
+	uint32_t* ev_count;		/* [nchunks] */
+	uint8_t* known;			/* [nchunks] chunk starts at a document start */
+	uint8_t* redo;			/* [nchunks] chunk has to be scanned again from start_state */
+	uint32_t* nbad;			/* number of chunks flagged by the last verification */
+	const uint64_t* ev_off;		/* [nchunks+1] exclusive prefix sum of ev_count */
+	SpRawEvent* events;
+	uint64_t* doc_ev_begin;		/* [ndocs+1] first event of every document */
+	SpMatchEvent* ar;		/* match event arrays, document d at doc_ev_begin[d]*ar_mult */
+	uint32_t ar_mult;		/* 2 if symbols are defined (an event may insert two elements) else 1 */
+	uint32_t* doc_kept;		/* [ndocs] elements of the match event array */
+	uint32_t* doc_nlex;		/* [ndocs] lexems written */
+	const uint64_t* lex_off;	/* [ndocs+1] exclusive prefix sum of doc_nlex */
+	sp_lexem* lexems;
+	uint32_t* status;		/* [ndocs] */
+} SpScanParams;
+
+struct SpNullSink
+{
+	SP_HD void accept( uint32_t, uint32_t, uint32_t) {}
+	SP_HD void docBegin( uint32_t) {}
+};
+
+SP_HD void spk_count_chunk( const SpScanParams& P, uint64_t j, int round)
+{
+	uint64_t begin = j * P.chunk, end = begin + P.chunk < P.total ? begin + P.chunk : P.total;
+	uint32_t state;
+	if (round == 0)
+	{
+		uint32_t d = sp_find_doc( P.doc_off, P.ndocs, begin);
+		uint64_t dstart = SP_LDG( P.doc_off + d);
+		state = P.T.fwd_init;
+		P.known[ j] = (dstart == begin);
+		P.redo[ j] = 0;
+		if (dstart != begin)
+		{
+			uint64_t wb = (begin - dstart > P.warmup) ? begin - P.warmup : dstart;
+			SpNullSink none;
+			state = sp_scan_range( P.T, P.text, P.doc_off, P.ndocs, wb, begin, wb == dstart ? P.T.fwd_init : P.T.fwd_init, none);
+		}
+		P.start_state[ j] = state;
+	}
+	else
+	{
+		if (!P.redo[ j]) return;
+		P.redo[ j] = 0;
+		state = P.start_state[ j];
+	}
+	SpCountSink sink; sink.T = &P.T; sink.count = 0;
+	P.end_state[ j] = sp_scan_range( P.T, P.text, P.doc_off, P.ndocs, begin, end, state, sink);
+	P.ev_count[ j] = sink.count;
+}
+
+// returns 1 if the chunk has to be scanned again
+SP_HD int spk_verify_chunk( const SpScanParams& P, uint64_t j)
+{
+	if (j == 0 || P.known[ j]) return 0;
+	uint32_t truth = P.end_state[ j-1];
+	if (P.start_state[ j] == truth) return 0;
+	P.start_state[ j] = truth;
+	P.redo[ j] = 1;
+	return 1;
+}
+
+SP_HD void spk_emit_chunk( const SpScanParams& P, uint64_t j)
+{
+	uint64_t begin = j * P.chunk, end = begin + P.chunk < P.total ? begin + P.chunk : P.total;
+	SpEmitSink sink; sink.T = &P.T; sink.events = P.events; sink.cursor = P.ev_off[ j]; sink.doc_ev_begin = P.doc_ev_begin;
+	sp_scan_range( P.T, P.text, P.doc_off, P.ndocs, begin, end, P.start_state[ j], sink);
+}
+
+SP_HD void spk_finish_event( const SpScanParams& P, uint64_t i)
+{
+	SpRawEvent ev = P.events[ i];
+	uint64_t dstart = SP_LDG( P.doc_off + ev.aux);
+	uint32_t doclen = (uint32_t)(SP_LDG( P.doc_off + ev.aux + 1) - dstart);
+	sp_finish_event( P.T, ev, P.text + dstart, doclen);
+	P.events[ i] = ev;
+}
+
+SP_HD void spk_resolve_doc( const SpScanParams& P, uint32_t d)
+{
+	uint64_t eb = P.doc_ev_begin[ d], ee = P.doc_ev_begin[ d+1];
+	SpMatchEvent* ar = P.ar + eb * P.ar_mult;
+	uint32_t n = 0, status = 0;
+	if (P.doc_off[ d+1] - P.doc_off[ d] >= 0xFFFFFFFFull) status = (uint32_t)-SP_ERR_RUNTIME;	// src/patternLexer.cpp:866-869
+	for (uint64_t i=eb; i<ee && !status; ++i)
+	{
+		SpRawEvent ev = P.events[ i];
+		if (ev.pat == SP_PAT_DROPPED) continue;
+		if (ev.pat == SP_PAT_SIZEERROR) {status = (uint32_t)-SP_ERR_RUNTIME; break;}
+		sp_supersede( P.T, ev, ar, n);
+	}
+	if (status) n = 0;
+	P.status[ d] = status;
+	P.doc_kept[ d] = n;
+	P.doc_nlex[ d] = sp_assign_ordpos( ar, n, 0);
+}
+
+SP_HD void spk_write_doc( const SpScanParams& P, uint32_t d)
+{
+	const SpMatchEvent* ar = P.ar + P.doc_ev_begin[ d] * P.ar_mult;
+	sp_assign_ordpos( ar, P.doc_kept[ d], P.lexems + P.lex_off[ d]);
+}
+
+#endif

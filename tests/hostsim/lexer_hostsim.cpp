@@ -1,0 +1,130 @@
+// TEST INFRASTRUCTURE (not product code): runs the kernel bodies of struspattern_b200/csrc/lexer_device.cuh
+// as plain loops on the CPU, with the tables produced by the product's host compiler. It lets the
+// "not gpu" test suite check the compiled tables and the per-thread logic against the oracle while no GPU
+// is present. Nothing under struspattern_b200/ links or loads this file; the shipped library has no CPU path.
+#include <cstdint>
+#include <cstring>
+struct uint4 {uint32_t x, y, z, w;};
+#include "lexer_compile.hpp"
+#include "lexer_device.cuh"
+#include <vector>
+#include <string>
+
+namespace {
+struct HostSim
+{
+	sp::LexerProgram prog;
+	std::string lasterror;
+	std::vector<sp_lexem> lexems;
+	std::vector<uint64_t> offsets;
+	std::vector<uint32_t> status;
+	std::vector<SpRawEvent> events;
+	std::vector<uint64_t> doc_ev_begin;
+	uint64_t fixups, rounds;
+};
+}
+
+extern "C" {
+
+void* hsim_create() {return new HostSim();}
+void hsim_destroy( void* h) {delete (HostSim*)h;}
+const char* hsim_last_error( void* h) {return ((HostSim*)h)->lasterror.c_str();}
+
+#define HSIM_TRY(stmt) HostSim* hs = (HostSim*)h; try {stmt; return 0;} \
+	catch (const sp::UnsupportedError& e) {hs->lasterror = std::string("unsupported: ") + e.what(); return -6;} \
+	catch (const sp::SyntaxError& e) {hs->lasterror = e.what(); return -2;} \
+	catch (const std::exception& e) {hs->lasterror = e.what(); return -1;}
+
+int hsim_define_option( void* h, const char* name, double) {HSIM_TRY( hs->prog.defineOption( name))}
+int hsim_define_lexem( void* h, uint32_t id, const char* expr, size_t exprlen, uint32_t resultIndex, uint32_t level, uint32_t posbind)
+	{HSIM_TRY( hs->prog.defineLexem( id, std::string( expr, exprlen), resultIndex, level, posbind))}
+int hsim_define_symbol( void* h, uint32_t symbolid, uint32_t lexemid, const char* name, size_t namelen)
+	{HSIM_TRY( hs->prog.defineSymbol( symbolid, lexemid, std::string( name, namelen)))}
+int hsim_compile( void* h) {HSIM_TRY( hs->prog.compile())}
+int64_t hsim_info( void* h, const char* key)
+{
+	HostSim* hs = (HostSim*)h;
+	std::string k( key);
+	if (k == "fwd_states") return hs->prog.forwardStates();
+	if (k == "fwd_stride") return hs->prog.tables().view.fwd_stride;
+	if (k == "rev_states") return hs->prog.reverseStates();
+	if (k == "fixups") return (int64_t)hs->fixups;
+	if (k == "rounds") return (int64_t)hs->rounds;
+	if (k == "raw_events") return (int64_t)hs->events.size();
+	return -1;
+}
+
+// text must be 16 byte aligned for the vector path to be exercised (numpy arrays are)
+int hsim_scan_batch( void* h, const uint8_t* text, const uint64_t* doc_off, uint32_t ndocs, uint32_t chunk, uint32_t warmup)
+{
+	HostSim* hs = (HostSim*)h;
+	if (!hs->prog.compiled()) {hs->lasterror = "called scan without calling 'compile'"; return -1;}
+	SpScanParams P; std::memset( &P, 0, sizeof(P));
+	P.T = hs->prog.tables().view;
+	P.text = text; P.doc_off = doc_off; P.ndocs = ndocs; P.total = doc_off[ ndocs];
+	P.chunk = chunk; P.warmup = warmup;
+	P.nchunks = (P.total + chunk - 1) / chunk;
+	std::vector<uint32_t> start_state( P.nchunks+1), end_state( P.nchunks+1), ev_count( P.nchunks+1);
+	std::vector<uint8_t> known( P.nchunks+1), redo( P.nchunks+1);
+	std::vector<uint64_t> ev_off( P.nchunks+1, 0);
+	P.start_state = start_state.data(); P.end_state = end_state.data(); P.ev_count = ev_count.data();
+	P.known = known.data(); P.redo = redo.data();
+	hs->fixups = 0; hs->rounds = 0;
+	for (uint64_t j=0; j<P.nchunks; ++j) spk_count_chunk( P, j, 0);
+	for (;;)
+	{
+		uint64_t nbad = 0;
+		for (uint64_t j=0; j<P.nchunks; ++j) nbad += spk_verify_chunk( P, j);
+		if (!nbad) break;
+		hs->fixups += nbad; hs->rounds += 1;
+		for (uint64_t j=0; j<P.nchunks; ++j) spk_count_chunk( P, j, 1);
+	}
+	for (uint64_t j=0; j<P.nchunks; ++j) ev_off[ j+1] = ev_off[ j] + ev_count[ j];
+	P.ev_off = ev_off.data();
+	uint64_t nev = ev_off[ P.nchunks];
+	hs->events.assign( nev + 1, SpRawEvent());
+	hs->doc_ev_begin.assign( ndocs + 1, 0);
+	hs->doc_ev_begin[ ndocs] = nev;
+	P.events = hs->events.data(); P.doc_ev_begin = hs->doc_ev_begin.data();
+	for (uint64_t j=0; j<P.nchunks; ++j) spk_emit_chunk( P, j);
+	hs->events.resize( nev);
+	for (uint64_t i=0; i<nev; ++i) spk_finish_event( P, i);
+	P.ar_mult = P.T.has_symbols ? 2 : 1;
+	std::vector<SpMatchEvent> ar( nev * P.ar_mult + 2);
+	std::vector<uint32_t> doc_kept( ndocs+1), doc_nlex( ndocs+1);
+	std::vector<uint64_t> lex_off( ndocs+1, 0);
+	hs->status.assign( ndocs, 0);
+	uint32_t dummy = 0;
+	P.ar = ar.data(); P.doc_kept = doc_kept.data(); P.doc_nlex = doc_nlex.data(); P.status = ndocs ? hs->status.data() : &dummy;
+	for (uint32_t d=0; d<ndocs; ++d) spk_resolve_doc( P, d);
+	for (uint32_t d=0; d<ndocs; ++d) lex_off[ d+1] = lex_off[ d] + doc_nlex[ d];
+	hs->lexems.assign( lex_off[ ndocs] + 1, sp_lexem());
+	P.lex_off = lex_off.data(); P.lexems = hs->lexems.data();
+	for (uint32_t d=0; d<ndocs; ++d) spk_write_doc( P, d);
+	hs->lexems.resize( lex_off[ ndocs]);
+	hs->offsets = lex_off;
+	return 0;
+}
+uint64_t hsim_result_count( void* h) {return ((HostSim*)h)->lexems.size();}
+uint64_t hsim_raw_event_count( void* h) {return ((HostSim*)h)->events.size();}
+int hsim_fetch( void* h, sp_lexem* lexems, uint64_t* offsets, uint32_t* status)
+{
+	HostSim* hs = (HostSim*)h;
+	if (lexems && !hs->lexems.empty()) std::memcpy( lexems, hs->lexems.data(), hs->lexems.size()*sizeof(sp_lexem));
+	if (offsets) std::memcpy( offsets, hs->offsets.data(), hs->offsets.size()*sizeof(uint64_t));
+	if (status && !hs->status.empty()) std::memcpy( status, hs->status.data(), hs->status.size()*sizeof(uint32_t));
+	return 0;
+}
+// raw events after start resolution as (definition index 1-based, from, to) triples + per document offsets
+int hsim_fetch_raw( void* h, uint32_t* triples, uint64_t* offsets)
+{
+	HostSim* hs = (HostSim*)h;
+	for (std::size_t i=0; i<hs->events.size(); ++i)
+	{
+		triples[ 3*i] = hs->events[i].pat + 1; triples[ 3*i+1] = hs->events[i].from; triples[ 3*i+2] = hs->events[i].to;
+	}
+	if (offsets) std::memcpy( offsets, hs->doc_ev_begin.data(), hs->doc_ev_begin.size()*sizeof(uint64_t));
+	return 0;
+}
+
+} // extern "C"
