@@ -1,0 +1,196 @@
+"""ctypes binding of libstrus_pattern_b200.so (include/strus_pattern_b200.h) for the test and benchmark
+harness. The classes mirror the reference's interface triple (instance -> context) for each level:
+
+  Lexer        = PatternLexerInstanceInterface   (src/patternLexer.cpp:961-1151)
+  LexerContext = PatternLexerContextInterface    (src/patternLexer.cpp:681-959), batched
+  Matcher / MatcherContext likewise              (src/patternMatcher.cpp:345-704, 107-341)
+
+There is no fallback: if the CUDA library is missing or no device is usable, calls raise."""
+import ctypes as C
+import os
+
+import numpy as np
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG, "libstrus_pattern_b200.so")
+
+LEXEM_DT = np.dtype([("id", "<u4"), ("ordpos", "<u4"), ("origpos", "<u4"), ("origsize", "<u4")])
+RESULT_DT = np.dtype([(n, "<u4") for n in ("name", "format", "ordpos", "ordend", "origseg", "origpos",
+                                            "endseg", "endpos", "item_begin", "item_count")])
+ITEM_DT = np.dtype([(n, "<u4") for n in ("variable", "format", "ordpos", "ordend", "origseg", "origpos",
+                                          "endseg", "endpos")])
+STATS_DT = np.dtype([(n, "<u8") for n in ("nof_programs_installed", "nof_altkey_programs_installed",
+                                           "nof_signals_fired", "nof_open_patterns", "nof_events")])
+
+BIND_CONTENT, BIND_SUCCESSOR, BIND_PREDECESSOR, BIND_UNIQUE = 0, 1, 2, 3
+OP_SEQUENCE, OP_SEQUENCE_IMM, OP_SEQUENCE_STRUCT, OP_WITHIN, OP_WITHIN_STRUCT, OP_ANY, OP_AND = range(7)
+
+_lib = None
+
+
+class PatternError(RuntimeError):
+    def __init__(self, code, msg):
+        RuntimeError.__init__(self, "%s (code %d)" % (msg, code))
+        self.code = code
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError("CUDA library %s is not built (run __graft_entry__.build()); there is no CPU fallback" % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        vp, cp, u32, u64p = C.c_void_p, C.c_char_p, C.c_uint32, C.c_void_p
+        sigs = {
+            "sp_lexer_create": (vp, []), "sp_lexer_destroy": (None, [vp]), "sp_lexer_last_error": (cp, [vp]),
+            "sp_lexer_define_option": (C.c_int, [vp, cp, C.c_double]),
+            "sp_lexer_define_lexem": (C.c_int, [vp, u32, cp, C.c_size_t, u32, u32, u32]),
+            "sp_lexer_define_symbol": (C.c_int, [vp, u32, u32, cp, C.c_size_t]),
+            "sp_lexer_get_symbol": (u32, [vp, u32, cp, C.c_size_t]),
+            "sp_lexer_compile": (C.c_int, [vp]), "sp_lexer_table_info": (C.c_int64, [vp, cp]),
+            "sp_lexer_ctx_create": (vp, [vp, vp]), "sp_lexer_ctx_destroy": (None, [vp]),
+            "sp_lexer_ctx_last_error": (cp, [vp]),
+            "sp_lexer_scan": (C.c_int, [vp, vp, C.c_int, u64p, u32]),
+            "sp_lexer_result_count": (C.c_int64, [vp]),
+            "sp_lexer_result_lexems_device": (vp, [vp]), "sp_lexer_result_offsets_device": (vp, [vp]),
+            "sp_lexer_result_status_device": (vp, [vp]),
+            "sp_lexer_fetch": (C.c_int, [vp, vp, vp, vp]), "sp_lexer_ctx_counter": (C.c_int64, [vp, cp]),
+            "sp_version": (cp, []), "sp_device_count": (C.c_int, []),
+        }
+        msigs = {
+            "sp_matcher_create": (vp, []), "sp_matcher_destroy": (None, [vp]), "sp_matcher_last_error": (cp, [vp]),
+            "sp_matcher_define_option": (C.c_int, [vp, cp, C.c_double]),
+            "sp_matcher_define_term_frequency": (C.c_int, [vp, u32, C.c_double]),
+            "sp_matcher_push_term": (C.c_int, [vp, u32]),
+            "sp_matcher_push_expression": (C.c_int, [vp, C.c_int, C.c_size_t, u32, u32]),
+            "sp_matcher_push_pattern": (C.c_int, [vp, cp]), "sp_matcher_attach_variable": (C.c_int, [vp, cp]),
+            "sp_matcher_define_pattern": (C.c_int, [vp, cp, cp, C.c_int]),
+            "sp_matcher_compile": (C.c_int, [vp]), "sp_matcher_upload": (C.c_int, [vp]),
+            "sp_matcher_pattern_name": (cp, [vp, u32]), "sp_matcher_variable_name": (cp, [vp, u32]),
+            "sp_matcher_table_info": (C.c_int64, [vp, cp]),
+            "sp_matcher_ctx_create": (vp, [vp, vp]), "sp_matcher_ctx_destroy": (None, [vp]),
+            "sp_matcher_ctx_last_error": (cp, [vp]),
+            "sp_matcher_run": (C.c_int, [vp, vp, vp, vp, u32, C.c_int]),
+            "sp_matcher_result_count": (C.c_int64, [vp]), "sp_matcher_item_count": (C.c_int64, [vp]),
+            "sp_matcher_results_device": (vp, [vp]), "sp_matcher_items_device": (vp, [vp]),
+            "sp_matcher_fetch": (C.c_int, [vp, vp, vp, vp, vp, vp, vp]),
+            "sp_matcher_run_lexer_output": (C.c_int, [vp, vp]),
+        }
+        for table in (sigs, msigs):
+            for name, (res, args) in table.items():
+                if table is msigs and not hasattr(L, name):
+                    continue
+                f = getattr(L, name)
+                f.restype, f.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+class Lexer:
+    def __init__(self):
+        self.L = lib()
+        self.h = self.L.sp_lexer_create()
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.sp_lexer_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise PatternError(rc, self.L.sp_lexer_last_error(self.h).decode(errors="replace"))
+
+    def define_option(self, name, value=0.0):
+        self._ck(self.L.sp_lexer_define_option(self.h, name.encode(), value))
+
+    def define_lexem(self, id, expr, result_index=0, level=0, posbind=BIND_CONTENT):
+        e = expr if isinstance(expr, bytes) else expr.encode()
+        self._ck(self.L.sp_lexer_define_lexem(self.h, id, e, len(e), result_index, level, posbind))
+
+    def define_symbol(self, symbolid, lexemid, name):
+        n = name if isinstance(name, bytes) else name.encode()
+        self._ck(self.L.sp_lexer_define_symbol(self.h, symbolid, lexemid, n, len(n)))
+
+    def get_symbol(self, lexemid, name):
+        n = name if isinstance(name, bytes) else name.encode()
+        return int(self.L.sp_lexer_get_symbol(self.h, lexemid, n, len(n)))
+
+    def compile(self):
+        self._ck(self.L.sp_lexer_compile(self.h))
+
+    def table_info(self, key):
+        return int(self.L.sp_lexer_table_info(self.h, key.encode()))
+
+    def create_context(self, stream=None):
+        return LexerContext(self, stream)
+
+    # convenience with the interface of the oracle classes (tests swap them)
+    def scan(self, text, doc_offsets, **_):
+        ctx = self.create_context()
+        try:
+            return ctx.scan(text, doc_offsets)
+        finally:
+            ctx.close()
+
+    def match(self, src):
+        b = src if isinstance(src, bytes) else src.encode()
+        out = self.scan(b, [0, len(b)])
+        return [tuple(int(x) for x in r) for r in out["lexems"]]
+
+
+class LexerContext:
+    def __init__(self, lexer, stream=None):
+        self.L = lexer.L
+        self.lexer = lexer  # keep the instance alive (src/patternLexer.cpp:685: raw pointer into the instance)
+        self.h = self.L.sp_lexer_ctx_create(lexer.h, stream)
+        if not self.h:
+            raise PatternError(-4, self.L.sp_lexer_last_error(lexer.h).decode(errors="replace"))
+        self.ndocs = 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.sp_lexer_ctx_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def _ck(self, rc):
+        if rc < 0:
+            raise PatternError(rc, self.L.sp_lexer_ctx_last_error(self.h).decode(errors="replace"))
+        return rc
+
+    def launch(self, text, doc_offsets, on_device=False):
+        """text: host uint8 array (or int device pointer when on_device); doc_offsets: host uint64[ndocs+1]."""
+        offs = np.ascontiguousarray(doc_offsets, dtype=np.uint64)
+        self.ndocs = len(offs) - 1
+        if on_device:
+            tp = C.c_void_p(int(text))
+        else:
+            self._text = np.frombuffer(text, dtype=np.uint8) if isinstance(text, (bytes, bytearray)) else np.ascontiguousarray(text, dtype=np.uint8)
+            tp = _ptr(self._text)
+        self._ck(self.L.sp_lexer_scan(self.h, tp, 1 if on_device else 0, _ptr(offs), self.ndocs))
+
+    def count(self):
+        return self._ck(self.L.sp_lexer_result_count(self.h))
+
+    def counter(self, key):
+        return int(self.L.sp_lexer_ctx_counter(self.h, key.encode()))
+
+    def fetch(self):
+        n = self.count()
+        out = {"lexems": np.zeros(n, dtype=LEXEM_DT), "offsets": np.zeros(self.ndocs + 1, dtype=np.uint64),
+               "status": np.zeros(self.ndocs, dtype=np.uint32)}
+        self._ck(self.L.sp_lexer_fetch(self.h, _ptr(out["lexems"]) if n else None, _ptr(out["offsets"]),
+                                       _ptr(out["status"]) if self.ndocs else None))
+        out["raw_event_count"] = self.counter("raw_events")
+        return out
+
+    def scan(self, text, doc_offsets, on_device=False):
+        self.launch(text, doc_offsets, on_device)
+        return self.fetch()

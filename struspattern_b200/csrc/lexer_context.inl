@@ -1,0 +1,180 @@
+// Batched PatternLexerContext (included by lexer_capi.cu): owns the per-batch device buffers and drives the
+// kernel pipeline count -> verify/fix-up -> scan -> emit -> finish -> resolve -> scan -> write.
+
+struct sp_lexer_ctx
+{
+	const sp_lexer* lx;
+	cudaStream_t stream;
+	std::string lasterror;
+	uint32_t chunk, warmup;
+	// device buffers (grow only)
+	DeviceBuffer text, doc_off, start_state, end_state, ev_count, known, redo, scalars, ev_off, events, doc_ev_begin,
+		     ar, doc_kept, doc_nlex, lex_off, lexems, status, scantmp;
+	// last batch
+	uint32_t ndocs;
+	uint64_t total, nchunks, nev, nlex, fixups, rounds;
+	bool valid;
+	uint64_t* pinned;	// [4] host staging for scalar read backs
+
+	sp_lexer_ctx( const sp_lexer* lx_, cudaStream_t stream_)
+		:lx(lx_),stream(stream_),chunk(512),warmup(96),ndocs(0),total(0),nchunks(0),nev(0),nlex(0),fixups(0),rounds(0),valid(false),pinned(0)
+	{
+		const char* e;
+		if ((e = std::getenv( "SP_LEXER_CHUNK")) != 0 && std::atoi( e) >= 16) chunk = (uint32_t)std::atoi( e);
+		if ((e = std::getenv( "SP_LEXER_WARMUP")) != 0 && std::atoi( e) >= 0) warmup = (uint32_t)std::atoi( e);
+		SP_CUDA( cudaMallocHost( (void**)&pinned, 4 * sizeof(uint64_t)));
+	}
+	~sp_lexer_ctx() {if (pinned) cudaFreeHost( pinned);}
+
+	uint64_t readScalar( const void* devptr, std::size_t bytes)
+	{
+		pinned[0] = 0;
+		SP_CUDA( cudaMemcpyAsync( pinned, devptr, bytes, cudaMemcpyDeviceToHost, stream));
+		SP_CUDA( cudaStreamSynchronize( stream));
+		return pinned[0];
+	}
+
+	void scan( const uint8_t* text_in, int text_on_device, const uint64_t* doc_offsets, uint32_t ndocs_)
+	{
+		valid = false;
+		if (!lx->uploaded) throw std::runtime_error( "called scan without calling 'compile'");
+		int dev = -1;
+		SP_CUDA( cudaGetDevice( &dev));
+		if (dev != lx->device) throw std::runtime_error( "lexer tables live on another device than the current one");
+		for (uint32_t d=0; d<ndocs_; ++d) if (doc_offsets[d+1] < doc_offsets[d]) throw std::runtime_error( "document offsets are not ascending");
+		if (ndocs_ && doc_offsets[0] != 0) throw std::runtime_error( "document offsets must start at 0");
+		ndocs = ndocs_;
+		total = ndocs ? doc_offsets[ ndocs] : 0;
+		nchunks = (total + chunk - 1) / chunk;
+		nev = nlex = fixups = rounds = 0;
+
+		SpScanParams P; std::memset( &P, 0, sizeof(P));
+		P.T = lx->dev;
+		if (text_on_device) P.text = text_in;
+		else
+		{
+			uint8_t* t = text.as<uint8_t>( total + 16);
+			if (total) SP_CUDA( cudaMemcpyAsync( t, text_in, total, cudaMemcpyHostToDevice, stream));
+			P.text = t;
+		}
+		uint64_t* d_doc_off = doc_off.as<uint64_t>( (std::size_t)ndocs + 1);
+		if (ndocs) SP_CUDA( cudaMemcpyAsync( d_doc_off, doc_offsets, ((std::size_t)ndocs + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, stream));
+		else SP_CUDA( cudaMemsetAsync( d_doc_off, 0, sizeof(uint64_t), stream));
+		P.doc_off = d_doc_off; P.ndocs = ndocs; P.total = total; P.chunk = chunk; P.warmup = warmup; P.nchunks = nchunks;
+		P.start_state = start_state.as<uint32_t>( nchunks); P.end_state = end_state.as<uint32_t>( nchunks);
+		P.ev_count = ev_count.as<uint32_t>( nchunks);
+		P.known = known.as<uint8_t>( nchunks); P.redo = redo.as<uint8_t>( nchunks);
+		uint64_t* d_scalars = scalars.as<uint64_t>( 4);
+		P.nbad = reinterpret_cast<uint32_t*>( d_scalars);
+		uint64_t* d_ev_off = ev_off.as<uint64_t>( nchunks + 1);
+		P.ev_off = d_ev_off;
+		uint64_t* d_doc_ev_begin = doc_ev_begin.as<uint64_t>( (std::size_t)ndocs + 1);
+		P.doc_ev_begin = d_doc_ev_begin;
+		P.doc_kept = doc_kept.as<uint32_t>( ndocs); P.doc_nlex = doc_nlex.as<uint32_t>( ndocs);
+		uint64_t* d_lex_off = lex_off.as<uint64_t>( (std::size_t)ndocs + 1);
+		P.lex_off = d_lex_off;
+		P.status = status.as<uint32_t>( ndocs);
+		P.ar_mult = lx->dev.has_symbols ? 2 : 1;
+
+		if (nchunks)
+		{
+			unsigned int grid = (unsigned int)((nchunks + LexScanThreads - 1) / LexScanThreads);
+			unsigned int vgrid = (unsigned int)((nchunks + 255) / 256);
+			k_lex_count<<<grid, LexScanThreads, 0, stream>>>( P, 0);
+			for (;;)
+			{
+				SP_CUDA( cudaMemsetAsync( P.nbad, 0, sizeof(uint32_t), stream));
+				k_lex_verify<<<vgrid, 256, 0, stream>>>( P);
+				SP_CUDA( cudaGetLastError());
+				uint32_t nbad = (uint32_t)readScalar( P.nbad, sizeof(uint32_t));
+				if (!nbad) break;
+				fixups += nbad; ++rounds;
+				k_lex_count<<<grid, LexScanThreads, 0, stream>>>( P, 1);
+			}
+		}
+		exclusiveScan( P.ev_count, nchunks, d_ev_off, scantmp, stream);
+		nev = readScalar( d_ev_off + nchunks, sizeof(uint64_t));
+		P.events = events.as<SpRawEvent>( nev);
+		SP_CUDA( cudaMemsetAsync( d_doc_ev_begin, 0, ((std::size_t)ndocs + 1) * sizeof(uint64_t), stream));
+		if (ndocs) SP_CUDA( cudaMemcpyAsync( d_doc_ev_begin + ndocs, d_ev_off + nchunks, sizeof(uint64_t), cudaMemcpyDeviceToDevice, stream));
+		if (nchunks)
+		{
+			unsigned int grid = (unsigned int)((nchunks + LexScanThreads - 1) / LexScanThreads);
+			k_lex_emit<<<grid, LexScanThreads, 0, stream>>>( P);
+		}
+		if (nev)
+		{
+			unsigned int grid = (unsigned int)((nev + LexEventThreads - 1) / LexEventThreads);
+			k_lex_finish<<<grid, LexEventThreads, 0, stream>>>( P, nev);
+		}
+		P.ar = ar.as<SpMatchEvent>( nev * P.ar_mult + 2);
+		if (ndocs)
+		{
+			unsigned int grid = (ndocs + LexDocThreads - 1) / LexDocThreads;
+			k_lex_resolve<<<grid, LexDocThreads, 0, stream>>>( P);
+		}
+		exclusiveScan( P.doc_nlex, ndocs, d_lex_off, scantmp, stream);
+		nlex = readScalar( d_lex_off + ndocs, sizeof(uint64_t));
+		P.lexems = lexems.as<sp_lexem>( nlex);
+		if (ndocs)
+		{
+			unsigned int grid = (ndocs + LexDocThreads - 1) / LexDocThreads;
+			k_lex_write<<<grid, LexDocThreads, 0, stream>>>( P);
+		}
+		SP_CUDA( cudaGetLastError());
+		valid = true;
+	}
+};
+
+extern "C" {
+
+sp_lexer_ctx* sp_lexer_ctx_create( const sp_lexer* lx, void* cuda_stream)
+{
+	try {return new sp_lexer_ctx( lx, (cudaStream_t)cuda_stream);}
+	catch (const std::exception& e) {const_cast<sp_lexer*>( lx)->lasterror = e.what(); return 0;}
+}
+void sp_lexer_ctx_destroy( sp_lexer_ctx* ctx) {delete ctx;}
+const char* sp_lexer_ctx_last_error( const sp_lexer_ctx* ctx) {return ctx->lasterror.c_str();}
+
+int sp_lexer_scan( sp_lexer_ctx* ctx, const uint8_t* text, int text_on_device, const uint64_t* doc_offsets, uint32_t ndocs)
+	{SP_LEXER_TRY( ctx, ctx->scan( text, text_on_device, doc_offsets, ndocs))}
+
+int64_t sp_lexer_result_count( sp_lexer_ctx* ctx)
+{
+	if (!ctx->valid) {ctx->lasterror = "no finished scan"; return SP_ERR_ARGUMENT;}
+	if (cudaStreamSynchronize( ctx->stream) != cudaSuccess) {ctx->lasterror = "kernel failure"; return SP_ERR_CUDA;}
+	return (int64_t)ctx->nlex;
+}
+const sp_lexem* sp_lexer_result_lexems_device( sp_lexer_ctx* ctx) {return ctx->valid ? (const sp_lexem*)ctx->lexems.ptr() : 0;}
+const uint64_t* sp_lexer_result_offsets_device( sp_lexer_ctx* ctx) {return ctx->valid ? (const uint64_t*)ctx->lex_off.ptr() : 0;}
+const uint32_t* sp_lexer_result_status_device( sp_lexer_ctx* ctx) {return ctx->valid ? (const uint32_t*)ctx->status.ptr() : 0;}
+
+int sp_lexer_fetch( sp_lexer_ctx* ctx, sp_lexem* lexems, uint64_t* offsets, uint32_t* status)
+{
+	SP_LEXER_TRY( ctx, {
+		if (!ctx->valid) throw std::runtime_error( "no finished scan");
+		if (lexems && ctx->nlex) SP_CUDA( cudaMemcpyAsync( lexems, ctx->lexems.ptr(), ctx->nlex * sizeof(sp_lexem), cudaMemcpyDeviceToHost, ctx->stream));
+		if (offsets) SP_CUDA( cudaMemcpyAsync( offsets, ctx->lex_off.ptr(), ((std::size_t)ctx->ndocs + 1) * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+		if (status && ctx->ndocs) SP_CUDA( cudaMemcpyAsync( status, ctx->status.ptr(), (std::size_t)ctx->ndocs * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+		SP_CUDA( cudaStreamSynchronize( ctx->stream));
+	})
+}
+
+int64_t sp_lexer_ctx_counter( sp_lexer_ctx* ctx, const char* key)
+{
+	std::string k( key);
+	if (k == "raw_events") return (int64_t)ctx->nev;
+	if (k == "lexems") return (int64_t)ctx->nlex;
+	if (k == "chunks") return (int64_t)ctx->nchunks;
+	if (k == "fixup_chunks") return (int64_t)ctx->fixups;
+	if (k == "fixup_rounds") return (int64_t)ctx->rounds;
+	if (k == "text_bytes") return (int64_t)ctx->total;
+	if (k == "chunk_bytes") return (int64_t)ctx->chunk;
+	if (k == "kernel_launches") return (int64_t)(1 + 2*ctx->rounds + 1 + 3 + 1 + 1 + 1 + 3 + 1);
+	return -1;
+}
+
+const char* sp_version(void) {return "strus_pattern_b200 0.1.0";}
+int sp_device_count(void) {int n = 0; return cudaGetDeviceCount( &n) == cudaSuccess ? n : 0;}
+
+} // extern "C"

@@ -13,7 +13,7 @@
 #include "strus_pattern_b200.h"
 
 #ifdef __CUDACC__
-#define SP_HD __host__ __device__ __forceinline__
+#define SP_HD __device__ __forceinline__
 #define SP_LDG(p) __ldg(p)
 #else
 #define SP_HD inline

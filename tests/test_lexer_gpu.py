@@ -1,0 +1,90 @@
+"""Parity of the CUDA lexer (through the C ABI) with the level-1 oracle and the reference's golden vector."""
+import numpy as np
+import pytest
+
+from lexer_cases import LEXEM_SETS, define_set, make_batch
+from oracle_util import OracleLexer
+from test_oracle_lexer import _golden_cases, build_case
+
+pytestmark = pytest.mark.gpu
+
+
+def _gpu_lexer():
+    from struspattern_b200 import Lexer
+    return Lexer
+
+
+def test_golden_case1_exact():
+    case = _golden_cases()[0]
+    lx = build_case(_gpu_lexer(), case)
+    lx.compile()
+    assert lx.match(case["src_latin1"].encode("latin-1")) == [tuple(r) for r in case["results"]]
+
+
+def _same(ro, rg):
+    assert (ro["status"] == rg["status"]).all()
+    assert (ro["offsets"] == rg["offsets"]).all()
+    assert len(ro["lexems"]) == len(rg["lexems"]) and (ro["lexems"] == rg["lexems"]).all()
+    assert ro["raw_event_count"] == rg["raw_event_count"]
+
+
+@pytest.mark.parametrize("name", sorted(LEXEM_SETS))
+def test_random_text_matches_oracle(name):
+    o = define_set(OracleLexer(), name)
+    g = define_set(_gpu_lexer()(), name)
+    text, offs = make_batch(seed=77 + len(name), ndocs=300, mean_bytes=2000)
+    _same(o.scan(text, offs, nthreads=8), g.scan(text, offs))
+
+
+def test_device_resident_text_and_context_reuse():
+    import torch
+    o = define_set(OracleLexer(), "phrases_dates")
+    g = define_set(_gpu_lexer()(), "phrases_dates")
+    ctx = g.create_context()
+    for seed in (1, 2, 3):
+        text, offs = make_batch(seed=seed, ndocs=50 * seed, mean_bytes=700)
+        dev = torch.from_numpy(text).cuda()
+        _same(o.scan(text, offs, nthreads=8), ctx.scan(dev.data_ptr(), offs, on_device=True))
+
+
+def test_speculation_is_repaired():
+    defs = [(1, r"x.*y", 0, 1, 0), (2, r"[a-z]+", 0, 0, 0)]
+    o, g = OracleLexer(), _gpu_lexer()()
+    for lx in (o, g):
+        lx.define_option("DOTALL")
+        for d in defs:
+            lx.define_lexem(*d)
+        lx.compile()
+    text = (b"x" + b"ab " * 1000 + b"y " + b"cd " * 500) * 2
+    offs = [0, len(text) // 2, len(text)]
+    ctx = g.create_context()
+    _same(o.scan(text, offs), ctx.scan(text, offs))
+    assert ctx.counter("fixup_chunks") > 0
+
+
+def test_edge_cases():
+    o = define_set(OracleLexer(), "words_numbers")
+    g = define_set(_gpu_lexer()(), "words_numbers")
+    docs = [b"", b"the", b"", b"", b"new york 42", b"a", b"", b"3.14, x."]
+    offs = np.cumsum([0] + [len(d) for d in docs]).astype(np.uint64)
+    _same(o.scan(b"".join(docs), offs), g.scan(b"".join(docs), offs))
+    for offs in ([0, 0, 0], [0]):
+        r = g.scan(b"", offs)
+        assert len(r["lexems"]) == 0 and (r["offsets"] == 0).all()
+    # token size limit: error of that document only (src/patternLexer.cpp:727-730)
+    g2 = _gpu_lexer()()
+    g2.define_lexem(1, "\\ba+\\b", 0, 0, 0)
+    g2.compile()
+    text = b"a" * 65535 + b"a" * 65534
+    out = g2.scan(text, [0, 65535, len(text)])
+    assert out["status"][0] != 0 and out["status"][1] == 0
+    assert [tuple(int(x) for x in r) for r in out["lexems"]] == [(1, 1, 0, 65534)]
+
+
+def test_double_insert_quirk_and_symbols():
+    lx = _gpu_lexer()()
+    lx.define_lexem(1, "[a-z]\\b", 0, 0, 0)
+    lx.define_lexem(2, "a b c\\b", 0, 0, 0)
+    lx.define_symbol(9, 2, "a b c")
+    lx.compile()
+    assert lx.match("a b c") == [(1, 1, 0, 1), (2, 1, 0, 5), (9, 1, 0, 5), (0, 1, 0, 0), (1, 2, 4, 1)]

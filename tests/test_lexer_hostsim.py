@@ -1,0 +1,107 @@
+"""Product host compiler (regex -> DFA tables) + per-thread kernel bodies, run as CPU loops by tests/hostsim,
+against the level-1 oracle and the reference's golden vector. No GPU needed; the GPU tests (test_lexer_gpu.py)
+run the same cases through the C ABI and the CUDA kernels."""
+import numpy as np
+import pytest
+
+from hostsim_util import HostSimLexer
+from lexer_cases import LEXEM_SETS, define_set, make_batch
+from oracle_util import OracleLexer
+from test_oracle_lexer import _golden_cases, build_case
+
+
+def test_golden_case1_exact():
+    case = _golden_cases()[0]
+    lx = build_case(HostSimLexer, case)
+    lx.compile()
+    assert lx.match(case["src_latin1"].encode("latin-1")) == [tuple(r) for r in case["results"]]
+
+
+@pytest.mark.parametrize("idx", [1, 2])
+def test_edit_distance_is_declared_unsupported(idx):
+    lx = build_case(HostSimLexer, _golden_cases()[idx])
+    with pytest.raises(RuntimeError, match="unsupported"):
+        lx.compile()
+
+
+def _same(ro, rh, captures):
+    assert (ro["status"] == rh["status"]).all()
+    assert (ro["offsets"] == rh["offsets"]).all()
+    assert len(ro["lexems"]) == len(rh["lexems"]) and (ro["lexems"] == rh["lexems"]).all()
+    # raw engine events: the oracle lists them before, the product after the sub expression selection
+    keep_o = ~np.isin(ro["raw"][:, 0], captures)
+    keep_h = ~np.isin(rh["raw"][:, 0], captures)
+    assert (ro["raw"][keep_o] == rh["raw"][keep_h]).all()
+
+
+@pytest.mark.parametrize("name", sorted(LEXEM_SETS))
+@pytest.mark.parametrize("chunk,warmup", [(16, 4), (64, 16), (512, 64)])
+def test_random_text_matches_oracle(name, chunk, warmup):
+    o = define_set(OracleLexer(), name)
+    h = define_set(HostSimLexer(chunk=chunk, warmup=warmup), name)
+    captures = [i + 1 for i, d in enumerate(LEXEM_SETS[name]) if d[2]]
+    text, offs = make_batch(seed=chunk * 1000 + len(name), ndocs=30, mean_bytes=250)
+    _same(o.scan(text, offs, nthreads=4, keep_raw=True), h.scan(text, offs, keep_raw=True), captures)
+
+
+def test_speculation_is_repaired():
+    """A lexem that carries state over any distance ('x.*y' with DOTALL) defeats the warm-up guess of the
+    chunk start states; the verify/fix-up rounds must still give the exact result."""
+    defs = [(1, r"x.*y", 0, 1, 0), (2, r"[a-z]+", 0, 0, 0)]
+    o, h = OracleLexer(), HostSimLexer(chunk=32, warmup=8)
+    for lx in (o, h):
+        lx.define_option("DOTALL")
+        for d in defs:
+            lx.define_lexem(*d)
+        lx.compile()
+    text = (b"x" + b"ab " * 100 + b"y " + b"cd " * 50) * 2
+    offs = [0, len(text) // 2, len(text)]
+    ro, rh = o.scan(text, offs, keep_raw=True), h.scan(text, offs, keep_raw=True)
+    _same(ro, rh, [])
+    assert h.info("fixups") > 0 and h.info("rounds") > 0
+
+
+def test_documents_smaller_than_a_chunk_and_empty_documents():
+    o = define_set(OracleLexer(), "words_numbers")
+    h = define_set(HostSimLexer(chunk=256, warmup=32), "words_numbers")
+    docs = [b"", b"the", b"", b"", b"new york 42", b"a", b"", b"3.14, x."]
+    offs = np.cumsum([0] + [len(d) for d in docs]).astype(np.uint64)
+    text = b"".join(docs)
+    _same(o.scan(text, offs, keep_raw=True), h.scan(text, offs, keep_raw=True), [])
+    # all documents empty, and no documents at all
+    for offs in ([0, 0, 0], [0]):
+        r = h.scan(b"", offs)
+        assert len(r["lexems"]) == 0 and (r["offsets"] == 0).all()
+
+
+def test_double_insert_quirk_and_symbols():
+    for cls in (OracleLexer, HostSimLexer):
+        lx = cls()
+        lx.define_lexem(1, "[a-z]\\b", 0, 0, 0)
+        lx.define_lexem(2, "a b c\\b", 0, 0, 0)
+        lx.define_symbol(9, 2, "a b c")
+        lx.compile()
+        assert lx.match("a b c") == [(1, 1, 0, 1), (2, 1, 0, 5), (9, 1, 0, 5), (0, 1, 0, 0), (1, 2, 4, 1)]
+
+
+def test_token_size_limit_is_an_error_of_the_document():
+    h = HostSimLexer(chunk=4096, warmup=64)
+    h.define_lexem(1, "\\ba+\\b", 0, 0, 0)
+    h.compile()
+    text = b"a" * 65535 + b"a" * 65534
+    out = h.scan(text, [0, 65535, len(text)])
+    assert out["status"][0] != 0 and out["status"][1] == 0
+    assert [tuple(int(x) for x in r) for r in out["lexems"]] == [(1, 1, 0, 65534)]
+
+
+def test_compile_errors_and_state_errors():
+    for bad in ["a(", "[a-", "a**", "(?=x)", "\\1", "x*"]:
+        lx = HostSimLexer()
+        lx.define_lexem(1, bad)
+        with pytest.raises(RuntimeError):
+            lx.compile()
+    lx = HostSimLexer()
+    lx.define_lexem(1, "a")
+    lx.compile()
+    with pytest.raises(RuntimeError):
+        lx.define_lexem(2, "b")  # src/patternLexer.cpp:999-1002
