@@ -1,0 +1,302 @@
+#!/usr/bin/env python3
+"""Benchmark of the strusPattern hot path on B200 (BASELINE.json metric: GB/s of UTF-8 text lexed).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--bytes B]
+
+A step = one pass of the lexer over one batch of synthetic text (workload C2 of SURVEY.md 8d: ~100 lexem
+regexes over 1 GiB of UTF-8 text in documents of 4-64 KiB), per GPU (weak scaling: every rank owns its own
+shard generated from (seed, rank)). `value` is measured with the text resident in HBM, `e2e` through the
+C ABI with pinned host buffers (H2D of the text and D2H of the lexems inside the timed region).
+--impl reference times the reference's CPU path of level 1; Hyperscan is not available here, so this is the
+CPU restatement (oracle/lexer_oracle.cpp, kind "port") on all host cores over a bounded sample.
+Prints ONE JSON line on rank 0."""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "GB/s UTF-8 text lexed+matched at 1/2/4/8 B200 vs same-box hyperscan CPU path"
+SEED = 0x5354525553000002
+FIXED_WORDS = None
+
+
+def fixed_words():
+    from struspattern_b200 import workloads as W
+    return W.PHRASE_FIRST + W.PHRASE_SECOND + W.ABBREVIATIONS + ["the", "of", "and", "to", "in", "a", "is", "that", "for", "it"]
+
+
+def make_corpus(nbytes, rank, pinned):
+    """-> (host uint8 array, offsets, keepalive)"""
+    from bench_util import corpus
+    vocab = corpus.vocabulary(SEED, 50000, fixed_words())
+    offs = corpus.layout(SEED + 1000 * rank, nbytes)
+    keep = None
+    if pinned:
+        import torch
+        keep = torch.empty(int(nbytes) + 64, dtype=torch.uint8, pin_memory=True)
+        text = keep.numpy()[:nbytes]
+    else:
+        text = np.zeros(int(nbytes), dtype=np.uint8)
+    corpus.fill(SEED + 1000 * rank, vocab, text, offs)
+    return text, offs, keep
+
+
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown," \
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                       "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        rows = [r.split(",") for r in open(self.f.name).read().strip().splitlines() if r.count(",") >= 8]
+        os.unlink(self.f.name)
+        sm, mx, reasons = [], [], set()
+        for r in rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                if v.strip().lower().startswith("active"):
+                    reasons.add(name)
+        if sm:
+            out = {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+        return out
+
+
+def measured_peak():
+    try:
+        d = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(d["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+def cpu_lexer_rate(text, offs, seconds_target, nthreads):
+    """Oracle (CPU restatement of level 1) on a bounded prefix of the corpus -> (GB/s, sample bytes, seconds)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from oracle_util import OracleLexer
+    from struspattern_b200 import workloads as W
+    o = W.define_lexer(OracleLexer())
+    # probe on ~1 MiB, then size the sample for the target duration
+    nd = int(np.searchsorted(offs, 1 << 20, side="right"))
+    nd = max(1, min(nd, len(offs) - 1))
+    t = time.perf_counter()
+    o.scan(text[:int(offs[nd])], offs[:nd + 1], nthreads=nthreads)
+    dt = time.perf_counter() - t
+    rate = float(offs[nd]) / max(dt, 1e-9)
+    want = rate * seconds_target
+    nd2 = int(np.searchsorted(offs, want, side="right"))
+    nd2 = max(nd, min(nd2, len(offs) - 1))
+    t = time.perf_counter()
+    o.scan(text[:int(offs[nd2])], offs[:nd2 + 1], nthreads=nthreads)
+    dt = time.perf_counter() - t
+    return float(offs[nd2]) / dt / 1e9, int(offs[nd2]), dt
+
+
+KERNELS = ["k_lex_count", "k_lex_verify", "k_lex_emit", "k_lex_finish", "k_lex_resolve", "k_lex_write", "k_scan"]
+
+
+def algorithmic_bytes(kernel, c):
+    """Bytes one launch of `kernel` has to move by the algorithm (DESIGN.md 'kernels'), c = batch counters."""
+    n_text, nev, nlex, ndocs, nchunks = c["text_bytes"], c["raw_events"], c["lexems"], c["ndocs"], c["chunks"]
+    return {
+        "k_lex_count": n_text + 12 * nchunks,                 # text read once, start/end state + count per chunk
+        "k_lex_verify": 9 * nchunks,
+        "k_lex_emit": n_text + 16 * nev + 12 * nchunks,       # text read once, one 16 B event record per raw event
+        "k_lex_finish": 32 * nev,                             # event record read + written (text re-reads hit L2)
+        "k_lex_resolve": 16 * nev + 16 * nlex + 16 * ndocs,   # events read, kept match events written
+        "k_lex_write": 32 * nlex + 24 * ndocs,                # kept match events read, 16 B lexem records written
+        "k_scan": 12 * (nchunks + ndocs),
+    }[kernel]
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return None
+    nthreads = os.cpu_count() or 1
+    text, offs, _ = make_corpus(min(args.bytes, 256 << 20), 0, pinned=False)
+    per_step = max(2.0, 60.0 / max(1, args.steps + args.warmup))
+    rates = []
+    sample = 0
+    for i in range(args.warmup + args.steps):
+        r, sample, dt = cpu_lexer_rate(text, offs, per_step, nthreads)
+        if i >= args.warmup:
+            rates.append((r, dt))
+    total_t = sum(dt for _, dt in rates)
+    value = sample * len(rates) / total_t / 1e9
+    return {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1000.0 * total_t / len(rates), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "C2 lexer only: %d lexem definitions, CPU sample of the 1 GiB corpus" % args.ndefs,
+                   "sample_bytes": sample},
+        "cpu_baseline": {"value": value, "unit": "GB/s", "cores": nthreads, "kind": "port",
+                         "sample": "first %d bytes of the C2 corpus per step; level-1 CPU restatement (Hyperscan/libtre not installable here)" % sample},
+        "e2e": {"value": value, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from struspattern_b200 import LEXEM_DT, Lexer
+    from struspattern_b200 import workloads as W
+
+    torch.cuda.set_device(local_rank)
+    lx = W.define_lexer(Lexer())
+    text, offs, keep = make_corpus(args.bytes, rank, pinned=True)
+    ndocs = len(offs) - 1
+    dev_text = torch.empty(len(text) + 64, dtype=torch.uint8, device="cuda")
+    dev_text[:len(text)].copy_(keep[:len(text)], non_blocking=False)
+    ctx = lx.create_context()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device resident
+    for _ in range(args.warmup):
+        ctx.launch(dev_text.data_ptr(), offs, on_device=True)
+        ctx.count()
+    counters = {k: ctx.counter(k) for k in ("raw_events", "lexems", "chunks", "fixup_chunks", "fixup_rounds", "text_bytes", "kernel_launches")}
+    counters["ndocs"] = ndocs
+    ctx.counter("profile:on"); ctx.counter("profile:reset")
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    launches = 0
+    for _ in range(args.steps):
+        ctx.launch(dev_text.data_ptr(), offs, on_device=True)
+        ctx.count()
+        launches += ctx.counter("kernel_launches")
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    ms = e0.elapsed_time(e1)
+    ktimes = {k: (ctx.counter("time_us:" + k), ctx.counter("calls:" + k)) for k in KERNELS}
+    ctx.counter("profile:off")
+
+    # ---- end to end through the C ABI with pinned host buffers
+    nlex = counters["lexems"]
+    out_keep = torch.empty((nlex + 1024) * 16, dtype=torch.uint8, pin_memory=True)
+    out_lex = out_keep.numpy().view(LEXEM_DT)
+    out_offs = torch.empty(ndocs + 1, dtype=torch.int64, pin_memory=True).numpy().view(np.uint64)
+    out_status = torch.empty(ndocs, dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)
+    e2e_steps = max(1, min(args.steps, 3))
+    ctx.launch(text, offs, on_device=False)
+    ctx.fetch_into(out_lex, out_offs, out_status)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        ctx.launch(text, offs, on_device=False)
+        ctx.fetch_into(out_lex, out_offs, out_status)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    if int(out_status.max(initial=0)) != 0:
+        raise RuntimeError("lexer reported document errors on the synthetic corpus")
+
+    times = torch.tensor([ms, e2e_s * 1000.0], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    ms_max, e2e_ms_max = float(times[0]), float(times[1])
+    if rank != 0:
+        return None
+    total_bytes = float(args.bytes) * world
+    value = total_bytes * args.steps / (ms_max / 1000.0) / 1e9
+    e2e_value = total_bytes * e2e_steps / (e2e_ms_max / 1000.0) / 1e9
+    dominant = max(KERNELS, key=lambda k: ktimes[k][0])
+    dom_us, dom_calls = ktimes[dominant]
+    peak, peak_kind = measured_peak()
+    achieved = algorithmic_bytes(dominant, counters) / (dom_us / max(1, dom_calls) * 1e-6) / 1e9 if dom_us else 0.0
+    # the count kernel runs 1 + fix-up rounds times per step; report per launch
+    line = {
+        "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "C2 lexer only: %d lexem definitions over %d bytes of synthetic UTF-8 text per GPU in %d documents (4-64 KiB)"
+                               % (lx.table_info("definitions"), args.bytes, ndocs),
+                   "l2": "input (%.0f MiB) larger than L2, no flush needed" % (args.bytes / 2**20),
+                   "lexems_per_step": counters["lexems"], "raw_events_per_step": counters["raw_events"],
+                   "fwd_states": lx.table_info("fwd_states"), "fwd_table_bytes": lx.table_info("fwd_table_bytes"),
+                   "fixup_chunks": counters["fixup_chunks"], "chunks": counters["chunks"]},
+        "clocks": clocks,
+        "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": int(args.bytes + 8 * (ndocs + 1)),
+                "d2h_bytes_per_step": int(16 * nlex + 8 * (ndocs + 1) + 4 * ndocs), "steps": e2e_steps},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": None, "peak_kind": peak_kind,
+                     "kernel_ms_per_step": {k: ktimes[k][0] / 1000.0 / args.steps for k in KERNELS}},
+        "matches_per_s": counters["lexems"] * world * args.steps / (ms_max / 1000.0),
+    }
+    if world == 1 and not args.no_cpu:
+        r, sample, dt = cpu_lexer_rate(text, offs, args.cpu_seconds, os.cpu_count() or 1)
+        line["cpu_baseline"] = {"value": r, "unit": "GB/s", "cores": os.cpu_count() or 1, "kind": "port",
+                                "sample": "first %d bytes of the same corpus, %.1f s; level-1 CPU restatement (Hyperscan not installable here)" % (sample, dt)}
+    return line
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--bytes", type=int, default=1 << 30)
+    ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.ndefs = 86
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        line = run_reference(args, rank, world)
+    else:
+        if world > 1:
+            import torch
+            import torch.distributed as dist
+            torch.cuda.set_device(local_rank)
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        line = run_ours(args, rank, world, local_rank)
+        if world > 1:
+            import torch.distributed as dist
+            dist.barrier()
+            dist.destroy_process_group()
+    if line is not None:
+        print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -191,6 +191,14 @@ class LexerContext:
         out["raw_event_count"] = self.counter("raw_events")
         return out
 
+    def fetch_into(self, lexems, offsets, status):
+        """Copy the results into caller provided (e.g. pinned) arrays; returns the number of lexems."""
+        n = self.count()
+        if n > len(lexems):
+            raise PatternError(-1, "result buffer too small: %d lexems" % n)
+        self._ck(self.L.sp_lexer_fetch(self.h, _ptr(lexems), _ptr(offsets), _ptr(status)))
+        return n
+
     def scan(self, text, doc_offsets, on_device=False):
         self.launch(text, doc_offsets, on_device)
         return self.fetch()

@@ -15,16 +15,58 @@ struct sp_lexer_ctx
 	uint64_t total, nchunks, nev, nlex, fixups, rounds;
 	bool valid;
 	uint64_t* pinned;	// [4] host staging for scalar read backs
+	// optional per kernel timing with CUDA events on the context's stream (SP_LEXER_PROFILE=1 or counter "profile:on")
+	enum KernelId {KCount, KVerify, KEmit, KFinish, KResolve, KWrite, KScan, NofKernelIds};
+	struct Span {int kernel; cudaEvent_t a, b;};
+	bool profile;
+	std::vector<Span> spans;
+	std::size_t nspans;
+	double kernel_ms[ NofKernelIds];
+	uint64_t kernel_calls[ NofKernelIds];
+
+	void spanBegin( int kernel)
+	{
+		if (!profile) return;
+		if (nspans == spans.size())
+		{
+			Span sp; sp.kernel = kernel;
+			SP_CUDA( cudaEventCreate( &sp.a)); SP_CUDA( cudaEventCreate( &sp.b));
+			spans.push_back( sp);
+		}
+		spans[ nspans].kernel = kernel;
+		SP_CUDA( cudaEventRecord( spans[ nspans].a, stream));
+	}
+	void spanEnd()
+	{
+		if (!profile) return;
+		SP_CUDA( cudaEventRecord( spans[ nspans].b, stream));
+		++nspans;
+	}
+	void collectSpans()
+	{
+		for (std::size_t i=0; i<nspans; ++i)
+		{
+			float ms = 0.0f;
+			if (cudaEventElapsedTime( &ms, spans[i].a, spans[i].b) == cudaSuccess) {kernel_ms[ spans[i].kernel] += ms; kernel_calls[ spans[i].kernel] += 1;}
+		}
+		nspans = 0;
+	}
 
 	sp_lexer_ctx( const sp_lexer* lx_, cudaStream_t stream_)
-		:lx(lx_),stream(stream_),chunk(512),warmup(96),ndocs(0),total(0),nchunks(0),nev(0),nlex(0),fixups(0),rounds(0),valid(false),pinned(0)
+		:lx(lx_),stream(stream_),chunk(512),warmup(96),ndocs(0),total(0),nchunks(0),nev(0),nlex(0),fixups(0),rounds(0),valid(false),pinned(0),profile(false),nspans(0)
 	{
+		std::memset( kernel_ms, 0, sizeof(kernel_ms)); std::memset( kernel_calls, 0, sizeof(kernel_calls));
+		if (std::getenv( "SP_LEXER_PROFILE")) profile = true;
 		const char* e;
 		if ((e = std::getenv( "SP_LEXER_CHUNK")) != 0 && std::atoi( e) >= 16) chunk = (uint32_t)std::atoi( e);
 		if ((e = std::getenv( "SP_LEXER_WARMUP")) != 0 && std::atoi( e) >= 0) warmup = (uint32_t)std::atoi( e);
 		SP_CUDA( cudaMallocHost( (void**)&pinned, 4 * sizeof(uint64_t)));
 	}
-	~sp_lexer_ctx() {if (pinned) cudaFreeHost( pinned);}
+	~sp_lexer_ctx()
+	{
+		if (pinned) cudaFreeHost( pinned);
+		for (Span& sp: spans) {cudaEventDestroy( sp.a); cudaEventDestroy( sp.b);}
+	}
 
 	uint64_t readScalar( const void* devptr, std::size_t bytes)
 	{
@@ -80,19 +122,19 @@ struct sp_lexer_ctx
 		{
 			unsigned int grid = (unsigned int)((nchunks + LexScanThreads - 1) / LexScanThreads);
 			unsigned int vgrid = (unsigned int)((nchunks + 255) / 256);
-			k_lex_count<<<grid, LexScanThreads, 0, stream>>>( P, 0);
+			spanBegin( KCount); k_lex_count<<<grid, LexScanThreads, 0, stream>>>( P, 0); spanEnd();
 			for (;;)
 			{
 				SP_CUDA( cudaMemsetAsync( P.nbad, 0, sizeof(uint32_t), stream));
-				k_lex_verify<<<vgrid, 256, 0, stream>>>( P);
+				spanBegin( KVerify); k_lex_verify<<<vgrid, 256, 0, stream>>>( P); spanEnd();
 				SP_CUDA( cudaGetLastError());
 				uint32_t nbad = (uint32_t)readScalar( P.nbad, sizeof(uint32_t));
 				if (!nbad) break;
 				fixups += nbad; ++rounds;
-				k_lex_count<<<grid, LexScanThreads, 0, stream>>>( P, 1);
+				spanBegin( KCount); k_lex_count<<<grid, LexScanThreads, 0, stream>>>( P, 1); spanEnd();
 			}
 		}
-		exclusiveScan( P.ev_count, nchunks, d_ev_off, scantmp, stream);
+		spanBegin( KScan); exclusiveScan( P.ev_count, nchunks, d_ev_off, scantmp, stream); spanEnd();
 		nev = readScalar( d_ev_off + nchunks, sizeof(uint64_t));
 		P.events = events.as<SpRawEvent>( nev);
 		SP_CUDA( cudaMemsetAsync( d_doc_ev_begin, 0, ((std::size_t)ndocs + 1) * sizeof(uint64_t), stream));
@@ -100,26 +142,26 @@ struct sp_lexer_ctx
 		if (nchunks)
 		{
 			unsigned int grid = (unsigned int)((nchunks + LexScanThreads - 1) / LexScanThreads);
-			k_lex_emit<<<grid, LexScanThreads, 0, stream>>>( P);
+			spanBegin( KEmit); k_lex_emit<<<grid, LexScanThreads, 0, stream>>>( P); spanEnd();
 		}
 		if (nev)
 		{
 			unsigned int grid = (unsigned int)((nev + LexEventThreads - 1) / LexEventThreads);
-			k_lex_finish<<<grid, LexEventThreads, 0, stream>>>( P, nev);
+			spanBegin( KFinish); k_lex_finish<<<grid, LexEventThreads, 0, stream>>>( P, nev); spanEnd();
 		}
 		P.ar = ar.as<SpMatchEvent>( nev * P.ar_mult + 2);
 		if (ndocs)
 		{
 			unsigned int grid = (ndocs + LexDocThreads - 1) / LexDocThreads;
-			k_lex_resolve<<<grid, LexDocThreads, 0, stream>>>( P);
+			spanBegin( KResolve); k_lex_resolve<<<grid, LexDocThreads, 0, stream>>>( P); spanEnd();
 		}
-		exclusiveScan( P.doc_nlex, ndocs, d_lex_off, scantmp, stream);
+		spanBegin( KScan); exclusiveScan( P.doc_nlex, ndocs, d_lex_off, scantmp, stream); spanEnd();
 		nlex = readScalar( d_lex_off + ndocs, sizeof(uint64_t));
 		P.lexems = lexems.as<sp_lexem>( nlex);
 		if (ndocs)
 		{
 			unsigned int grid = (ndocs + LexDocThreads - 1) / LexDocThreads;
-			k_lex_write<<<grid, LexDocThreads, 0, stream>>>( P);
+			spanBegin( KWrite); k_lex_write<<<grid, LexDocThreads, 0, stream>>>( P); spanEnd();
 		}
 		SP_CUDA( cudaGetLastError());
 		valid = true;
@@ -170,6 +212,22 @@ int64_t sp_lexer_ctx_counter( sp_lexer_ctx* ctx, const char* key)
 	if (k == "fixup_rounds") return (int64_t)ctx->rounds;
 	if (k == "text_bytes") return (int64_t)ctx->total;
 	if (k == "chunk_bytes") return (int64_t)ctx->chunk;
+	if (k == "profile:on") {ctx->profile = true; return 1;}
+	if (k == "profile:off") {ctx->profile = false; return 0;}
+	if (k == "profile:reset") {std::memset( ctx->kernel_ms, 0, sizeof(ctx->kernel_ms)); std::memset( ctx->kernel_calls, 0, sizeof(ctx->kernel_calls)); return 0;}
+	if (k.compare( 0, 8, "time_us:") == 0 || k.compare( 0, 6, "calls:") == 0)
+	{
+		static const char* names[] = {"k_lex_count","k_lex_verify","k_lex_emit","k_lex_finish","k_lex_resolve","k_lex_write","k_scan"};
+		if (cudaStreamSynchronize( ctx->stream) != cudaSuccess) return -1;
+		try {ctx->collectSpans();} catch (...) {return -1;}
+		bool calls = k[0] == 'c';
+		std::string name = k.substr( calls ? 6 : 8);
+		for (int i=0; i<sp_lexer_ctx::NofKernelIds; ++i)
+		{
+			if (name == names[i]) return calls ? (int64_t)ctx->kernel_calls[i] : (int64_t)(ctx->kernel_ms[i] * 1000.0);
+		}
+		return -1;
+	}
 	if (k == "kernel_launches") return (int64_t)(1 + 2*ctx->rounds + 1 + 3 + 1 + 1 + 1 + 3 + 1);
 	return -1;
 }
