@@ -4,6 +4,7 @@
 #include "strus_pattern_b200.h"
 #include "lexer_compile.hpp"
 #include "lexer_kernels.cuh"
+#include "lexer_islands.cuh"
 #include "device_util.cuh"
 #include <vector>
 #include <string>

@@ -9,14 +9,18 @@ struct sp_lexer_ctx
 	uint32_t chunk, warmup;
 	// device buffers (grow only)
 	DeviceBuffer text, doc_off, start_state, end_state, ev_count, known, redo, scalars, ev_off, events, doc_ev_begin,
-		     ar, doc_kept, doc_nlex, lex_off, lexems, status, scantmp;
+		     ar, doc_kept, doc_nlex, lex_off, lexems, status, scantmp,
+		     ev_doc, isl_flags, tile_nisl, tile_isl_off, isl_start, isl_kept, isl_off, elem, elem_doc, doc_has_content,
+		     doc_elem_begin, aggmax, aggmin, aggord;
+	bool sequential;	// SP_LEXER_SEQUENTIAL=1: one thread per document for resolution and ordinal positions (A/B check)
+	uint64_t nisl, nelem;
 	// last batch
 	uint32_t ndocs;
 	uint64_t total, nchunks, nev, nlex, fixups, rounds;
 	bool valid;
 	uint64_t* pinned;	// [4] host staging for scalar read backs
 	// optional per kernel timing with CUDA events on the context's stream (SP_LEXER_PROFILE=1 or counter "profile:on")
-	enum KernelId {KCount, KVerify, KEmit, KFinish, KResolve, KWrite, KScan, NofKernelIds};
+	enum KernelId {KCount, KVerify, KEmit, KFinish, KResolve, KWrite, KScan, KIslFlags, KIslResolve, KOrdpos, NofKernelIds};
 	struct Span {int kernel; cudaEvent_t a, b;};
 	bool profile;
 	std::vector<Span> spans;
@@ -57,6 +61,8 @@ struct sp_lexer_ctx
 	{
 		std::memset( kernel_ms, 0, sizeof(kernel_ms)); std::memset( kernel_calls, 0, sizeof(kernel_calls));
 		if (std::getenv( "SP_LEXER_PROFILE")) profile = true;
+		sequential = std::getenv( "SP_LEXER_SEQUENTIAL") != 0;
+		nisl = nelem = 0;
 		const char* e;
 		if ((e = std::getenv( "SP_LEXER_CHUNK")) != 0 && std::atoi( e) >= 16) chunk = (uint32_t)std::atoi( e);
 		if ((e = std::getenv( "SP_LEXER_WARMUP")) != 0 && std::atoi( e) >= 0) warmup = (uint32_t)std::atoi( e);
@@ -74,6 +80,74 @@ struct sp_lexer_ctx
 		SP_CUDA( cudaMemcpyAsync( pinned, devptr, bytes, cudaMemcpyDeviceToHost, stream));
 		SP_CUDA( cudaStreamSynchronize( stream));
 		return pinned[0];
+	}
+
+
+	// island-parallel resolution + scan based ordinal positions (lexer_islands.cuh)
+	void resolveIslands( const SpScanParams& P, uint64_t* d_lex_off)
+	{
+		nisl = nelem = nlex = 0;
+		SP_CUDA( cudaMemsetAsync( P.status, 0, (std::size_t)ndocs * sizeof(uint32_t) + 4, stream));
+		if (!nev)
+		{
+			SP_CUDA( cudaMemsetAsync( d_lex_off, 0, ((std::size_t)ndocs + 1) * sizeof(uint64_t), stream));
+			(void)lexems.as<sp_lexem>( 1);
+			return;
+		}
+		if (nev >= 0xFFFFFFFFull) throw std::runtime_error( "batch too large: more than 2^32 raw events (split the batch)");
+		IslandParams Q; std::memset( &Q, 0, sizeof(Q));
+		Q.T = P.T; Q.events = P.events; Q.ev_doc = P.ev_doc; Q.nev = nev; Q.ndocs = ndocs; Q.ar_mult = P.ar_mult;
+		uint64_t ntiles = (nev + TsTile - 1) / TsTile;
+		Q.flags = isl_flags.as<uint8_t>( nev);
+		Q.tile_nisl = tile_nisl.as<uint32_t>( ntiles);
+		uint64_t* d_tile_isl_off = tile_isl_off.as<uint64_t>( ntiles + 1);
+		Q.tile_isl_off = d_tile_isl_off;
+		uint64_t* d_aggmax = aggmax.as<uint64_t>( ntiles); uint64_t* d_aggmin = aggmin.as<uint64_t>( ntiles);
+		Q.doc_status = P.status;
+		Q.doc_has_content = doc_has_content.as<uint8_t>( ndocs);
+		Q.doc_elem_begin = doc_elem_begin.as<uint64_t>( (std::size_t)ndocs + 1);
+		Q.lex_off = d_lex_off;
+		SP_CUDA( cudaMemsetAsync( Q.doc_has_content, 0, (std::size_t)ndocs + 1, stream));
+		spanBegin( KIslFlags);
+		k_isl_reduce<<<(unsigned int)ntiles, TsThreads, 0, stream>>>( Q, d_aggmax, d_aggmin);
+		k_tile_carry<OpMax><<<1, 1024, 0, stream>>>( d_aggmax, ntiles, 0, (uint64_t*)0);
+		k_tile_carry<OpMin><<<1, 1024, 0, stream>>>( d_aggmin, ntiles, 1, (uint64_t*)0);
+		k_isl_flags<<<(unsigned int)ntiles, TsThreads, 0, stream>>>( Q, d_aggmax, d_aggmin);
+		exclusiveScan( Q.tile_nisl, ntiles, d_tile_isl_off, scantmp, stream);
+		spanEnd();
+		nisl = readScalar( d_tile_isl_off + ntiles, sizeof(uint64_t));
+		Q.nisl = nisl;
+		Q.isl_start = isl_start.as<uint32_t>( nisl + 1);
+		Q.isl_kept = isl_kept.as<uint32_t>( nisl);
+		uint64_t* d_isl_off = isl_off.as<uint64_t>( nisl + 1);
+		Q.isl_off = d_isl_off;
+		Q.scratch = ar.as<SpMatchEvent>( nev * P.ar_mult + 2);
+		unsigned int igrid = (unsigned int)((nisl + 127) / 128);
+		spanBegin( KIslFlags); k_isl_compact<<<(unsigned int)ntiles, TsThreads, 0, stream>>>( Q); spanEnd();
+		spanBegin( KIslResolve); k_isl_resolve<<<igrid, 128, 0, stream>>>( Q, 0); spanEnd();
+		spanBegin( KScan); exclusiveScan( Q.isl_kept, nisl, d_isl_off, scantmp, stream); spanEnd();
+		nelem = readScalar( d_isl_off + nisl, sizeof(uint64_t));
+		Q.nelem = nelem;
+		Q.elem = elem.as<SpMatchEvent>( nelem);
+		Q.elem_doc = elem_doc.as<uint32_t>( nelem);
+		Q.lexems = lexems.as<sp_lexem>( nelem);
+		spanBegin( KIslResolve); k_isl_resolve<<<igrid, 128, 0, stream>>>( Q, 1); spanEnd();
+		uint64_t* d_scalars = (uint64_t*)scalars.ptr();
+		SP_CUDA( cudaMemsetAsync( d_scalars + 1, 0, sizeof(uint64_t), stream));
+		if (nelem)
+		{
+			uint64_t* d_agg = aggord.as<uint64_t>( (nelem + TsTile - 1) / TsTile);
+			spanBegin( KOrdpos);
+			OrdScanA fa; fa.elem = Q.elem; fa.elem_doc = Q.elem_doc;
+			tileScan( fa, nelem, d_agg, stream);
+			OrdScanB fb; fb.elem = Q.elem; fb.elem_doc = Q.elem_doc; fb.doc_status = Q.doc_status; fb.doc_has_content = Q.doc_has_content;
+			tileScan( fb, nelem, d_agg, stream);
+			OrdScanC fc; fc.elem = Q.elem; fc.elem_doc = Q.elem_doc; fc.doc_elem_begin = Q.doc_elem_begin; fc.lexems = Q.lexems; fc.lex_off = Q.lex_off;
+			tileScan( fc, nelem, d_agg, stream, d_scalars + 1);
+			spanEnd();
+		}
+		k_ord_tail<<<(ndocs + 256) / 256, 256, 0, stream>>>( Q, d_scalars + 1);
+		nlex = readScalar( d_scalars + 1, sizeof(uint64_t));
 	}
 
 	void scan( const uint8_t* text_in, int text_on_device, const uint64_t* doc_offsets, uint32_t ndocs_)
@@ -144,25 +218,30 @@ struct sp_lexer_ctx
 			unsigned int grid = (unsigned int)((nchunks + LexScanThreads - 1) / LexScanThreads);
 			spanBegin( KEmit); k_lex_emit<<<grid, LexScanThreads, 0, stream>>>( P); spanEnd();
 		}
+		P.ev_doc = ev_doc.as<uint32_t>( nev);
 		if (nev)
 		{
 			unsigned int grid = (unsigned int)((nev + LexEventThreads - 1) / LexEventThreads);
 			spanBegin( KFinish); k_lex_finish<<<grid, LexEventThreads, 0, stream>>>( P, nev); spanEnd();
 		}
-		P.ar = ar.as<SpMatchEvent>( nev * P.ar_mult + 2);
-		if (ndocs)
+		if (sequential)
 		{
-			unsigned int grid = (ndocs + LexDocThreads - 1) / LexDocThreads;
-			spanBegin( KResolve); k_lex_resolve<<<grid, LexDocThreads, 0, stream>>>( P); spanEnd();
+			P.ar = ar.as<SpMatchEvent>( nev * P.ar_mult + 2);
+			if (ndocs)
+			{
+				unsigned int grid = (ndocs + LexDocThreads - 1) / LexDocThreads;
+				spanBegin( KResolve); k_lex_resolve<<<grid, LexDocThreads, 0, stream>>>( P); spanEnd();
+			}
+			spanBegin( KScan); exclusiveScan( P.doc_nlex, ndocs, d_lex_off, scantmp, stream); spanEnd();
+			nlex = readScalar( d_lex_off + ndocs, sizeof(uint64_t));
+			P.lexems = lexems.as<sp_lexem>( nlex);
+			if (ndocs)
+			{
+				unsigned int grid = (ndocs + LexDocThreads - 1) / LexDocThreads;
+				spanBegin( KWrite); k_lex_write<<<grid, LexDocThreads, 0, stream>>>( P); spanEnd();
+			}
 		}
-		spanBegin( KScan); exclusiveScan( P.doc_nlex, ndocs, d_lex_off, scantmp, stream); spanEnd();
-		nlex = readScalar( d_lex_off + ndocs, sizeof(uint64_t));
-		P.lexems = lexems.as<sp_lexem>( nlex);
-		if (ndocs)
-		{
-			unsigned int grid = (ndocs + LexDocThreads - 1) / LexDocThreads;
-			spanBegin( KWrite); k_lex_write<<<grid, LexDocThreads, 0, stream>>>( P); spanEnd();
-		}
+		else resolveIslands( P, d_lex_off);
 		SP_CUDA( cudaGetLastError());
 		valid = true;
 	}
@@ -210,6 +289,8 @@ int64_t sp_lexer_ctx_counter( sp_lexer_ctx* ctx, const char* key)
 	if (k == "chunks") return (int64_t)ctx->nchunks;
 	if (k == "fixup_chunks") return (int64_t)ctx->fixups;
 	if (k == "fixup_rounds") return (int64_t)ctx->rounds;
+	if (k == "islands") return (int64_t)ctx->nisl;
+	if (k == "elements") return (int64_t)ctx->nelem;
 	if (k == "text_bytes") return (int64_t)ctx->total;
 	if (k == "chunk_bytes") return (int64_t)ctx->chunk;
 	if (k == "profile:on") {ctx->profile = true; return 1;}
@@ -217,7 +298,7 @@ int64_t sp_lexer_ctx_counter( sp_lexer_ctx* ctx, const char* key)
 	if (k == "profile:reset") {std::memset( ctx->kernel_ms, 0, sizeof(ctx->kernel_ms)); std::memset( ctx->kernel_calls, 0, sizeof(ctx->kernel_calls)); return 0;}
 	if (k.compare( 0, 8, "time_us:") == 0 || k.compare( 0, 6, "calls:") == 0)
 	{
-		static const char* names[] = {"k_lex_count","k_lex_verify","k_lex_emit","k_lex_finish","k_lex_resolve","k_lex_write","k_scan"};
+		static const char* names[] = {"k_lex_count","k_lex_verify","k_lex_emit","k_lex_finish","k_lex_resolve","k_lex_write","k_scan","k_isl_flags","k_isl_resolve","k_ordpos"};
 		if (cudaStreamSynchronize( ctx->stream) != cudaSuccess) return -1;
 		try {ctx->collectSpans();} catch (...) {return -1;}
 		bool calls = k[0] == 'c';
@@ -228,7 +309,7 @@ int64_t sp_lexer_ctx_counter( sp_lexer_ctx* ctx, const char* key)
 		}
 		return -1;
 	}
-	if (k == "kernel_launches") return (int64_t)(1 + 2*ctx->rounds + 1 + 3 + 1 + 1 + 1 + 3 + 1);
+	if (k == "kernel_launches") return (int64_t)(ctx->sequential ? (1 + 2*ctx->rounds + 1 + 3 + 1 + 1 + 1 + 3 + 1) : (1 + 2*ctx->rounds + 1 + 3 + 1 + 1 + 4 + 3 + 1 + 1 + 3 + 1 + 9 + 1));
 	return -1;
 }
 

@@ -397,6 +397,7 @@ typedef struct SpScanParams
 	uint32_t* nbad;			/* number of chunks flagged by the last verification */
 	const uint64_t* ev_off;		/* [nchunks+1] exclusive prefix sum of ev_count */
 	SpRawEvent* events;
+	uint32_t* ev_doc;		/* [nev] document of every event (written by the finish step) */
 	uint64_t* doc_ev_begin;		/* [ndocs+1] first event of every document */
 	SpMatchEvent* ar;		/* match event arrays, document d at doc_ev_begin[d]*ar_mult */
 	uint32_t ar_mult;		/* 2 if symbols are defined (an event may insert two elements) else 1 */
@@ -464,6 +465,7 @@ SP_HD void spk_emit_chunk( const SpScanParams& P, uint64_t j)
 SP_HD void spk_finish_event( const SpScanParams& P, uint64_t i)
 {
 	SpRawEvent ev = P.events[ i];
+	if (P.ev_doc) P.ev_doc[ i] = ev.aux;
 	uint64_t dstart = SP_LDG( P.doc_off + ev.aux);
 	uint32_t doclen = (uint32_t)(SP_LDG( P.doc_off + ev.aux + 1) - dstart);
 	sp_finish_event( P.T, ev, P.text + dstart, doclen);
@@ -493,6 +495,70 @@ SP_HD void spk_write_doc( const SpScanParams& P, uint32_t d)
 {
 	const SpMatchEvent* ar = P.ar + P.doc_ev_begin[ d] * P.ar_mult;
 	sp_assign_ordpos( ar, P.doc_kept[ d], P.lexems + P.lex_off[ d]);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Parallel formulation of the resolution (DESIGN.md "islands"): the supersede logic only ever touches array
+// elements that overlap the new event, so the event sequence of a document can be cut wherever every earlier
+// event ends at or before the start of every later one; each such "island" is resolved independently and the
+// results are concatenated. Ordinal positions are then three scans over the kept elements.
+
+// Span of an event as the cut criterion sees it: [lo, r). Events of length 0 (empty selected sub expression)
+// are widened by one byte on both sides so that they never sit on a cut.
+SP_HD uint64_t sp_event_lo_key( const SpRawEvent& ev, uint32_t doc)
+{
+	if (ev.pat >= SP_PAT_SIZEERROR) return ~0ull;
+	uint32_t lo = (ev.to == ev.from && ev.from) ? ev.from - 1 : ev.from;
+	return ((uint64_t)doc << 32) | lo;
+}
+SP_HD uint64_t sp_event_r_key( const SpRawEvent& ev, uint32_t doc)
+{
+	if (ev.pat >= SP_PAT_SIZEERROR) return 0;
+	uint32_t r = ev.to > ev.from ? ev.to : ev.from + 1;
+	return ((uint64_t)doc << 32) | r;
+}
+
+#define SP_ISLAND_LOCAL 16	/* islands whose elements fit are resolved in thread local memory */
+#define SP_META_BIND( meta) (((meta) >> 8) & 0xFF)
+#define SP_META_INC 0x10000u	/* dense element: ordinal position advances here */
+#define SP_DENSE_BIND( sizeword) (((sizeword) >> 16) & 0xFF)
+#define SP_SIZE_EMIT 0x80000000u	/* dense element, origsize word: element is part of the output */
+
+// Resolves the events [eb,ee) of one island into `ar`; returns the number of kept elements. A size error
+// marks the document.
+SP_HD uint32_t sp_resolve_island( const SpLexerTables& T, const SpRawEvent* events, uint64_t eb, uint64_t ee, SpMatchEvent* ar, uint32_t* doc_status)
+{
+	uint32_t n = 0;
+	for (uint64_t i=eb; i<ee; ++i)
+	{
+		SpRawEvent ev = events[ i];
+		if (ev.pat == SP_PAT_DROPPED) continue;
+		if (ev.pat == SP_PAT_SIZEERROR) {*doc_status = (uint32_t)-SP_ERR_RUNTIME; continue;}
+		sp_supersede( T, ev, ar, n);
+	}
+	return n;
+}
+
+// scan 1 (prefix max): key of an element that can advance the ordinal position, else 0.
+// prev_* describe the element in front (same document) for the BindUnique rule (src/patternLexer.cpp:926-929).
+SP_HD uint64_t sp_ord_key( uint32_t bind, uint32_t origpos, uint32_t doc, bool hasPrev, uint32_t prevBind)
+{
+	if (bind == SP_BIND_CONTENT || (bind == SP_BIND_UNIQUE && !(hasPrev && prevBind == SP_BIND_UNIQUE)))
+	{
+		return ((uint64_t)doc << 32) | ((uint64_t)origpos + 1);
+	}
+	return 0;
+}
+
+// after scan 2 (segmented count of advances, inclusive): final ordinal position and whether the element is emitted
+SP_HD bool sp_ord_decide( uint32_t bind, bool counts, uint32_t cnt, uint32_t& ordpos)
+{
+	switch (bind)
+	{
+		case SP_BIND_CONTENT: case SP_BIND_UNIQUE: ordpos = cnt; return counts;
+		case SP_BIND_SUCCESSOR: ordpos = cnt + 1; return true;
+		default: ordpos = cnt; return cnt > 0;	// BindPredecessor: dropped in front of the first content element
+	}
 }
 
 #endif

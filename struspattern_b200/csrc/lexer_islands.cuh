@@ -1,0 +1,251 @@
+// Island-parallel resolution and scan-based ordinal positions (second half of the lexer pipeline).
+//
+//   k_isl_reduce / k_isl_carry / k_isl_flags   prefix max of event ends and suffix min of event starts (keys carry the
+//                   document in the upper half, so no segmentation is needed); event k starts an island iff
+//                   min(start of k..) >= max(end of ..k-1). Also counts the island starts per tile.
+//   k_isl_compact   island start list from the flags.
+//   k_isl_resolve   one thread per island: reference supersede logic (src/patternLexer.cpp:754-822) in thread local
+//                   memory (global scratch for oversized islands); pass 0 counts, pass 1 writes the kept elements densely.
+//   ordinal positions (src/patternLexer.cpp:893-945) over the dense elements:
+//       scan A (max)     which elements advance the position        -> SP_META_INC
+//       scan B (segsum)  position per element, emit decision        -> ordpos / SP_SIZE_EMIT
+//       scan C (sum)     output index, lexem records and per document offsets
+#ifndef SP_LEXER_ISLANDS_CUH_INCLUDED
+#define SP_LEXER_ISLANDS_CUH_INCLUDED
+#include "lexer_device.cuh"
+#include "tile_scan.cuh"
+
+namespace sp {
+
+struct IslandParams
+{
+	SpLexerTables T;
+	const SpRawEvent* events;
+	const uint32_t* ev_doc;		// [nev] document of every event
+	uint64_t nev;
+	uint8_t* flags;			// [nev] 1 = first event of an island
+	uint32_t* tile_nisl;		// [ntiles] island starts per tile
+	const uint64_t* tile_isl_off;	// [ntiles+1]
+	uint32_t* isl_start;		// [nisl+1] event index
+	uint64_t nisl;
+	uint32_t* isl_kept;		// [nisl]
+	const uint64_t* isl_off;	// [nisl+1] dense element offsets
+	SpMatchEvent* scratch;		// [nev*ar_mult] for islands that do not fit thread local memory
+	uint32_t ar_mult;
+	SpMatchEvent* elem;		// dense kept elements
+	uint32_t* elem_doc;
+	uint64_t nelem;
+	uint32_t* doc_status;		// [ndocs]
+	uint8_t* doc_has_content;	// [ndocs]
+	uint64_t* doc_elem_begin;	// [ndocs+1] first dense element of every document
+	uint32_t ndocs;
+	sp_lexem* lexems;
+	uint64_t* lex_off;		// [ndocs+1]
+};
+
+static __global__ void __launch_bounds__(TsThreads) k_isl_reduce( IslandParams P, uint64_t* aggmax, uint64_t* aggmin)
+{
+	__shared__ uint64_t smem[ 33];
+	uint64_t first = (uint64_t)blockIdx.x * TsTile + (uint64_t)threadIdx.x * TsItems;
+	uint64_t mx = 0, mn = ~0ull;
+	#pragma unroll
+	for (int k=0; k<TsItems; ++k)
+	{
+		if (first + k >= P.nev) break;
+		SpRawEvent ev = P.events[ first + k];
+		uint32_t doc = P.ev_doc[ first + k];
+		mx = OpMax::apply( mx, sp_event_r_key( ev, doc));
+		mn = OpMin::apply( mn, sp_event_lo_key( ev, doc));
+	}
+	uint64_t excl, total;
+	blockScan<OpMax>( mx, smem, excl, total);
+	if (threadIdx.x == 0) aggmax[ blockIdx.x] = total;
+	blockScan<OpMin>( mn, smem, excl, total);
+	if (threadIdx.x == 0) aggmin[ blockIdx.x] = total;
+}
+
+static __global__ void __launch_bounds__(TsThreads) k_isl_flags( IslandParams P, const uint64_t* carrymax, const uint64_t* carrymin)
+{
+	__shared__ uint64_t smem[ 33];
+	__shared__ uint64_t mirror[ TsThreads];
+	__shared__ uint32_t warpcnt[ TsThreads/32];
+	uint64_t first = (uint64_t)blockIdx.x * TsTile + (uint64_t)threadIdx.x * TsItems;
+	uint64_t rk[ TsItems], lk[ TsItems];
+	uint64_t mx = 0, mn = ~0ull;
+	#pragma unroll
+	for (int k=0; k<TsItems; ++k)
+	{
+		rk[k] = 0; lk[k] = ~0ull;
+		if (first + k < P.nev)
+		{
+			SpRawEvent ev = P.events[ first + k];
+			uint32_t doc = P.ev_doc[ first + k];
+			rk[k] = sp_event_r_key( ev, doc); lk[k] = sp_event_lo_key( ev, doc);
+		}
+		mx = OpMax::apply( mx, rk[k]); mn = OpMin::apply( mn, lk[k]);
+	}
+	uint64_t exmax, exmin, total;
+	blockScan<OpMax>( mx, smem, exmax, total);
+	// suffix min over the threads: prefix scan in mirrored thread order
+	mirror[ TsThreads-1-threadIdx.x] = mn;
+	__syncthreads();
+	uint64_t mv = mirror[ threadIdx.x];
+	__syncthreads();
+	blockScan<OpMin>( mv, smem, exmin, total);
+	mirror[ TsThreads-1-threadIdx.x] = exmin;
+	__syncthreads();
+	exmin = mirror[ threadIdx.x];
+	uint64_t premax[ TsItems];
+	uint64_t run = OpMax::apply( carrymax[ blockIdx.x], exmax);
+	#pragma unroll
+	for (int k=0; k<TsItems; ++k) {premax[k] = run; run = OpMax::apply( run, rk[k]);}
+	uint64_t suf = OpMin::apply( carrymin[ blockIdx.x], exmin);
+	uint32_t cnt = 0;
+	#pragma unroll
+	for (int k=TsItems-1; k>=0; --k)
+	{
+		suf = OpMin::apply( suf, lk[k]);
+		if (first + k < P.nev)
+		{
+			uint8_t f = (suf >= premax[k]) ? 1 : 0;
+			P.flags[ first + k] = f;
+			cnt += f;
+		}
+	}
+	#pragma unroll
+	for (int ofs=16; ofs>0; ofs>>=1) cnt += __shfl_down_sync( 0xFFFFFFFFu, cnt, ofs);
+	if ((threadIdx.x & 31) == 0) warpcnt[ threadIdx.x >> 5] = cnt;
+	__syncthreads();
+	if (threadIdx.x == 0)
+	{
+		uint32_t t = 0;
+		for (int w=0; w<TsThreads/32; ++w) t += warpcnt[ w];
+		P.tile_nisl[ blockIdx.x] = t;
+	}
+}
+
+static __global__ void __launch_bounds__(TsThreads) k_isl_compact( IslandParams P)
+{
+	__shared__ uint64_t smem[ 33];
+	uint64_t first = (uint64_t)blockIdx.x * TsTile + (uint64_t)threadIdx.x * TsItems;
+	uint32_t f[ TsItems]; uint64_t cnt = 0;
+	#pragma unroll
+	for (int k=0; k<TsItems; ++k) {f[k] = (first + k < P.nev) ? P.flags[ first + k] : 0; cnt += f[k];}
+	uint64_t excl, total;
+	blockScan<OpSum>( cnt, smem, excl, total);
+	uint64_t pos = P.tile_isl_off[ blockIdx.x] + excl;
+	#pragma unroll
+	for (int k=0; k<TsItems; ++k) if (f[k]) P.isl_start[ pos++] = (uint32_t)(first + k);
+	if (blockIdx.x == 0 && threadIdx.x == 0) P.isl_start[ P.nisl] = (uint32_t)P.nev;
+}
+
+static __global__ void __launch_bounds__(128) k_isl_resolve( IslandParams P, int pass)
+{
+	uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= P.nisl) return;
+	uint64_t eb = P.isl_start[ i], ee = P.isl_start[ i+1];
+	uint32_t doc = P.ev_doc[ eb];
+	SpMatchEvent local[ SP_ISLAND_LOCAL];
+	SpMatchEvent* ar = ((ee - eb) * P.ar_mult <= SP_ISLAND_LOCAL) ? local : P.scratch + eb * P.ar_mult;
+	uint32_t n = sp_resolve_island( P.T, P.events, eb, ee, ar, P.doc_status + doc);
+	if (pass == 0) {P.isl_kept[ i] = n; return;}
+	uint64_t out = P.isl_off[ i];
+	bool content = false;
+	for (uint32_t k=0; k<n; ++k)
+	{
+		SpMatchEvent e = ar[ k];
+		uint32_t bind = SP_META_BIND( e.meta);
+		content |= (bind == SP_BIND_CONTENT || bind == SP_BIND_UNIQUE);
+		e.origsize |= bind << 16;	// dense element: origsize | bind << 16 (| SP_SIZE_EMIT later), meta = scan state
+		e.meta = 0;
+		P.elem[ out + k] = e;
+		P.elem_doc[ out + k] = doc;
+	}
+	if (content) P.doc_has_content[ doc] = 1;
+	// first island of a document (and the empty documents in front of it) -> first dense element
+	if (eb == 0 || P.ev_doc[ eb-1] != doc)
+	{
+		uint32_t dprev = eb ? P.ev_doc[ eb-1] + 1 : 0;
+		for (uint32_t d=dprev; d<=doc; ++d) P.doc_elem_begin[ d] = out;
+	}
+	if (i + 1 == P.nisl) for (uint32_t d=doc+1; d<=P.ndocs; ++d) P.doc_elem_begin[ d] = P.nelem;
+}
+
+// ---- scan A: prefix max of the keys of elements that may advance the ordinal position
+struct OrdScanA
+{
+	typedef OpMax Op;
+	SpMatchEvent* elem; const uint32_t* elem_doc;
+	__device__ uint64_t load( uint64_t j) const
+	{
+		SpMatchEvent e = elem[ j];
+		uint32_t doc = elem_doc[ j];
+		bool hasPrev = j > 0 && elem_doc[ j-1] == doc;
+		uint32_t prevBind = hasPrev ? SP_DENSE_BIND( elem[ j-1].origsize) : 0;
+		return sp_ord_key( SP_DENSE_BIND( e.origsize), e.origpos, doc, hasPrev, prevBind);
+	}
+	__device__ void store( uint64_t j, uint64_t excl, uint64_t incl) const
+	{
+		// advance iff the element counts and starts behind everything counted before (in its document)
+		if (incl > excl) elem[ j].meta |= SP_META_INC;
+	}
+};
+// NOTE: the bind of the element in front is read from its origsize word, which scan A never writes; scan B
+// only sets bit 31 of it (SP_SIZE_EMIT) while neighbours read bits 16..23, a benign race.
+
+// ---- scan B: count of advances inside the document -> ordinal position, emit decision
+struct OrdScanB
+{
+	typedef OpSegSum Op;
+	SpMatchEvent* elem; const uint32_t* elem_doc; const uint32_t* doc_status; const uint8_t* doc_has_content;
+	__device__ uint64_t load( uint64_t j) const
+	{
+		return ((uint64_t)elem_doc[ j] << 32) | ((elem[ j].meta & SP_META_INC) ? 1 : 0);
+	}
+	__device__ void store( uint64_t j, uint64_t, uint64_t incl) const
+	{
+		SpMatchEvent e = elem[ j];
+		uint32_t doc = elem_doc[ j];
+		uint32_t bind = SP_DENSE_BIND( e.origsize);
+		bool hasPrev = j > 0 && elem_doc[ j-1] == doc;
+		uint32_t prevBind = hasPrev ? SP_DENSE_BIND( elem[ j-1].origsize) : 0;
+		bool counts = sp_ord_key( bind, e.origpos, doc, hasPrev, prevBind) != 0;
+		uint32_t ordpos;
+		bool emit = sp_ord_decide( bind, counts, (uint32_t)incl, ordpos) && doc_has_content[ doc] && !doc_status[ doc];
+		elem[ j].meta = ordpos;
+		if (emit) elem[ j].origsize = e.origsize | SP_SIZE_EMIT;
+	}
+};
+
+// ---- scan C: output index
+struct OrdScanC
+{
+	typedef OpSum Op;
+	const SpMatchEvent* elem; const uint32_t* elem_doc; const uint64_t* doc_elem_begin; sp_lexem* lexems; uint64_t* lex_off;
+	__device__ uint64_t load( uint64_t j) const {return (elem[ j].origsize & SP_SIZE_EMIT) ? 1 : 0;}
+	__device__ void store( uint64_t j, uint64_t excl, uint64_t) const
+	{
+		SpMatchEvent e = elem[ j];
+		if (e.origsize & SP_SIZE_EMIT)
+		{
+			sp_lexem lx; lx.id = e.id; lx.ordpos = e.meta; lx.origpos = e.origpos; lx.origsize = e.origsize & 0xFFFF;
+			lexems[ excl] = lx;
+		}
+		// first dense element of its document (and of the element-less documents in front): output offset
+		for (uint32_t d=elem_doc[ j];; --d)
+		{
+			if (doc_elem_begin[ d] != j) break;
+			lex_off[ d] = excl;
+			if (d == 0) break;
+		}
+	}
+};
+
+static __global__ void k_ord_tail( IslandParams P, const uint64_t* total)
+{
+	uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
+	if (d <= P.ndocs && P.doc_elem_begin[ d] >= P.nelem) P.lex_off[ d] = *total;
+}
+
+} // namespace sp
+#endif
