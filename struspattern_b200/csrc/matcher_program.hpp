@@ -1,0 +1,444 @@
+// Host side of the level-2 matcher: the expression stack of PatternMatcherInstance and the rule graph it
+// builds, the stop-word key-event optimisation, and the flattening of the graph into the device tables of
+// matcher_tables.h. Pure host C++ (no CUDA), shared by the C ABI (matcher_capi.cu) and the host simulation tests.
+//
+// Reference behaviour restated here (file:line under the strusPattern tree):
+//   eventHandle                                     src/patternMatcher.cpp:100-105
+//   pushTerm / pushExpression / pushPattern         src/patternMatcher.cpp:366-520
+//   attachVariable / definePattern / defineOption   src/patternMatcher.cpp:522-584, 614-644
+//   createProgram / createTrigger / doneProgram     src/ruleMatcherAutomaton.cpp:268-339
+//   calcEventWeight / getAltEventId / optimize      src/ruleMatcherAutomaton.cpp:341-442, 478-586
+// The reference keeps trigger definitions and program lists in LIFO linked lists; here they are plain vectors
+// in definition order that are read backwards where the reference iterates its lists.
+#ifndef SP_MATCHER_PROGRAM_HPP_INCLUDED
+#define SP_MATCHER_PROGRAM_HPP_INCLUDED
+#include "matcher_tables.h"
+#include "strus_pattern_b200.h"
+#include <vector>
+#include <string>
+#include <deque>
+#include <map>
+#include <set>
+#include <unordered_map>
+#include <stdexcept>
+#include <limits>
+#include <algorithm>
+#include <cstring>
+#include <strings.h>
+
+namespace sp {
+
+enum EventType {TermEvent=0, ExpressionEvent=1, ReferenceEvent=2};
+
+inline uint32_t eventHandle( EventType type, uint32_t idx)
+{
+	if (idx >= (1u<<29)) throw std::runtime_error( "event handle out of range");
+	return idx | ((uint32_t)type << 29);
+}
+
+// string <-> dense 1-based handle in insertion order (strusBase SymbolTable as used by src/patternMatcher.cpp:45-65)
+class NameTable
+{
+public:
+	uint32_t getOrCreate( const std::string& name)
+	{
+		std::unordered_map<std::string,uint32_t>::const_iterator it = m_index.find( name);
+		if (it != m_index.end()) return it->second;
+		m_names.push_back( name);
+		return m_index[ name] = (uint32_t)m_names.size();
+	}
+	const char* key( uint32_t handle) const {return (handle == 0 || handle > m_names.size()) ? 0 : m_names[ handle-1].c_str();}
+	std::size_t size() const {return m_names.size();}
+private:
+	std::unordered_map<std::string,uint32_t> m_index;
+	std::deque<std::string> m_names;
+};
+
+struct MatcherTablesHost
+{
+	std::vector<SpProgram> programs;
+	std::vector<SpTriggerDef> trigger_defs;
+	std::vector<SpProgramTrigger> program_triggers;
+	std::vector<SpEventSlot> event_slots;
+	std::vector<uint32_t> stopwords;	// event id per stop word index (0-based)
+	SpMatcherTables view;			// pointers are filled by the owner (host or device addresses)
+};
+
+class MatcherProgram
+{
+public:
+	MatcherProgram()
+		:m_expressionEventCnt(0),m_totalNofPrograms(0),m_stopwordOccurrenceFactor(0.01f),m_weightFactor(10.0f),m_maxRange(5)
+		,m_maxResultSize(100),m_exclusive(false),m_flattened(false){}
+
+	// ---- PatternMatcherInstanceInterface
+	void defineOption( const std::string& name, double value)
+	{
+		const char* nam = name.c_str();
+		if (0==strcasecmp( nam, "stopwordOccurrenceFactor")) m_stopwordOccurrenceFactor = (float)value;
+		else if (0==strcasecmp( nam, "weightFactor")) m_weightFactor = (float)value;
+		else if (0==strcasecmp( nam, "maxRange")) m_maxRange = (uint32_t)(value + std::numeric_limits<double>::epsilon());
+		else if (0==strcasecmp( nam, "maxResultSize")) m_maxResultSize = (uint32_t)(value + std::numeric_limits<double>::epsilon());
+		else if (0==strcasecmp( nam, "exclusive")) m_exclusive = true;
+		else throw std::runtime_error( "unknown token pattern match option: '" + name + "'");
+		m_flattened = false;
+	}
+	void defineTermFrequency( uint32_t termid, double df)
+	{
+		if (df <= std::numeric_limits<double>::epsilon()) throw std::runtime_error( "illegal value for df (must be positive)");
+		m_frequency[ eventHandle( TermEvent, termid)] = df;
+	}
+	void pushTerm( uint32_t termid)
+	{
+		m_stack.push_back( Node( eventHandle( TermEvent, termid)));
+	}
+	void pushPattern( const std::string& name)
+	{
+		m_stack.push_back( Node( eventHandle( ReferenceEvent, m_patterns.getOrCreate( name))));
+	}
+	void attachVariable( const std::string& name)
+	{
+		if (m_stack.empty()) throw std::runtime_error( "illegal operation attach variable when no node on the stack");
+		if (m_stack.back().variable) throw std::runtime_error( "more than one variable assignment to a node");
+		m_stack.back().variable = m_variables.getOrCreate( name);
+	}
+	void pushExpression( int joinop, std::size_t argc, uint32_t range, uint32_t cardinality)
+	{
+		if (argc > m_stack.size() || argc > (std::size_t)std::numeric_limits<uint32_t>::max())
+		{
+			throw std::runtime_error( "expression references more arguments than nodes on the stack");
+		}
+		Rule rule;
+		rule.range = range;
+		rule.initsigval = 0;
+		rule.initcount = cardinality ? cardinality : (uint32_t)argc;
+		rule.event = eventHandle( ExpressionEvent, ++m_expressionEventCnt);
+		rule.resultHandle = rule.formatHandle = 0;
+		uint8_t slotSig = SP_SIG_ANY;
+		switch (joinop)
+		{
+			case SP_OP_SEQUENCE: slotSig = SP_SIG_SEQUENCE; rule.initsigval = (uint32_t)argc; break;
+			case SP_OP_SEQUENCE_IMM: slotSig = SP_SIG_SEQUENCE_IMM; rule.initsigval = (uint32_t)argc; break;
+			case SP_OP_SEQUENCE_STRUCT: slotSig = SP_SIG_SEQUENCE; rule.initsigval = (uint32_t)argc - 1; --rule.initcount; break;
+			case SP_OP_WITHIN:
+			case SP_OP_WITHIN_STRUCT:
+				slotSig = SP_SIG_WITHIN;
+				if (argc > 32) throw std::runtime_error( joinop == SP_OP_WITHIN ? "operator 'within': number of arguments out of range (32)" : "operator 'within_struct': number of arguments out of range (32)");
+				rule.initsigval = 0xFFFFFFFFu;
+				if (joinop == SP_OP_WITHIN_STRUCT) --rule.initcount;
+				break;
+			case SP_OP_ANY: slotSig = SP_SIG_ANY; rule.initcount = cardinality ? cardinality : 1u; break;
+			case SP_OP_AND: slotSig = SP_SIG_AND; break;
+			default: throw std::runtime_error( "unknown join operation");
+		}
+		for (std::size_t ai=0; ai<argc; ++ai)
+		{
+			const Node& arg = m_stack[ m_stack.size() - argc + ai];
+			SpTriggerDef def; std::memset( &def, 0, sizeof(def));
+			def.event = arg.event; def.variable = arg.variable; def.sigtype = slotSig;
+			switch (joinop)
+			{
+				case SP_OP_SEQUENCE_STRUCT:
+					if (ai == 0) def.sigtype = SP_SIG_DEL;		// structure delimiter
+					else {def.sigval = (uint32_t)(argc - ai); def.is_key = (ai == 1);}
+					break;
+				case SP_OP_WITHIN_STRUCT:
+					if (ai == 0) def.sigtype = SP_SIG_DEL;
+					else {def.sigval = 1u << (argc - ai); def.is_key = 1;}
+					break;
+				case SP_OP_SEQUENCE:
+					def.sigval = (uint32_t)(argc - ai); def.is_key = (ai == 0);
+					break;
+				case SP_OP_SEQUENCE_IMM:
+					if (ai == 0) def.sigtype = SP_SIG_SEQUENCE;	// the first element has no predecessor
+					def.sigval = (uint32_t)(argc - ai); def.is_key = (ai == 0);
+					break;
+				case SP_OP_WITHIN:
+					def.sigval = 1u << (argc - ai - 1); def.is_key = 1;
+					break;
+				default:
+					def.is_key = 1;
+					break;
+			}
+			rule.defs.push_back( def);
+			m_eventOccurrence[ def.event] += 1;
+		}
+		uint32_t program = addRule( rule);
+		m_stack.resize( m_stack.size() - argc);
+		m_stack.push_back( Node( rule.event, program));
+		m_flattened = false;
+	}
+	// returns the format handle assigned (0 = no format string)
+	uint32_t definePattern( const std::string& name, const std::string& formatstring, bool visible)
+	{
+		if (m_stack.empty()) throw std::runtime_error( "illegal operation close pattern when no node on the stack");
+		Node& top = m_stack.back();
+		uint32_t resultHandle = m_patterns.getOrCreate( name);
+		uint32_t resultEvent = eventHandle( ReferenceEvent, resultHandle);
+		uint32_t formatHandle = 0;
+		if (!formatstring.empty())
+		{
+			m_formats.push_back( formatstring);
+			formatHandle = (uint32_t)m_formats.size();
+		}
+		uint32_t program = top.program;
+		if (!program)
+		{
+			// a bare term or reference is enveloped into a program of its own
+			Rule rule;
+			rule.range = 0; rule.initsigval = 0; rule.initcount = 1;
+			rule.event = resultEvent; rule.resultHandle = resultHandle; rule.formatHandle = formatHandle;
+			SpTriggerDef def; std::memset( &def, 0, sizeof(def));
+			def.event = top.event; def.variable = top.variable; def.sigtype = SP_SIG_ANY; def.is_key = 1;
+			rule.defs.push_back( def);
+			m_eventOccurrence[ def.event] += 1;
+			program = addRule( rule);
+		}
+		else if (top.variable)
+		{
+			throw std::runtime_error( "variable assignments only allowed to subexpressions of pattern");
+		}
+		Rule& rule = m_rules[ program-1];
+		rule.event = resultEvent;
+		rule.resultHandle = visible ? resultHandle : 0;
+		rule.formatHandle = formatHandle;
+		m_flattened = false;
+		return formatHandle;
+	}
+	// ProgramTable::optimize
+	void compile()
+	{
+		eliminateUnusedEvents();
+		std::vector<uint32_t> eventsToMove;
+		for (EventListMap::const_iterator ei = m_eventPrograms.begin(); ei != m_eventPrograms.end(); ++ei)
+		{
+			std::map<uint32_t,uint32_t>::const_iterator ki = m_keyOccurrence.find( ei->first);
+			if (ki != m_keyOccurrence.end() && ki->second >= (float)m_totalNofPrograms * m_stopwordOccurrenceFactor)
+			{
+				eventsToMove.push_back( ei->first);
+			}
+		}
+		for (uint32_t eventid: eventsToMove)
+		{
+			EventListMap::iterator ei = m_eventPrograms.find( eventid);
+			if (ei == m_eventPrograms.end()) continue;
+			const uint32_t oldlist = ei->second;
+			std::vector<SpProgramTrigger> kept;
+			double weight = eventWeight( eventid);
+			// the list is visited last-pushed first; the kept entries are pushed onto a fresh list in that order
+			for (std::size_t li = m_lists[ oldlist].size(); li > 0; --li)
+			{
+				SpProgramTrigger pt = m_lists[ oldlist][ li-1];
+				const Rule& rule = m_rules[ pt.program-1];
+				uint32_t alt = alternativeKeyEvent( eventid, rule);
+				bool moved = false;
+				if (alt)
+				{
+					double altWeight = eventWeight( alt) * m_weightFactor;
+					if (!pt.past_event && m_maxRange >= rule.range && weight > altWeight)
+					{
+						addEventProgram( alt, pt.program, eventid);
+						for (const SpTriggerDef& def: rule.defs) if (def.sigtype == SP_SIG_DEL) m_stopwords.insert( def.event);
+						moved = true;
+					}
+				}
+				if (!moved) kept.push_back( pt);
+			}
+			ei = m_eventPrograms.find( eventid);	// addEventProgram may have rehashed the map
+			if (!kept.empty()) m_lists[ ei->second].swap( kept);
+			else {m_lists[ ei->second].clear(); m_eventPrograms.erase( ei);}
+		}
+		m_flattened = false;
+	}
+
+	const char* patternName( uint32_t handle) const {return m_patterns.key( handle);}
+	const char* variableName( uint32_t handle) const {return m_variables.key( handle);}
+	const char* formatString( uint32_t handle) const {return (handle == 0 || handle > m_formats.size()) ? 0 : m_formats[ handle-1].c_str();}
+	bool exclusive() const {return m_exclusive;}
+	uint32_t maxResultSize() const {return m_maxResultSize;}
+	std::size_t nofPrograms() const {return m_rules.size();}
+	std::size_t nofStopwords() const {return m_stopwords.size();}
+
+	// Flat tables (pointers inside `view` address the vectors of the returned object).
+	const MatcherTablesHost& tables()
+	{
+		if (m_flattened) return m_tables;
+		MatcherTablesHost& T = m_tables;
+		T = MatcherTablesHost();
+		uint32_t maxdefs = 0;
+		for (const Rule& rule: m_rules)
+		{
+			SpProgram p;
+			p.initsigval = rule.initsigval; p.initcount = rule.initcount; p.event = rule.event;
+			p.resultHandle = rule.resultHandle; p.formatHandle = rule.formatHandle; p.range = rule.range;
+			p.trig_begin = (uint32_t)T.trigger_defs.size(); p.trig_count = (uint32_t)rule.defs.size();
+			for (std::size_t di = rule.defs.size(); di > 0; --di) T.trigger_defs.push_back( rule.defs[ di-1]);
+			maxdefs = std::max( maxdefs, p.trig_count);
+			T.programs.push_back( p);
+		}
+		std::map<uint32_t,uint32_t> stopidx;
+		for (uint32_t ev: m_stopwords) {T.stopwords.push_back( ev); stopidx[ ev] = (uint32_t)T.stopwords.size();}
+		std::set<uint32_t> keys( m_stopwords.begin(), m_stopwords.end());
+		for (EventListMap::const_iterator ei = m_eventPrograms.begin(); ei != m_eventPrograms.end(); ++ei) keys.insert( ei->first);
+		uint32_t nslots = 8;
+		while (nslots < 2 * keys.size() + 2) nslots <<= 1;
+		SpEventSlot empty; std::memset( &empty, 0, sizeof(empty));
+		T.event_slots.assign( nslots, empty);
+		for (uint32_t ev: keys)
+		{
+			SpEventSlot slot; slot.key = ev + 1; slot.prog_begin = (uint32_t)T.program_triggers.size(); slot.prog_count = 0; slot.stopword = 0;
+			EventListMap::const_iterator ei = m_eventPrograms.find( ev);
+			if (ei != m_eventPrograms.end())
+			{
+				const std::vector<SpProgramTrigger>& list = m_lists[ ei->second];
+				for (std::size_t li = list.size(); li > 0; --li)
+				{
+					SpProgramTrigger pt = list[ li-1];
+					pt.program -= 1;
+					T.program_triggers.push_back( pt);
+				}
+				slot.prog_count = (uint32_t)list.size();
+			}
+			std::map<uint32_t,uint32_t>::const_iterator si = stopidx.find( ev);
+			if (si != stopidx.end()) slot.stopword = si->second;
+			uint32_t h = sp_event_slot_hash( ev) & (nslots-1);
+			while (T.event_slots[ h].key) h = (h + 1) & (nslots-1);
+			T.event_slots[ h] = slot;
+		}
+		std::memset( &T.view, 0, sizeof(T.view));
+		T.view.programs = T.programs.data(); T.view.trigger_defs = T.trigger_defs.data();
+		T.view.program_triggers = T.program_triggers.data(); T.view.event_slots = T.event_slots.data();
+		T.view.event_mask = nslots - 1;
+		T.view.nprograms = (uint32_t)T.programs.size(); T.view.ntrigger_defs = (uint32_t)T.trigger_defs.size();
+		T.view.nprogram_triggers = (uint32_t)T.program_triggers.size();
+		T.view.nstopwords = (uint32_t)T.stopwords.size();
+		T.view.exclusive = m_exclusive ? 1 : 0; T.view.max_result_size = m_maxResultSize;
+		T.view.max_trigger_defs = maxdefs;
+		m_flattened = true;
+		return T;
+	}
+
+private:
+	struct Node
+	{
+		uint32_t event, program, variable;
+		explicit Node( uint32_t event_, uint32_t program_=0) :event(event_),program(program_),variable(0){}
+	};
+	struct Rule
+	{
+		uint32_t initsigval, initcount, event, resultHandle, formatHandle, range;
+		std::vector<SpTriggerDef> defs;		// definition order (argument 0 first)
+	};
+	typedef std::unordered_map<uint32_t,uint32_t> EventListMap;	// event -> index into m_lists; same container and insertion
+									// sequence as the reference so that compile() visits events in the same order
+
+	// createProgram + createTrigger* + doneProgram; returns the 1-based program index
+	uint32_t addRule( const Rule& rule)
+	{
+		m_rules.push_back( rule);
+		uint32_t program = (uint32_t)m_rules.size();
+		for (std::size_t di = rule.defs.size(); di > 0; --di)
+		{
+			if (rule.defs[ di-1].is_key) {addEventProgram( rule.defs[ di-1].event, program, 0); ++m_totalNofPrograms;}
+		}
+		return program;
+	}
+	void addEventProgram( uint32_t eventid, uint32_t program, uint32_t past_event)
+	{
+		SpProgramTrigger pt; pt.program = program; pt.past_event = past_event;
+		EventListMap::iterator ei = m_eventPrograms.find( eventid);
+		if (ei == m_eventPrograms.end())
+		{
+			m_lists.push_back( std::vector<SpProgramTrigger>( 1, pt));
+			m_eventPrograms[ eventid] = (uint32_t)m_lists.size()-1;
+		}
+		else m_lists[ ei->second].push_back( pt);
+		m_keyOccurrence[ eventid] += 1;
+		if (past_event)
+		{
+			m_keyOccurrence[ past_event] -= 1;
+			m_stopwords.insert( past_event);
+		}
+	}
+	double eventWeight( uint32_t eventid) const
+	{
+		double kf = 1.0;
+		std::map<uint32_t,double>::const_iterator fi = m_frequency.find( eventid);
+		if (fi != m_frequency.end() && fi->second > 0.0) kf = fi->second;
+		std::map<uint32_t,uint32_t>::const_iterator ki = m_keyOccurrence.find( eventid);
+		if (ki != m_keyOccurrence.end() && ki->second > 0.0) kf *= ki->second;
+		return kf;
+	}
+	// getAltEventId: the event (other than the key) whose trigger has the highest signal value; 0 = none
+	uint32_t alternativeKeyEvent( uint32_t eventid, const Rule& rule) const
+	{
+		uint32_t selected = 0, selectedSigval = 0;
+		uint8_t sigtype = SP_SIG_ANY;
+		for (std::size_t di = rule.defs.size(); di > 0; --di)
+		{
+			const SpTriggerDef& def = rule.defs[ di-1];
+			bool sequenceCase = false;
+			switch (def.sigtype)
+			{
+				case SP_SIG_ANY: return 0;
+				case SP_SIG_AND:
+					if (sigtype == def.sigtype) {if (def.event != eventid) {selected = def.event; sigtype = def.sigtype;}}
+					else if (sigtype == SP_SIG_ANY && def.event != eventid) {selected = def.event; sigtype = def.sigtype;}
+					else return 0;
+					sequenceCase = true;	// the reference falls through into the sequence case (no break, :371-391)
+					break;
+				case SP_SIG_SEQUENCE: case SP_SIG_SEQUENCE_IMM: case SP_SIG_WITHIN:
+					sequenceCase = true;
+					break;
+				default: break;	// SigDel
+			}
+			if (!sequenceCase) continue;
+			if (sigtype == def.sigtype)
+			{
+				if (selectedSigval < def.sigval && def.event != eventid) {selected = def.event; selectedSigval = def.sigval; sigtype = def.sigtype;}
+			}
+			else if (sigtype == SP_SIG_ANY && def.event != eventid) {selected = def.event; selectedSigval = def.sigval; sigtype = def.sigtype;}
+			else if (sigtype == SP_SIG_SEQUENCE_IMM && def.sigtype == SP_SIG_SEQUENCE)
+			{
+				if (selectedSigval < def.sigval && def.event != eventid) {selected = def.event; selectedSigval = def.sigval; sigtype = def.sigtype;}
+			}
+			else return 0;
+		}
+		return selected;
+	}
+	void eliminateUnusedEvents()
+	{
+		std::set<uint32_t> used, programs;
+		for (EventListMap::const_iterator ei = m_eventPrograms.begin(); ei != m_eventPrograms.end(); ++ei)
+		{
+			for (const SpProgramTrigger& pt: m_lists[ ei->second])
+			{
+				programs.insert( pt.program);
+				for (const SpTriggerDef& def: m_rules[ pt.program-1].defs) used.insert( def.event);
+			}
+		}
+		for (uint32_t program: programs)
+		{
+			Rule& rule = m_rules[ program-1];
+			if (used.find( rule.event) == used.end()) rule.event = 0;
+		}
+	}
+
+	std::vector<Node> m_stack;
+	std::vector<Rule> m_rules;
+	std::vector<std::vector<SpProgramTrigger> > m_lists;	// program lists in push order (1-based program indices)
+	EventListMap m_eventPrograms;
+	std::set<uint32_t> m_stopwords;
+	std::map<uint32_t,uint32_t> m_keyOccurrence, m_eventOccurrence;
+	std::map<uint32_t,double> m_frequency;
+	NameTable m_patterns, m_variables;
+	std::vector<std::string> m_formats;
+	uint32_t m_expressionEventCnt, m_totalNofPrograms;
+	float m_stopwordOccurrenceFactor, m_weightFactor;
+	uint32_t m_maxRange, m_maxResultSize;
+	bool m_exclusive, m_flattened;
+	MatcherTablesHost m_tables;
+};
+
+} // namespace sp
+#endif

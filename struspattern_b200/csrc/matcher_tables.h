@@ -1,0 +1,85 @@
+// Compiled rule graph of the level-2 matcher as it lives in HBM: flat, index addressed, read-only tables.
+// Built by matcher_program.hpp from the pushTerm/pushExpression/definePattern calls; this is what replaces
+// the ProgramTable arenas of the reference (src/ruleMatcherAutomaton.hpp:344-413: PodStackPool trigger-def
+// lists, program-trigger lists and the unordered_map event -> program list).
+#ifndef SP_MATCHER_TABLES_H_INCLUDED
+#define SP_MATCHER_TABLES_H_INCLUDED
+#include <stdint.h>
+
+/* Trigger::SigType, src/ruleMatcherAutomaton.hpp:48 */
+#define SP_SIG_ANY          0
+#define SP_SIG_SEQUENCE     1
+#define SP_SIG_SEQUENCE_IMM 2
+#define SP_SIG_WITHIN       3
+#define SP_SIG_DEL          4
+#define SP_SIG_AND          5
+
+/* Program (src/ruleMatcherAutomaton.hpp:319) with its ActionSlotDef (:291) inlined. 32 bytes. */
+typedef struct SpProgram
+{
+	uint32_t initsigval;
+	uint32_t initcount;
+	uint32_t event;			/* follow event emitted on a match (0 = none) */
+	uint32_t resultHandle;		/* pattern handle of a visible result (0 = none) */
+	uint32_t formatHandle;
+	uint32_t range;			/* positionRange */
+	uint32_t trig_begin;		/* trigger definitions [trig_begin, trig_begin+trig_count) */
+	uint32_t trig_count;
+} SpProgram;
+
+/* TriggerDef (src/ruleMatcherAutomaton.hpp:305). Stored per program in the order the reference's LIFO list
+ * is iterated: last argument first (src/ruleMatcherAutomaton.cpp:276, podStackPoolBase.hpp:48-62). 16 bytes. */
+typedef struct SpTriggerDef
+{
+	uint32_t event;
+	uint32_t sigval;
+	uint32_t variable;
+	uint8_t sigtype;
+	uint8_t is_key;
+	uint16_t reserved;
+} SpTriggerDef;
+
+/* ProgramTrigger (src/ruleMatcherAutomaton.hpp:331), stored per key event in list iteration order. */
+typedef struct SpProgramTrigger
+{
+	uint32_t program;		/* 0-based index into programs */
+	uint32_t past_event;		/* original key event of a program moved to an alternative key, else 0 */
+} SpProgramTrigger;
+
+/* Open addressing hash table over every event that is a key event or a stop word. */
+typedef struct SpEventSlot
+{
+	uint32_t key;			/* event id + 1; 0 = empty slot */
+	uint32_t prog_begin;		/* program triggers [prog_begin, prog_begin+prog_count) */
+	uint32_t prog_count;
+	uint32_t stopword;		/* 1-based index into the per document stop word log, 0 = not a stop word */
+} SpEventSlot;
+
+typedef struct SpMatcherTables
+{
+	const SpProgram* programs;
+	const SpTriggerDef* trigger_defs;
+	const SpProgramTrigger* program_triggers;
+	const SpEventSlot* event_slots;
+	uint32_t event_mask;		/* number of slots - 1 (power of two) */
+	uint32_t nprograms;
+	uint32_t ntrigger_defs;
+	uint32_t nprogram_triggers;
+	uint32_t nstopwords;
+	uint32_t exclusive;		/* option "exclusive" (src/patternMatcher.cpp:632) */
+	uint32_t max_result_size;	/* option "maxResultSize" (:628) */
+	uint32_t max_trigger_defs;	/* largest trig_count */
+} SpMatcherTables;
+
+#ifdef __CUDACC__
+#define SP_TAB_HD __host__ __device__ __forceinline__
+#else
+#define SP_TAB_HD inline
+#endif
+SP_TAB_HD uint32_t sp_event_slot_hash( uint32_t event)
+{
+	uint32_t h = event * 0x9E3779B1u;
+	return h ^ (h >> 15);
+}
+
+#endif
