@@ -164,7 +164,7 @@ public:
 			m_eventOccurrence[ def.event] += 1;
 		}
 		uint32_t program = addRule( rule);
-		m_stack.resize( m_stack.size() - argc);
+		m_stack.erase( m_stack.end() - argc, m_stack.end());
 		m_stack.push_back( Node( rule.event, program));
 		m_flattened = false;
 	}

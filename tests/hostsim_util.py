@@ -98,3 +98,104 @@ class HostSimLexer:
         b = src if isinstance(src, bytes) else src.encode()
         out = self.scan(b, [0, len(b)])
         return [tuple(int(x) for x in r) for r in out["lexems"]]
+
+
+HS_MATCHER_LIB = os.path.join(HS_DIR, "_build", "libsp_hostsim_matcher.so")
+
+
+def build_hostsim_matcher(force=False):
+    srcs = [os.path.join(HS_DIR, "matcher_hostsim.cpp")] + [
+        os.path.join(ROOT, "struspattern_b200", "csrc", f)
+        for f in ("matcher_program.hpp", "matcher_device.cuh", "matcher_tables.h")]
+    if not force and os.path.exists(HS_MATCHER_LIB) and all(os.path.getmtime(HS_MATCHER_LIB) >= os.path.getmtime(s) for s in srcs):
+        return
+    os.makedirs(os.path.dirname(HS_MATCHER_LIB), exist_ok=True)
+    subprocess.run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-w", "-I", os.path.join(ROOT, "include"),
+                    "-I", os.path.join(ROOT, "struspattern_b200", "csrc"), "-o", HS_MATCHER_LIB, srcs[0]], check=True)
+
+
+class HostSimMatcher:
+    """The product's rule-graph builder + per-document state machine run on the CPU (tests/hostsim/matcher_hostsim.cpp).
+    Same interface as oracle_util.RefMatcher."""
+    _lib = None
+
+    @classmethod
+    def lib(cls):
+        if cls._lib is None:
+            build_hostsim_matcher()
+            L = C.CDLL(HS_MATCHER_LIB)
+            L.msim_create.restype = C.c_void_p
+            for f in ("msim_last_error", "msim_pattern_name", "msim_variable_name"):
+                getattr(L, f).restype = C.c_char_p
+            for f in ("msim_result_count", "msim_item_count", "msim_retries"):
+                getattr(L, f).restype = C.c_uint64
+            L.msim_info.restype = C.c_int64
+            cls._lib = L
+        return cls._lib
+
+    def __init__(self, caps=None):
+        self.L = self.lib()
+        self.h = C.c_void_p(self.L.msim_create())
+        if caps:
+            self.L.msim_set_caps(self.h, *[C.c_uint32(c) for c in caps])
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.msim_destroy(self.h)
+            self.h = None
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise RuntimeError(self.L.msim_last_error(self.h).decode(errors="replace"))
+
+    def define_option(self, name, value=0.0):
+        self._ck(self.L.msim_define_option(self.h, name.encode(), C.c_double(value)))
+
+    def define_term_frequency(self, termid, df):
+        self._ck(self.L.msim_define_term_frequency(self.h, C.c_uint32(termid), C.c_double(df)))
+
+    def push_term(self, termid):
+        self._ck(self.L.msim_push_term(self.h, C.c_uint32(termid)))
+
+    def push_expression(self, op, argc, rng, card):
+        self._ck(self.L.msim_push_expression(self.h, C.c_int(op), C.c_size_t(argc), C.c_uint32(rng), C.c_uint32(card)))
+
+    def push_pattern(self, name):
+        self._ck(self.L.msim_push_pattern(self.h, name.encode()))
+
+    def attach_variable(self, name):
+        self._ck(self.L.msim_attach_variable(self.h, name.encode()))
+
+    def define_pattern(self, name, fmt="", visible=True):
+        self._ck(self.L.msim_define_pattern(self.h, name.encode(), fmt.encode(), C.c_int(1 if visible else 0)))
+
+    def compile(self):
+        self._ck(self.L.msim_compile(self.h))
+
+    def info(self, key):
+        return int(self.L.msim_info(self.h, key.encode()))
+
+    def retries(self):
+        return int(self.L.msim_retries(self.h))
+
+    def run(self, tokens, tok_offsets, origsegs=None, nthreads=1, with_results=True):
+        from oracle_util import ITEM_DT, RESULT_DT, STATS_DT
+        tokens = np.ascontiguousarray(tokens, dtype=LEXEM_DT)
+        tok_offsets = np.ascontiguousarray(tok_offsets, dtype=np.uint64)
+        ndocs = len(tok_offsets) - 1
+        if origsegs is not None:
+            origsegs = np.ascontiguousarray(origsegs, dtype=np.uint32)
+        self._ck(self.L.msim_run_batch(self.h, _ptr(tokens), _ptr(origsegs), _ptr(tok_offsets), C.c_uint32(ndocs), C.c_int(1), C.c_int(1)))
+        nres, nitems = int(self.L.msim_result_count(self.h)), int(self.L.msim_item_count(self.h))
+        out = {"results": np.zeros(nres, dtype=RESULT_DT), "result_offsets": np.zeros(ndocs + 1, dtype=np.uint64),
+               "items": np.zeros(nitems, dtype=ITEM_DT), "item_offsets": np.zeros(ndocs + 1, dtype=np.uint64),
+               "stats": np.zeros(ndocs, dtype=STATS_DT), "status": np.zeros(ndocs, dtype=np.uint32)}
+        self.L.msim_fetch(self.h, _ptr(out["results"]) if nres else None, _ptr(out["result_offsets"]),
+                          _ptr(out["items"]) if nitems else None, _ptr(out["item_offsets"]), _ptr(out["stats"]), _ptr(out["status"]))
+        return out
+
+    def result_name(self, idx):
+        return self.L.msim_pattern_name(self.h, C.c_uint32(int(idx))).decode()
+
+    def item_name(self, idx):
+        return self.L.msim_variable_name(self.h, C.c_uint32(int(idx))).decode()

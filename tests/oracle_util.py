@@ -116,8 +116,11 @@ class RefMatcher:
     def name(self, idx):
         return self.L.refm_name(self.h, C.c_uint32(int(idx))).decode()
 
+    result_name = name
+    item_name = name
 
-def canonical_results(out, result_name, item_name):
+
+def canonical_results(out, result_name, item_name, sort=True):
     """Per document: sorted list of (name, ordpos, ordend, origseg, origpos, endseg, endpos, (items...))
     with items in emission order -- the multiset the parity contract compares."""
     docs = []
@@ -131,7 +134,8 @@ def canonical_results(out, result_name, item_name):
                         for i in items[int(r["item_begin"]):int(r["item_begin"]) + int(r["item_count"])])
             recs.append((result_name(r["name"]), int(r["ordpos"]), int(r["ordend"]), int(r["origseg"]), int(r["origpos"]),
                          int(r["endseg"]), int(r["endpos"]), its))
-        recs.sort()
+        if sort:
+            recs.sort()
         docs.append(recs)
     return docs
 
