@@ -169,6 +169,8 @@ int sp_matcher_compile( sp_matcher* m);
 int sp_matcher_upload( sp_matcher* m);
 const char* sp_matcher_pattern_name( const sp_matcher* m, uint32_t handle);    /* patternMap.key, :250 */
 const char* sp_matcher_variable_name( const sp_matcher* m, uint32_t handle);   /* variableMap.key, :170 */
+/* format string of a format handle (sp_result.format / sp_item.format), resultFormatHandles, :560-566 */
+const char* sp_matcher_format_string( const sp_matcher* m, uint32_t handle);
 int64_t sp_matcher_table_info( const sp_matcher* m, const char* key);
 
 sp_matcher_ctx* sp_matcher_ctx_create( sp_matcher* m, void* cuda_stream);      /* :586 */
@@ -190,6 +192,10 @@ const sp_item* sp_matcher_items_device( sp_matcher_ctx* ctx);
  * stats[ndocs], status[ndocs]; each may be NULL. */
 int sp_matcher_fetch( sp_matcher_ctx* ctx, sp_result* results, uint64_t* result_offsets,
 		      sp_item* items, uint64_t* item_offsets, sp_matcher_stats* stats, uint32_t* status);
+
+/* Counters of the last run ("results", "items", "tokens", "arena_retries", "pool_retries", "kernel_launches", ...)
+ * and tuning knobs ("arena=N", "warps_per_sm=N"); -1 if unknown. */
+int64_t sp_matcher_ctx_counter( sp_matcher_ctx* ctx, const char* key);
 
 /* Fused pipeline: lexems of a finished sp_lexer_scan are fed to the matcher without leaving the device. */
 int sp_matcher_run_lexer_output( sp_matcher_ctx* ctx, sp_lexer_ctx* lexer_ctx);

@@ -67,7 +67,8 @@ def lib():
             "sp_matcher_define_pattern": (C.c_int, [vp, cp, cp, C.c_int]),
             "sp_matcher_compile": (C.c_int, [vp]), "sp_matcher_upload": (C.c_int, [vp]),
             "sp_matcher_pattern_name": (cp, [vp, u32]), "sp_matcher_variable_name": (cp, [vp, u32]),
-            "sp_matcher_table_info": (C.c_int64, [vp, cp]),
+            "sp_matcher_table_info": (C.c_int64, [vp, cp]), "sp_matcher_format_string": (cp, [vp, u32]),
+            "sp_matcher_ctx_counter": (C.c_int64, [vp, cp]),
             "sp_matcher_ctx_create": (vp, [vp, vp]), "sp_matcher_ctx_destroy": (None, [vp]),
             "sp_matcher_ctx_last_error": (cp, [vp]),
             "sp_matcher_run": (C.c_int, [vp, vp, vp, vp, u32, C.c_int]),
@@ -78,8 +79,6 @@ def lib():
         }
         for table in (sigs, msigs):
             for name, (res, args) in table.items():
-                if table is msigs and not hasattr(L, name):
-                    continue
                 f = getattr(L, name)
                 f.restype, f.argtypes = res, args
         _lib = L
@@ -201,4 +200,135 @@ class LexerContext:
 
     def scan(self, text, doc_offsets, on_device=False):
         self.launch(text, doc_offsets, on_device)
+        return self.fetch()
+
+
+class Matcher:
+    """PatternMatcherInstanceInterface over the C ABI; same method names as oracle_util.RefMatcher."""
+
+    def __init__(self):
+        self.L = lib()
+        self.h = self.L.sp_matcher_create()
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.sp_matcher_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise PatternError(rc, self.L.sp_matcher_last_error(self.h).decode(errors="replace"))
+
+    def define_option(self, name, value=0.0):
+        self._ck(self.L.sp_matcher_define_option(self.h, name.encode(), value))
+
+    def define_term_frequency(self, termid, df):
+        self._ck(self.L.sp_matcher_define_term_frequency(self.h, termid, df))
+
+    def push_term(self, termid):
+        self._ck(self.L.sp_matcher_push_term(self.h, termid))
+
+    def push_expression(self, op, argc, rng, card):
+        self._ck(self.L.sp_matcher_push_expression(self.h, op, argc, rng, card))
+
+    def push_pattern(self, name):
+        self._ck(self.L.sp_matcher_push_pattern(self.h, name.encode()))
+
+    def attach_variable(self, name):
+        self._ck(self.L.sp_matcher_attach_variable(self.h, name.encode()))
+
+    def define_pattern(self, name, fmt="", visible=True):
+        self._ck(self.L.sp_matcher_define_pattern(self.h, name.encode(), fmt.encode(), 1 if visible else 0))
+
+    def compile(self):
+        self._ck(self.L.sp_matcher_compile(self.h))
+
+    def table_info(self, key):
+        return int(self.L.sp_matcher_table_info(self.h, key.encode()))
+
+    def result_name(self, handle):
+        s = self.L.sp_matcher_pattern_name(self.h, int(handle))
+        return s.decode() if s else ""
+
+    def item_name(self, handle):
+        s = self.L.sp_matcher_variable_name(self.h, int(handle))
+        return s.decode() if s else ""
+
+    def create_context(self, stream=None):
+        return MatcherContext(self, stream)
+
+    def run(self, tokens, tok_offsets, origsegs=None, **_):
+        ctx = self.create_context()
+        try:
+            return ctx.run(tokens, tok_offsets, origsegs)
+        finally:
+            ctx.close()
+
+
+class MatcherContext:
+    def __init__(self, matcher, stream=None):
+        self.L = matcher.L
+        self.matcher = matcher
+        self.h = self.L.sp_matcher_ctx_create(matcher.h, stream)
+        if not self.h:
+            raise PatternError(-4, self.L.sp_matcher_last_error(matcher.h).decode(errors="replace"))
+        self.ndocs = 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.sp_matcher_ctx_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def _ck(self, rc):
+        if rc < 0:
+            raise PatternError(rc, self.L.sp_matcher_ctx_last_error(self.h).decode(errors="replace"))
+        return rc
+
+    def counter(self, key):
+        return int(self.L.sp_matcher_ctx_counter(self.h, key.encode()))
+
+    def launch(self, tokens, tok_offsets, origsegs=None, on_device=False, ndocs=None):
+        """Host arrays (LEXEM_DT tokens, uint64 offsets, optional uint32 segments) or, with on_device, int device pointers."""
+        if on_device:
+            self.ndocs = int(ndocs)
+            self._ck(self.L.sp_matcher_run(self.h, C.c_void_p(int(tokens)), C.c_void_p(int(origsegs)) if origsegs else None,
+                                           C.c_void_p(int(tok_offsets)), self.ndocs, 1))
+            return
+        self._tok = np.ascontiguousarray(tokens, dtype=LEXEM_DT)
+        self._off = np.ascontiguousarray(tok_offsets, dtype=np.uint64)
+        self._seg = np.ascontiguousarray(origsegs, dtype=np.uint32) if origsegs is not None else None
+        self.ndocs = len(self._off) - 1
+        self._ck(self.L.sp_matcher_run(self.h, _ptr(self._tok), _ptr(self._seg), _ptr(self._off), self.ndocs, 0))
+
+    def launch_lexer_output(self, lexer_ctx):
+        self.ndocs = lexer_ctx.ndocs
+        self._ck(self.L.sp_matcher_run_lexer_output(self.h, lexer_ctx.h))
+
+    def count(self):
+        return self._ck(self.L.sp_matcher_result_count(self.h)), self._ck(self.L.sp_matcher_item_count(self.h))
+
+    def fetch(self):
+        nres, nitems = self.count()
+        nd = self.ndocs
+        out = {"results": np.zeros(nres, dtype=RESULT_DT), "result_offsets": np.zeros(nd + 1, dtype=np.uint64),
+               "items": np.zeros(nitems, dtype=ITEM_DT), "item_offsets": np.zeros(nd + 1, dtype=np.uint64),
+               "stats": np.zeros(nd, dtype=STATS_DT), "status": np.zeros(nd, dtype=np.uint32)}
+        self._ck(self.L.sp_matcher_fetch(self.h, _ptr(out["results"]) if nres else None, _ptr(out["result_offsets"]),
+                                         _ptr(out["items"]) if nitems else None, _ptr(out["item_offsets"]),
+                                         _ptr(out["stats"]) if nd else None, _ptr(out["status"]) if nd else None))
+        return out
+
+    def fetch_into(self, results, result_offsets, items, item_offsets, stats, status):
+        nres, nitems = self.count()
+        if nres > len(results) or nitems > len(items):
+            raise PatternError(-1, "result buffers too small: %d results, %d items" % (nres, nitems))
+        self._ck(self.L.sp_matcher_fetch(self.h, _ptr(results), _ptr(result_offsets), _ptr(items), _ptr(item_offsets), _ptr(stats), _ptr(status)))
+        return nres, nitems
+
+    def run(self, tokens, tok_offsets, origsegs=None):
+        self.launch(tokens, tok_offsets, origsegs)
         return self.fetch()

@@ -292,6 +292,7 @@ int64_t sp_lexer_ctx_counter( sp_lexer_ctx* ctx, const char* key)
 	if (k == "islands") return (int64_t)ctx->nisl;
 	if (k == "elements") return (int64_t)ctx->nelem;
 	if (k == "text_bytes") return (int64_t)ctx->total;
+	if (k == "ndocs") return ctx->valid ? (int64_t)ctx->ndocs : -1;
 	if (k == "chunk_bytes") return (int64_t)ctx->chunk;
 	if (k == "profile:on") {ctx->profile = true; return 1;}
 	if (k == "profile:off") {ctx->profile = false; return 0;}

@@ -1,0 +1,281 @@
+// Batched PatternMatcherContext (included by matcher_capi.cu): owns the per-warp arenas, the output pools and the
+// result buffers, and drives k_match_documents -> k_match_collect (-> another round for overflowed documents)
+// -> prefix sums -> k_match_compact.
+
+struct sp_matcher_ctx
+{
+	sp_matcher* m;
+	cudaStream_t stream;
+	std::string lasterror;
+	// configuration
+	SpArenaCaps cap;		// arena capacities of the first round (grown by 4 for documents that overflow)
+	uint32_t warps_per_sm;
+	uint64_t arena_budget;		// bytes of HBM the arenas may take
+	int nsm;
+	// device buffers (grow only)
+	DeviceBuffer tokens, origsegs, tok_off, arenas, res_pool, item_pool, scalars, doc_res_begin, doc_res_count, doc_item_begin,
+		     doc_item_count, stats, status, list_a, list_b, res_off, item_off, results, items, scantmp;
+	double res_per_token, items_per_token;	// output pool sizing, learned from the last run
+	// last batch
+	uint32_t ndocs;
+	uint64_t ntokens, nres, nitems, retries, pool_retries, launches;
+	bool valid;
+	uint64_t* pinned;		// host staging for scalar read backs [8]
+	cudaEvent_t ev_a, ev_b;
+	double kernel_ms; uint64_t kernel_calls;
+	bool profile;
+
+	sp_matcher_ctx( sp_matcher* m_, cudaStream_t stream_)
+		:m(m_),stream(stream_),warps_per_sm(16),arena_budget(0),nsm(0),res_per_token(0.5),items_per_token(1.0)
+		,ndocs(0),ntokens(0),nres(0),nitems(0),retries(0),pool_retries(0),launches(0),valid(false),pinned(0),ev_a(0),ev_b(0)
+		,kernel_ms(0.0),kernel_calls(0),profile(false)
+	{
+		cap.rules = 2048; cap.triggers = 2048; cap.items = 8192; cap.datarefs = 4096; cap.results = 4096;
+		cap.follow = 256; cap.dispose = 2048; cap.heap = 1024;
+		const char* e;
+		if ((e = std::getenv( "SP_MATCHER_ARENA")) != 0 && std::atoi( e) >= 4)
+		{
+			uint32_t n = (uint32_t)std::atoi( e);
+			cap.rules = cap.triggers = cap.datarefs = cap.results = cap.dispose = n; cap.items = 4*n; cap.follow = n < 64 ? n : n/8; cap.heap = n/2 + 1;
+		}
+		if ((e = std::getenv( "SP_MATCHER_WARPS_PER_SM")) != 0 && std::atoi( e) >= 1) warps_per_sm = (uint32_t)std::atoi( e);
+		if (std::getenv( "SP_MATCHER_PROFILE")) profile = true;
+		int dev = 0;
+		SP_CUDA( cudaGetDevice( &dev));
+		SP_CUDA( cudaDeviceGetAttribute( &nsm, cudaDevAttrMultiProcessorCount, dev));
+		std::size_t freeb = 0, totalb = 0;
+		SP_CUDA( cudaMemGetInfo( &freeb, &totalb));
+		arena_budget = freeb / 4;
+		SP_CUDA( cudaMallocHost( (void**)&pinned, 8 * sizeof(uint64_t)));
+		SP_CUDA( cudaEventCreate( &ev_a)); SP_CUDA( cudaEventCreate( &ev_b));
+	}
+	~sp_matcher_ctx()
+	{
+		if (pinned) cudaFreeHost( pinned);
+		if (ev_a) cudaEventDestroy( ev_a);
+		if (ev_b) cudaEventDestroy( ev_b);
+	}
+
+	void readScalars( const void* devptr, std::size_t bytes)
+	{
+		SP_CUDA( cudaMemcpyAsync( pinned, devptr, bytes, cudaMemcpyDeviceToHost, stream));
+		SP_CUDA( cudaStreamSynchronize( stream));
+	}
+
+	// tokens / origsegs / tok_offsets already on the device; ntokens known
+	void runDevice( const sp_lexem* d_tokens, const uint32_t* d_origsegs, const uint64_t* d_tok_off, uint32_t ndocs_, uint64_t ntokens_)
+	{
+		valid = false;
+		m->upload();
+		int dev = -1;
+		SP_CUDA( cudaGetDevice( &dev));
+		if (dev != m->device) throw std::runtime_error( "matcher tables live on another device than the current one");
+		ndocs = ndocs_; ntokens = ntokens_;
+		nres = nitems = 0;
+
+		MatchParams P; std::memset( &P, 0, sizeof(P));
+		P.T = m->dev;
+		P.tokens = d_tokens; P.origsegs = d_origsegs; P.tok_off = d_tok_off; P.ndocs = ndocs;
+		P.doc_res_begin = doc_res_begin.as<uint64_t>( ndocs); P.doc_res_count = doc_res_count.as<uint32_t>( ndocs);
+		P.doc_item_begin = doc_item_begin.as<uint64_t>( ndocs); P.doc_item_count = doc_item_count.as<uint32_t>( ndocs);
+		P.stats = stats.as<sp_matcher_stats>( ndocs); P.status = status.as<uint32_t>( ndocs);
+		uint64_t* d_scalars = scalars.as<uint64_t>( 8);
+		P.cursors = reinterpret_cast<unsigned long long*>( d_scalars);
+		uint32_t* d_words = reinterpret_cast<uint32_t*>( d_scalars + 2);	// [0] next_doc [1] list count [2..4] overflow kinds
+		P.next_doc = d_words;
+		uint64_t* d_res_off = res_off.as<uint64_t>( (std::size_t)ndocs + 1);
+		uint64_t* d_item_off = item_off.as<uint64_t>( (std::size_t)ndocs + 1);
+
+		if (ndocs)
+		{
+			uint64_t res_cap = (uint64_t)(res_per_token * 1.25 * (double)ntokens) + 4096;
+			uint64_t item_cap = (uint64_t)(items_per_token * 1.25 * (double)ntokens) + 8192;
+			SpArenaCaps curcap = cap;
+			uint32_t* d_list = 0; uint32_t nlist = 0;
+			bool flip = false;
+			for (int round=0;; ++round)
+			{
+				if (round > 12) throw std::runtime_error( "matcher arenas keep overflowing (rule set too large for the device memory)");
+				sp_arena_layout( curcap, P.T.nstopwords, P.layout);
+				uint32_t ntodo = d_list ? nlist : ndocs;
+				uint64_t maxwarps = arena_budget / P.layout.bytes;
+				if (maxwarps < 1) throw std::runtime_error( "matcher arena does not fit the device memory");
+				uint64_t nwarps = std::min<uint64_t>( std::min<uint64_t>( ntodo, (uint64_t)nsm * warps_per_sm), maxwarps);
+				uint32_t nblocks = (uint32_t)((nwarps + MatchWarpsPerBlock - 1) / MatchWarpsPerBlock);
+				P.arena_base = arenas.as<uint8_t>( (std::size_t)nblocks * MatchWarpsPerBlock * P.layout.bytes);
+				// the stop word log is validated by a per-warp document stamp that restarts with every launch
+				SP_CUDA( cudaMemset2DAsync( P.arena_base + P.layout.stoplog, P.layout.bytes, 0, ((std::size_t)P.T.nstopwords + 1) * sizeof(SpStopLog),
+							    (std::size_t)nblocks * MatchWarpsPerBlock, stream));
+				P.res_pool = res_pool.as<sp_result>( res_cap); P.item_pool = item_pool.as<sp_item>( item_cap);
+				P.res_cap = res_cap; P.item_cap = item_cap;
+				P.doc_list = d_list; P.nlist = nlist;
+				if (!d_list) SP_CUDA( cudaMemsetAsync( d_scalars, 0, 8 * sizeof(uint64_t), stream));
+				else SP_CUDA( cudaMemsetAsync( d_words, 0, 5 * sizeof(uint32_t), stream));
+				uint32_t* d_newlist = (flip ? list_b : list_a).as<uint32_t>( ntodo);
+				if (profile) SP_CUDA( cudaEventRecord( ev_a, stream));
+				k_match_documents<<<nblocks, MatchThreads, 0, stream>>>( P);
+				if (profile) SP_CUDA( cudaEventRecord( ev_b, stream));
+				k_match_collect<<<(ndocs + 255) / 256, 256, 0, stream>>>( P.status, ndocs, d_newlist, d_words + 1, d_words + 2);
+				SP_CUDA( cudaGetLastError());
+				launches += 2;
+				readScalars( d_scalars, 8 * sizeof(uint64_t));
+				if (profile)
+				{
+					float ms = 0.0f;
+					if (cudaEventElapsedTime( &ms, ev_a, ev_b) == cudaSuccess) {kernel_ms += ms; kernel_calls += 1;}
+				}
+				uint64_t want_res = pinned[0], want_items = pinned[1];
+				const uint32_t* words = reinterpret_cast<const uint32_t*>( pinned + 2);
+				uint32_t listcount = words[1];
+				bool ovfArena = words[2] != 0, ovfOutput = words[3] != 0, ovfDepth = words[4] != 0;
+				if (ovfDepth) throw std::runtime_error( "nesting of result items too deep");
+				if (ovfOutput)
+				{
+					// output pools too small: size them from what this round asked for and run everything again
+					++pool_retries;
+					res_cap = std::max<uint64_t>( res_cap * 2, want_res + want_res / 4 + 4096);
+					item_cap = std::max<uint64_t>( item_cap * 2, want_items + want_items / 4 + 8192);
+					d_list = 0; nlist = 0;
+					continue;
+				}
+				nres = want_res; nitems = want_items;
+				if (!ovfArena) break;
+				++retries;
+				curcap.rules *= 4; curcap.triggers *= 4; curcap.items *= 4; curcap.datarefs *= 4;
+				curcap.results *= 4; curcap.follow *= 4; curcap.dispose *= 4; curcap.heap *= 4;
+				d_list = d_newlist; nlist = listcount; flip = !flip;
+			}
+			if (ntokens)
+			{
+				res_per_token = std::max( 0.01, (double)nres / (double)ntokens);
+				items_per_token = std::max( 0.01, (double)nitems / (double)ntokens);
+			}
+		}
+		// document order: offsets by prefix sum, then one warp per document copies its records
+		exclusiveScan( P.doc_res_count, ndocs, d_res_off, scantmp, stream);
+		exclusiveScan( P.doc_item_count, ndocs, d_item_off, scantmp, stream);
+		launches += 6;
+		readScalars( d_res_off + ndocs, sizeof(uint64_t)); nres = pinned[0];
+		readScalars( d_item_off + ndocs, sizeof(uint64_t)); nitems = pinned[0];
+		sp_result* d_results = results.as<sp_result>( nres);
+		sp_item* d_items = items.as<sp_item>( nitems);
+		if (ndocs)
+		{
+			k_match_compact<<<(ndocs + 7) / 8, 256, 0, stream>>>( P, d_res_off, d_item_off, d_results, d_items);
+			SP_CUDA( cudaGetLastError());
+			launches += 1;
+		}
+		valid = true;
+	}
+
+	void run( const sp_lexem* tokens_in, const uint32_t* origsegs_in, const uint64_t* tok_offsets, uint32_t ndocs_, int on_device)
+	{
+		valid = false;
+		if (on_device)
+		{
+			uint64_t total = 0;
+			if (ndocs_) {readScalars( tok_offsets + ndocs_, sizeof(uint64_t)); total = pinned[0];}
+			runDevice( tokens_in, origsegs_in, tok_offsets, ndocs_, total);
+			return;
+		}
+		for (uint32_t d=0; d<ndocs_; ++d) if (tok_offsets[d+1] < tok_offsets[d]) throw std::runtime_error( "token offsets are not ascending");
+		uint64_t total = ndocs_ ? tok_offsets[ ndocs_] : 0;
+		sp_lexem* d_tokens = tokens.as<sp_lexem>( total);
+		uint32_t* d_segs = 0;
+		uint64_t* d_off = tok_off.as<uint64_t>( (std::size_t)ndocs_ + 1);
+		if (total) SP_CUDA( cudaMemcpyAsync( d_tokens, tokens_in, total * sizeof(sp_lexem), cudaMemcpyHostToDevice, stream));
+		if (origsegs_in)
+		{
+			d_segs = origsegs.as<uint32_t>( total);
+			if (total) SP_CUDA( cudaMemcpyAsync( d_segs, origsegs_in, total * sizeof(uint32_t), cudaMemcpyHostToDevice, stream));
+		}
+		if (ndocs_) SP_CUDA( cudaMemcpyAsync( d_off, tok_offsets, ((std::size_t)ndocs_ + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, stream));
+		runDevice( d_tokens, d_segs, d_off, ndocs_, total);
+	}
+};
+
+extern "C" {
+
+sp_matcher_ctx* sp_matcher_ctx_create( sp_matcher* m, void* cuda_stream)
+{
+	try {m->upload(); return new sp_matcher_ctx( m, (cudaStream_t)cuda_stream);}
+	catch (const std::exception& e) {m->lasterror = e.what(); return 0;}
+}
+void sp_matcher_ctx_destroy( sp_matcher_ctx* ctx) {delete ctx;}
+const char* sp_matcher_ctx_last_error( const sp_matcher_ctx* ctx) {return ctx->lasterror.c_str();}
+
+int sp_matcher_run( sp_matcher_ctx* ctx, const sp_lexem* tokens, const uint32_t* origsegs, const uint64_t* tok_offsets, uint32_t ndocs, int on_device)
+	{SP_MATCHER_TRY( ctx, ctx->run( tokens, origsegs, tok_offsets, ndocs, on_device))}
+
+int sp_matcher_run_lexer_output( sp_matcher_ctx* ctx, sp_lexer_ctx* lexer_ctx)
+{
+	SP_MATCHER_TRY( ctx, {
+		int64_t nlex = sp_lexer_result_count( lexer_ctx);
+		int64_t nd = sp_lexer_ctx_counter( lexer_ctx, "ndocs");
+		if (nlex < 0 || nd < 0) throw std::runtime_error( "lexer context holds no finished scan");
+		ctx->runDevice( sp_lexer_result_lexems_device( lexer_ctx), 0, sp_lexer_result_offsets_device( lexer_ctx), (uint32_t)nd, (uint64_t)nlex);
+	})
+}
+
+int64_t sp_matcher_result_count( sp_matcher_ctx* ctx)
+{
+	if (!ctx->valid) {ctx->lasterror = "no finished run"; return SP_ERR_ARGUMENT;}
+	if (cudaStreamSynchronize( ctx->stream) != cudaSuccess) {ctx->lasterror = "kernel failure"; return SP_ERR_CUDA;}
+	return (int64_t)ctx->nres;
+}
+int64_t sp_matcher_item_count( sp_matcher_ctx* ctx)
+{
+	if (!ctx->valid) {ctx->lasterror = "no finished run"; return SP_ERR_ARGUMENT;}
+	return (int64_t)ctx->nitems;
+}
+const sp_result* sp_matcher_results_device( sp_matcher_ctx* ctx) {return ctx->valid ? (const sp_result*)ctx->results.ptr() : 0;}
+const sp_item* sp_matcher_items_device( sp_matcher_ctx* ctx) {return ctx->valid ? (const sp_item*)ctx->items.ptr() : 0;}
+
+int sp_matcher_fetch( sp_matcher_ctx* ctx, sp_result* results, uint64_t* result_offsets, sp_item* items, uint64_t* item_offsets, sp_matcher_stats* stats, uint32_t* status)
+{
+	SP_MATCHER_TRY( ctx, {
+		if (!ctx->valid) throw std::runtime_error( "no finished run");
+		std::size_t nd = ctx->ndocs;
+		cudaStream_t st = ctx->stream;
+		if (results && ctx->nres) SP_CUDA( cudaMemcpyAsync( results, ctx->results.ptr(), ctx->nres * sizeof(sp_result), cudaMemcpyDeviceToHost, st));
+		if (result_offsets) SP_CUDA( cudaMemcpyAsync( result_offsets, ctx->res_off.ptr(), (nd + 1) * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+		if (items && ctx->nitems) SP_CUDA( cudaMemcpyAsync( items, ctx->items.ptr(), ctx->nitems * sizeof(sp_item), cudaMemcpyDeviceToHost, st));
+		if (item_offsets) SP_CUDA( cudaMemcpyAsync( item_offsets, ctx->item_off.ptr(), (nd + 1) * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+		if (stats && nd) SP_CUDA( cudaMemcpyAsync( stats, ctx->stats.ptr(), nd * sizeof(sp_matcher_stats), cudaMemcpyDeviceToHost, st));
+		if (status && nd) SP_CUDA( cudaMemcpyAsync( status, ctx->status.ptr(), nd * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+		SP_CUDA( cudaStreamSynchronize( st));
+	})
+}
+
+int64_t sp_matcher_ctx_counter( sp_matcher_ctx* ctx, const char* key)
+{
+	std::string k( key);
+	if (k == "results") return (int64_t)ctx->nres;
+	if (k == "items") return (int64_t)ctx->nitems;
+	if (k == "tokens") return (int64_t)ctx->ntokens;
+	if (k == "ndocs") return (int64_t)ctx->ndocs;
+	if (k == "arena_retries") return (int64_t)ctx->retries;
+	if (k == "pool_retries") return (int64_t)ctx->pool_retries;
+	if (k == "kernel_launches") return (int64_t)ctx->launches;
+	if (k == "launches:reset") {ctx->launches = 0; return 0;}
+	if (k == "profile:on") {ctx->profile = true; return 1;}
+	if (k == "profile:off") {ctx->profile = false; return 0;}
+	if (k == "profile:reset") {ctx->kernel_ms = 0.0; ctx->kernel_calls = 0; return 0;}
+	if (k == "time_us:k_match_documents") return (int64_t)(ctx->kernel_ms * 1000.0);
+	if (k == "calls:k_match_documents") return (int64_t)ctx->kernel_calls;
+	if (k == "warps_per_sm") return (int64_t)ctx->warps_per_sm;
+	if (k.compare( 0, 13, "warps_per_sm=") == 0) {int v = std::atoi( k.c_str() + 13); if (v >= 1) ctx->warps_per_sm = (uint32_t)v; return ctx->warps_per_sm;}
+	if (k.compare( 0, 6, "arena=") == 0)
+	{
+		int n = std::atoi( k.c_str() + 6);
+		if (n >= 4)
+		{
+			SpArenaCaps& c = ctx->cap;
+			c.rules = c.triggers = c.datarefs = c.results = c.dispose = (uint32_t)n; c.items = 4u*n; c.follow = n < 64 ? n : n/8; c.heap = n/2 + 1;
+		}
+		return ctx->cap.rules;
+	}
+	return -1;
+}
+
+} // extern "C"

@@ -24,7 +24,9 @@
 #ifdef __CUDACC__
 #define SP_MHD __device__ __forceinline__
 #define SP_MLDG(p) __ldg(p)
+#define SP_MHOSTDEV __host__ __device__ __forceinline__
 #else
+#define SP_MHOSTDEV inline
 #define SP_MHD inline
 #define SP_MLDG(p) (*(p))
 #endif
@@ -818,9 +820,9 @@ typedef struct SpArenaLayout
 	uint64_t bytes;
 } SpArenaLayout;
 
-SP_MHD uint64_t sp_align128( uint64_t v) {return (v + 127) & ~(uint64_t)127;}
+SP_MHOSTDEV uint64_t sp_align128( uint64_t v) {return (v + 127) & ~(uint64_t)127;}
 
-SP_MHD void sp_arena_layout( const SpArenaCaps& cap, uint32_t nstopwords, SpArenaLayout& L)
+SP_MHOSTDEV void sp_arena_layout( const SpArenaCaps& cap, uint32_t nstopwords, SpArenaLayout& L)
 {
 	L.cap = cap; L.nstopwords = nstopwords;
 	uint64_t o = 0;
@@ -838,7 +840,7 @@ SP_MHD void sp_arena_layout( const SpArenaCaps& cap, uint32_t nstopwords, SpAren
 	L.bytes = o;
 }
 
-SP_MHD void sp_arena_bind( const SpArenaLayout& L, uint8_t* base, SpArena& A)
+SP_MHOSTDEV void sp_arena_bind( const SpArenaLayout& L, uint8_t* base, SpArena& A)
 {
 	A.cap = L.cap;
 	A.rules = (SpRule*)(base + L.rules); A.triggers = (SpTrigger*)(base + L.triggers);
