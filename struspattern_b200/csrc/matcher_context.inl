@@ -10,6 +10,7 @@ struct sp_matcher_ctx
 	// configuration
 	SpArenaCaps cap;		// arena capacities of the first round (grown by 4 for documents that overflow)
 	uint32_t warps_per_sm;
+	uint32_t cap_growths;
 	uint64_t arena_budget;		// bytes of HBM the arenas may take
 	int nsm;
 	// device buffers (grow only)
@@ -26,7 +27,7 @@ struct sp_matcher_ctx
 	bool profile;
 
 	sp_matcher_ctx( sp_matcher* m_, cudaStream_t stream_)
-		:m(m_),stream(stream_),warps_per_sm(16),arena_budget(0),nsm(0),res_per_token(0.5),items_per_token(1.0)
+		:m(m_),stream(stream_),warps_per_sm(16),cap_growths(0),arena_budget(0),nsm(0),res_per_token(0.5),items_per_token(1.0)
 		,ndocs(0),ntokens(0),nres(0),nitems(0),retries(0),pool_retries(0),launches(0),valid(false),pinned(0),ev_a(0),ev_b(0)
 		,kernel_ms(0.0),kernel_calls(0),profile(false)
 	{
@@ -93,6 +94,7 @@ struct sp_matcher_ctx
 			SpArenaCaps curcap = cap;
 			uint32_t* d_list = 0; uint32_t nlist = 0;
 			bool flip = false;
+			uint32_t retry_docs = 0;
 			for (int round=0;; ++round)
 			{
 				if (round > 12) throw std::runtime_error( "matcher arenas keep overflowing (rule set too large for the device memory)");
@@ -144,7 +146,10 @@ struct sp_matcher_ctx
 				curcap.rules *= 4; curcap.triggers *= 4; curcap.items *= 4; curcap.datarefs *= 4;
 				curcap.results *= 4; curcap.follow *= 4; curcap.dispose *= 4; curcap.heap *= 4;
 				d_list = d_newlist; nlist = listcount; flip = !flip;
+				retry_docs = std::max( retry_docs, listcount);
 			}
+			// documents of the next batch will look like these: start with the arenas that were needed (two growth steps at most)
+			if (curcap.rules > cap.rules && cap_growths < 2 && (uint64_t)retry_docs * 50 >= ndocs) {cap = curcap; ++cap_growths;}
 			if (ntokens)
 			{
 				res_per_token = std::max( 0.01, (double)nres / (double)ntokens);
