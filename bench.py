@@ -123,7 +123,7 @@ def cpu_lexer_rate(text, offs, seconds_target, nthreads):
 
 
 KERNELS = ["k_lex_count", "k_lex_verify", "k_lex_emit", "k_lex_finish", "k_lex_resolve", "k_lex_write", "k_scan",
-           "k_isl_flags", "k_isl_resolve", "k_ordpos"]
+           "k_isl_flags", "k_isl_resolve", "k_ordpos", "k_isl_slots", "k_slot_scan"]
 
 
 def algorithmic_bytes(kernel, c):
@@ -141,6 +141,9 @@ def algorithmic_bytes(kernel, c):
         "k_isl_flags": 20 * nev + nev + 4 * c.get("islands", 0),       # events + document ids read, flags + island starts written
         "k_isl_resolve": 2 * 20 * nev + 20 * c.get("elements", 0),    # events read by both passes, dense elements written
         "k_ordpos": 20 * c.get("elements", 0) + 16 * nlex,           # dense elements read once, lexem records written
+        # slot pipeline (default): events + document ids read once, one 16 B slot per event written; slots read once, lexems written
+        "k_isl_slots": 20 * nev + 16 * nev * c.get("ar_mult", 1),
+        "k_slot_scan": 16 * nev * c.get("ar_mult", 1) + 16 * nlex + 16 * ndocs,
     }[kernel]
 
 
@@ -190,14 +193,15 @@ def run_ours(args, rank, world, local_rank):
         torch.cuda.synchronize()
 
     # ---- device resident
+    sampler = ClockSampler(local_rank)
+    sampler.start()
     for _ in range(args.warmup):
         ctx.launch(dev_text.data_ptr(), offs, on_device=True)
         ctx.count()
     counters = {k: ctx.counter(k) for k in ("raw_events", "lexems", "chunks", "fixup_chunks", "fixup_rounds", "text_bytes", "kernel_launches", "islands", "elements")}
     counters["ndocs"] = ndocs
+    counters["ar_mult"] = 2 if lx.table_info("symbols") else 1
     ctx.counter("profile:on"); ctx.counter("profile:reset")
-    sampler = ClockSampler(local_rank)
-    sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()

@@ -11,7 +11,8 @@ struct sp_lexer_ctx
 	DeviceBuffer text, doc_off, start_state, end_state, ev_count, known, redo, scalars, ev_off, events, doc_ev_begin,
 		     ar, doc_kept, doc_nlex, lex_off, lexems, status, scantmp,
 		     ev_doc, isl_flags, tile_nisl, tile_isl_off, isl_start, isl_kept, isl_off, elem, elem_doc, doc_has_content,
-		     doc_elem_begin, aggmax, aggmin, aggord;
+		     doc_elem_begin, aggmax, aggmin, aggord, slots, doc_first_content, fix_list, doc_base;
+	bool dense;		// SP_LEXER_DENSE=1: first island pipeline (two resolution passes, dense elements, three scans)
 	bool sequential;	// SP_LEXER_SEQUENTIAL=1: one thread per document for resolution and ordinal positions (A/B check)
 	uint64_t nisl, nelem;
 	// last batch
@@ -20,7 +21,7 @@ struct sp_lexer_ctx
 	bool valid;
 	uint64_t* pinned;	// [4] host staging for scalar read backs
 	// optional per kernel timing with CUDA events on the context's stream (SP_LEXER_PROFILE=1 or counter "profile:on")
-	enum KernelId {KCount, KVerify, KEmit, KFinish, KResolve, KWrite, KScan, KIslFlags, KIslResolve, KOrdpos, NofKernelIds};
+	enum KernelId {KCount, KVerify, KEmit, KFinish, KResolve, KWrite, KScan, KIslFlags, KIslResolve, KOrdpos, KIslSlots, KSlotScan, NofKernelIds};
 	struct Span {int kernel; cudaEvent_t a, b;};
 	bool profile;
 	std::vector<Span> spans;
@@ -62,6 +63,7 @@ struct sp_lexer_ctx
 		std::memset( kernel_ms, 0, sizeof(kernel_ms)); std::memset( kernel_calls, 0, sizeof(kernel_calls));
 		if (std::getenv( "SP_LEXER_PROFILE")) profile = true;
 		sequential = std::getenv( "SP_LEXER_SEQUENTIAL") != 0;
+		dense = std::getenv( "SP_LEXER_DENSE") != 0;
 		nisl = nelem = 0;
 		const char* e;
 		if ((e = std::getenv( "SP_LEXER_CHUNK")) != 0 && std::atoi( e) >= 16) chunk = (uint32_t)std::atoi( e);
@@ -82,6 +84,85 @@ struct sp_lexer_ctx
 		return pinned[0];
 	}
 
+
+
+	// Island discovery shared by both island pipelines: flags, per tile counts, island start list. Returns nisl.
+	uint64_t findIslands( IslandParams& Q)
+	{
+		uint64_t ntiles = (nev + TsTile - 1) / TsTile;
+		Q.flags = isl_flags.as<uint8_t>( nev);
+		Q.tile_nisl = tile_nisl.as<uint32_t>( ntiles);
+		uint64_t* d_tile_isl_off = tile_isl_off.as<uint64_t>( ntiles + 1);
+		Q.tile_isl_off = d_tile_isl_off;
+		uint64_t* d_aggmax = aggmax.as<uint64_t>( ntiles); uint64_t* d_aggmin = aggmin.as<uint64_t>( ntiles);
+		spanBegin( KIslFlags);
+		k_isl_reduce<<<(unsigned int)ntiles, TsThreads, 0, stream>>>( Q, d_aggmax, d_aggmin);
+		k_tile_carry<OpMax><<<1, 1024, 0, stream>>>( d_aggmax, ntiles, 0, (uint64_t*)0);
+		k_tile_carry<OpMin><<<1, 1024, 0, stream>>>( d_aggmin, ntiles, 1, (uint64_t*)0);
+		k_isl_flags<<<(unsigned int)ntiles, TsThreads, 0, stream>>>( Q, d_aggmax, d_aggmin);
+		exclusiveScan( Q.tile_nisl, ntiles, d_tile_isl_off, scantmp, stream);
+		spanEnd();
+		uint64_t n = readScalar( d_tile_isl_off + ntiles, sizeof(uint64_t));
+		Q.nisl = n;
+		Q.isl_start = isl_start.as<uint32_t>( n + 1);
+		spanBegin( KIslFlags); k_isl_compact<<<(unsigned int)ntiles, TsThreads, 0, stream>>>( Q); spanEnd();
+		return n;
+	}
+
+	// slot pipeline (lexer_islands.cuh): one resolution pass per island + one sum scan over the slots
+	void resolveSlots( const SpScanParams& P, uint64_t* d_lex_off)
+	{
+		nisl = nelem = nlex = 0;
+		SP_CUDA( cudaMemsetAsync( P.status, 0, (std::size_t)ndocs * sizeof(uint32_t) + 4, stream));
+		if (!nev)
+		{
+			SP_CUDA( cudaMemsetAsync( d_lex_off, 0, ((std::size_t)ndocs + 1) * sizeof(uint64_t), stream));
+			(void)lexems.as<sp_lexem>( 1);
+			return;
+		}
+		const uint64_t nslots = nev * P.ar_mult;
+		if (nslots >= 0xFFFFFFFFull) throw std::runtime_error( "batch too large: more than 2^32 event slots (split the batch)");
+		IslandParams Q; std::memset( &Q, 0, sizeof(Q));
+		Q.T = P.T; Q.events = P.events; Q.ev_doc = P.ev_doc; Q.nev = nev; Q.ndocs = ndocs; Q.ar_mult = P.ar_mult;
+		nisl = findIslands( Q);
+		SpSlotParams S; std::memset( &S, 0, sizeof(S));
+		S.T = P.T; S.events = P.events; S.ev_doc = P.ev_doc; S.nev = nev; S.ar_mult = P.ar_mult;
+		S.slots = slots.as<SpSlot>( nslots);
+		S.isl_start = Q.isl_start; S.nisl = nisl;
+		S.doc_status = P.status;
+		S.doc_has_content = doc_has_content.as<uint8_t>( ndocs);
+		S.doc_first_content = doc_first_content.as<uint32_t>( ndocs);
+		S.fix_list = fix_list.as<uint32_t>( nisl);
+		uint64_t* d_scalars = (uint64_t*)scalars.ptr();
+		S.fix_count = reinterpret_cast<uint32_t*>( d_scalars + 2);
+		S.doc_ev_begin = P.doc_ev_begin; S.ndocs = ndocs;
+		S.doc_base = doc_base.as<uint64_t>( (std::size_t)ndocs + 1);
+		S.lex_off = d_lex_off;
+		SP_CUDA( cudaMemsetAsync( S.doc_has_content, 0, (std::size_t)ndocs + 1, stream));
+		SP_CUDA( cudaMemsetAsync( S.doc_first_content, 0xFF, ((std::size_t)ndocs + 1) * sizeof(uint32_t), stream));
+		SP_CUDA( cudaMemsetAsync( d_scalars + 1, 0, 2 * sizeof(uint64_t), stream));
+		spanBegin( KIslSlots);
+		k_isl_to_slots<<<(unsigned int)((nisl + 127) / 128), 128, 0, stream>>>( S);
+		k_isl_fix<<<64, 128, 0, stream>>>( S);
+		spanEnd();
+		// the output holds at most one lexem per slot; its exact size is known after the carry step, so the lexem
+		// buffer is sized by the number of valid slots' upper bound (nslots) only when it has to grow
+		uint64_t ntiles = (nslots + TsTile - 1) / TsTile;
+		uint64_t* d_agg = aggord.as<uint64_t>( ntiles);
+		SlotScan f; f.P = S;
+		spanBegin( KSlotScan);
+		k_tile_reduce<SlotScan><<<(unsigned int)ntiles, TsThreads, 0, stream>>>( f, nslots, d_agg);
+		k_tile_carry<OpSum><<<1, 1024, 0, stream>>>( d_agg, ntiles, 0, d_scalars + 1);
+		spanEnd();
+		nlex = readScalar( d_scalars + 1, sizeof(uint64_t)) >> 32;
+		S.lexems = lexems.as<sp_lexem>( nlex);
+		f.P = S;
+		spanBegin( KSlotScan);
+		k_doc_bases<<<(ndocs + 1 + 7) / 8, 256, 0, stream>>>( S, d_agg, d_scalars + 1);
+		k_tile_apply<SlotScan><<<(unsigned int)ntiles, TsThreads, 0, stream>>>( f, nslots, d_agg);
+		spanEnd();
+		SP_CUDA( cudaGetLastError());
+	}
 
 	// island-parallel resolution + scan based ordinal positions (lexer_islands.cuh)
 	void resolveIslands( const SpScanParams& P, uint64_t* d_lex_off)
@@ -241,7 +322,8 @@ struct sp_lexer_ctx
 				spanBegin( KWrite); k_lex_write<<<grid, LexDocThreads, 0, stream>>>( P); spanEnd();
 			}
 		}
-		else resolveIslands( P, d_lex_off);
+		else if (dense) resolveIslands( P, d_lex_off);
+		else resolveSlots( P, d_lex_off);
 		SP_CUDA( cudaGetLastError());
 		valid = true;
 	}
@@ -299,7 +381,7 @@ int64_t sp_lexer_ctx_counter( sp_lexer_ctx* ctx, const char* key)
 	if (k == "profile:reset") {std::memset( ctx->kernel_ms, 0, sizeof(ctx->kernel_ms)); std::memset( ctx->kernel_calls, 0, sizeof(ctx->kernel_calls)); return 0;}
 	if (k.compare( 0, 8, "time_us:") == 0 || k.compare( 0, 6, "calls:") == 0)
 	{
-		static const char* names[] = {"k_lex_count","k_lex_verify","k_lex_emit","k_lex_finish","k_lex_resolve","k_lex_write","k_scan","k_isl_flags","k_isl_resolve","k_ordpos"};
+		static const char* names[] = {"k_lex_count","k_lex_verify","k_lex_emit","k_lex_finish","k_lex_resolve","k_lex_write","k_scan","k_isl_flags","k_isl_resolve","k_ordpos","k_isl_slots","k_slot_scan"};
 		if (cudaStreamSynchronize( ctx->stream) != cudaSuccess) return -1;
 		try {ctx->collectSpans();} catch (...) {return -1;}
 		bool calls = k[0] == 'c';
@@ -310,7 +392,14 @@ int64_t sp_lexer_ctx_counter( sp_lexer_ctx* ctx, const char* key)
 		}
 		return -1;
 	}
-	if (k == "kernel_launches") return (int64_t)(ctx->sequential ? (1 + 2*ctx->rounds + 1 + 3 + 1 + 1 + 1 + 3 + 1) : (1 + 2*ctx->rounds + 1 + 3 + 1 + 1 + 4 + 3 + 1 + 1 + 3 + 1 + 9 + 1));
+	if (k == "kernel_launches")
+	{
+		// count, verify (+2 per repair round), 3 scan, emit, finish; then the chosen second half
+		int64_t first = 1 + 1 + 2*(int64_t)ctx->rounds + 3 + 1 + 1;
+		if (ctx->sequential) return first + 1 + 3 + 1;
+		if (ctx->dense) return first + 8 + 1 + 3 + 1 + 9 + 1;
+		return first + 8 + 2 + 2 + 2;
+	}
 	return -1;
 }
 

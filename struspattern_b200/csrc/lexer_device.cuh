@@ -561,4 +561,183 @@ SP_HD bool sp_ord_decide( uint32_t bind, bool counts, uint32_t cnt, uint32_t& or
 	}
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// Slot formulation of the second half of the pipeline (DESIGN.md "lexer pipeline", steps 7-8): every island is
+// resolved ONCE and its kept elements are written into the island's own slot range [eb*M, ee*M) (M = ar_mult;
+// an island never keeps more than M elements per event), unused slots are marked empty. The decisions of the
+// ordinal position passes that only need the island are taken right there:
+//   COUNTS  the element can advance the position (BindContent, or BindUnique not behind a BindUnique; :926-934)
+//   INC     it does advance it: its start lies behind every counting element in front of it. Elements of earlier
+//           islands of the document start strictly in front of this island's first event, so the running
+//           maximum is seeded with that start and no scan over the document is needed.
+// One sum scan over the slots (low word: INC, high word: emitted) then yields ordinal positions and output indices.
+typedef struct SpSlot
+{
+	uint32_t id;
+	uint32_t origpos;
+	uint32_t info;		/* origsize (16 bit) | bind << 16 | SP_SLOT_* flags */
+	uint32_t doc;
+} SpSlot;
+
+#define SP_SLOT_VALID  0x01000000u
+#define SP_SLOT_COUNTS 0x02000000u
+#define SP_SLOT_INC    0x04000000u
+#define SP_SLOT_BIND( info) (((info) >> 16) & 0xFF)
+#define SP_NO_SLOT 0xFFFFFFFFu
+
+#ifdef __CUDACC__
+#define SP_ATOMIC_MIN( ptr, val) atomicMin( (ptr), (val))
+#else
+#define SP_ATOMIC_MIN( ptr, val) do {if ((val) < *(ptr)) *(ptr) = (val);} while (0)
+#endif
+
+// COUNTS/INC flags of the elements of one island, one element after the other. prevBind: bind of the element in
+// front of the island in the same document (SP_BIND_CONTENT if there is none); minStart: smallest event start of the island.
+typedef struct SpFlagState
+{
+	uint32_t prevBind, mx, ncounting;
+} SpFlagState;
+
+SP_HD void sp_flags_begin( SpFlagState& st, uint32_t prevBind, uint32_t minStart)
+{
+	st.prevBind = prevBind; st.mx = minStart; st.ncounting = 0;	// keys are origpos+1; earlier islands hold keys <= minStart
+}
+SP_HD uint32_t sp_flags_next( SpFlagState& st, uint32_t bind, uint32_t origpos)
+{
+	uint32_t f = SP_SLOT_VALID;
+	if (bind == SP_BIND_CONTENT || (bind == SP_BIND_UNIQUE && st.prevBind != SP_BIND_UNIQUE))
+	{
+		f |= SP_SLOT_COUNTS;
+		st.ncounting += 1;
+		if (origpos + 1 > st.mx) {st.mx = origpos + 1; f |= SP_SLOT_INC;}
+	}
+	st.prevBind = bind;
+	return f;
+}
+
+typedef struct SpSlotParams
+{
+	SpLexerTables T;
+	const SpRawEvent* events;
+	const uint32_t* ev_doc;
+	uint64_t nev;
+	uint32_t ar_mult;
+	SpSlot* slots;			/* [nev*ar_mult] */
+	const uint32_t* isl_start;	/* [nisl+1] */
+	uint64_t nisl;
+	uint32_t* doc_status;		/* [ndocs] */
+	uint8_t* doc_has_content;	/* [ndocs] */
+	uint32_t* doc_first_content;	/* [ndocs] slot of the first counting element (SP_NO_SLOT = none) */
+	uint32_t* fix_list;		/* islands whose first element is BindUnique: flags depend on the element in front */
+	uint32_t* fix_count;
+	const uint64_t* doc_ev_begin;	/* [ndocs+1] */
+	uint32_t ndocs;
+	uint64_t* doc_base;		/* [ndocs+1] scan value in front of the first slot of every document */
+	sp_lexem* lexems;
+	uint64_t* lex_off;		/* [ndocs+1] */
+} SpSlotParams;
+
+// Resolves island i into its slots. `ar` is a work array of (ee-eb)*M elements: thread local memory, or the slot
+// range of the island itself (same record size; element k is read before slot k is written).
+// Returns 1 if the island goes on the fix list.
+SP_HD int sp_island_to_slots( const SpSlotParams& P, uint64_t i, SpMatchEvent* ar)
+{
+	const uint64_t eb = P.isl_start[ i], ee = P.isl_start[ i+1];
+	const uint32_t doc = P.ev_doc[ eb], M = P.ar_mult;
+	uint32_t n = 0, minStart = SP_NO_POS;
+	for (uint64_t e=eb; e<ee; ++e)
+	{
+		SpRawEvent ev = P.events[ e];
+		if (ev.pat == SP_PAT_DROPPED) continue;
+		if (ev.pat == SP_PAT_SIZEERROR) {P.doc_status[ doc] = (uint32_t)-SP_ERR_RUNTIME; continue;}
+		if (ev.from < minStart) minStart = ev.from;
+		sp_supersede( P.T, ev, ar, n);
+	}
+	if (minStart == SP_NO_POS) minStart = 0;
+	SpSlot* out = P.slots + eb * M;
+	const uint32_t cap = (uint32_t)(ee - eb) * M;
+	SpFlagState st; sp_flags_begin( st, SP_BIND_CONTENT, minStart);
+	uint32_t first = SP_NO_SLOT, firstBind = SP_BIND_CONTENT;
+	for (uint32_t k=0; k<cap; ++k)
+	{
+		SpSlot s; s.id = 0; s.origpos = 0; s.info = 0; s.doc = doc;
+		if (k < n)
+		{
+			SpMatchEvent e = ar[ k];
+			uint32_t bind = SP_META_BIND( e.meta);
+			if (k == 0) firstBind = bind;
+			uint32_t f = sp_flags_next( st, bind, e.origpos);
+			if ((f & SP_SLOT_COUNTS) && first == SP_NO_SLOT) first = k;
+			s.id = e.id; s.origpos = e.origpos; s.info = (e.origsize & 0xFFFFu) | (bind << 16) | f;
+		}
+		out[ k] = s;
+	}
+	if (first != SP_NO_SLOT)
+	{
+		// most islands lose against an earlier one: look before the atomic (the value only ever decreases)
+		uint32_t cand = (uint32_t)(eb * M) + first;
+		if (!P.doc_has_content[ doc]) P.doc_has_content[ doc] = 1;
+		if (cand < P.doc_first_content[ doc]) SP_ATOMIC_MIN( P.doc_first_content + doc, cand);
+	}
+	// a leading BindUnique element is dropped if the element in front of the island is BindUnique too
+	bool firstOfDoc = (eb == 0 || P.ev_doc[ eb-1] != doc);
+	return (n && !firstOfDoc && firstBind == SP_BIND_UNIQUE) ? 1 : 0;
+}
+
+// Second look at an island that starts with a BindUnique element: bind of the last valid slot in front of it.
+SP_HD void sp_island_fix_unique( const SpSlotParams& P, uint64_t i)
+{
+	const uint64_t eb = P.isl_start[ i], ee = P.isl_start[ i+1];
+	const uint32_t M = P.ar_mult, doc = P.ev_doc[ eb];
+	uint64_t s = eb * M;
+	uint32_t prevBind = SP_BIND_CONTENT;
+	while (s > 0)
+	{
+		SpSlot prev = P.slots[ s-1];
+		if (prev.doc != doc) break;
+		if (prev.info & SP_SLOT_VALID) {prevBind = SP_SLOT_BIND( prev.info); break;}
+		--s;
+	}
+	if (prevBind != SP_BIND_UNIQUE) return;
+	SpSlot* slots = P.slots + eb * M;
+	const uint32_t cap = (uint32_t)(ee - eb) * M;
+	uint32_t minStart = SP_NO_POS;
+	for (uint64_t e=eb; e<ee; ++e) {SpRawEvent ev = P.events[ e]; if (ev.pat < SP_PAT_SIZEERROR && ev.from < minStart) minStart = ev.from;}
+	if (minStart == SP_NO_POS) minStart = 0;
+	SpFlagState st; sp_flags_begin( st, prevBind, minStart);
+	for (uint32_t k=0; k<cap && (slots[ k].info & SP_SLOT_VALID); ++k)
+	{
+		uint32_t info = slots[ k].info;
+		slots[ k].info = (info & 0x00FFFFFFu) | sp_flags_next( st, SP_SLOT_BIND( info), slots[ k].origpos);
+	}
+}
+
+// Scan value of slot j: low word 1 if the position advances here, high word 1 if the element is part of the output.
+SP_HD uint64_t sp_slot_value( const SpSlotParams& P, uint64_t j, const SpSlot& s)
+{
+	if (!(s.info & SP_SLOT_VALID)) return 0;
+	uint64_t v = (s.info & SP_SLOT_INC) ? 1 : 0;
+	if (SP_LDG( P.doc_status + s.doc) || !SP_LDG( P.doc_has_content + s.doc)) return v;
+	bool emit;
+	switch (SP_SLOT_BIND( s.info))
+	{
+		case SP_BIND_CONTENT: emit = true; break;
+		case SP_BIND_UNIQUE: emit = (s.info & SP_SLOT_COUNTS) != 0; break;
+		case SP_BIND_SUCCESSOR: emit = true; break;
+		default: emit = j > SP_LDG( P.doc_first_content + s.doc); break;	// BindPredecessor: dropped in front of the first content element
+	}
+	return emit ? (v | (1ull << 32)) : v;
+}
+
+// Writes the lexem of slot j given the exclusive scan value in front of it.
+SP_HD void sp_slot_emit( const SpSlotParams& P, uint64_t j, const SpSlot& s, uint64_t excl, uint64_t value)
+{
+	if (!(value >> 32)) return;
+	uint32_t cnt = (uint32_t)(excl + value) - (uint32_t)SP_LDG( P.doc_base + s.doc);	// positions advanced in the document up to here
+	sp_lexem lx; lx.id = s.id; lx.origpos = s.origpos; lx.origsize = s.info & 0xFFFFu;
+	lx.ordpos = (SP_SLOT_BIND( s.info) == SP_BIND_SUCCESSOR) ? cnt + 1 : cnt;
+	P.lexems[ excl >> 32] = lx;
+}
+
 #endif

@@ -247,5 +247,69 @@ static __global__ void k_ord_tail( IslandParams P, const uint64_t* total)
 	if (d <= P.ndocs && P.doc_elem_begin[ d] >= P.nelem) P.lex_off[ d] = *total;
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// Slot pipeline (lexer_device.cuh "slot formulation"): one resolution pass per island, one sum scan over the slots.
+//   k_isl_to_slots  one thread per island: supersede logic, COUNTS/INC flags, slot records; lists the islands whose
+//                   first element is BindUnique
+//   k_isl_fix       the listed islands look at the element in front of them (rare)
+//   SlotScan        tile reduce / carry / apply over the slots: low word positions advanced, high word elements emitted
+//   k_doc_bases     scan value in front of the first slot of every document -> ordinal position base, lexem offsets
+static __global__ void __launch_bounds__(128) k_isl_to_slots( SpSlotParams P)
+{
+	uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= P.nisl) return;
+	uint64_t eb = P.isl_start[ i], ee = P.isl_start[ i+1];
+	SpMatchEvent local[ SP_ISLAND_LOCAL];
+	// oversized islands work in their own slot range (HBM) instead of thread local memory
+	SpMatchEvent* ar = ((ee - eb) * P.ar_mult <= SP_ISLAND_LOCAL) ? local : reinterpret_cast<SpMatchEvent*>( P.slots + eb * P.ar_mult);
+	if (sp_island_to_slots( P, i, ar)) P.fix_list[ atomicAdd( P.fix_count, 1u)] = (uint32_t)i;
+}
+
+static __global__ void __launch_bounds__(128) k_isl_fix( SpSlotParams P)
+{
+	const uint32_t nfix = *P.fix_count;
+	for (uint32_t f = blockIdx.x * blockDim.x + threadIdx.x; f < nfix; f += gridDim.x * blockDim.x) sp_island_fix_unique( P, P.fix_list[ f]);
+}
+
+struct SlotScan
+{
+	typedef OpSum Op;
+	SpSlotParams P;
+	__device__ uint64_t load( uint64_t j) const
+	{
+		SpSlot s = reinterpret_cast<const SpSlot*>( P.slots)[ j];
+		return sp_slot_value( P, j, s);
+	}
+	__device__ void store( uint64_t j, uint64_t excl, uint64_t incl) const
+	{
+		uint64_t value = incl - excl;
+		if (!(value >> 32)) return;
+		SpSlot s = P.slots[ j];
+		sp_slot_emit( P, j, s, excl, value);
+	}
+};
+
+static __global__ void __launch_bounds__(256) k_doc_bases( SpSlotParams P, const uint64_t* carry, const uint64_t* total)
+{
+	const unsigned int lane = threadIdx.x & 31;
+	const uint32_t d = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	if (d > P.ndocs) return;
+	const uint64_t nslots = P.nev * P.ar_mult;
+	const uint64_t fs = P.doc_ev_begin[ d] * P.ar_mult;
+	uint64_t base;
+	if (fs >= nslots) base = *total;
+	else
+	{
+		const uint64_t tile = fs / TsTile;
+		uint64_t sum = 0;
+		for (uint64_t j = tile * TsTile + lane; j < fs; j += 32) sum += sp_slot_value( P, j, P.slots[ j]);
+		#pragma unroll
+		for (int ofs=16; ofs>0; ofs>>=1) sum += __shfl_down_sync( 0xFFFFFFFFu, sum, ofs);
+		base = carry[ tile] + __shfl_sync( 0xFFFFFFFFu, sum, 0);
+	}
+	if (lane == 0) {P.doc_base[ d] = base; P.lex_off[ d] = base >> 32;}
+}
+
 } // namespace sp
 #endif

@@ -21,6 +21,9 @@ struct HostSim
 	std::vector<SpRawEvent> events;
 	std::vector<uint64_t> doc_ev_begin;
 	uint64_t fixups, rounds;
+	int mode;	// 0: one loop per document (reference order), 1: island + slot formulation
+	uint64_t nislands, nfixed;
+	HostSim() :fixups(0),rounds(0),mode(0),nislands(0),nfixed(0){}
 };
 }
 
@@ -41,6 +44,7 @@ int hsim_define_lexem( void* h, uint32_t id, const char* expr, size_t exprlen, u
 int hsim_define_symbol( void* h, uint32_t symbolid, uint32_t lexemid, const char* name, size_t namelen)
 	{HSIM_TRY( hs->prog.defineSymbol( symbolid, lexemid, std::string( name, namelen)))}
 int hsim_compile( void* h) {HSIM_TRY( hs->prog.compile())}
+int hsim_set_mode( void* h, int mode) {((HostSim*)h)->mode = mode; return 0;}
 int64_t hsim_info( void* h, const char* key)
 {
 	HostSim* hs = (HostSim*)h;
@@ -51,6 +55,8 @@ int64_t hsim_info( void* h, const char* key)
 	if (k == "fixups") return (int64_t)hs->fixups;
 	if (k == "rounds") return (int64_t)hs->rounds;
 	if (k == "raw_events") return (int64_t)hs->events.size();
+	if (k == "islands") return (int64_t)hs->nislands;
+	if (k == "fixed_islands") return (int64_t)hs->nfixed;
 	return -1;
 }
 
@@ -96,12 +102,66 @@ int hsim_scan_batch( void* h, const uint8_t* text, const uint64_t* doc_off, uint
 	hs->status.assign( ndocs, 0);
 	uint32_t dummy = 0;
 	P.ar = ar.data(); P.doc_kept = doc_kept.data(); P.doc_nlex = doc_nlex.data(); P.status = ndocs ? hs->status.data() : &dummy;
-	for (uint32_t d=0; d<ndocs; ++d) spk_resolve_doc( P, d);
-	for (uint32_t d=0; d<ndocs; ++d) lex_off[ d+1] = lex_off[ d] + doc_nlex[ d];
-	hs->lexems.assign( lex_off[ ndocs] + 1, sp_lexem());
-	P.lex_off = lex_off.data(); P.lexems = hs->lexems.data();
-	for (uint32_t d=0; d<ndocs; ++d) spk_write_doc( P, d);
-	hs->lexems.resize( lex_off[ ndocs]);
+	if (hs->mode == 0)
+	{
+		for (uint32_t d=0; d<ndocs; ++d) spk_resolve_doc( P, d);
+		for (uint32_t d=0; d<ndocs; ++d) lex_off[ d+1] = lex_off[ d] + doc_nlex[ d];
+		hs->lexems.assign( lex_off[ ndocs] + 1, sp_lexem());
+		P.lex_off = lex_off.data(); P.lexems = hs->lexems.data();
+		for (uint32_t d=0; d<ndocs; ++d) spk_write_doc( P, d);
+		hs->lexems.resize( lex_off[ ndocs]);
+	}
+	else
+	{
+		// the slot pipeline of lexer_islands.cuh as plain loops (same per-thread functions)
+		std::vector<uint32_t> ev_doc( nev + 1);
+		for (uint32_t d=0; d<ndocs; ++d) for (uint64_t e=hs->doc_ev_begin[ d]; e<hs->doc_ev_begin[ d+1]; ++e) ev_doc[ e] = d;
+		std::vector<uint64_t> sufmin( nev + 1, ~0ull);
+		for (uint64_t k=nev; k>0; --k) {uint64_t lo = sp_event_lo_key( hs->events[ k-1], ev_doc[ k-1]); sufmin[ k-1] = lo < sufmin[ k] ? lo : sufmin[ k];}
+		std::vector<uint32_t> isl_start;
+		uint64_t premax = 0;
+		for (uint64_t k=0; k<nev; ++k)
+		{
+			if (sufmin[ k] >= premax) isl_start.push_back( (uint32_t)k);
+			uint64_t r = sp_event_r_key( hs->events[ k], ev_doc[ k]);
+			if (r > premax) premax = r;
+		}
+		uint64_t nisl = isl_start.size();
+		isl_start.push_back( (uint32_t)nev);
+		hs->nislands = nisl; hs->nfixed = 0;
+		const uint64_t nslots = nev * P.ar_mult;
+		std::vector<SpSlot> slots( nslots + 1);
+		std::vector<uint8_t> has_content( ndocs + 1, 0);
+		std::vector<uint32_t> first_content( ndocs + 1, SP_NO_SLOT), fix_list;
+		std::vector<uint64_t> doc_base( ndocs + 1, 0);
+		SpSlotParams S; std::memset( &S, 0, sizeof(S));
+		S.T = P.T; S.events = hs->events.data(); S.ev_doc = ev_doc.data(); S.nev = nev; S.ar_mult = P.ar_mult;
+		S.slots = slots.data(); S.isl_start = isl_start.data(); S.nisl = nisl;
+		S.doc_status = P.status; S.doc_has_content = has_content.data(); S.doc_first_content = first_content.data();
+		S.doc_ev_begin = hs->doc_ev_begin.data(); S.ndocs = ndocs; S.doc_base = doc_base.data(); S.lex_off = lex_off.data();
+		for (uint64_t i=0; i<nisl; ++i)
+		{
+			uint64_t cap = (uint64_t)(isl_start[ i+1] - isl_start[ i]) * P.ar_mult;
+			SpMatchEvent local[ SP_ISLAND_LOCAL];
+			// small islands in "thread local" memory, oversized ones in their own slot range, like the kernel
+			SpMatchEvent* work = cap <= SP_ISLAND_LOCAL ? local : reinterpret_cast<SpMatchEvent*>( slots.data() + (uint64_t)isl_start[ i] * P.ar_mult);
+			if (sp_island_to_slots( S, i, work)) fix_list.push_back( (uint32_t)i);
+		}
+		for (uint32_t i: fix_list) sp_island_fix_unique( S, i);
+		hs->nfixed = fix_list.size();
+		std::vector<uint64_t> excl( nslots + 1, 0);
+		for (uint64_t j=0; j<nslots; ++j) excl[ j+1] = excl[ j] + sp_slot_value( S, j, slots[ j]);
+		for (uint32_t d=0; d<=ndocs; ++d)
+		{
+			uint64_t fs = hs->doc_ev_begin[ d] * P.ar_mult;
+			doc_base[ d] = excl[ fs < nslots ? fs : nslots];
+			lex_off[ d] = doc_base[ d] >> 32;
+		}
+		hs->lexems.assign( (excl[ nslots] >> 32) + 1, sp_lexem());
+		S.lexems = hs->lexems.data();
+		for (uint64_t j=0; j<nslots; ++j) sp_slot_emit( S, j, slots[ j], excl[ j], excl[ j+1] - excl[ j]);
+		hs->lexems.resize( excl[ nslots] >> 32);
+	}
 	hs->offsets = lex_off;
 	return 0;
 }

@@ -88,3 +88,45 @@ def test_double_insert_quirk_and_symbols():
     lx.define_symbol(9, 2, "a b c")
     lx.compile()
     assert lx.match("a b c") == [(1, 1, 0, 1), (2, 1, 0, 5), (9, 1, 0, 5), (0, 1, 0, 0), (1, 2, 4, 1)]
+
+
+def test_unique_elements_across_islands_and_all_three_formulations(monkeypatch):
+    """BindUnique behind BindUnique across island borders; the three second halves of the pipeline (per document
+    loop, dense island pipeline, slot pipeline = default) must give the oracle's output."""
+    defs = [(1, r"x+", 0, 0, 3), (2, r"[a-w]+", 0, 0, 0), (3, r"#", 0, 0, 1), (4, r"[.,]", 0, 0, 2), (5, r"y", 0, 1, 3)]
+    rng = np.random.default_rng(3)
+    docs = []
+    for _ in range(400):
+        toks = rng.choice(["x", "xx", "y", "ab", "#", ".", ",", "q"], size=int(rng.integers(0, 200)), p=[0.3, 0.1, 0.15, 0.15, 0.1, 0.08, 0.07, 0.05])
+        docs.append(" ".join(toks).encode())
+    docs += [b"x x x", b". x", b"# . # x x y y ab", b"x", b""]
+    offs = np.cumsum([0] + [len(d) for d in docs]).astype(np.uint64)
+    text = np.frombuffer(b"".join(docs), dtype=np.uint8)
+    o, g = OracleLexer(), _gpu_lexer()()
+    for lx in (o, g):
+        for d in defs:
+            lx.define_lexem(*d)
+        lx.compile()
+    ro = o.scan(text, offs, nthreads=8)
+    for env in (None, "SP_LEXER_DENSE", "SP_LEXER_SEQUENTIAL"):
+        if env:
+            monkeypatch.setenv(env, "1")
+        ctx = g.create_context()
+        _same(ro, ctx.scan(text, offs))
+        ctx.close()
+        if env:
+            monkeypatch.delenv(env)
+
+
+def test_large_islands_use_their_slot_range():
+    # one long chain of overlapping matches = one island far larger than the thread local array
+    defs = [(1, r"[a-z]+ [a-z]+", 0, 1, 0), (2, r"[a-z]+", 0, 0, 0), (3, r"[a-z]+ [a-z]+ [a-z]+", 0, 2, 0)]
+    o, g = OracleLexer(), _gpu_lexer()()
+    for lx in (o, g):
+        for d in defs:
+            lx.define_lexem(*d)
+        lx.define_symbol(77, 2, "ab")
+        lx.compile()
+    text = (b"ab cd ef gh " * 40 + b". ") * 20
+    offs = [0, len(text) // 2 + 3, len(text)]
+    _same(o.scan(text, offs), g.scan(text, offs))

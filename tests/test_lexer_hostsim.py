@@ -105,3 +105,36 @@ def test_compile_errors_and_state_errors():
     lx.compile()
     with pytest.raises(RuntimeError):
         lx.define_lexem(2, "b")  # src/patternLexer.cpp:999-1002
+
+
+def test_unique_elements_across_islands_and_both_formulations():
+    """BindUnique behind BindUnique is dropped (src/patternLexer.cpp:926-929) even when the two sit in different
+    islands; the per-document loop (mode 0) and the island/slot formulation (mode 1) must agree with the oracle."""
+    defs = [(1, r"x+", 0, 0, 3), (2, r"[a-w]+", 0, 0, 0), (3, r"#", 0, 0, 1), (4, r"[.,]", 0, 0, 2), (5, r"y", 0, 1, 3)]
+    rng = np.random.default_rng(3)
+    docs = []
+    for _ in range(40):
+        toks = rng.choice(["x", "xx", "y", "ab", "#", ".", ",", "q"], size=int(rng.integers(0, 60)), p=[0.3, 0.1, 0.15, 0.15, 0.1, 0.08, 0.07, 0.05])
+        docs.append(" ".join(toks).encode())
+    docs += [b"x x x", b". x", b"# . # x x y y ab", b"x", b""]
+    offs = np.cumsum([0] + [len(d) for d in docs]).astype(np.uint64)
+    text = b"".join(docs)
+    outs = []
+    for lx in (OracleLexer(), HostSimLexer(chunk=32, warmup=8, mode=0), HostSimLexer(chunk=32, warmup=8, mode=1)):
+        for d in defs:
+            lx.define_lexem(*d)
+        lx.compile()
+        outs.append((lx, lx.scan(text, offs)))
+    ref = outs[0][1]
+    for lx, out in outs[1:]:
+        assert (out["offsets"] == ref["offsets"]).all() and (out["lexems"] == ref["lexems"]).all()
+    assert outs[2][0].info("fixed_islands") > 0 and outs[2][0].info("islands") > 100
+
+
+@pytest.mark.parametrize("name", ["words_numbers", "no_boundaries"])
+def test_per_document_loop_still_matches(name):
+    o = define_set(OracleLexer(), name)
+    h = define_set(HostSimLexer(chunk=64, warmup=16, mode=0), name)
+    text, offs = make_batch(seed=77, ndocs=20, mean_bytes=300)
+    ro, rh = o.scan(text, offs), h.scan(text, offs)
+    assert (ro["offsets"] == rh["offsets"]).all() and (ro["lexems"] == rh["lexems"]).all()
