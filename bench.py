@@ -217,24 +217,79 @@ def run_ours(args, rank, world, local_rank):
     ktimes = {k: (ctx.counter("time_us:" + k), ctx.counter("calls:" + k)) for k in KERNELS}
     ctx.counter("profile:off")
 
-    # ---- end to end through the C ABI with pinned host buffers
+    # ---- end to end through the C ABI with pinned host buffers: the batch is cut into sub-batches of whole documents
+    # that several host threads (one context + CUDA stream each) push through scan + fetch, so that the H2D copy of one
+    # sub-batch, the kernels of another and the D2H copy of a third overlap (PCIe is full duplex)
+    import threading
     nlex = counters["lexems"]
+    del ctx
     out_keep = torch.empty((nlex + 1024) * 16, dtype=torch.uint8, pin_memory=True)
     out_lex = out_keep.numpy().view(LEXEM_DT)
     out_offs = torch.empty(ndocs + 1, dtype=torch.int64, pin_memory=True).numpy().view(np.uint64)
     out_status = torch.empty(ndocs, dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)
     e2e_steps = max(1, min(args.steps, 3))
-    ctx.launch(text, offs, on_device=False)
-    ctx.fetch_into(out_lex, out_offs, out_status)
+    cuts = [0]
+    while cuts[-1] < ndocs:
+        nxt = int(np.searchsorted(offs, offs[cuts[-1]] + np.uint64(args.e2e_sub_bytes), side="right")) - 1
+        cuts.append(min(ndocs, max(nxt, cuts[-1] + 1)))
+    subs = [(cuts[i], cuts[i + 1]) for i in range(len(cuts) - 1)]
+    sub_offs = [np.ascontiguousarray(offs[b:e + 1] - offs[b]) for b, e in subs]
+    sub_lex_begin = [0] * (len(subs) + 1)     # filled by the untimed first pass (sizes are deterministic)
+    streams = [torch.cuda.Stream() for _ in range(args.e2e_threads)]
+    ctxs = [lx.create_context(s.cuda_stream) for s in streams]
+    scratch_offs = [np.zeros(max(e - b for b, e in subs) + 1, dtype=np.uint64) for _ in ctxs]
+    errors = []
+
+    def e2e_pass(measure_only):
+        nxt = [0]
+        lock = threading.Lock()
+
+        def worker(w):
+            try:
+                torch.cuda.set_device(local_rank)
+                while True:
+                    with lock:
+                        k = nxt[0]
+                        nxt[0] += 1
+                    if k >= len(subs):
+                        return
+                    b, e = subs[k]
+                    ctxs[w].launch(text[int(offs[b]):int(offs[e])], sub_offs[k], on_device=False)
+                    if measure_only:
+                        sub_lex_begin[k + 1] = ctxs[w].count()
+                    else:
+                        lb = sub_lex_begin[k]
+                        ctxs[w].fetch_into(out_lex[lb:sub_lex_begin[k + 1] + 1], scratch_offs[w], out_status[b:e])
+                        out_offs[b:e + 1] = scratch_offs[w][:e - b + 1] + np.uint64(lb)
+            except Exception as exc:  # surfaced after the join
+                errors.append(exc)
+
+        threads = [threading.Thread(target=worker, args=(w,)) for w in range(len(ctxs))]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        if errors:
+            raise errors[0]
+
+    e2e_pass(True)
+    for k in range(len(subs)):
+        sub_lex_begin[k + 1] += sub_lex_begin[k]
+    assert sub_lex_begin[-1] == nlex, "sub-batches give another lexem count than the whole batch"
+    e2e_pass(False)
     barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
-        ctx.launch(text, offs, on_device=False)
-        ctx.fetch_into(out_lex, out_offs, out_status)
+        e2e_pass(False)
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     if int(out_status.max(initial=0)) != 0:
         raise RuntimeError("lexer reported document errors on the synthetic corpus")
+    if args.verify_e2e:
+        whole = lx.create_context()
+        ref = whole.scan(dev_text.data_ptr(), offs, on_device=True)
+        assert (ref["offsets"] == out_offs).all() and (ref["lexems"] == out_lex[:nlex]).all(), "pipelined end-to-end output differs from the single batch"
+        del whole
 
     times = torch.tensor([ms, e2e_s * 1000.0], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -262,7 +317,8 @@ def run_ours(args, rank, world, local_rank):
                    "fixup_chunks": counters["fixup_chunks"], "chunks": counters["chunks"]},
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": int(args.bytes + 8 * (ndocs + 1)),
-                "d2h_bytes_per_step": int(16 * nlex + 8 * (ndocs + 1) + 4 * ndocs), "steps": e2e_steps},
+                "d2h_bytes_per_step": int(16 * nlex + 8 * (ndocs + len(subs)) + 4 * ndocs), "steps": e2e_steps,
+                "pipeline": "%d host threads x (context + stream), sub-batches of %d MiB" % (args.e2e_threads, args.e2e_sub_bytes >> 20)},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": None, "peak_kind": peak_kind,
@@ -285,6 +341,9 @@ def main():
     ap.add_argument("--bytes", type=int, default=1 << 30)
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--e2e-threads", type=int, default=4)
+    ap.add_argument("--e2e-sub-bytes", type=int, default=64 << 20)
+    ap.add_argument("--verify-e2e", action="store_true")
     args = ap.parse_args()
     args.ndefs = 86
     rank = int(os.environ.get("RANK", "0"))
