@@ -143,6 +143,12 @@ typedef struct SpArena
 	uint32_t* dispose;		/* rules to deactivate after the current event */
 	SpExpiry* heap;
 	SpStopLog* stoplog;		/* [nstopwords] */
+	uint32_t* free_rules;		/* stacks of released record numbers, one per pool */
+	uint32_t* free_triggers;
+	uint32_t* free_items;
+	uint32_t* free_datarefs;
+	uint32_t* win_rules;		/* [64][cap.rules] expiry lists by position % 64, read backwards (last in, first out) */
+	uint32_t* scratch;		/* [cap.triggers] ordered list of the triggers removed by one batch of deactivations */
 } SpArena;
 
 /* Scalars of the document in flight (shared memory of the warp). */
@@ -154,11 +160,12 @@ typedef struct SpDocState
 	uint32_t stamp;			/* document sequence number of this warp (validates stoplog entries) */
 	uint32_t nof_triggers;
 	uint32_t nfollow, ndispose, nresults, nheap;
-	uint32_t rule_free, rule_top, trig_free, trig_top, item_free, item_top, dref_free, dref_top;
+	int32_t rule_nfree, trig_nfree, item_nfree, dref_nfree;	/* fill of the free stacks */
+	uint32_t rule_top, trig_top, item_top, dref_top;		/* records handed out so far (bump allocation) */
 	uint32_t installed, altkey_installed, signals;
 	uint64_t open_patterns;
 	uint32_t bucket_size[ SP_NOF_BUCKETS];
-	uint32_t window[ SP_DISPOSE_WINDOW];	/* expiry lists by position % 64 (rule index, 0 = empty) */
+	uint32_t win_count[ SP_DISPOSE_WINDOW];	/* fill of the expiry lists */
 } SpDocState;
 
 SP_MHD uint32_t sp_evhash( uint32_t a)
@@ -174,13 +181,39 @@ SP_MHD void sp_doc_begin( SpDocState& S)
 	uint32_t stamp = S.stamp + 1;
 	S.status = 0; S.curpos = 0; S.timestmp = 0; S.stamp = stamp; S.nof_triggers = 0;
 	S.nfollow = S.ndispose = S.nresults = S.nheap = 0;
-	S.rule_free = S.rule_top = S.trig_free = S.trig_top = S.item_free = S.item_top = S.dref_free = S.dref_top = 0;
+	S.rule_nfree = S.trig_nfree = S.item_nfree = S.dref_nfree = 0;
+	S.rule_top = S.trig_top = S.item_top = S.dref_top = 0;
 	S.installed = S.altkey_installed = S.signals = 0; S.open_patterns = 0;
 	for (int i=0; i<SP_NOF_BUCKETS; ++i) S.bucket_size[i] = 0;
-	for (int i=0; i<SP_DISPOSE_WINDOW; ++i) S.window[i] = 0;
+	for (int i=0; i<SP_DISPOSE_WINDOW; ++i) S.win_count[i] = 0;
 }
 
 SP_MHD void sp_fail( SpDocState& S, uint32_t code) {if (!S.status) S.status = code;}
+
+// ---- record pools. Record numbers are 1-based and private to this implementation (never observable). A pool hands out
+// released records first (stack), then fresh ones. The counters are updated atomically so that the lanes of a warp can
+// allocate concurrently in the phases that only allocate, and release concurrently in the phases that only release.
+#ifdef __CUDACC__
+#define SP_AADD( ptr, v) atomicAdd( (ptr), (v))
+#else
+template <typename T> inline T sp_host_fetch_add( T* ptr, T v) {T old = *ptr; *ptr = old + v; return old;}
+#define SP_AADD( ptr, v) sp_host_fetch_add( (ptr), (v))
+#endif
+
+SP_MHD uint32_t sp_pool_alloc( int32_t* nfree, uint32_t* top, const uint32_t* stack, uint32_t cap)
+{
+	int32_t old = SP_AADD( nfree, (int32_t)-1);
+	if (old > 0) return stack[ old-1];
+	SP_AADD( nfree, (int32_t)1);
+	uint32_t b = SP_AADD( top, 1u);
+	if (b < cap) return b + 1;
+	SP_AADD( top, (uint32_t)-1);
+	return 0;
+}
+SP_MHD void sp_pool_free( int32_t* nfree, uint32_t* stack, uint32_t id)
+{
+	stack[ SP_AADD( nfree, (int32_t)1)] = id;
+}
 
 // ---- lookup of an event in the compiled tables
 SP_MHD bool sp_find_event( const SpMatcherTables& T, uint32_t event, SpEventSlot& slot)
@@ -198,10 +231,9 @@ SP_MHD bool sp_find_event( const SpMatcherTables& T, uint32_t event, SpEventSlot
 SP_MHD uint32_t sp_trigger_add( SpArena& A, SpDocState& S, uint32_t event, uint32_t rule, uint32_t sigtype, uint32_t sigval, uint32_t variable)
 {
 	uint32_t b = sp_evhash( event), n = S.bucket_size[ b];
-	uint32_t t = S.trig_free;
-	if (t) S.trig_free = A.triggers[ t-1].next;
-	else if (S.trig_top < A.cap.triggers) t = ++S.trig_top;
-	if (!t || n >= A.cap.triggers) {sp_fail( S, SP_MST_OVF_TRIGGERS); return 0;}
+	if (n >= A.cap.triggers) {sp_fail( S, SP_MST_OVF_TRIGGERS); return 0;}
+	uint32_t t = sp_pool_alloc( &S.trig_nfree, &S.trig_top, A.free_triggers, A.cap.triggers);
+	if (!t) {sp_fail( S, SP_MST_OVF_TRIGGERS); return 0;}
 	SpTrigger& rec = A.triggers[ t-1];
 	rec.link = (b << 28) | n; rec.rule = rule; rec.sigtype = sigtype; rec.sigval = sigval; rec.variable = variable; rec.next = 0;
 	A.bucket_event[ (size_t)b * A.cap.triggers + n] = event;
@@ -227,8 +259,7 @@ SP_MHD void sp_trigger_remove( SpArena& A, SpDocState& S, uint32_t t)
 	}
 	S.bucket_size[ b] = last;
 	S.nof_triggers -= 1;
-	rec.next = S.trig_free;
-	S.trig_free = t;
+	sp_pool_free( &S.trig_nfree, A.free_triggers, t);
 }
 
 SP_MHD uint32_t sp_trigger_event( const SpArena& A, uint32_t t)
@@ -240,10 +271,8 @@ SP_MHD uint32_t sp_trigger_event( const SpArena& A, uint32_t t)
 // ---- event data: item lists with reference counts
 SP_MHD uint32_t sp_dataref_create( SpArena& A, SpDocState& S)
 {
-	uint32_t d = S.dref_free;
-	if (d) S.dref_free = A.datarefs[ d-1].items;
-	else if (S.dref_top < A.cap.datarefs) d = ++S.dref_top;
-	else {sp_fail( S, SP_MST_OVF_DATAREFS); return 0;}
+	uint32_t d = sp_pool_alloc( &S.dref_nfree, &S.dref_top, A.free_datarefs, A.cap.datarefs);
+	if (!d) {sp_fail( S, SP_MST_OVF_DATAREFS); return 0;}
 	A.datarefs[ d-1].items = 0; A.datarefs[ d-1].refcount = 1;
 	return d;
 }
@@ -254,26 +283,23 @@ SP_MHD void sp_dataref_release( SpArena& A, SpDocState& S, uint32_t d)
 	if (ref.refcount > 1) {--ref.refcount; return;}
 	if (ref.refcount == 0) {sp_fail( S, SP_MST_RUNTIME); return;}		// "illegal free of event data reference"
 	ref.refcount = 0;
-	// the item list goes back to the free list; like the reference, the sub data of the items stays referenced
+	// the items go back to their pool; like the reference, the sub data of the items stays referenced
 	uint32_t it = ref.items;
 	while (it)
 	{
 		uint32_t nx = A.items[ it-1].next;
-		A.items[ it-1].next = S.item_free;
-		S.item_free = it;
+		sp_pool_free( &S.item_nfree, A.free_items, it);
 		it = nx;
 	}
-	ref.items = S.dref_free;
-	S.dref_free = d;
+	ref.items = 0;
+	sp_pool_free( &S.dref_nfree, A.free_datarefs, d);
 }
 
 SP_MHD void sp_dataref_push( SpArena& A, SpDocState& S, uint32_t d, uint32_t variable, const SpEventData& data)
 {
-	if (data.subdataref) A.datarefs[ data.subdataref-1].refcount += 1;
-	uint32_t it = S.item_free;
-	if (it) S.item_free = A.items[ it-1].next;
-	else if (S.item_top < A.cap.items) it = ++S.item_top;
-	else {sp_fail( S, SP_MST_OVF_ITEMS); return;}
+	if (data.subdataref) SP_AADD( &A.datarefs[ data.subdataref-1].refcount, 1u);	// several lanes may take the same event
+	uint32_t it = sp_pool_alloc( &S.item_nfree, &S.item_top, A.free_items, A.cap.items);
+	if (!it) {sp_fail( S, SP_MST_OVF_ITEMS); return;}
 	SpItem& rec = A.items[ it-1];
 	rec.variable = variable; rec.data = data; rec.next = A.datarefs[ d-1].items;
 	A.datarefs[ d-1].items = it;
@@ -318,8 +344,7 @@ SP_MHD void sp_rule_deactivate( SpArena& A, SpDocState& S, uint32_t r)
 SP_MHD void sp_rule_dispose( SpArena& A, SpDocState& S, uint32_t r)
 {
 	sp_rule_deactivate( A, S, r);
-	A.rules[ r-1].next = S.rule_free;
-	S.rule_free = r;
+	sp_pool_free( &S.rule_nfree, A.free_rules, r);
 }
 
 // expiry heap: std::push_heap / std::pop_heap of libstdc++ with DisposeEvent::operator< (a < b iff a.pos > b.pos),
@@ -368,17 +393,35 @@ SP_MHD void sp_heap_pop( SpArena& A, SpDocState& S)
 	S.nheap = n;
 }
 
+SP_MHD void sp_window_push( SpArena& A, SpDocState& S, uint32_t w, uint32_t r)
+{
+	uint32_t n = S.win_count[ w];
+	if (n >= A.cap.rules) {sp_fail( S, SP_MST_OVF_RULES); return;}
+	A.win_rules[ (size_t)w * A.cap.rules + n] = r;
+	S.win_count[ w] = n + 1;
+}
+
 // defineDisposeRule
 SP_MHD void sp_expiry_define( SpArena& A, SpDocState& S, uint32_t pos, uint32_t r)
 {
 	if (pos < S.curpos) {sp_fail( S, SP_MST_RUNTIME); return;}
-	if (pos < S.curpos + SP_DISPOSE_WINDOW)
-	{
-		uint32_t w = pos % SP_DISPOSE_WINDOW;
-		A.rules[ r-1].next = S.window[ w];
-		S.window[ w] = r;
-	}
+	if (pos < S.curpos + SP_DISPOSE_WINDOW) sp_window_push( A, S, pos % SP_DISPOSE_WINDOW, r);
 	else sp_heap_push( A, S, pos, r);
+}
+
+// Moves the heap entries that expire within the next 64 positions into the ring (start of a new round of the ring).
+// Returns true if any was moved.
+SP_MHD bool sp_heap_to_window( SpArena& A, SpDocState& S)
+{
+	bool moved = false;
+	while (S.nheap && A.heap[ 0].pos < S.curpos + SP_DISPOSE_WINDOW && !S.status)
+	{
+		moved = true;
+		SpExpiry top = A.heap[ 0];
+		sp_window_push( A, S, top.pos % SP_DISPOSE_WINDOW, top.rule);
+		sp_heap_pop( A, S);
+	}
+	return moved;
 }
 
 // setCurrentPos: disposes every rule whose last position lies in front of `pos`
@@ -389,29 +432,11 @@ SP_MHD void sp_set_current_pos( SpArena& A, SpDocState& S, uint32_t pos)
 	for (; wcnt < SP_DISPOSE_WINDOW && S.curpos < pos; ++wcnt, ++S.curpos)
 	{
 		uint32_t w = S.curpos % SP_DISPOSE_WINDOW;
-		if (w == 0)
-		{
-			while (S.nheap && A.heap[ 0].pos < S.curpos + SP_DISPOSE_WINDOW)
-			{
-				wcnt = 0;
-				SpExpiry top = A.heap[ 0];
-				uint32_t tw = top.pos % SP_DISPOSE_WINDOW;
-				A.rules[ top.rule-1].next = S.window[ tw];
-				S.window[ tw] = top.rule;
-				sp_heap_pop( A, S);
-			}
-		}
-		uint32_t r = S.window[ w];
-		if (r)
-		{
-			while (r)
-			{
-				uint32_t nx = A.rules[ r-1].next;
-				sp_rule_dispose( A, S, r);
-				r = nx;
-			}
-			S.window[ w] = 0;
-		}
+		if (w == 0 && sp_heap_to_window( A, S)) wcnt = 0;
+		// the list is visited last in, first out
+		const uint32_t* list = A.win_rules + (size_t)w * A.cap.rules;
+		for (uint32_t n = S.win_count[ w]; n > 0; --n) sp_rule_dispose( A, S, list[ n-1]);
+		S.win_count[ w] = 0;
 	}
 	if (S.curpos < pos)
 	{
@@ -432,13 +457,24 @@ SP_MHD void sp_follow_add( SpArena& A, SpDocState& S, const SpEventData& data, u
 	S.nfollow += 1;
 }
 
-// fireSignal: one signal on the slot of rule r. `replay`: called from the replay of a logged stop word, where a
-// follow event is an error of the rule set ("encountered past trigger with follow").
-SP_MHD void sp_fire_signal( SpArena& A, SpDocState& S, uint32_t r, uint32_t sigtype, uint32_t sigval, uint32_t variable, const SpEventData& data, bool replay)
+// What one signal appends to the ordered lists of the document (dispose list, follow list, results). The slot
+// update itself is private to the rule; keeping the appends apart lets the lanes of a warp fire the hits of one event
+// on different rules concurrently and then commit their appends in trigger order.
+typedef struct SpFireOut
+{
+	uint32_t dispose_rule;		/* rule to queue for deactivation or 0 */
+	uint32_t has_follow, has_result;
+	SpFollow follow;
+	SpPendingResult result;
+} SpFireOut;
+
+// fireSignal without the appends and without the signal counter. `replay`: called from the replay of a logged stop
+// word, where a follow event is an error of the rule set ("encountered past trigger with follow").
+SP_MHD void sp_fire_core( SpArena& A, SpDocState& S, uint32_t r, uint32_t sigtype, uint32_t sigval, uint32_t variable, const SpEventData& data, bool replay, SpFireOut& out)
 {
 	SpRule& rule = A.rules[ r-1];
 	bool match = false, take = false, finished = false;
-	S.signals += 1;
+	out.dispose_rule = 0; out.has_follow = 0; out.has_result = 0;
 	switch (sigtype)
 	{
 		case SP_SIG_ANY:
@@ -494,7 +530,7 @@ SP_MHD void sp_fire_signal( SpArena& A, SpDocState& S, uint32_t r, uint32_t sigt
 		case SP_SIG_DEL:
 			rule.count = 0;
 			rule.value = 0;
-			sp_dispose_add( A, S, r);
+			out.dispose_rule = r;
 			return;
 		default:
 			break;
@@ -534,29 +570,50 @@ SP_MHD void sp_fire_signal( SpArena& A, SpDocState& S, uint32_t r, uint32_t sigt
 			if (rule.event)
 			{
 				if (replay) {sp_fail( S, SP_MST_RUNTIME); return;}
-				SpEventData fd;
+				SpEventData& fd = out.follow.data;
 				fd.start_origseg = rule.start_origseg; fd.start_origpos = rule.start_origpos;
 				fd.end_origseg = data.end_origseg; fd.end_origpos = data.end_origpos;
 				fd.start_ordpos = rule.start_ordpos; fd.end_ordpos = rule.end_ordpos;
 				fd.subdataref = rule.dataref; fd.formathandle = rule.formatHandle;
-				if (rule.dataref) A.datarefs[ rule.dataref-1].refcount += 1;
-				sp_follow_add( A, S, fd, rule.event);
+				out.follow.event = rule.event;
+				out.has_follow = 1;
+				if (rule.dataref) SP_AADD( &A.datarefs[ rule.dataref-1].refcount, 1u);
 			}
 			if (rule.resultHandle)
 			{
-				if (S.nresults >= A.cap.results) {sp_fail( S, SP_MST_OVF_RESULTS); return;}
-				SpPendingResult& res = A.results[ S.nresults++];
+				SpPendingResult& res = out.result;
 				res.resultHandle = rule.resultHandle; res.formatHandle = rule.formatHandle; res.dataref = rule.dataref;
 				res.start_ordpos = rule.start_ordpos; res.end_ordpos = rule.end_ordpos;
 				res.start_origseg = rule.start_origseg; res.start_origpos = rule.start_origpos;
 				res.end_origseg = data.end_origseg; res.end_origpos = data.end_origpos;
 				res.eliminated = 0;
-				if (rule.dataref) A.datarefs[ rule.dataref-1].refcount += 1;
+				out.has_result = 1;
+				if (rule.dataref) SP_AADD( &A.datarefs[ rule.dataref-1].refcount, 1u);
 			}
 			rule.done = 1;
 		}
-		if (finished) sp_dispose_add( A, S, r);
+		if (finished) out.dispose_rule = r;
 	}
+}
+
+// appends of one signal in the order of the reference: follow event, result, dispose entry
+SP_MHD void sp_fire_commit( SpArena& A, SpDocState& S, const SpFireOut& out)
+{
+	if (out.has_follow) sp_follow_add( A, S, out.follow.data, out.follow.event);
+	if (out.has_result)
+	{
+		if (S.nresults >= A.cap.results) {sp_fail( S, SP_MST_OVF_RESULTS); return;}
+		A.results[ S.nresults++] = out.result;
+	}
+	if (out.dispose_rule) sp_dispose_add( A, S, out.dispose_rule);
+}
+
+SP_MHD void sp_fire_signal( SpArena& A, SpDocState& S, uint32_t r, uint32_t sigtype, uint32_t sigval, uint32_t variable, const SpEventData& data, bool replay)
+{
+	SpFireOut out;
+	S.signals += 1;
+	sp_fire_core( A, S, r, sigtype, sigval, variable, data, replay, out);
+	sp_fire_commit( A, S, out);
 }
 
 // replayPastEvent: an alternative-key program was installed by a later element; the logged latest occurrence of
@@ -601,10 +658,8 @@ SP_MHD void sp_install_program( const SpMatcherTables& T, SpArena& A, SpDocState
 {
 	const SpProgram P = T.programs[ pt.program];
 	if (data.start_ordpos + P.range < S.curpos) return;	// the rule cannot match anymore
-	uint32_t r = S.rule_free;
-	if (r) S.rule_free = A.rules[ r-1].next;
-	else if (S.rule_top < A.cap.rules) r = ++S.rule_top;
-	else {sp_fail( S, SP_MST_OVF_RULES); return;}
+	uint32_t r = sp_pool_alloc( &S.rule_nfree, &S.rule_top, A.free_rules, A.cap.rules);
+	if (!r) {sp_fail( S, SP_MST_OVF_RULES); return;}
 	SpRule& rule = A.rules[ r-1];
 	rule.value = P.initsigval; rule.count = P.initcount & 0xFFFFu; rule.event = P.event;
 	rule.resultHandle = P.resultHandle; rule.formatHandle = P.formatHandle;
@@ -817,6 +872,7 @@ typedef struct SpArenaLayout
 	SpArenaCaps cap;
 	uint32_t nstopwords;
 	uint64_t rules, triggers, bucket_event, bucket_trigger, items, datarefs, results, follow, dispose, heap, stoplog;
+	uint64_t free_rules, free_triggers, free_items, free_datarefs, win_rules, scratch;
 	uint64_t bytes;
 } SpArenaLayout;
 
@@ -837,6 +893,12 @@ SP_MHOSTDEV void sp_arena_layout( const SpArenaCaps& cap, uint32_t nstopwords, S
 	L.dispose = o; o = sp_align128( o + (uint64_t)cap.dispose * sizeof(uint32_t));
 	L.heap = o; o = sp_align128( o + (uint64_t)cap.heap * sizeof(SpExpiry));
 	L.stoplog = o; o = sp_align128( o + (uint64_t)(nstopwords + 1) * sizeof(SpStopLog));
+	L.free_rules = o; o = sp_align128( o + (uint64_t)cap.rules * sizeof(uint32_t));
+	L.free_triggers = o; o = sp_align128( o + (uint64_t)cap.triggers * sizeof(uint32_t));
+	L.free_items = o; o = sp_align128( o + (uint64_t)cap.items * sizeof(uint32_t));
+	L.free_datarefs = o; o = sp_align128( o + (uint64_t)cap.datarefs * sizeof(uint32_t));
+	L.win_rules = o; o = sp_align128( o + (uint64_t)cap.rules * SP_DISPOSE_WINDOW * sizeof(uint32_t));
+	L.scratch = o; o = sp_align128( o + (uint64_t)cap.triggers * sizeof(uint32_t));
 	L.bytes = o;
 }
 
@@ -849,6 +911,9 @@ SP_MHOSTDEV void sp_arena_bind( const SpArenaLayout& L, uint8_t* base, SpArena& 
 	A.results = (SpPendingResult*)(base + L.results); A.follow = (SpFollow*)(base + L.follow);
 	A.dispose = (uint32_t*)(base + L.dispose); A.heap = (SpExpiry*)(base + L.heap);
 	A.stoplog = (SpStopLog*)(base + L.stoplog);
+	A.free_rules = (uint32_t*)(base + L.free_rules); A.free_triggers = (uint32_t*)(base + L.free_triggers);
+	A.free_items = (uint32_t*)(base + L.free_items); A.free_datarefs = (uint32_t*)(base + L.free_datarefs);
+	A.win_rules = (uint32_t*)(base + L.win_rules); A.scratch = (uint32_t*)(base + L.scratch);
 }
 
 // ---- one document, all steps in sequence on one thread: the definition of the result the warp kernel must

@@ -58,3 +58,109 @@ def define_lexer(lx, nphrases=40, nabbrev=30, symbols=()):
         lx.define_symbol(sid, lid, name)
     lx.compile()
     return lx
+
+
+# ---------------------------------------------------------------------------------------------------------
+# Token pattern sets of the full pipeline configurations (C3 and C4). The generators only call the
+# common matcher interface (push_term / attach_variable / push_expression / define_pattern), so the same call
+# sequence reaches the product and the reference oracle.
+OP_SEQUENCE, OP_SEQUENCE_IMM, OP_SEQUENCE_STRUCT, OP_WITHIN, OP_WITHIN_STRUCT, OP_ANY, OP_AND = range(7)
+SYMBOL_BASE = 1000
+
+
+def _zipf_ranks(rng, n, size, s):
+    import numpy as np
+    k = np.arange(1, size + 1, dtype=np.float64)
+    cum = np.cumsum(1.0 / k ** s)
+    return np.searchsorted(cum, rng.random(n) * cum[-1], side="right")
+
+
+def symbol_table(vocab, nsymbols, lexemid=WORD):
+    """(symbolid, lexemid, name) for the most frequent vocabulary words; symbol id = SYMBOL_BASE + rank."""
+    out = []
+    for rank, w in enumerate(vocab[:nsymbols]):
+        out.append((SYMBOL_BASE + rank, lexemid, w))
+    return out
+
+
+def define_c3_patterns(m, seed, npatterns, nsymbols, lexem_share=0.1):
+    """C3: 50 % sequence_imm of 2-4 terms (range = argc), 30 % within of 2-3 terms (range 3-10), 10 % *_struct with the
+    sentence delimiter, 10 % any of 2-5 terms nested as first argument of a sequence; cardinality 0 except 5 % of
+    within/any with cardinality 2; variables on all leaf terms; terms are symbols of vocabulary words (Zipf 0.8) or,
+    with probability lexem_share, plain lexem ids."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    plain = [NUMBER, DECIMAL, DATE, CAPWORD, ABBREV, AMOUNT]
+
+    def term(var):
+        if rng.random() < lexem_share:
+            m.push_term(int(plain[int(rng.integers(0, len(plain)))]))
+        else:
+            m.push_term(SYMBOL_BASE + int(_zipf_ranks(rng, 1, nsymbols, 0.8)[0]))
+        m.attach_variable("v%d" % var)
+
+    for r in range(npatterns):
+        u = rng.random()
+        if u < 0.5:
+            n = int(rng.integers(2, 5))
+            for i in range(n):
+                term(i)
+            m.push_expression(OP_SEQUENCE_IMM, n, n, 0)
+            name = "seqimm%d" % n
+        elif u < 0.8:
+            n = int(rng.integers(2, 4))
+            for i in range(n):
+                term(i)
+            m.push_expression(OP_WITHIN, n, int(rng.integers(3, 11)), 2 if rng.random() < 0.05 else 0)
+            name = "within%d" % n
+        elif u < 0.9:
+            n = int(rng.integers(2, 4))
+            m.push_term(SENT)
+            for i in range(n):
+                term(i)
+            op = OP_SEQUENCE_STRUCT if rng.random() < 0.5 else OP_WITHIN_STRUCT
+            m.push_expression(op, n + 1, int(rng.integers(3, 11)), 0)
+            name = "struct%d" % n
+        else:
+            n = int(rng.integers(2, 6))
+            for i in range(n):
+                term(i)
+            m.push_expression(OP_ANY, n, 1, 2 if rng.random() < 0.05 else 0)
+            m.attach_variable("alt")
+            term(9)
+            m.push_expression(OP_SEQUENCE, 2, int(rng.integers(2, 8)), 0)
+            name = "anyseq%d" % n
+        m.define_pattern("%s_%d" % (name, r % 97), "", True)
+
+
+def define_c4_patterns(m, seed, npatterns, vocab_size):
+    """C4 (dictionary style): sequence_imm patterns of 2-5 terms drawn Zipf(0.8) from the vocabulary, so that the most
+    frequent terms are key events of very many patterns (high trigger fan-out, exercises the alt-key optimisation)."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    for r in range(npatterns):
+        n = int(rng.integers(2, 6))
+        ranks = _zipf_ranks(rng, n, vocab_size, 0.8)
+        for i in range(n):
+            m.push_term(SYMBOL_BASE + int(ranks[i]))
+            m.attach_variable("t%d" % i)
+        m.push_expression(OP_SEQUENCE_IMM, n, n, 0)
+        m.define_pattern("dict%d" % (r % 1009), "", True)
+
+
+def c4_token_documents(seed, ndocs, vocab_size, min_tokens=1000, max_tokens=4000):
+    """C4 input: token records (one token per ordinal position, ids Zipf(1) over the vocabulary)."""
+    import numpy as np
+    from .capi import LEXEM_DT
+    rng = np.random.default_rng(seed)
+    sizes = rng.integers(min_tokens, max_tokens + 1, size=ndocs)
+    offs = np.zeros(ndocs + 1, dtype=np.uint64)
+    offs[1:] = np.cumsum(sizes)
+    total = int(offs[-1])
+    toks = np.zeros(total, dtype=LEXEM_DT)
+    toks["id"] = SYMBOL_BASE + _zipf_ranks(rng, total, vocab_size, 1.0)
+    pos = np.arange(total, dtype=np.uint64) - np.repeat(offs[:-1], sizes)
+    toks["ordpos"] = pos + 1
+    toks["origpos"] = pos * 6
+    toks["origsize"] = 5
+    return toks, offs
