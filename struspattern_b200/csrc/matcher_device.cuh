@@ -731,19 +731,32 @@ SP_MHD void sp_event_finish( const SpMatcherTables& T, SpArena& A, SpDocState& S
 	else if (follow.data.subdataref) sp_dataref_release( A, S, follow.data.subdataref);
 }
 
-// putInput up to the start of the event loop: order and range checks, rule expiry, first entry of the follow list
-SP_MHD void sp_input_begin( SpArena& A, SpDocState& S, const sp_lexem& tok, uint32_t origseg)
+// putInput up to the start of the event loop, in three steps: order and range checks, rule expiry, first entry of the
+// follow list. Returns false if the token is rejected (the document fails).
+SP_MHD bool sp_input_check( SpDocState& S, const sp_lexem& tok, uint32_t origseg)
 {
-	if (S.curpos > tok.ordpos) {sp_fail( S, SP_MST_RUNTIME); return;}	// "term events not fed in ascending order"
-	if (S.curpos < tok.ordpos) sp_set_current_pos( A, S, tok.ordpos);
-	else if (tok.origsize >= 0x7FFFFFFFu || origseg >= 0x7FFFFFFFu || tok.origpos >= 0x7FFFFFFFu) {sp_fail( S, SP_MST_RUNTIME); return;}
-	if (tok.id >= (1u<<29)) {sp_fail( S, SP_MST_RUNTIME); return;}	// "event handle out of range"
+	if (S.curpos > tok.ordpos) {sp_fail( S, SP_MST_RUNTIME); return false;}	// "term events not fed in ascending order"
+	if (S.curpos == tok.ordpos && (tok.origsize >= 0x7FFFFFFFu || origseg >= 0x7FFFFFFFu || tok.origpos >= 0x7FFFFFFFu)) {sp_fail( S, SP_MST_RUNTIME); return false;}
+	if (tok.id >= (1u<<29)) {sp_fail( S, SP_MST_RUNTIME); return false;}	// "event handle out of range"
+	return true;
+}
+SP_MHD void sp_input_queue( SpArena& A, SpDocState& S, const sp_lexem& tok, uint32_t origseg)
+{
 	SpEventData data;
 	data.start_origseg = origseg; data.start_origpos = tok.origpos; data.end_origseg = origseg; data.end_origpos = tok.origpos + tok.origsize;
 	data.start_ordpos = tok.ordpos; data.end_ordpos = tok.ordpos + 1; data.subdataref = 0; data.formathandle = 0;
 	S.open_patterns += S.nof_triggers;
 	S.nfollow = 0;
 	sp_follow_add( A, S, data, tok.id);
+}
+SP_MHD void sp_input_begin( SpArena& A, SpDocState& S, const sp_lexem& tok, uint32_t origseg)
+{
+	// the reference advances the position before it looks at the event id (src/patternMatcher.cpp:136-156)
+	if (S.curpos > tok.ordpos) {sp_fail( S, SP_MST_RUNTIME); return;}
+	if (S.curpos < tok.ordpos) sp_set_current_pos( A, S, tok.ordpos);
+	else if (tok.origsize >= 0x7FFFFFFFu || origseg >= 0x7FFFFFFFu || tok.origpos >= 0x7FFFFFFFu) {sp_fail( S, SP_MST_RUNTIME); return;}
+	if (tok.id >= (1u<<29)) {sp_fail( S, SP_MST_RUNTIME); return;}
+	sp_input_queue( A, S, tok, origseg);
 }
 
 // One signal of the trigger scan: the trigger at position i of bucket b waits for the current event.

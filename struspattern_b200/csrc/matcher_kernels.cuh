@@ -12,6 +12,7 @@
 #ifndef SP_MATCHER_KERNELS_CUH_INCLUDED
 #define SP_MATCHER_KERNELS_CUH_INCLUDED
 #include "matcher_device.cuh"
+#include "matcher_warp.cuh"
 
 namespace sp {
 
@@ -39,6 +40,9 @@ struct MatchParams
 	uint32_t* status;
 };
 
+// uniform view of the document status (lanes may look at the word at different times)
+__device__ __forceinline__ bool warpFailed( const SpDocState& S) {return __any_sync( SP_FULL, S.status != 0) != 0;}
+
 static __global__ void __launch_bounds__(MatchThreads) k_match_documents( MatchParams P)
 {
 	__shared__ SpDocState states[ MatchWarpsPerBlock];
@@ -52,58 +56,67 @@ static __global__ void __launch_bounds__(MatchThreads) k_match_documents( MatchP
 	{
 		uint32_t slot = 0;
 		if (lane == 0) slot = atomicAdd( P.next_doc, 1u);
-		slot = __shfl_sync( 0xFFFFFFFFu, slot, 0);
+		slot = __shfl_sync( SP_FULL, slot, 0);
 		if (slot >= ntodo) break;
 		const uint32_t d = P.doc_list ? P.doc_list[ slot] : slot;
 		const uint64_t tb = P.tok_off[ d], te = P.tok_off[ d+1];
 		if (lane == 0) sp_doc_begin( S);
 		__syncwarp();
 		uint64_t nevents = 0;
-		uint32_t status = 0;
-		for (uint64_t ti=tb; ti<te; ++ti)
+		bool failed = false;
+		for (uint64_t ti=tb; ti<te && !failed; ++ti)
 		{
-			if (lane == 0)
-			{
-				sp_lexem tok = P.tokens[ ti];
-				sp_input_begin( A, S, tok, P.origsegs ? P.origsegs[ ti] : 0);
-			}
+			// putInput: checks, rule expiry by the whole warp, first entry of the follow list
+			const sp_lexem tok = P.tokens[ ti];
+			const uint32_t seg = P.origsegs ? P.origsegs[ ti] : 0;
+			if (lane == 0) sp_input_check( S, tok, seg);
+			__syncwarp();
+			if ((failed = warpFailed( S))) break;
+			warpSetCurrentPos( A, S, lane, tok.ordpos);
+			if (lane == 0 && !S.status) sp_input_queue( A, S, tok, seg);
+			__syncwarp();
+			if ((failed = warpFailed( S))) break;
+			// doTransition: the follow list grows while it is worked off
 			for (uint32_t fi=0;; ++fi)
 			{
-				// everything the other lanes need from the state lane 0 mutates is read between two barriers
-				__syncwarp();
-				status = S.status;
 				const uint32_t nfollow = S.nfollow;
-				uint32_t ev = 0, b = 0, n = 0;
-				if (!status && fi < nfollow)
+				__syncwarp();
+				if (fi >= nfollow) break;
+				const SpFollow follow = A.follow[ fi];
+				if (follow.event)
 				{
-					ev = A.follow[ fi].event;
-					if (ev) {b = sp_evhash( ev); n = S.bucket_size[ b];}
+					const uint32_t b = sp_evhash( follow.event), n = S.bucket_size[ b];
+					__syncwarp();
+					warpFireHits( A, S, lane, follow.event, b, n, follow.data);
+					if ((failed = warpFailed( S))) break;
+				}
+				SpEventSlot es; es.prog_count = 0; es.stopword = 0;
+				const bool known = sp_find_event( P.T, follow.event, es);
+				if (known && es.prog_count)
+				{
+					warpInstall( P.T, A, S, lane, follow.event, es, follow.data);
+					if ((failed = warpFailed( S))) break;
+				}
+				const uint32_t ndispose = S.ndispose;
+				__syncwarp();
+				if (ndispose)
+				{
+					warpDeactivate( A, S, lane, A.dispose, ndispose, false, false);
+					if (lane == 0) S.ndispose = 0;
+				}
+				if (lane == 0)
+				{
+					if (known && es.stopword)
+					{
+						SpStopLog& log = A.stoplog[ es.stopword-1];
+						log.data = follow.data; log.timestmp = ++S.timestmp; log.stamp = S.stamp;
+					}
+					else if (follow.data.subdataref) sp_dataref_release( A, S, follow.data.subdataref);
 				}
 				__syncwarp();
-				if (status || fi >= nfollow) break;
-				if (ev)
-				{
-					const uint32_t* evs = A.bucket_event + (size_t)b * A.cap.triggers;
-					for (uint32_t base=0; base<n; base+=32)
-					{
-						uint32_t e = (base + lane < n) ? evs[ base + lane] : 0xFFFFFFFFu;
-						unsigned int hits = __ballot_sync( 0xFFFFFFFFu, e == ev);
-						if (hits && lane == 0)
-						{
-							SpEventData data = A.follow[ fi].data;
-							while (hits && !S.status)
-							{
-								int i = __ffs( hits) - 1;
-								hits &= hits - 1;
-								sp_fire_trigger_at( A, S, b, base + i, data);
-							}
-						}
-					}
-				}
-				if (lane == 0 && !S.status) sp_event_finish( P.T, A, S, fi);
+				if ((failed = warpFailed( S))) break;
 			}
-			if (status) break;
-			++nevents;
+			if (!failed) ++nevents;
 		}
 		__syncwarp();
 		if (lane == 0)
