@@ -106,6 +106,7 @@ typedef struct SpPendingResult		/* Result, :273 */
 {
 	uint32_t resultHandle, formatHandle, dataref, start_ordpos, end_ordpos, start_origseg, end_origseg, start_origpos, end_origpos;
 	uint32_t eliminated;
+	uint32_t out_index, item_begin;	/* place in the output of the document (filled when the document is finished) */
 } SpPendingResult;
 
 typedef struct SpFollow			/* EventStruct, :220 */

@@ -119,19 +119,55 @@ static __global__ void __launch_bounds__(MatchThreads) k_match_documents( MatchP
 			if (!failed) ++nevents;
 		}
 		__syncwarp();
+		// fetchResults: one lane per result counts its items, the document claims pool space once, the lanes write
+		if (lane == 0 && !S.status && P.T.exclusive) sp_mark_covered( P.T, A, S);
+		__syncwarp();
+		const uint32_t npending = warpFailed( S) ? 0 : S.nresults;
+		uint32_t nres = 0, nitems = 0;
+		for (uint32_t base=0; base<npending; base+=32)
+		{
+			const uint32_t i = base + lane;
+			uint32_t keep = 0, cnt = 0;
+			if (i < npending && !A.results[ i].eliminated)
+			{
+				keep = 1;
+				if (A.results[ i].dataref) cnt = sp_gather_items( A, S, A.results[ i].dataref, 0);
+			}
+			uint32_t ki = keep, ci = cnt;
+			#pragma unroll
+			for (int ofs=1; ofs<32; ofs<<=1)
+			{
+				uint32_t uk = __shfl_up_sync( SP_FULL, ki, ofs), uc = __shfl_up_sync( SP_FULL, ci, ofs);
+				if (lane >= (unsigned int)ofs) {ki += uk; ci += uc;}
+			}
+			if (keep) {A.results[ i].out_index = nres + ki - 1; A.results[ i].item_begin = nitems + ci - cnt;}
+			nres += __shfl_sync( SP_FULL, ki, 31);
+			nitems += __shfl_sync( SP_FULL, ci, 31);
+		}
+		__syncwarp();
+		if (warpFailed( S)) {nres = 0; nitems = 0;}
+		unsigned long long rb = 0, ib = 0;
 		if (lane == 0)
 		{
-			uint32_t nres = 0, nitems = 0;
-			if (!S.status) sp_doc_count_output( P.T, A, S, nres, nitems);
-			if (S.status) {nres = 0; nitems = 0;}
-			uint64_t rb = 0, ib = 0;
 			if (nres) rb = atomicAdd( P.cursors + 0, (unsigned long long)nres);
 			if (nitems) ib = atomicAdd( P.cursors + 1, (unsigned long long)nitems);
-			if (rb + nres > P.res_cap || ib + nitems > P.item_cap)
+			if (rb + nres > P.res_cap || ib + nitems > P.item_cap) S.status = SP_MST_OVF_OUTPUT;
+		}
+		rb = __shfl_sync( SP_FULL, rb, 0); ib = __shfl_sync( SP_FULL, ib, 0);
+		__syncwarp();
+		if (warpFailed( S)) {nres = 0; nitems = 0;}
+		if (nres)
+		{
+			for (uint32_t i=lane; i<npending; i+=32)
 			{
-				S.status = SP_MST_OVF_OUTPUT; nres = 0; nitems = 0;
+				const SpPendingResult res = A.results[ i];
+				if (res.eliminated) continue;
+				uint32_t cnt = res.dataref ? sp_gather_items( A, S, res.dataref, P.item_pool + ib + res.item_begin) : 0;
+				sp_result_record( res, res.item_begin, cnt, P.res_pool[ rb + res.out_index]);
 			}
-			else if (nres) sp_doc_write_output( A, S, P.res_pool + rb, P.item_pool + ib);
+		}
+		if (lane == 0)
+		{
 			P.doc_res_begin[ d] = rb; P.doc_res_count[ d] = nres;
 			P.doc_item_begin[ d] = ib; P.doc_item_count[ d] = nitems;
 			sp_matcher_stats st;

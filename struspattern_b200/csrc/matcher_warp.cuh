@@ -236,10 +236,10 @@ __device__ __forceinline__ void warpInstall( const SpMatcherTables& T, SpArena& 
 		{
 			for (uint32_t j=0; j<P.trig_count; ++j) if (T.trigger_defs[ P.trig_begin + j].event == event) {++nkey; keydef = P.trig_begin + j;}
 		}
-		const bool hard = active && (pt.past_event != 0 || expiry >= curpos + SP_DISPOSE_WINDOW || P.trig_count > 7 || nkey != 1);
+		const bool hard = active && (expiry >= curpos + SP_DISPOSE_WINDOW || P.trig_count > 7 || nkey != 1);
 		if (__ballot_sync( SP_FULL, hard))
 		{
-			// replay of a past event, expiry beyond the ring, several key definitions: the sequential path, in list order
+			// expiry beyond the ring, several key definitions, many definitions: the sequential path, in list order
 			if (lane == 0)
 			{
 				const uint32_t end = min( base + 32, es.prog_count);
@@ -279,10 +279,61 @@ __device__ __forceinline__ void warpInstall( const SpMatcherTables& T, SpArena& 
 				if (!(grp >> (lane + 1))) S.win_count[ w] = fill + __popc( grp);	// highest lane of the group
 			}
 		}
+		// 2b. alternative-key program: replay of the logged latest occurrence of its original key event
+		// (replayPastEvent, src/ruleMatcherAutomaton.cpp:1272-1334) on the triggers the rule is about to get, last
+		// installed first. A rule that the replay finishes or that a later delimiter has cut off is deactivated at once;
+		// its triggers would be the last of their buckets and leave them unchanged, so they are not installed at all.
+		const uint32_t slotcount = P.initcount & 0xFFFFu;
+		bool dead = false;
+		uint32_t nreplayed = 0;
+		if (active && pt.past_event)
+		{
+			SpEventSlot ps;
+			if (sp_find_event( T, pt.past_event, ps) && ps.stopword)
+			{
+				const SpStopLog log = A.stoplog[ ps.stopword-1];
+				if (log.stamp == S.stamp && !(log.data.start_ordpos + P.range < curpos))
+				{
+					bool cut = false;
+					for (uint32_t j=P.trig_count; j>0 && !S.status; --j)
+					{
+						const SpTriggerDef def = T.trigger_defs[ P.trig_begin + j - 1];
+						if (!installsTrigger( def, event, slotcount)) continue;
+						if (def.sigtype == SP_SIG_DEL)
+						{
+							SpEventSlot ds;
+							if (sp_find_event( T, def.event, ds) && ds.stopword)
+							{
+								const SpStopLog& dl = A.stoplog[ ds.stopword-1];
+								if (dl.stamp == S.stamp && dl.timestmp > log.timestmp) cut = true;
+							}
+						}
+						if (def.event == pt.past_event)
+						{
+							SpFireOut ro;
+							sp_fire_core( A, S, r, def.sigtype, def.sigval, def.variable, log.data, true, ro);
+							if (ro.dispose_rule) dead = true;
+							++nreplayed;
+						}
+					}
+					if (cut) dead = true;
+				}
+			}
+		}
+		const unsigned int replayed = __ballot_sync( SP_FULL, active && pt.past_event != 0);
+		__syncwarp();
+		if (dead)
+		{
+			// deactivateRule of a rule without live triggers (free-only step: no lane allocates here)
+			SpRule& rule = A.rules[ r-1];
+			rule.active = 0;
+			if (rule.dataref) {sp_dataref_release( A, S, rule.dataref); rule.dataref = 0;}
+		}
+		__syncwarp();
+		const bool live = active && !dead;
 		// 3. live triggers: per bucket the positions follow program order, then definition order
 		BucketCounts mine; mine.lo = mine.hi = 0;
-		const uint32_t slotcount = P.initcount & 0xFFFFu;
-		if (active)
+		if (live)
 		{
 			for (uint32_t j=0; j<P.trig_count; ++j)
 			{
@@ -304,7 +355,7 @@ __device__ __forceinline__ void warpInstall( const SpMatcherTables& T, SpArena& 
 		__syncwarp();
 		if (__ballot_sync( SP_FULL, bovf)) {sp_fail( S, SP_MST_OVF_TRIGGERS); break;}
 		bool tfail = false;
-		if (active)
+		if (live)
 		{
 			SpRule& rule = A.rules[ r-1];
 			for (uint32_t j=0; j<P.trig_count; ++j)
@@ -333,18 +384,22 @@ __device__ __forceinline__ void warpInstall( const SpMatcherTables& T, SpArena& 
 			for (uint32_t b=0; b<SP_NOF_BUCKETS; ++b) sum += total.get( b);
 			S.nof_triggers += sum;
 			S.installed += __popc( amask);
-			S.signals += __popc( amask);
+			S.altkey_installed += __popc( replayed);
 		}
 		__syncwarp();
 		// 4. the key definition fires on the new rule; appends in program order
 		SpFireOut out; out.dispose_rule = 0; out.has_follow = 0; out.has_result = 0;
-		if (active)
+		if (live)
 		{
 			const SpTriggerDef def = T.trigger_defs[ keydef];
 			sp_fire_core( A, S, r, def.sigtype, def.sigval, def.variable, data, false, out);
 		}
 		__syncwarp();
-		warpCommit( A, S, lane, active, out);
+		warpCommit( A, S, lane, live, out);
+		const unsigned int fired = __ballot_sync( SP_FULL, live);
+		#pragma unroll
+		for (int ofs=16; ofs>0; ofs>>=1) nreplayed += __shfl_down_sync( SP_FULL, nreplayed, ofs);
+		if (lane == 0) S.signals += __popc( fired) + nreplayed;
 	}
 	__syncwarp();
 }
