@@ -123,7 +123,7 @@ def cpu_lexer_rate(text, offs, seconds_target, nthreads):
 
 
 KERNELS = ["k_lex_count", "k_lex_verify", "k_lex_emit", "k_lex_finish", "k_lex_resolve", "k_lex_write", "k_scan",
-           "k_isl_flags", "k_isl_resolve", "k_ordpos", "k_isl_slots", "k_slot_scan"]
+           "k_isl_flags", "k_isl_resolve", "k_ordpos", "k_isl_slots", "k_slot_scan", "k_lex_fused", "k_fused_scan", "k_fused_write"]
 
 
 def algorithmic_bytes(kernel, c):
@@ -144,6 +144,11 @@ def algorithmic_bytes(kernel, c):
         # slot pipeline (default): events + document ids read once, one 16 B slot per event written; slots read once, lexems written
         "k_isl_slots": 20 * nev + 16 * nev * c.get("ar_mult", 1),
         "k_slot_scan": 16 * nev * c.get("ar_mult", 1) + 16 * nlex + 16 * ndocs,
+        # fused segment pipeline (default): text read once, one 16 B record per kept element (>= lexems) written, per chunk
+        # start state + event offset read and 30 B of counters written; then kept elements read once, 16 B lexem records written
+        "k_lex_fused": n_text + 16 * nlex + 42 * nchunks,
+        "k_fused_scan": 40 * nchunks + 28 * ndocs,
+        "k_fused_write": 32 * nlex + 20 * nchunks,
     }[kernel]
 
 
@@ -198,7 +203,7 @@ def run_ours(args, rank, world, local_rank):
     for _ in range(args.warmup):
         ctx.launch(dev_text.data_ptr(), offs, on_device=True)
         ctx.count()
-    counters = {k: ctx.counter(k) for k in ("raw_events", "lexems", "chunks", "fixup_chunks", "fixup_rounds", "text_bytes", "kernel_launches", "islands", "elements")}
+    counters = {k: ctx.counter(k) for k in ("raw_events", "lexems", "chunks", "fixup_chunks", "fixup_rounds", "text_bytes", "kernel_launches", "islands", "elements", "fused", "fused_fallbacks")}
     counters["ndocs"] = ndocs
     counters["ar_mult"] = 2 if lx.table_info("symbols") else 1
     ctx.counter("profile:on"); ctx.counter("profile:reset")
@@ -314,7 +319,8 @@ def run_ours(args, rank, world, local_rank):
                    "l2": "input (%.0f MiB) larger than L2, no flush needed" % (args.bytes / 2**20),
                    "lexems_per_step": counters["lexems"], "raw_events_per_step": counters["raw_events"],
                    "fwd_states": lx.table_info("fwd_states"), "fwd_table_bytes": lx.table_info("fwd_table_bytes"),
-                   "fixup_chunks": counters["fixup_chunks"], "chunks": counters["chunks"]},
+                   "fixup_chunks": counters["fixup_chunks"], "chunks": counters["chunks"],
+                   "second_half": "fused segment kernel" if counters["fused"] else "island/slot pipeline"},
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": int(args.bytes + 8 * (ndocs + 1)),
                 "d2h_bytes_per_step": int(16 * nlex + 8 * (ndocs + len(subs)) + 4 * ndocs), "steps": e2e_steps,

@@ -350,6 +350,8 @@ struct Dfa
 	std::vector<std::vector<uint32_t> > accepts;	// per state: definitions whose match ended in front of the byte that led here
 	uint32_t init[4];			// initial state by kind of the previous byte (ByteKind)
 	uint32_t dead;				// anchored mode: state with no future (else 0xFFFFFFFF)
+	std::vector<uint8_t> cut;		// unanchored mode, per state: 1 if no thread that was alive in front of the byte that
+						// led here survived it, i.e. every match reported later starts at that byte or behind it
 
 	uint32_t stride() const {return nclasses+1;}
 };
@@ -358,8 +360,9 @@ struct DfaOptions
 {
 	bool unanchored;	// start states are re-entered at every position (forward multi pattern scan)
 	bool allowEmpty;	// report matches of length 0 (anchored helper automata of the capture selection)
+	bool markCuts;		// unanchored: distinguish states reached by a transition no older thread survived (Dfa::cut)
 	uint32_t maxStates;
-	DfaOptions() :unanchored(true),allowEmpty(false),maxStates(60000){}
+	DfaOptions() :unanchored(true),allowEmpty(false),markCuts(false),maxStates(60000){}
 };
 
 struct DfaTooLarge :public std::runtime_error
@@ -401,7 +404,7 @@ public:
 		for (uint32_t s=0; s<m_keys.size(); ++s)
 		{
 			const std::vector<int> cur = m_keys[s];	// copy: m_keys grows
-			int pk = cur[0]; bool initial = cur[1] != 0; int nacc = cur[2];
+			int pk = cur[0]; bool initial = cur[1] == 1; int nacc = cur[2];
 			std::vector<int> base( cur.begin()+3+nacc, cur.end());
 			for (std::size_t r=0; r<=m_runs.size(); ++r)
 			{
@@ -409,6 +412,7 @@ public:
 				int nk = eot ? (int)KindEdge : (int)kindOfByte( m_runs[r].first);
 				acc.clear();
 				expand( base, pk, nk, closure, (initial && !m_opt.allowEmpty) ? 0 : &acc);
+				std::size_t nold = closure.size();
 				if (m_opt.unanchored && !eot)
 				{
 					std::vector<int> fresh;
@@ -416,12 +420,13 @@ public:
 					closure.insert( closure.end(), fresh.begin(), fresh.end());
 				}
 				target.clear();
+				bool oldSurvives = false;
 				if (!eot)
 				{
 					unsigned int b = m_runs[r].first;
-					for (int c: closure)
+					for (std::size_t ci=0; ci<closure.size(); ++ci)
 					{
-						for (const ByteNfa::Edge& e: m_nfa.st[c].edges) if (e.lo <= b && b <= e.hi) target.push_back( e.to);
+						for (const ByteNfa::Edge& e: m_nfa.st[ closure[ci]].edges) if (e.lo <= b && b <= e.hi) {target.push_back( e.to); if (ci < nold) oldSurvives = true;}
 					}
 					std::sort( target.begin(), target.end());
 					target.erase( std::unique( target.begin(), target.end()), target.end());
@@ -431,7 +436,7 @@ public:
 				key.clear();
 				bool noFuture = target.empty() && (!m_opt.unanchored || eot);
 				key.push_back( (noFuture && acc.empty()) ? 0 : (eot ? (int)KindEdge : nk));
-				key.push_back( 0);
+				key.push_back( (m_opt.unanchored && m_opt.markCuts && !eot && !oldSurvives) ? 2 : 0);
 				key.push_back( (int)acc.size());
 				key.insert( key.end(), acc.begin(), acc.end());
 				key.insert( key.end(), target.begin(), target.end());
@@ -467,10 +472,12 @@ public:
 			dfa.next[ (std::size_t)s*dfa.stride() + dfa.nclasses] = rows[ (std::size_t)s*(nruns+1) + nruns];
 		}
 		dfa.accepts.resize( nstates);
+		dfa.cut.assign( nstates, 0);
 		for (uint32_t s=0; s<nstates; ++s)
 		{
 			const std::vector<int>& k = m_keys[s];
 			dfa.accepts[s].assign( k.begin()+3, k.begin()+3+k[2]);
+			dfa.cut[s] = (k[1] == 2);
 		}
 		return dfa;
 	}

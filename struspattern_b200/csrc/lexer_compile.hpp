@@ -265,14 +265,29 @@ private:
 
 	void buildForward( const ByteNfa& nfa, const std::vector<int>& entries)
 	{
-		DfaOptions opt; opt.unanchored = true; opt.allowEmpty = false; opt.maxStates = 65000;
-		Dfa dfa = DfaBuilder( nfa, entries, opt).build();
-		// renumber: states that report matches last, so that the scan loop tests `state >= fwd_acc_base`
+		// States reached by a transition that no older thread survived are told apart (Dfa::cut): behind such a byte no
+		// pending match reaches back in front of it, which is where the fused kernel closes a segment of events. If
+		// that split makes the automaton too large, it is built without (the lexer then runs the island pipeline only).
+		DfaOptions opt; opt.unanchored = true; opt.allowEmpty = false; opt.maxStates = 65000; opt.markCuts = true;
+		Dfa dfa;
+		try {dfa = DfaBuilder( nfa, entries, opt).build();}
+		catch (const DfaTooLarge&) {opt.markCuts = false; dfa = DfaBuilder( nfa, entries, opt).build();}
+		// renumber: [plain][plain, cut][reporting, cut][reporting] so that the scan loop tests `state >= fwd_acc_base`
+		// for matches and `state - fwd_cut_lo < fwd_cut_n` for cuts
 		std::vector<uint32_t> newid( dfa.nstates);
-		uint32_t nplain = 0;
-		for (uint32_t s=0; s<dfa.nstates; ++s) if (dfa.accepts[s].empty()) newid[s] = nplain++;
-		uint32_t nextid = nplain;
-		for (uint32_t s=0; s<dfa.nstates; ++s) if (!dfa.accepts[s].empty()) newid[s] = nextid++;
+		uint32_t nextid = 0, nplain = 0, cutlo = 0;
+		for (int group=0; group<4; ++group)
+		{
+			if (group == 1) cutlo = nextid;
+			if (group == 2) nplain = nextid;
+			for (uint32_t s=0; s<dfa.nstates; ++s)
+			{
+				bool acc = !dfa.accepts[s].empty(), cut = dfa.cut[s] != 0;
+				int g = acc ? (cut ? 2 : 3) : (cut ? 1 : 0);
+				if (g == group) newid[s] = nextid++;
+			}
+			if (group == 2) {m_tables.view.fwd_cut_lo = cutlo; m_tables.view.fwd_cut_n = nextid - cutlo;}
+		}
 		uint32_t stride = dfa.stride();
 		LexerTablesHost& T = m_tables;
 		T.fwd_next.resize( (std::size_t)dfa.nstates * stride);
@@ -289,6 +304,8 @@ private:
 			for (uint32_t p: acc[a]) T.fwd_acc_pat.push_back( (uint16_t)p);	// ascending definition index = canonical event order
 		}
 		T.fwd_acc_off[ acc.size()] = (uint32_t)T.fwd_acc_pat.size();
+		T.view.fwd_max_acc = 0;
+		for (std::size_t a=0; a<acc.size(); ++a) if (acc[a].size() > T.view.fwd_max_acc) T.view.fwd_max_acc = (uint32_t)acc[a].size();
 		T.fwd_class.assign( dfa.byteclass, dfa.byteclass + 256);
 		T.view.fwd_states = dfa.nstates;
 		T.view.fwd_stride = stride;

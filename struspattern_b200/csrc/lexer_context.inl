@@ -11,7 +11,11 @@ struct sp_lexer_ctx
 	DeviceBuffer text, doc_off, start_state, end_state, ev_count, known, redo, scalars, ev_off, events, doc_ev_begin,
 		     ar, doc_kept, doc_nlex, lex_off, lexems, status, scantmp,
 		     ev_doc, isl_flags, tile_nisl, tile_isl_off, isl_start, isl_kept, isl_off, elem, elem_doc, doc_has_content,
-		     doc_elem_begin, aggmax, aggmin, aggord, slots, doc_first_content, fix_list, doc_base;
+		     doc_elem_begin, aggmax, aggmin, aggord, slots, doc_first_content, fix_list, doc_base,
+		     f_region, f_kept, f_agg, f_lead, f_inctail, f_docstart, f_prefix, f_doc_chunk, f_doc_local, f_succ;
+	bool fused;		// SP_LEXER_FUSED=0 switches the fused segment kernel off (island/slot pipeline for every batch)
+	uint64_t fused_batches, fused_fallbacks;
+	bool last_fused;
 	bool dense;		// SP_LEXER_DENSE=1: first island pipeline (two resolution passes, dense elements, three scans)
 	bool sequential;	// SP_LEXER_SEQUENTIAL=1: one thread per document for resolution and ordinal positions (A/B check)
 	uint64_t nisl, nelem;
@@ -21,7 +25,7 @@ struct sp_lexer_ctx
 	bool valid;
 	uint64_t* pinned;	// [4] host staging for scalar read backs
 	// optional per kernel timing with CUDA events on the context's stream (SP_LEXER_PROFILE=1 or counter "profile:on")
-	enum KernelId {KCount, KVerify, KEmit, KFinish, KResolve, KWrite, KScan, KIslFlags, KIslResolve, KOrdpos, KIslSlots, KSlotScan, NofKernelIds};
+	enum KernelId {KCount, KVerify, KEmit, KFinish, KResolve, KWrite, KScan, KIslFlags, KIslResolve, KOrdpos, KIslSlots, KSlotScan, KFused, KFusedScan, KFusedWrite, NofKernelIds};
 	struct Span {int kernel; cudaEvent_t a, b;};
 	bool profile;
 	std::vector<Span> spans;
@@ -64,6 +68,9 @@ struct sp_lexer_ctx
 		if (std::getenv( "SP_LEXER_PROFILE")) profile = true;
 		sequential = std::getenv( "SP_LEXER_SEQUENTIAL") != 0;
 		dense = std::getenv( "SP_LEXER_DENSE") != 0;
+		const char* fe = std::getenv( "SP_LEXER_FUSED");
+		fused = !(fe && fe[0] == '0');
+		fused_batches = fused_fallbacks = 0; last_fused = false;
 		nisl = nelem = 0;
 		const char* e;
 		if ((e = std::getenv( "SP_LEXER_CHUNK")) != 0 && std::atoi( e) >= 16) chunk = (uint32_t)std::atoi( e);
@@ -107,6 +114,53 @@ struct sp_lexer_ctx
 		Q.isl_start = isl_start.as<uint32_t>( n + 1);
 		spanBegin( KIslFlags); k_isl_compact<<<(unsigned int)ntiles, TsThreads, 0, stream>>>( Q); spanEnd();
 		return n;
+	}
+
+	// fused segment pipeline (lexer_fused.cuh). Returns false if the batch needs the island pipeline.
+	bool resolveFused( const SpScanParams& P, uint64_t* d_lex_off)
+	{
+		const uint32_t M = P.ar_mult;
+		SpFusedParams F; std::memset( &F, 0, sizeof(F));
+		F.T = P.T; F.text = P.text; F.doc_off = P.doc_off; F.ndocs = ndocs; F.total = total; F.chunk = chunk; F.nchunks = nchunks;
+		F.start_state = P.start_state; F.ev_off = P.ev_off; F.ar_mult = M;
+		F.slots = slots.as<SpSlot>( nev * M + 1);
+		F.region_begin = f_region.as<uint64_t>( nchunks); F.kept = f_kept.as<uint32_t>( nchunks); F.agg = f_agg.as<uint64_t>( nchunks);
+		F.lead_pred = f_lead.as<uint32_t>( nchunks); F.inc_tail = f_inctail.as<uint32_t>( nchunks); F.has_docstart = f_docstart.as<uint8_t>( nchunks);
+		uint64_t* d_prefix = f_prefix.as<uint64_t>( nchunks + 1);
+		F.prefix = d_prefix;
+		F.doc_chunk = f_doc_chunk.as<uint32_t>( (std::size_t)ndocs + 1); F.doc_local = f_doc_local.as<uint64_t>( (std::size_t)ndocs + 1);
+		F.doc_has_content = doc_has_content.as<uint8_t>( (std::size_t)ndocs + 1); F.doc_succ_early = f_succ.as<uint8_t>( (std::size_t)ndocs + 1);
+		F.doc_base = doc_base.as<uint64_t>( (std::size_t)ndocs + 1); F.lex_off = d_lex_off;
+		uint64_t* d_scalars = (uint64_t*)scalars.ptr();
+		F.need_legacy = reinterpret_cast<uint32_t*>( d_scalars + 2);
+		SP_CUDA( cudaMemsetAsync( F.doc_chunk, 0, ((std::size_t)ndocs + 1) * sizeof(uint32_t), stream));
+		SP_CUDA( cudaMemsetAsync( F.doc_local, 0, ((std::size_t)ndocs + 1) * sizeof(uint64_t), stream));
+		SP_CUDA( cudaMemsetAsync( F.doc_has_content, 0, (std::size_t)ndocs + 1, stream));
+		SP_CUDA( cudaMemsetAsync( F.doc_succ_early, 0, (std::size_t)ndocs + 1, stream));
+		SP_CUDA( cudaMemsetAsync( d_scalars + 1, 0, 2 * sizeof(uint64_t), stream));
+		unsigned int grid = (unsigned int)((nchunks + LexFusedThreads - 1) / LexFusedThreads);
+		static bool smemSet = false;
+		if (!smemSet) {SP_CUDA( cudaFuncSetAttribute( k_lex_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LexFusedSmem)); smemSet = true;}
+		spanBegin( KFused); k_lex_fused<<<grid, LexFusedThreads, LexFusedSmem, stream>>>( F); spanEnd();
+		spanBegin( KFusedScan);
+		k_fused_fix<<<(unsigned int)((nchunks + 255) / 256), 256, 0, stream>>>( F);
+		AggScan f; f.agg = F.agg; f.prefix = d_prefix;
+		tileScan( f, nchunks, aggord.as<uint64_t>( (nchunks + TsTile - 1) / TsTile), stream, d_scalars + 1);
+		k_fused_docs<<<(ndocs + 1 + 255) / 256, 256, 0, stream>>>( F, d_scalars + 1);
+		spanEnd();
+		SP_CUDA( cudaMemcpyAsync( pinned, d_scalars + 1, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, stream));
+		SP_CUDA( cudaStreamSynchronize( stream));
+		if ((uint32_t)pinned[1]) {++fused_fallbacks; return false;}
+		nlex = pinned[0] >> 32;
+		F.lexems = lexems.as<sp_lexem>( nlex);
+		SP_CUDA( cudaMemsetAsync( P.status, 0, (std::size_t)ndocs * sizeof(uint32_t) + 4, stream));
+		spanBegin( KFusedWrite);
+		k_fused_write<<<(unsigned int)((nchunks + LexWriteThreads/32 - 1) / (LexWriteThreads/32)), LexWriteThreads, 0, stream>>>( F);
+		spanEnd();
+		SP_CUDA( cudaGetLastError());
+		nisl = nelem = 0;
+		++fused_batches;
+		return true;
 	}
 
 	// slot pipeline (lexer_islands.cuh): one resolution pass per island + one sum scan over the slots
@@ -231,6 +285,44 @@ struct sp_lexer_ctx
 		nlex = readScalar( d_scalars + 1, sizeof(uint64_t));
 	}
 
+	// island pipeline: raw events through HBM (emit, finish), then one of the three second halves
+	void resolveLegacy( SpScanParams& P, uint64_t* d_ev_off, uint64_t* d_doc_ev_begin, uint64_t* d_lex_off)
+	{
+		P.events = events.as<SpRawEvent>( nev);
+		SP_CUDA( cudaMemsetAsync( d_doc_ev_begin, 0, ((std::size_t)ndocs + 1) * sizeof(uint64_t), stream));
+		if (ndocs) SP_CUDA( cudaMemcpyAsync( d_doc_ev_begin + ndocs, d_ev_off + nchunks, sizeof(uint64_t), cudaMemcpyDeviceToDevice, stream));
+		if (nchunks)
+		{
+			unsigned int grid = (unsigned int)((nchunks + LexScanThreads - 1) / LexScanThreads);
+			spanBegin( KEmit); k_lex_emit<<<grid, LexScanThreads, 0, stream>>>( P); spanEnd();
+		}
+		P.ev_doc = ev_doc.as<uint32_t>( nev);
+		if (nev)
+		{
+			unsigned int grid = (unsigned int)((nev + LexEventThreads - 1) / LexEventThreads);
+			spanBegin( KFinish); k_lex_finish<<<grid, LexEventThreads, 0, stream>>>( P, nev); spanEnd();
+		}
+		if (sequential)
+		{
+			P.ar = ar.as<SpMatchEvent>( nev * P.ar_mult + 2);
+			if (ndocs)
+			{
+				unsigned int grid = (ndocs + LexDocThreads - 1) / LexDocThreads;
+				spanBegin( KResolve); k_lex_resolve<<<grid, LexDocThreads, 0, stream>>>( P); spanEnd();
+			}
+			spanBegin( KScan); exclusiveScan( P.doc_nlex, ndocs, d_lex_off, scantmp, stream); spanEnd();
+			nlex = readScalar( d_lex_off + ndocs, sizeof(uint64_t));
+			P.lexems = lexems.as<sp_lexem>( nlex);
+			if (ndocs)
+			{
+				unsigned int grid = (ndocs + LexDocThreads - 1) / LexDocThreads;
+				spanBegin( KWrite); k_lex_write<<<grid, LexDocThreads, 0, stream>>>( P); spanEnd();
+			}
+		}
+		else if (dense) resolveIslands( P, d_lex_off);
+		else resolveSlots( P, d_lex_off);
+	}
+
 	void scan( const uint8_t* text_in, int text_on_device, const uint64_t* doc_offsets, uint32_t ndocs_)
 	{
 		valid = false;
@@ -291,39 +383,9 @@ struct sp_lexer_ctx
 		}
 		spanBegin( KScan); exclusiveScan( P.ev_count, nchunks, d_ev_off, scantmp, stream); spanEnd();
 		nev = readScalar( d_ev_off + nchunks, sizeof(uint64_t));
-		P.events = events.as<SpRawEvent>( nev);
-		SP_CUDA( cudaMemsetAsync( d_doc_ev_begin, 0, ((std::size_t)ndocs + 1) * sizeof(uint64_t), stream));
-		if (ndocs) SP_CUDA( cudaMemcpyAsync( d_doc_ev_begin + ndocs, d_ev_off + nchunks, sizeof(uint64_t), cudaMemcpyDeviceToDevice, stream));
-		if (nchunks)
-		{
-			unsigned int grid = (unsigned int)((nchunks + LexScanThreads - 1) / LexScanThreads);
-			spanBegin( KEmit); k_lex_emit<<<grid, LexScanThreads, 0, stream>>>( P); spanEnd();
-		}
-		P.ev_doc = ev_doc.as<uint32_t>( nev);
-		if (nev)
-		{
-			unsigned int grid = (unsigned int)((nev + LexEventThreads - 1) / LexEventThreads);
-			spanBegin( KFinish); k_lex_finish<<<grid, LexEventThreads, 0, stream>>>( P, nev); spanEnd();
-		}
-		if (sequential)
-		{
-			P.ar = ar.as<SpMatchEvent>( nev * P.ar_mult + 2);
-			if (ndocs)
-			{
-				unsigned int grid = (ndocs + LexDocThreads - 1) / LexDocThreads;
-				spanBegin( KResolve); k_lex_resolve<<<grid, LexDocThreads, 0, stream>>>( P); spanEnd();
-			}
-			spanBegin( KScan); exclusiveScan( P.doc_nlex, ndocs, d_lex_off, scantmp, stream); spanEnd();
-			nlex = readScalar( d_lex_off + ndocs, sizeof(uint64_t));
-			P.lexems = lexems.as<sp_lexem>( nlex);
-			if (ndocs)
-			{
-				unsigned int grid = (ndocs + LexDocThreads - 1) / LexDocThreads;
-				spanBegin( KWrite); k_lex_write<<<grid, LexDocThreads, 0, stream>>>( P); spanEnd();
-			}
-		}
-		else if (dense) resolveIslands( P, d_lex_off);
-		else resolveSlots( P, d_lex_off);
+		last_fused = false;
+		if (fused && !sequential && !dense && nchunks && nev && P.T.fwd_cut_n && P.T.npat <= SP_FUSED_MAXPAT && P.T.fwd_max_acc + 1 <= SP_FUSED_BUF) last_fused = resolveFused( P, d_lex_off);
+		if (!last_fused) resolveLegacy( P, d_ev_off, d_doc_ev_begin, d_lex_off);
 		SP_CUDA( cudaGetLastError());
 		valid = true;
 	}
@@ -372,6 +434,9 @@ int64_t sp_lexer_ctx_counter( sp_lexer_ctx* ctx, const char* key)
 	if (k == "fixup_chunks") return (int64_t)ctx->fixups;
 	if (k == "fixup_rounds") return (int64_t)ctx->rounds;
 	if (k == "islands") return (int64_t)ctx->nisl;
+	if (k == "fused") return ctx->last_fused ? 1 : 0;
+	if (k == "fused_batches") return (int64_t)ctx->fused_batches;
+	if (k == "fused_fallbacks") return (int64_t)ctx->fused_fallbacks;
 	if (k == "elements") return (int64_t)ctx->nelem;
 	if (k == "text_bytes") return (int64_t)ctx->total;
 	if (k == "ndocs") return ctx->valid ? (int64_t)ctx->ndocs : -1;
@@ -381,7 +446,8 @@ int64_t sp_lexer_ctx_counter( sp_lexer_ctx* ctx, const char* key)
 	if (k == "profile:reset") {std::memset( ctx->kernel_ms, 0, sizeof(ctx->kernel_ms)); std::memset( ctx->kernel_calls, 0, sizeof(ctx->kernel_calls)); return 0;}
 	if (k.compare( 0, 8, "time_us:") == 0 || k.compare( 0, 6, "calls:") == 0)
 	{
-		static const char* names[] = {"k_lex_count","k_lex_verify","k_lex_emit","k_lex_finish","k_lex_resolve","k_lex_write","k_scan","k_isl_flags","k_isl_resolve","k_ordpos","k_isl_slots","k_slot_scan"};
+		static const char* names[] = {"k_lex_count","k_lex_verify","k_lex_emit","k_lex_finish","k_lex_resolve","k_lex_write","k_scan","k_isl_flags","k_isl_resolve","k_ordpos","k_isl_slots","k_slot_scan","k_lex_fused","k_fused_scan","k_fused_write"};
+		static_assert( sizeof(names)/sizeof(names[0]) == sp_lexer_ctx::NofKernelIds, "kernel name table out of date");
 		if (cudaStreamSynchronize( ctx->stream) != cudaSuccess) return -1;
 		try {ctx->collectSpans();} catch (...) {return -1;}
 		bool calls = k[0] == 'c';
@@ -395,6 +461,8 @@ int64_t sp_lexer_ctx_counter( sp_lexer_ctx* ctx, const char* key)
 	if (k == "kernel_launches")
 	{
 		// count, verify (+2 per repair round), 3 scan, emit, finish; then the chosen second half
+		// fused: count, verify (+2 per repair round), 3 scan, fused, fix, 3 scan, docs, write
+		if (ctx->last_fused) return 1 + 1 + 2*(int64_t)ctx->rounds + 3 + 1 + 1 + 3 + 1 + 1;
 		int64_t first = 1 + 1 + 2*(int64_t)ctx->rounds + 3 + 1 + 1;
 		if (ctx->sequential) return first + 1 + 3 + 1;
 		if (ctx->dense) return first + 8 + 1 + 3 + 1 + 9 + 1;

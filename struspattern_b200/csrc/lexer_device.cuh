@@ -167,6 +167,49 @@ SP_HD uint32_t sp_leftmost_start( const SpLexerTables& T, const SpPatternInfo& P
 	return from;
 }
 
+// The same with a memo of the last walk of the definition (exact: the reverse automaton is deterministic). A run of
+// matches of one definition that end at consecutive offsets ("h", "he", "hel", ...) would walk back over the whole
+// match for every end offset; but as soon as the walk from `to` is, behind the byte in front of the memorized end offset,
+// in the row the memorized walk was in at that place, the rest of the two walks is the same and its outcome is known.
+typedef struct SpStartMemo
+{
+	uint32_t pat;		/* definition (SP_NO_POS = empty) */
+	uint32_t to;		/* end offset the memorized walk started from (same document) */
+	uint32_t row1;		/* its row behind the first byte (SP_NO_POS: it stopped there) */
+	uint32_t fromAfter;	/* its result counting only starts reported behind the first byte (SP_NO_POS: none) */
+} SpStartMemo;
+
+SP_HD uint32_t sp_leftmost_start_memo( const SpLexerTables& T, uint32_t pat, const SpPatternInfo& P, const uint8_t* doc, uint32_t doclen, uint32_t to, SpStartMemo& m)
+{
+	const uint32_t pk = (to < doclen) ? sp_kind_of_byte( SP_LDG( doc + to)) : 3;
+	uint32_t row = P.rev_init[ pk];
+	const uint8_t* cls = T.rev_classes + P.rev_class;
+	const bool usable = m.pat == pat && m.to < to;
+	const uint32_t mto = m.to, mrow1 = m.row1, mfrom = m.fromAfter;
+	uint32_t from = SP_NO_POS, fromAfter = SP_NO_POS, row1 = SP_NO_POS;
+	uint32_t i = to;
+	for (; i>0; --i)
+	{
+		const uint32_t e = SP_LDG( T.rev_next + row + SP_LDG( cls + SP_LDG( doc + i - 1)));
+		if (e & SP_REV_ACCEPT) {from = i; if (i != to) fromAfter = i;}
+		if (e & SP_REV_STOP) break;
+		row = e & SP_REV_ROWMASK;
+		if (i == to) row1 = row;
+		if (usable && i == mto && row == mrow1)
+		{
+			if (mfrom != SP_NO_POS) from = fromAfter = mfrom;
+			break;
+		}
+	}
+	if (i == 0)
+	{
+		const uint32_t e = SP_LDG( T.rev_next + row + (P.rev_stride-1));
+		if (e & SP_REV_ACCEPT) {from = 0; if (to) fromAfter = 0;}
+	}
+	m.pat = pat; m.to = to; m.row1 = row1; m.fromAfter = fromAfter;
+	return from;
+}
+
 // ---- capture selection (libtre re-match of the reference restated with anchored automata)
 // true if the automaton matches exactly doc[a,b) with the real neighbours visible to assertions
 SP_HD bool sp_cap_span( const SpLexerTables& T, const SpAnchoredDfa& A, const uint8_t* doc, uint32_t doclen, uint32_t a, uint32_t b)
@@ -251,16 +294,22 @@ SP_HD uint32_t sp_symbol_lookup( const SpLexerTables& T, uint32_t symtab, const 
 	}
 }
 
-// Completes one raw event: leftmost start, size check, sub expression selection, symbol.
-SP_HD void sp_finish_event( const SpLexerTables& T, SpRawEvent& ev, const uint8_t* doc, uint32_t doclen)
+// Completes one raw event whose leftmost start is known: size check, sub expression selection, symbol.
+SP_HD void sp_finish_event_from( const SpLexerTables& T, const SpPatternInfo& P, SpRawEvent& ev, uint32_t from, const uint8_t* doc, uint32_t doclen)
 {
-	const SpPatternInfo P = T.pat[ ev.pat];
-	uint32_t from = sp_leftmost_start( T, P, doc, doclen, ev.to), to = ev.to;
+	uint32_t to = ev.to;
 	ev.aux = 0;
 	if (from == SP_NO_POS || to - from >= 65535) {ev.pat = SP_PAT_SIZEERROR; ev.from = 0; return;}	// src/patternLexer.cpp:727-730
 	if (P.resultidx && !sp_select_subexpression( T, P, doc, doclen, from, to)) {ev.pat = SP_PAT_DROPPED; ev.from = from; return;}
 	ev.from = from; ev.to = to;
 	if (P.symtab) ev.aux = sp_symbol_lookup( T, P.symtab, doc + from, to - from);
+}
+
+// Completes one raw event: leftmost start, size check, sub expression selection, symbol.
+SP_HD void sp_finish_event( const SpLexerTables& T, SpRawEvent& ev, const uint8_t* doc, uint32_t doclen)
+{
+	const SpPatternInfo P = T.pat[ ev.pat];
+	sp_finish_event_from( T, P, ev, sp_leftmost_start( T, P, doc, doclen, ev.to), doc, doclen);
 }
 
 SP_HD SpMatchEvent sp_make_match_event( uint32_t id, const SpPatternInfo& P, uint32_t from, uint32_t to)
@@ -270,7 +319,8 @@ SP_HD SpMatchEvent sp_make_match_event( uint32_t id, const SpPatternInfo& P, uin
 }
 
 // match_event_handler (src/patternLexer.cpp:746-822) for one completed event on the array ar[0..n).
-SP_HD void sp_supersede( const SpLexerTables& T, const SpRawEvent& rev, SpMatchEvent* ar, uint32_t& n)
+template <class EventArray>	/* SpMatchEvent* or an accessor with operator[] (lexer_fused.cuh) */
+SP_HD void sp_supersede( const SpLexerTables& T, const SpRawEvent& rev, EventArray ar, uint32_t& n)
 {
 	const SpPatternInfo P = T.pat[ rev.pat];
 	SpMatchEvent ev = sp_make_match_event( P.id, P, rev.from, rev.to);

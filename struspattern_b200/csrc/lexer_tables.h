@@ -53,6 +53,9 @@ typedef struct SpLexerTables
 	uint32_t fwd_stride;
 	uint32_t fwd_init;
 	uint32_t fwd_acc_base;		/* states >= fwd_acc_base report matches */
+	uint32_t fwd_cut_lo;		/* states in [fwd_cut_lo, fwd_cut_lo+fwd_cut_n): every match still pending started at the byte just consumed or later */
+	uint32_t fwd_cut_n;		/* 0 = automaton built without cut states (fused kernel not usable) */
+	uint32_t fwd_max_acc;		/* largest number of definitions one state reports */
 	/* reverse automata, one per definition */
 	const uint32_t* rev_next;	/* entries: absolute row offset | SP_REV_ACCEPT | SP_REV_STOP */
 	const uint8_t* rev_classes;

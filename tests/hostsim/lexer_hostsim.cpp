@@ -5,8 +5,10 @@
 #include <cstdint>
 #include <cstring>
 struct uint4 {uint32_t x, y, z, w;};
+struct uint2 {uint32_t x, y;};
 #include "lexer_compile.hpp"
 #include "lexer_device.cuh"
+#include "lexer_fused.cuh"
 #include <vector>
 #include <string>
 
@@ -21,9 +23,9 @@ struct HostSim
 	std::vector<SpRawEvent> events;
 	std::vector<uint64_t> doc_ev_begin;
 	uint64_t fixups, rounds;
-	int mode;	// 0: one loop per document (reference order), 1: island + slot formulation
-	uint64_t nislands, nfixed;
-	HostSim() :fixups(0),rounds(0),mode(0),nislands(0),nfixed(0){}
+	int mode;	// 0: one loop per document (reference order), 1: island + slot formulation, 2: fused segment formulation
+	uint64_t nislands, nfixed, fused, legacy, cutstates, leadfixed;
+	HostSim() :fixups(0),rounds(0),mode(0),nislands(0),nfixed(0),fused(0),legacy(0),cutstates(0),leadfixed(0){}
 };
 }
 
@@ -57,6 +59,10 @@ int64_t hsim_info( void* h, const char* key)
 	if (k == "raw_events") return (int64_t)hs->events.size();
 	if (k == "islands") return (int64_t)hs->nislands;
 	if (k == "fixed_islands") return (int64_t)hs->nfixed;
+	if (k == "fused") return (int64_t)hs->fused;
+	if (k == "fused_legacy") return (int64_t)hs->legacy;
+	if (k == "lead_fixed") return (int64_t)hs->leadfixed;
+	if (k == "cut_states") return (int64_t)hs->prog.tables().view.fwd_cut_n;
 	return -1;
 }
 
@@ -102,7 +108,46 @@ int hsim_scan_batch( void* h, const uint8_t* text, const uint64_t* doc_off, uint
 	hs->status.assign( ndocs, 0);
 	uint32_t dummy = 0;
 	P.ar = ar.data(); P.doc_kept = doc_kept.data(); P.doc_nlex = doc_nlex.data(); P.status = ndocs ? hs->status.data() : &dummy;
-	if (hs->mode == 0)
+	hs->fused = 0; hs->legacy = 0; hs->leadfixed = 0;
+	bool fusedDone = false;
+	if (hs->mode == 2 && P.T.fwd_cut_n && P.T.npat <= SP_FUSED_MAXPAT && P.nchunks && P.T.fwd_max_acc + 1 <= SP_FUSED_BUF)
+	{
+		// the fused segment pipeline of lexer_fused.cuh as plain loops (same per-thread functions as the kernels)
+		const uint64_t nch = P.nchunks;
+		std::vector<SpSlot> slots( nev * P.ar_mult + 1);
+		std::vector<uint64_t> region_begin( nch), agg( nch), prefix( nch + 1, 0), doc_local( ndocs + 1, 0), doc_base( ndocs + 1, 0);
+		std::vector<uint32_t> kept( nch), lead_pred( nch), inc_tail( nch), doc_chunk( ndocs + 1, 0);
+		std::vector<uint8_t> has_docstart( nch), has_content( ndocs + 1, 0), succ_early( ndocs + 1, 0);
+		uint32_t need_legacy = 0;
+		SpFusedParams F; std::memset( &F, 0, sizeof(F));
+		F.T = P.T; F.text = text; F.doc_off = doc_off; F.ndocs = ndocs; F.total = P.total; F.chunk = chunk; F.nchunks = nch;
+		F.start_state = start_state.data(); F.ev_off = ev_off.data(); F.ar_mult = P.ar_mult; F.slots = slots.data();
+		F.region_begin = region_begin.data(); F.kept = kept.data(); F.agg = agg.data(); F.lead_pred = lead_pred.data();
+		F.inc_tail = inc_tail.data(); F.has_docstart = has_docstart.data(); F.prefix = prefix.data();
+		F.doc_chunk = doc_chunk.data(); F.doc_local = doc_local.data(); F.doc_has_content = has_content.data();
+		F.doc_succ_early = succ_early.data(); F.doc_base = doc_base.data(); F.lex_off = lex_off.data(); F.need_legacy = &need_legacy;
+		for (uint64_t j=0; j<nch; ++j)
+		{
+			uint32_t buf[ SP_FUSED_BUF]; SpMatchEvent arlocal[ SP_FUSED_AR]; SpStartMemo memo[ SP_FUSED_MEMO];
+			SpStridedEvents ar; ar.base = arlocal; ar.stride = 1;
+			spk_fused_chunk( F, j, buf, 1, ar, memo);
+		}
+		for (uint64_t j=0; j<nch; ++j) {uint32_t before = lead_pred[ j]; spk_fused_fix_chunk( F, j); if (before) hs->leadfixed += 1;}
+		for (uint64_t j=0; j<nch; ++j) prefix[ j+1] = prefix[ j] + agg[ j];
+		for (uint32_t d=0; d<=ndocs; ++d) spk_fused_doc( F, d, prefix[ nch]);
+		if (need_legacy) hs->legacy = 1;
+		else
+		{
+			hs->lexems.assign( (prefix[ nch] >> 32) + 1, sp_lexem());
+			F.lexems = hs->lexems.data();
+			for (uint64_t j=0; j<nch; ++j) spk_fused_write_chunk( F, j);
+			hs->lexems.resize( prefix[ nch] >> 32);
+			hs->fused = 1;
+			fusedDone = true;
+		}
+	}
+	if (fusedDone) {}
+	else if (hs->mode == 0)
 	{
 		for (uint32_t d=0; d<ndocs; ++d) spk_resolve_doc( P, d);
 		for (uint32_t d=0; d<ndocs; ++d) lex_off[ d+1] = lex_off[ d] + doc_nlex[ d];

@@ -16,7 +16,7 @@ HS_LIB = os.path.join(HS_DIR, "_build", "libsp_hostsim.so")
 def build_hostsim(force=False):
     srcs = [os.path.join(HS_DIR, "lexer_hostsim.cpp")] + [
         os.path.join(ROOT, "struspattern_b200", "csrc", f)
-        for f in ("regex.hpp", "automaton.hpp", "lexer_compile.hpp", "lexer_device.cuh", "lexer_tables.h")]
+        for f in ("regex.hpp", "automaton.hpp", "lexer_compile.hpp", "lexer_device.cuh", "lexer_fused.cuh", "lexer_tables.h")]
     if not force and os.path.exists(HS_LIB) and all(os.path.getmtime(HS_LIB) >= os.path.getmtime(s) for s in srcs):
         return
     os.makedirs(os.path.dirname(HS_LIB), exist_ok=True)
@@ -43,7 +43,7 @@ class HostSimLexer:
     def __init__(self, chunk=64, warmup=16, mode=1):
         self.L = self.lib()
         self.h = C.c_void_p(self.L.hsim_create())
-        self.L.hsim_set_mode(self.h, C.c_int(mode))  # 0: per document loop, 1: island + slot formulation
+        self.L.hsim_set_mode(self.h, C.c_int(mode))  # 0: per document loop, 1: island + slot formulation, 2: fused segments
         self.chunk, self.warmup = chunk, warmup
 
     def __del__(self):

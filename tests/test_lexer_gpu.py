@@ -130,3 +130,66 @@ def test_large_islands_use_their_slot_range():
     text = (b"ab cd ef gh " * 40 + b". ") * 20
     offs = [0, len(text) // 2 + 3, len(text)]
     _same(o.scan(text, offs), g.scan(text, offs))
+
+
+# ---------------------------------------------------------------------------------------------------------
+# Fused segment kernel (k_lex_fused / k_fused_fix / k_fused_docs / k_fused_write): default second half.
+@pytest.mark.parametrize("name", sorted(LEXEM_SETS))
+@pytest.mark.parametrize("chunk", [16, 48, 512])
+def test_fused_kernel_matches_oracle(name, chunk, monkeypatch):
+    monkeypatch.setenv("SP_LEXER_CHUNK", str(chunk))
+    monkeypatch.setenv("SP_LEXER_WARMUP", str(max(4, chunk // 8)))
+    o = define_set(OracleLexer(), name)
+    g = define_set(_gpu_lexer()(), name)
+    ctx = g.create_context()
+    text, offs = make_batch(seed=chunk + 31 * len(name), ndocs=200, mean_bytes=1500)
+    _same(o.scan(text, offs, nthreads=8), ctx.scan(text, offs))
+    assert ctx.counter("chunk_bytes") == chunk
+    if name != "no_boundaries":
+        assert ctx.counter("fused") == 1 and ctx.counter("fused_fallbacks") == 0
+    ctx.close()
+
+
+def test_fused_kernel_equals_island_pipeline_on_the_bench_lexem_set(monkeypatch):
+    import sys, os
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from struspattern_b200 import workloads as W
+    from bench_util import corpus
+    g = W.define_lexer(_gpu_lexer()())
+    vocab = corpus.vocabulary(11, 5000, W.PHRASE_FIRST + W.PHRASE_SECOND + W.ABBREVIATIONS)
+    nbytes = 8 << 20
+    offs = corpus.layout(12, nbytes)
+    text = np.zeros(nbytes, dtype=np.uint8)
+    corpus.fill(12, vocab, text, offs)
+    ctx = g.create_context()
+    rf = ctx.scan(text, offs)
+    assert ctx.counter("fused") == 1
+    ctx.close()
+    monkeypatch.setenv("SP_LEXER_FUSED", "0")
+    ctx = g.create_context()
+    rl = ctx.scan(text, offs)
+    assert ctx.counter("fused") == 0
+    ctx.close()
+    _same(rl, rf)
+    o = W.define_lexer(OracleLexer())
+    nd = 40
+    ro = o.scan(text[:int(offs[nd])], offs[:nd + 1], nthreads=8)
+    assert (ro["lexems"] == rf["lexems"][:len(ro["lexems"])]).all() and (ro["offsets"] == rf["offsets"][:nd + 1]).all()
+
+
+def test_fused_kernel_falls_back_to_the_island_pipeline():
+    cases = [
+        ([(1, r"[a-z]+", 0, 0, 0), (3, r"#", 0, 0, 1)], [b"# # #", b"ab # cd"]),
+        ([(1, r"x([0-9]*)y", 1, 0, 0), (2, r"[a-z]+", 0, 0, 0)], [b"ab xy x12y cd xy"]),
+    ]
+    for defs, docs in cases:
+        offs = np.cumsum([0] + [len(d) for d in docs]).astype(np.uint64)
+        o, g = OracleLexer(), _gpu_lexer()()
+        for lx in (o, g):
+            for d in defs:
+                lx.define_lexem(*d)
+            lx.compile()
+        ctx = g.create_context()
+        _same(o.scan(b"".join(docs), offs), ctx.scan(b"".join(docs), offs))
+        assert ctx.counter("fused") == 0 and ctx.counter("fused_fallbacks") == 1
+        ctx.close()

@@ -138,3 +138,81 @@ def test_per_document_loop_still_matches(name):
     text, offs = make_batch(seed=77, ndocs=20, mean_bytes=300)
     ro, rh = o.scan(text, offs), h.scan(text, offs)
     assert (ro["offsets"] == rh["offsets"]).all() and (ro["lexems"] == rh["lexems"]).all()
+
+
+# ---------------------------------------------------------------------------------------------------------
+# Fused segment formulation (lexer_fused.cuh, mode 2): the same per-thread functions the kernels k_lex_fused,
+# k_fused_fix, k_fused_docs and k_fused_write run.
+@pytest.mark.parametrize("name", sorted(LEXEM_SETS))
+@pytest.mark.parametrize("chunk,warmup", [(16, 4), (48, 16), (512, 64)])
+def test_fused_segments_match_oracle(name, chunk, warmup):
+    o = define_set(OracleLexer(), name)
+    h = define_set(HostSimLexer(chunk=chunk, warmup=warmup, mode=2), name)
+    assert h.info("cut_states") > 0
+    for seed in (1, 2):
+        text, offs = make_batch(seed=seed * 7919 + chunk + len(name), ndocs=40, mean_bytes=300)
+        ro, rh = o.scan(text, offs, nthreads=4), h.scan(text, offs)
+        assert (ro["status"] == rh["status"]).all() and (ro["offsets"] == rh["offsets"]).all()
+        assert len(ro["lexems"]) == len(rh["lexems"]) and (ro["lexems"] == rh["lexems"]).all()
+        # every set except the one with BindUnique lexems stays on the fused path
+        if name != "no_boundaries":
+            assert h.info("fused") == 1 and h.info("fused_legacy") == 0
+
+
+def test_fused_leading_predecessor_elements_are_decided_by_the_ranges_in_front():
+    """Punctuation (BindPredecessor) at the begin of a thread's range is emitted iff its document has a content
+    element before: documents that start with punctuation runs longer than a chunk exercise the look back."""
+    defs = [(1, r"[a-z]+", 0, 0, 0), (2, r"[.,;]", 0, 0, 2), (3, r"#", 0, 0, 1)]
+    docs = [b". , ; . , ; . , ; . , ; . , ; ab . , ; . , ; . , ; . , ; cd .", b", , , , , , , , , , , , , , , , ,",
+            b"ab" + b" ." * 40, b"# # . . ab , #", b"", b". ." * 30 + b" x" + b" ;" * 30]
+    offs = np.cumsum([0] + [len(d) for d in docs]).astype(np.uint64)
+    text = b"".join(docs)
+    o = OracleLexer()
+    for d in defs:
+        o.define_lexem(*d)
+    o.compile()
+    ro = o.scan(text, offs)
+    for chunk in (8, 16, 32, 512):
+        h = HostSimLexer(chunk=chunk, warmup=4, mode=2)
+        for d in defs:
+            h.define_lexem(*d)
+        h.compile()
+        rh = h.scan(text, offs)
+        assert (ro["offsets"] == rh["offsets"]).all() and (ro["lexems"] == rh["lexems"]).all()
+        assert h.info("fused") == 1
+        if chunk <= 32:
+            assert h.info("lead_fixed") > 0
+
+
+def test_fused_falls_back_where_it_must():
+    """Successor elements in a document without content, long chains of overlapping matches, empty selected sub
+    expressions and oversized terms are answered by the island pipeline (fused_legacy) with the oracle's output."""
+    cases = [
+        ([(1, r"[a-z]+", 0, 0, 0), (3, r"#", 0, 0, 1)], [b"# # #", b"ab # cd"]),
+        ([(1, r"[a-z]+ [a-z]+", 0, 1, 0), (2, r"[a-z]+", 0, 0, 0), (3, r"[a-z]+ [a-z]+ [a-z]+", 0, 2, 0)], [(b"ab cd ef gh " * 40 + b". ") * 3]),
+        ([(1, r"x([0-9]*)y", 1, 0, 0), (2, r"[a-z]+", 0, 0, 0)], [b"ab xy x12y cd xy"]),
+    ]
+    for defs, docs in cases:
+        offs = np.cumsum([0] + [len(d) for d in docs]).astype(np.uint64)
+        text = b"".join(docs)
+        o, h = OracleLexer(), HostSimLexer(chunk=32, warmup=8, mode=2)
+        for lx in (o, h):
+            for d in defs:
+                lx.define_lexem(*d)
+            lx.compile()
+        ro, rh = o.scan(text, offs), h.scan(text, offs)
+        assert (ro["offsets"] == rh["offsets"]).all() and (ro["lexems"] == rh["lexems"]).all()
+        assert h.info("fused_legacy") == 1 and h.info("fused") == 0
+
+
+def test_fused_golden_case_and_symbol_quirk():
+    case = _golden_cases()[0]
+    lx = build_case(lambda: HostSimLexer(chunk=16, warmup=8, mode=2), case)
+    lx.compile()
+    assert lx.match(case["src_latin1"].encode("latin-1")) == [tuple(r) for r in case["results"]]
+    lx = HostSimLexer(chunk=512, warmup=8, mode=2)
+    lx.define_lexem(1, "[a-z]\\b", 0, 0, 0)
+    lx.define_lexem(2, "a b c\\b", 0, 0, 0)
+    lx.define_symbol(9, 2, "a b c")
+    lx.compile()
+    assert lx.match("a b c") == [(1, 1, 0, 1), (2, 1, 0, 5), (9, 1, 0, 5), (0, 1, 0, 0), (1, 2, 4, 1)]
