@@ -123,7 +123,7 @@ def cpu_lexer_rate(text, offs, seconds_target, nthreads):
 
 
 KERNELS = ["k_lex_count", "k_lex_verify", "k_lex_emit", "k_lex_finish", "k_lex_resolve", "k_lex_write", "k_scan",
-           "k_isl_flags", "k_isl_resolve", "k_ordpos", "k_isl_slots", "k_slot_scan", "k_lex_fused", "k_fused_scan", "k_fused_write"]
+           "k_isl_flags", "k_isl_resolve", "k_ordpos", "k_isl_slots", "k_slot_scan", "k_lex_fused", "k_fused_scan", "k_fused_write", "k_lex_resolve_chunks"]
 
 
 def algorithmic_bytes(kernel, c):
@@ -149,6 +149,8 @@ def algorithmic_bytes(kernel, c):
         "k_lex_fused": n_text + 16 * nlex + 42 * nchunks,
         "k_fused_scan": 40 * nchunks + 28 * ndocs,
         "k_fused_write": 32 * nlex + 20 * nchunks,
+        # chunk resolution over completed events (default): event + document id + segment flag read, kept elements written
+        "k_lex_resolve_chunks": 21 * nev + 16 * nlex + 42 * nchunks,
     }[kernel]
 
 
@@ -203,7 +205,7 @@ def run_ours(args, rank, world, local_rank):
     for _ in range(args.warmup):
         ctx.launch(dev_text.data_ptr(), offs, on_device=True)
         ctx.count()
-    counters = {k: ctx.counter(k) for k in ("raw_events", "lexems", "chunks", "fixup_chunks", "fixup_rounds", "text_bytes", "kernel_launches", "islands", "elements", "fused", "fused_fallbacks")}
+    counters = {k: ctx.counter(k) for k in ("raw_events", "lexems", "chunks", "fixup_chunks", "fixup_rounds", "text_bytes", "kernel_launches", "islands", "elements", "fused", "fused_fallbacks", "second_half")}
     counters["ndocs"] = ndocs
     counters["ar_mult"] = 2 if lx.table_info("symbols") else 1
     ctx.counter("profile:on"); ctx.counter("profile:reset")
@@ -320,7 +322,8 @@ def run_ours(args, rank, world, local_rank):
                    "lexems_per_step": counters["lexems"], "raw_events_per_step": counters["raw_events"],
                    "fwd_states": lx.table_info("fwd_states"), "fwd_table_bytes": lx.table_info("fwd_table_bytes"),
                    "fixup_chunks": counters["fixup_chunks"], "chunks": counters["chunks"],
-                   "second_half": "fused segment kernel" if counters["fused"] else "island/slot pipeline"},
+                   "second_half": {0: "per document loop", 1: "dense island pipeline", 2: "island/slot pipeline", 3: "fused segment kernel",
+                                   4: "chunk resolution over completed events"}.get(counters["second_half"], "?")},
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": int(args.bytes + 8 * (ndocs + 1)),
                 "d2h_bytes_per_step": int(16 * nlex + 8 * (ndocs + len(subs)) + 4 * ndocs), "steps": e2e_steps,

@@ -12,10 +12,12 @@ struct sp_lexer_ctx
 		     ar, doc_kept, doc_nlex, lex_off, lexems, status, scantmp,
 		     ev_doc, isl_flags, tile_nisl, tile_isl_off, isl_start, isl_kept, isl_off, elem, elem_doc, doc_has_content,
 		     doc_elem_begin, aggmax, aggmin, aggord, slots, doc_first_content, fix_list, doc_base,
-		     f_region, f_kept, f_agg, f_lead, f_inctail, f_docstart, f_prefix, f_doc_chunk, f_doc_local, f_succ;
+		     f_region, f_kept, f_agg, f_lead, f_inctail, f_docstart, f_prefix, f_doc_chunk, f_doc_local, f_succ, head;
+	bool hybrid;		// SP_LEXER_HYBRID=0: never resolve per chunk over the completed events (island/slot pipeline instead)
+	int last_path;		// second half of the last batch: 0 sequential, 1 dense islands, 2 slots, 3 fused, 4 chunk resolution
 	bool fused;		// SP_LEXER_FUSED=0 switches the fused segment kernel off (island/slot pipeline for every batch)
 	uint64_t fused_batches, fused_fallbacks;
-	bool last_fused;
+	bool last_fused, fusedGaveUp;
 	bool dense;		// SP_LEXER_DENSE=1: first island pipeline (two resolution passes, dense elements, three scans)
 	bool sequential;	// SP_LEXER_SEQUENTIAL=1: one thread per document for resolution and ordinal positions (A/B check)
 	uint64_t nisl, nelem;
@@ -25,7 +27,7 @@ struct sp_lexer_ctx
 	bool valid;
 	uint64_t* pinned;	// [4] host staging for scalar read backs
 	// optional per kernel timing with CUDA events on the context's stream (SP_LEXER_PROFILE=1 or counter "profile:on")
-	enum KernelId {KCount, KVerify, KEmit, KFinish, KResolve, KWrite, KScan, KIslFlags, KIslResolve, KOrdpos, KIslSlots, KSlotScan, KFused, KFusedScan, KFusedWrite, NofKernelIds};
+	enum KernelId {KCount, KVerify, KEmit, KFinish, KResolve, KWrite, KScan, KIslFlags, KIslResolve, KOrdpos, KIslSlots, KSlotScan, KFused, KFusedScan, KFusedWrite, KResolveChunks, NofKernelIds};
 	struct Span {int kernel; cudaEvent_t a, b;};
 	bool profile;
 	std::vector<Span> spans;
@@ -69,7 +71,10 @@ struct sp_lexer_ctx
 		sequential = std::getenv( "SP_LEXER_SEQUENTIAL") != 0;
 		dense = std::getenv( "SP_LEXER_DENSE") != 0;
 		const char* fe = std::getenv( "SP_LEXER_FUSED");
-		fused = !(fe && fe[0] == '0');
+		fused = (fe && fe[0] == '1');	// the fully fused scan kernel is correct but slower than emit + finish + chunk resolution
+		const char* he = std::getenv( "SP_LEXER_HYBRID");
+		hybrid = !(he && he[0] == '0');
+		last_path = -1;
 		fused_batches = fused_fallbacks = 0; last_fused = false;
 		nisl = nelem = 0;
 		const char* e;
@@ -117,7 +122,7 @@ struct sp_lexer_ctx
 	}
 
 	// fused segment pipeline (lexer_fused.cuh). Returns false if the batch needs the island pipeline.
-	bool resolveFused( const SpScanParams& P, uint64_t* d_lex_off)
+	bool resolveFused( const SpScanParams& P, uint64_t* d_lex_off, bool overEvents=false)
 	{
 		const uint32_t M = P.ar_mult;
 		SpFusedParams F; std::memset( &F, 0, sizeof(F));
@@ -133,15 +138,23 @@ struct sp_lexer_ctx
 		F.doc_base = doc_base.as<uint64_t>( (std::size_t)ndocs + 1); F.lex_off = d_lex_off;
 		uint64_t* d_scalars = (uint64_t*)scalars.ptr();
 		F.need_legacy = reinterpret_cast<uint32_t*>( d_scalars + 2);
-		SP_CUDA( cudaMemsetAsync( F.doc_chunk, 0, ((std::size_t)ndocs + 1) * sizeof(uint32_t), stream));
+		F.events = P.events; F.ev_doc = P.ev_doc; F.head = P.head; F.nev = nev;
+		SP_CUDA( cudaMemsetAsync( F.doc_chunk, overEvents ? 0xFF : 0, ((std::size_t)ndocs + 1) * sizeof(uint32_t), stream));
 		SP_CUDA( cudaMemsetAsync( F.doc_local, 0, ((std::size_t)ndocs + 1) * sizeof(uint64_t), stream));
 		SP_CUDA( cudaMemsetAsync( F.doc_has_content, 0, (std::size_t)ndocs + 1, stream));
 		SP_CUDA( cudaMemsetAsync( F.doc_succ_early, 0, (std::size_t)ndocs + 1, stream));
 		SP_CUDA( cudaMemsetAsync( d_scalars + 1, 0, 2 * sizeof(uint64_t), stream));
 		unsigned int grid = (unsigned int)((nchunks + LexFusedThreads - 1) / LexFusedThreads);
-		static bool smemSet = false;
-		if (!smemSet) {SP_CUDA( cudaFuncSetAttribute( k_lex_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LexFusedSmem)); smemSet = true;}
-		spanBegin( KFused); k_lex_fused<<<grid, LexFusedThreads, LexFusedSmem, stream>>>( F); spanEnd();
+		if (overEvents)
+		{
+			spanBegin( KResolveChunks); k_lex_resolve_chunks<<<grid, LexFusedThreads, 0, stream>>>( F); spanEnd();
+		}
+		else
+		{
+			static bool smemSet = false;
+			if (!smemSet) {SP_CUDA( cudaFuncSetAttribute( k_lex_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LexFusedSmem)); smemSet = true;}
+			spanBegin( KFused); k_lex_fused<<<grid, LexFusedThreads, LexFusedSmem, stream>>>( F); spanEnd();
+		}
 		spanBegin( KFusedScan);
 		k_fused_fix<<<(unsigned int)((nchunks + 255) / 256), 256, 0, stream>>>( F);
 		AggScan f; f.agg = F.agg; f.prefix = d_prefix;
@@ -160,6 +173,7 @@ struct sp_lexer_ctx
 		SP_CUDA( cudaGetLastError());
 		nisl = nelem = 0;
 		++fused_batches;
+		last_path = overEvents ? 4 : 3;
 		return true;
 	}
 
@@ -289,6 +303,9 @@ struct sp_lexer_ctx
 	void resolveLegacy( SpScanParams& P, uint64_t* d_ev_off, uint64_t* d_doc_ev_begin, uint64_t* d_lex_off)
 	{
 		P.events = events.as<SpRawEvent>( nev);
+		// (not tried again behind a fused scan that gave up: it would give up for the same reason)
+		const bool chunkResolution = hybrid && !sequential && !dense && nchunks && nev && P.T.fwd_cut_n && !fusedGaveUp;
+		P.head = chunkResolution ? head.as<uint32_t>( nchunks) : 0;
 		SP_CUDA( cudaMemsetAsync( d_doc_ev_begin, 0, ((std::size_t)ndocs + 1) * sizeof(uint64_t), stream));
 		if (ndocs) SP_CUDA( cudaMemcpyAsync( d_doc_ev_begin + ndocs, d_ev_off + nchunks, sizeof(uint64_t), cudaMemcpyDeviceToDevice, stream));
 		if (nchunks)
@@ -312,6 +329,7 @@ struct sp_lexer_ctx
 			}
 			spanBegin( KScan); exclusiveScan( P.doc_nlex, ndocs, d_lex_off, scantmp, stream); spanEnd();
 			nlex = readScalar( d_lex_off + ndocs, sizeof(uint64_t));
+			last_path = 0;
 			P.lexems = lexems.as<sp_lexem>( nlex);
 			if (ndocs)
 			{
@@ -319,8 +337,13 @@ struct sp_lexer_ctx
 				spanBegin( KWrite); k_lex_write<<<grid, LexDocThreads, 0, stream>>>( P); spanEnd();
 			}
 		}
-		else if (dense) resolveIslands( P, d_lex_off);
-		else resolveSlots( P, d_lex_off);
+		else if (dense) {resolveIslands( P, d_lex_off); last_path = 1;}
+		else if (chunkResolution && resolveFused( P, d_lex_off, true)) {}
+		else
+		{
+			if (chunkResolution && nev) k_evdoc_clear<<<(unsigned int)((nev + 255) / 256), 256, 0, stream>>>( P.ev_doc, nev);
+			resolveSlots( P, d_lex_off); last_path = 2;
+		}
 	}
 
 	void scan( const uint8_t* text_in, int text_on_device, const uint64_t* doc_offsets, uint32_t ndocs_)
@@ -384,7 +407,9 @@ struct sp_lexer_ctx
 		spanBegin( KScan); exclusiveScan( P.ev_count, nchunks, d_ev_off, scantmp, stream); spanEnd();
 		nev = readScalar( d_ev_off + nchunks, sizeof(uint64_t));
 		last_fused = false;
+		const uint64_t fallbacksBefore = fused_fallbacks;
 		if (fused && !sequential && !dense && nchunks && nev && P.T.fwd_cut_n && P.T.npat <= SP_FUSED_MAXPAT && P.T.fwd_max_acc + 1 <= SP_FUSED_BUF) last_fused = resolveFused( P, d_lex_off);
+		fusedGaveUp = !last_fused && fused_fallbacks != fallbacksBefore;
 		if (!last_fused) resolveLegacy( P, d_ev_off, d_doc_ev_begin, d_lex_off);
 		SP_CUDA( cudaGetLastError());
 		valid = true;
@@ -435,6 +460,7 @@ int64_t sp_lexer_ctx_counter( sp_lexer_ctx* ctx, const char* key)
 	if (k == "fixup_rounds") return (int64_t)ctx->rounds;
 	if (k == "islands") return (int64_t)ctx->nisl;
 	if (k == "fused") return ctx->last_fused ? 1 : 0;
+	if (k == "second_half") return ctx->last_path;
 	if (k == "fused_batches") return (int64_t)ctx->fused_batches;
 	if (k == "fused_fallbacks") return (int64_t)ctx->fused_fallbacks;
 	if (k == "elements") return (int64_t)ctx->nelem;
@@ -446,7 +472,7 @@ int64_t sp_lexer_ctx_counter( sp_lexer_ctx* ctx, const char* key)
 	if (k == "profile:reset") {std::memset( ctx->kernel_ms, 0, sizeof(ctx->kernel_ms)); std::memset( ctx->kernel_calls, 0, sizeof(ctx->kernel_calls)); return 0;}
 	if (k.compare( 0, 8, "time_us:") == 0 || k.compare( 0, 6, "calls:") == 0)
 	{
-		static const char* names[] = {"k_lex_count","k_lex_verify","k_lex_emit","k_lex_finish","k_lex_resolve","k_lex_write","k_scan","k_isl_flags","k_isl_resolve","k_ordpos","k_isl_slots","k_slot_scan","k_lex_fused","k_fused_scan","k_fused_write"};
+		static const char* names[] = {"k_lex_count","k_lex_verify","k_lex_emit","k_lex_finish","k_lex_resolve","k_lex_write","k_scan","k_isl_flags","k_isl_resolve","k_ordpos","k_isl_slots","k_slot_scan","k_lex_fused","k_fused_scan","k_fused_write","k_lex_resolve_chunks"};
 		static_assert( sizeof(names)/sizeof(names[0]) == sp_lexer_ctx::NofKernelIds, "kernel name table out of date");
 		if (cudaStreamSynchronize( ctx->stream) != cudaSuccess) return -1;
 		try {ctx->collectSpans();} catch (...) {return -1;}
@@ -462,7 +488,9 @@ int64_t sp_lexer_ctx_counter( sp_lexer_ctx* ctx, const char* key)
 	{
 		// count, verify (+2 per repair round), 3 scan, emit, finish; then the chosen second half
 		// fused: count, verify (+2 per repair round), 3 scan, fused, fix, 3 scan, docs, write
-		if (ctx->last_fused) return 1 + 1 + 2*(int64_t)ctx->rounds + 3 + 1 + 1 + 3 + 1 + 1;
+		if (ctx->last_path == 3) return 1 + 1 + 2*(int64_t)ctx->rounds + 3 + 1 + 1 + 3 + 1 + 1;
+		// chunk resolution: count, verify, 3 scan, emit, finish, resolve, fix, 3 scan, docs, write
+		if (ctx->last_path == 4) return 1 + 1 + 2*(int64_t)ctx->rounds + 3 + 1 + 1 + 1 + 1 + 3 + 1 + 1;
 		int64_t first = 1 + 1 + 2*(int64_t)ctx->rounds + 3 + 1 + 1;
 		if (ctx->sequential) return first + 1 + 3 + 1;
 		if (ctx->dense) return first + 8 + 1 + 3 + 1 + 9 + 1;

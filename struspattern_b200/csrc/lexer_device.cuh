@@ -67,7 +67,10 @@ struct SpCountSink
 		count += SP_LDG( T->fwd_acc_off + a + 1) - SP_LDG( T->fwd_acc_off + a);
 	}
 	SP_HD void docBegin( uint32_t) {}
+	SP_HD void cut() {}
 };
+
+#define SP_HEAD_NOCUT 0xFFFFFFFFu	/* chunk without a cut: all its events belong to a segment that began in front of it */
 
 struct SpEmitSink
 {
@@ -75,17 +78,22 @@ struct SpEmitSink
 	SpRawEvent* events;
 	uint64_t cursor;
 	uint64_t* doc_ev_begin;
+	uint32_t pendingCut, seenCut, head;	/* a cut lies between the next event and the one in front of it; events in front of the first cut */
 	SP_HD void accept( uint32_t state, uint32_t to, uint32_t doc)
 	{
 		uint32_t a = state - T->fwd_acc_base;
 		uint32_t pi = SP_LDG( T->fwd_acc_off + a), pe = SP_LDG( T->fwd_acc_off + a + 1);
 		for (; pi < pe; ++pi)
 		{
-			SpRawEvent ev; ev.pat = SP_LDG( T->fwd_acc_pat + pi); ev.from = SP_NO_POS; ev.to = to; ev.aux = doc;
+			// until the start is resolved `from` says whether the event is the first one behind a cut
+			SpRawEvent ev; ev.pat = SP_LDG( T->fwd_acc_pat + pi); ev.from = pendingCut; ev.to = to; ev.aux = doc;
+			pendingCut = 0;
+			if (!seenCut) ++head;
 			events[ cursor++] = ev;
 		}
 	}
 	SP_HD void docBegin( uint32_t doc) {doc_ev_begin[ doc] = cursor;}
+	SP_HD void cut() {pendingCut = 1; seenCut = 1;}
 };
 
 // Forward scan of the global byte range [begin,end) of the concatenated documents starting in `state`
@@ -117,6 +125,7 @@ SP_HD uint32_t sp_scan_range( const SpLexerTables& T, const uint8_t* text, const
 						uint32_t b = (w[wi] >> (8*bi)) & 0xFF;
 						state = SP_LDG( T.fwd_next + state * stride + SP_LDG( T.fwd_class + b));
 						if (state >= accbase) sink.accept( state, (uint32_t)(pos - dstart), d);
+						if ((state - T.fwd_cut_lo) < T.fwd_cut_n) sink.cut();
 						++pos;
 					}
 				}
@@ -126,6 +135,7 @@ SP_HD uint32_t sp_scan_range( const SpLexerTables& T, const uint8_t* text, const
 				uint32_t b = SP_LDG( text + pos);
 				state = SP_LDG( T.fwd_next + state * stride + SP_LDG( T.fwd_class + b));
 				if (state >= accbase) sink.accept( state, (uint32_t)(pos - dstart), d);
+						if ((state - T.fwd_cut_lo) < T.fwd_cut_n) sink.cut();
 				++pos;
 			}
 		}
@@ -134,6 +144,7 @@ SP_HD uint32_t sp_scan_range( const SpLexerTables& T, const uint8_t* text, const
 			// end of the document: the virtual end-of-text symbol reports the matches that end here
 			state = SP_LDG( T.fwd_next + state * stride + (stride-1));
 			if (state >= accbase) sink.accept( state, (uint32_t)(dend - dstart), d);
+			sink.cut();	// a document border closes every segment
 			state = T.fwd_init;
 			for (++d; d < ndocs; ++d)
 			{
@@ -456,12 +467,14 @@ typedef struct SpScanParams
 	const uint64_t* lex_off;	/* [ndocs+1] exclusive prefix sum of doc_nlex */
 	sp_lexem* lexems;
 	uint32_t* status;		/* [ndocs] */
+	uint32_t* head;			/* [nchunks] events of the chunk in front of its first cut, SP_HEAD_NOCUT if it has none */
 } SpScanParams;
 
 struct SpNullSink
 {
 	SP_HD void accept( uint32_t, uint32_t, uint32_t) {}
 	SP_HD void docBegin( uint32_t) {}
+	SP_HD void cut() {}
 };
 
 SP_HD void spk_count_chunk( const SpScanParams& P, uint64_t j, int round)
@@ -509,13 +522,16 @@ SP_HD void spk_emit_chunk( const SpScanParams& P, uint64_t j)
 {
 	uint64_t begin = j * P.chunk, end = begin + P.chunk < P.total ? begin + P.chunk : P.total;
 	SpEmitSink sink; sink.T = &P.T; sink.events = P.events; sink.cursor = P.ev_off[ j]; sink.doc_ev_begin = P.doc_ev_begin;
+	sink.head = 0;
+	sink.pendingCut = sink.seenCut = P.known[ j] ? 1 : 0;	// a chunk that starts with a document starts with a cut
 	sp_scan_range( P.T, P.text, P.doc_off, P.ndocs, begin, end, P.start_state[ j], sink);
+	if (P.head) P.head[ j] = sink.seenCut ? sink.head : SP_HEAD_NOCUT;
 }
 
 SP_HD void spk_finish_event( const SpScanParams& P, uint64_t i)
 {
 	SpRawEvent ev = P.events[ i];
-	if (P.ev_doc) P.ev_doc[ i] = ev.aux;
+	if (P.ev_doc) P.ev_doc[ i] = P.head ? (ev.aux | (ev.from << 31)) : ev.aux;	// chunk resolution: bit 31 = first event behind a cut
 	uint64_t dstart = SP_LDG( P.doc_off + ev.aux);
 	uint32_t doclen = (uint32_t)(SP_LDG( P.doc_off + ev.aux + 1) - dstart);
 	sp_finish_event( P.T, ev, P.text + dstart, doclen);

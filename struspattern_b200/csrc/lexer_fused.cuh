@@ -18,19 +18,20 @@
 // k_fused_write turns the kept elements into sp_lexem records (src/patternLexer.cpp:893-945).
 //
 // Not handled here (need_legacy is raised and the batch runs through the island pipeline instead): matched
-// terms of 65535 bytes or more, empty selected sub expressions, segments with more open elements than
-// SP_FUSED_AR or reaching further than SP_FUSED_MAXREL bytes, a BindUnique element as first element of a thread's
+// terms of 65535 bytes or more, empty selected sub expressions, segments reaching further than SP_FUSED_MAXREL bytes
+// behind the begin of their chunk (fused scan only), a BindUnique element as first element of a thread's
 // range, BindSuccessor elements in a document without content element.
 #ifndef SP_LEXER_FUSED_CUH_INCLUDED
 #define SP_LEXER_FUSED_CUH_INCLUDED
 #include "lexer_device.cuh"
 
 #define SP_FUSED_BUF 24			/* pending entries per thread */
-#define SP_FUSED_AR 16			/* elements of an open segment */
+#define SP_FUSED_AR 8			/* elements of an open segment kept in the thread's fast work memory */
 #define SP_FUSED_MEMO 4			/* memorized reverse walks per thread (power of two) */
 #define SP_FUSED_MAXREL 65000u		/* a thread never scans further than this behind the begin of its chunk */
 #define SP_FUSED_CUTMARK 0x80000000u	/* pending entry: segment ends here; else definition | relative end << 15 */
 #define SP_FUSED_MAXPAT 32767u
+#define SP_EVDOC_CUT 0x80000000u
 
 typedef struct SpFusedParams
 {
@@ -63,14 +64,26 @@ typedef struct SpFusedParams
 	uint64_t* lex_off;		/* [ndocs+1] */
 	uint32_t* need_legacy;
 	sp_lexem* lexems;
+	/* chunk resolution over completed events (spk_resolve_chunk) */
+	const SpRawEvent* events;	/* [nev] completed by the finish step */
+	const uint32_t* ev_doc;		/* [nev] document | SP_EVDOC_CUT if the event is the first one behind a cut */
+	const uint32_t* head;		/* [nchunks] */
+	uint64_t nev;
 } SpFusedParams;
 
 // Per thread work memory lives outside the thread state so that the kernel can keep it in shared memory, element i of
 // thread t at [i*stride + t]: all lanes of a warp hit different banks whatever their indices are.
+// Elements SP_FUSED_AR and up of an open segment (rare: long chains of overlapping matches) live in the slots they will
+// end up in: the segment's kept elements go to the slots from *out on, element k is read before slot k is written, and
+// the thread's slot range has room for ar_mult elements per event.
 struct SpStridedEvents
 {
 	SpMatchEvent* base; uint32_t stride;
-	SP_HD SpMatchEvent& operator[]( uint32_t i) const {return base[ (size_t)i * stride];}
+	SpSlot* slots; const uint64_t* out;
+	SP_HD SpMatchEvent& operator[]( uint32_t i) const
+	{
+		return i < SP_FUSED_AR ? base[ (size_t)i * stride] : reinterpret_cast<SpMatchEvent*>( slots + *out)[ i];
+	}
 };
 
 typedef struct SpFusedThread
@@ -110,7 +123,7 @@ SP_HD void sp_fused_finalize( const SpFusedParams& P, SpFusedThread& st)
 			if (k == 0 && st.prevUnknown && bind == SP_BIND_UNIQUE) st.legacy = 1;	// depends on the element in front of the range
 			const uint32_t f = sp_flags_next( fs, bind, e.origpos);
 			SpSlot s; s.id = e.id; s.origpos = e.origpos; s.info = (e.origsize & 0xFFFFu) | (bind << 16) | f; s.doc = st.doc;
-			sp_store_slot( P.slots + st.out++, s);
+			sp_store_slot( P.slots + st.out + k, s);	// st.out itself stays until the loop is through: the accessor refers to it
 			if (f & SP_SLOT_INC) {st.inc += 1; st.docinc += 1;}
 			if ((f & SP_SLOT_COUNTS) && st.contentDoc != st.doc) {P.doc_has_content[ st.doc] = 1; st.contentDoc = st.doc;}
 			switch (bind)
@@ -125,7 +138,7 @@ SP_HD void sp_fused_finalize( const SpFusedParams& P, SpFusedThread& st)
 					break;
 			}
 		}
-		st.nkept += st.n;
+		st.nkept += st.n; st.out += st.n;
 		st.prevBind = fs.prevBind; st.prevUnknown = 0;
 	}
 	st.n = 0; st.minStart = SP_NO_POS;
@@ -148,7 +161,7 @@ SP_HD void sp_fused_drain( const SpFusedParams& P, SpFusedThread& st)
 		*mp = m;
 		sp_finish_event_from( P.T, I, ev, from, st.docptr, st.doclen);
 		if (ev.pat == SP_PAT_DROPPED) continue;
-		if (ev.pat == SP_PAT_SIZEERROR || ev.from == ev.to || st.n + M > SP_FUSED_AR) {st.legacy = 1; continue;}
+		if (ev.pat == SP_PAT_SIZEERROR || ev.from == ev.to) {st.legacy = 1; continue;}
 		if (ev.from < st.minStart) st.minStart = ev.from;
 		sp_supersede( P.T, ev, st.ar, st.n);
 	}
@@ -221,7 +234,7 @@ SP_HD void sp_fused_set_doc( const SpFusedParams& P, SpFusedThread& st, SpFusedW
 // Start of the work of the thread of chunk j. buf: SP_FUSED_BUF entries, ar: SP_FUSED_AR elements (both strided).
 SP_HD void sp_fused_init( const SpFusedParams& P, uint64_t j, SpFusedThread& st, SpFusedWalk& w, uint32_t* buf, uint32_t bstride, SpStridedEvents ar, SpStartMemo* memo)
 {
-	st.buf = buf; st.bstride = bstride; st.ar = ar; st.memo = memo;
+	st.buf = buf; st.bstride = bstride; st.ar = ar; st.ar.slots = P.slots; st.ar.out = &st.out; st.memo = memo;
 	st.nbuf = 0; st.n = 0; st.minStart = SP_NO_POS;
 	st.prevBind = SP_BIND_CONTENT; st.prevUnknown = 0; st.docinc = 0; st.docSeenBegin = 0;
 	st.inc = st.emit = st.lead = st.nkept = 0; st.legacy = 0; st.contentDoc = 0xFFFFFFFFu;
@@ -320,6 +333,106 @@ SP_HD void spk_fused_chunk( const SpFusedParams& P, uint64_t j, uint32_t* buf, u
 	sp_fused_store( P, j, st, w);
 }
 
+// ------------------------------------------------------------------------------------------------
+// Chunk resolution over completed events: the second half of the fused formulation alone. The emit step has marked the
+// events behind a cut (bit 31 of ev_doc) and counted the events in front of the first cut of every chunk (head); the finish
+// step has completed the events. The thread of chunk j resolves the events from its first cut up to the first cut of
+// the next chunk that has one, exactly like the fused thread does, and leaves the same per chunk / per document records.
+typedef struct SpChunkRange
+{
+	uint64_t a, b;		/* events of the thread */
+	uint32_t curdoc;	/* document of the event in front of the current one */
+} SpChunkRange;
+
+SP_HD void sp_resolve_begin( const SpFusedParams& P, uint64_t j, SpFusedThread& st, SpChunkRange& R, SpStridedEvents ar)
+{
+	st.buf = 0; st.bstride = 1; st.ar = ar; st.ar.slots = P.slots; st.ar.out = &st.out; st.memo = 0;
+	st.nbuf = 0; st.n = 0; st.minStart = SP_NO_POS;
+	st.prevBind = SP_BIND_CONTENT; st.prevUnknown = 1; st.docinc = 0; st.docSeenBegin = 0;
+	st.inc = st.emit = st.lead = st.nkept = 0; st.legacy = 0; st.contentDoc = 0xFFFFFFFFu;
+	st.docptr = 0; st.doclen = 0; st.relbase = 0;
+	const uint32_t h = P.head[ j];
+	R.a = P.ev_off[ j+1]; R.b = R.a;
+	if (h != SP_HEAD_NOCUT)
+	{
+		R.a = P.ev_off[ j] + h;
+		uint64_t k = j + 1;
+		while (k < P.nchunks && P.head[ k] == SP_HEAD_NOCUT) ++k;
+		R.b = (k < P.nchunks) ? P.ev_off[ k] + P.head[ k] : P.nev;
+	}
+	st.out = R.a * P.ar_mult;
+	R.curdoc = R.a ? (P.ev_doc[ R.a-1] & ~SP_EVDOC_CUT) : 0xFFFFFFFFu;
+	st.doc = R.curdoc;
+}
+
+// One completed event of the thread's range; dflag = its ev_doc word.
+SP_HD void sp_resolve_event( const SpFusedParams& P, uint64_t j, SpFusedThread& st, SpChunkRange& R, const SpRawEvent& ev, uint32_t dflag)
+{
+	const uint32_t d = dflag & ~SP_EVDOC_CUT;
+	if (d != R.curdoc)
+	{
+		// first event of its document: the documents up to it begin here as far as the output is concerned
+		sp_fused_finalize( P, st);
+		for (uint32_t dd=R.curdoc+1; dd<=d; ++dd)
+		{
+			P.doc_chunk[ dd] = (uint32_t)j;
+			P.doc_local[ dd] = (uint64_t)st.inc | ((uint64_t)st.emit << 32);
+		}
+		R.curdoc = d; st.doc = d;
+		st.prevBind = SP_BIND_CONTENT; st.prevUnknown = 0; st.docinc = 0; st.docSeenBegin = 1;
+	}
+	else if (dflag & SP_EVDOC_CUT) sp_fused_finalize( P, st);
+	if (ev.pat == SP_PAT_DROPPED) return;
+	if (ev.pat == SP_PAT_SIZEERROR || ev.from == ev.to) {st.legacy = 1; return;}
+	if (ev.from < st.minStart) st.minStart = ev.from;
+	sp_supersede( P.T, ev, st.ar, st.n);
+}
+
+// The events [0,left) of the thread's stream as `src` shows them (src.ev(k), src.df(k)); streamEnds: the stream ends
+// behind them. (A separate short way for segments of one or two events was measured and dropped: two code paths in
+// one warp cost more than the loops of the general one, 35 ms against 23 ms per GiB.)
+template <class Source>
+SP_HD void sp_resolve_view( const SpFusedParams& P, uint64_t j, SpFusedThread& st, SpChunkRange& R, const Source& src, uint32_t left, bool streamEnds)
+{
+	(void)streamEnds;
+	for (uint32_t k=0; k<left; ++k) sp_resolve_event( P, j, st, R, src.ev( k), src.df( k));
+}
+
+struct SpEventStream	/* completed events in HBM from index `first` on */
+{
+	const SpRawEvent* events; const uint32_t* ev_doc; uint64_t first;
+	SP_HD SpRawEvent ev( uint32_t k) const {return events[ first + k];}
+	SP_HD uint32_t df( uint32_t k) const {return ev_doc[ first + k];}
+};
+
+SP_HD void sp_resolve_end( const SpFusedParams& P, uint64_t j, SpFusedThread& st, const SpChunkRange& R)
+{
+	sp_fused_finalize( P, st);
+	P.region_begin[ j] = R.a * P.ar_mult;
+	P.kept[ j] = st.nkept;
+	P.agg[ j] = (uint64_t)st.inc | ((uint64_t)st.emit << 32);
+	P.lead_pred[ j] = st.lead;
+	P.inc_tail[ j] = st.docinc;
+	P.has_docstart[ j] = (uint8_t)st.docSeenBegin;
+	if (st.legacy) *P.need_legacy = 1;
+}
+
+// Sequential form (tests/hostsim); k_lex_resolve_chunks feeds the same functions from shared memory tiles that the
+// warp fills with coalesced loads.
+SP_HD void spk_resolve_chunk( const SpFusedParams& P, uint64_t j, SpStridedEvents ar)
+{
+	SpFusedThread st; SpChunkRange R;
+	sp_resolve_begin( P, j, st, R, ar);
+	// in views of at most 8 events like the kernel's tiles, so that the borders between views are exercised as well
+	for (uint64_t i=R.a; i<R.b; i+=8)
+	{
+		SpEventStream src; src.events = P.events; src.ev_doc = P.ev_doc; src.first = i;
+		const uint32_t left = (uint32_t)(R.b - i < 8 ? R.b - i : 8);
+		sp_resolve_view( P, j, st, R, src, left, i + left == R.b);
+	}
+	sp_resolve_end( P, j, st, R);
+}
+
 // Fix step: BindPredecessor elements at the begin of a range are emitted iff the document has advanced its position
 // before; look at the ranges in front until one answers.
 SP_HD void spk_fused_fix_chunk( const SpFusedParams& P, uint64_t j)
@@ -342,7 +455,7 @@ SP_HD void spk_fused_doc( const SpFusedParams& P, uint32_t d, uint64_t total)
 	if (d < P.ndocs)
 	{
 		const uint32_t c = P.doc_chunk[ d];
-		base = P.prefix[ c] + P.doc_local[ d] - ((uint64_t)P.lead_pred[ c] << 32);
+		if (c != 0xFFFFFFFFu) base = P.prefix[ c] + P.doc_local[ d] - ((uint64_t)P.lead_pred[ c] << 32);	// else: behind the last event
 		if (P.doc_succ_early[ d] && !P.doc_has_content[ d]) *P.need_legacy = 1;
 	}
 	P.doc_base[ d] = base;

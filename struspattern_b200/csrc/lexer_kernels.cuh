@@ -85,6 +85,73 @@ static __global__ void __launch_bounds__(LexFusedThreads) k_lex_fused( SpFusedPa
 	if (j < P.nchunks) spk_fused_chunk( P, j, s_buf + threadIdx.x, LexFusedThreads, ar, s_memo + threadIdx.x);
 }
 
+// chunk resolution over completed events (second half of the fused formulation alone): one thread per chunk, open
+// segment elements in shared memory, element i of thread t at [i*LexFusedThreads + t]
+enum {LexResolveTile = 8};	// events per lane and refill
+
+struct TileSource	/* the lane's column of the warp's event tile: element k at [k*33] */
+{
+	const uint4* ev_tile; const uint32_t* doc_tile;
+	__device__ __forceinline__ SpRawEvent ev( uint32_t k) const
+	{
+		const uint4 v = ev_tile[ k * 33];
+		SpRawEvent e; e.pat = v.x; e.from = v.y; e.to = v.z; e.aux = v.w;
+		return e;
+	}
+	__device__ __forceinline__ uint32_t df( uint32_t k) const {return doc_tile[ k * 33];}
+};
+
+static __global__ void __launch_bounds__(LexFusedThreads) k_lex_resolve_chunks( SpFusedParams P)
+{
+	__shared__ uint4 s_ar[ SP_FUSED_AR * LexFusedThreads];
+	// event tiles of the warps, [warp][k][lane]: every lane consumes its own stream of events, which lies 2-3 KB away from
+	// its neighbour's; the warp fetches LexResolveTile events of every stream with coalesced loads (4 streams x 128 bytes
+	// per instruction) instead of 32 scattered 16 byte loads per step
+	__shared__ uint4 s_ev[ LexFusedThreads/32][ LexResolveTile][ 33];
+	__shared__ uint32_t s_doc[ LexFusedThreads/32][ LexResolveTile][ 33];
+	const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	SpStridedEvents ar; ar.base = reinterpret_cast<SpMatchEvent*>( s_ar) + threadIdx.x; ar.stride = LexFusedThreads;
+	SpFusedThread st; SpChunkRange R;
+	const bool active = j < P.nchunks;
+	if (active) sp_resolve_begin( P, j, st, R, ar); else {R.a = R.b = 0;}
+	uint64_t pos = R.a;
+	for (;;)
+	{
+		if (!__any_sync( 0xFFFFFFFFu, pos < R.b)) break;
+		const uint32_t plo = (uint32_t)pos, phi = (uint32_t)(pos >> 32);
+		const uint32_t left = (uint32_t)((R.b - pos) < LexResolveTile ? (R.b - pos) : LexResolveTile);
+		#pragma unroll
+		for (int r=0; r<LexResolveTile; ++r)
+		{
+			const unsigned int s = r * 4 + (lane & 3), k = lane >> 2;
+			const uint64_t p = ((uint64_t)__shfl_sync( 0xFFFFFFFFu, phi, s) << 32) | __shfl_sync( 0xFFFFFFFFu, plo, s);
+			const uint32_t n = __shfl_sync( 0xFFFFFFFFu, left, s);
+			if (k < n)
+			{
+				s_ev[ warp][ k][ s] = *reinterpret_cast<const uint4*>( P.events + p + k);
+				s_doc[ warp][ k][ s] = P.ev_doc[ p + k];
+			}
+		}
+		__syncwarp();
+		if (left)
+		{
+			TileSource src; src.ev_tile = &s_ev[ warp][ 0][ lane]; src.doc_tile = &s_doc[ warp][ 0][ lane];
+			sp_resolve_view( P, j, st, R, src, left, pos + left == R.b);
+		}
+		pos += left;
+		__syncwarp();
+	}
+	if (active) sp_resolve_end( P, j, st, R);
+}
+
+// island pipeline behind a chunk resolution that gave up: plain document ids again
+static __global__ void __launch_bounds__(256) k_evdoc_clear( uint32_t* ev_doc, uint64_t nev)
+{
+	uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < nev) ev_doc[ i] &= ~SP_EVDOC_CUT;
+}
+
 static __global__ void __launch_bounds__(256) k_fused_fix( SpFusedParams P)
 {
 	uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;

@@ -98,6 +98,8 @@ int hsim_scan_batch( void* h, const uint8_t* text, const uint64_t* doc_off, uint
 	hs->doc_ev_begin.assign( ndocs + 1, 0);
 	hs->doc_ev_begin[ ndocs] = nev;
 	P.events = hs->events.data(); P.doc_ev_begin = hs->doc_ev_begin.data();
+	std::vector<uint32_t> head( P.nchunks + 1, 0), ev_docflag( nev + 1, 0);
+	P.head = head.data(); P.ev_doc = ev_docflag.data();
 	for (uint64_t j=0; j<P.nchunks; ++j) spk_emit_chunk( P, j);
 	hs->events.resize( nev);
 	for (uint64_t i=0; i<nev; ++i) spk_finish_event( P, i);
@@ -110,13 +112,15 @@ int hsim_scan_batch( void* h, const uint8_t* text, const uint64_t* doc_off, uint
 	P.ar = ar.data(); P.doc_kept = doc_kept.data(); P.doc_nlex = doc_nlex.data(); P.status = ndocs ? hs->status.data() : &dummy;
 	hs->fused = 0; hs->legacy = 0; hs->leadfixed = 0;
 	bool fusedDone = false;
-	if (hs->mode == 2 && P.T.fwd_cut_n && P.T.npat <= SP_FUSED_MAXPAT && P.nchunks && P.T.fwd_max_acc + 1 <= SP_FUSED_BUF)
+	if ((hs->mode == 3 && P.T.fwd_cut_n && P.nchunks)
+	||  (hs->mode == 2 && P.T.fwd_cut_n && P.T.npat <= SP_FUSED_MAXPAT && P.nchunks && P.T.fwd_max_acc + 1 <= SP_FUSED_BUF))
 	{
 		// the fused segment pipeline of lexer_fused.cuh as plain loops (same per-thread functions as the kernels)
 		const uint64_t nch = P.nchunks;
 		std::vector<SpSlot> slots( nev * P.ar_mult + 1);
 		std::vector<uint64_t> region_begin( nch), agg( nch), prefix( nch + 1, 0), doc_local( ndocs + 1, 0), doc_base( ndocs + 1, 0);
-		std::vector<uint32_t> kept( nch), lead_pred( nch), inc_tail( nch), doc_chunk( ndocs + 1, 0);
+		std::vector<uint32_t> kept( nch), lead_pred( nch), inc_tail( nch), doc_chunk( ndocs + 1, hs->mode == 3 ? 0xFFFFFFFFu : 0);
+
 		std::vector<uint8_t> has_docstart( nch), has_content( ndocs + 1, 0), succ_early( ndocs + 1, 0);
 		uint32_t need_legacy = 0;
 		SpFusedParams F; std::memset( &F, 0, sizeof(F));
@@ -126,11 +130,12 @@ int hsim_scan_batch( void* h, const uint8_t* text, const uint64_t* doc_off, uint
 		F.inc_tail = inc_tail.data(); F.has_docstart = has_docstart.data(); F.prefix = prefix.data();
 		F.doc_chunk = doc_chunk.data(); F.doc_local = doc_local.data(); F.doc_has_content = has_content.data();
 		F.doc_succ_early = succ_early.data(); F.doc_base = doc_base.data(); F.lex_off = lex_off.data(); F.need_legacy = &need_legacy;
+		F.events = hs->events.data(); F.ev_doc = ev_docflag.data(); F.head = head.data(); F.nev = nev;
 		for (uint64_t j=0; j<nch; ++j)
 		{
 			uint32_t buf[ SP_FUSED_BUF]; SpMatchEvent arlocal[ SP_FUSED_AR]; SpStartMemo memo[ SP_FUSED_MEMO];
 			SpStridedEvents ar; ar.base = arlocal; ar.stride = 1;
-			spk_fused_chunk( F, j, buf, 1, ar, memo);
+			if (hs->mode == 3) spk_resolve_chunk( F, j, ar); else spk_fused_chunk( F, j, buf, 1, ar, memo);
 		}
 		for (uint64_t j=0; j<nch; ++j) {uint32_t before = lead_pred[ j]; spk_fused_fix_chunk( F, j); if (before) hs->leadfixed += 1;}
 		for (uint64_t j=0; j<nch; ++j) prefix[ j+1] = prefix[ j] + agg[ j];

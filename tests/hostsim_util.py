@@ -43,7 +43,7 @@ class HostSimLexer:
     def __init__(self, chunk=64, warmup=16, mode=1):
         self.L = self.lib()
         self.h = C.c_void_p(self.L.hsim_create())
-        self.L.hsim_set_mode(self.h, C.c_int(mode))  # 0: per document loop, 1: island + slot formulation, 2: fused segments
+        self.L.hsim_set_mode(self.h, C.c_int(mode))  # 0: per document loop, 1: island + slot formulation, 2: fused segments, 3: chunk resolution over completed events
         self.chunk, self.warmup = chunk, warmup
 
     def __del__(self):

@@ -1,4 +1,6 @@
 """Parity of the CUDA lexer (through the C ABI) with the level-1 oracle and the reference's golden vector."""
+import os
+
 import numpy as np
 import pytest
 
@@ -133,10 +135,14 @@ def test_large_islands_use_their_slot_range():
 
 
 # ---------------------------------------------------------------------------------------------------------
-# Fused segment kernel (k_lex_fused / k_fused_fix / k_fused_docs / k_fused_write): default second half.
+# Segment formulations: chunk resolution over the completed events (k_lex_resolve_chunks, the default second half,
+# counter second_half == 4) and the fully fused scan kernel (k_lex_fused, SP_LEXER_FUSED=1, second_half == 3); both
+# end in k_fused_fix / AggScan / k_fused_docs / k_fused_write.
+@pytest.mark.parametrize("fused", [0, 1])
 @pytest.mark.parametrize("name", sorted(LEXEM_SETS))
 @pytest.mark.parametrize("chunk", [16, 48, 512])
-def test_fused_kernel_matches_oracle(name, chunk, monkeypatch):
+def test_fused_kernel_matches_oracle(name, chunk, fused, monkeypatch):
+    monkeypatch.setenv("SP_LEXER_FUSED", str(fused))
     monkeypatch.setenv("SP_LEXER_CHUNK", str(chunk))
     monkeypatch.setenv("SP_LEXER_WARMUP", str(max(4, chunk // 8)))
     o = define_set(OracleLexer(), name)
@@ -146,7 +152,7 @@ def test_fused_kernel_matches_oracle(name, chunk, monkeypatch):
     _same(o.scan(text, offs, nthreads=8), ctx.scan(text, offs))
     assert ctx.counter("chunk_bytes") == chunk
     if name != "no_boundaries":
-        assert ctx.counter("fused") == 1 and ctx.counter("fused_fallbacks") == 0
+        assert ctx.counter("second_half") == (3 if fused else 4) and ctx.counter("fused_fallbacks") == 0
     ctx.close()
 
 
@@ -163,12 +169,19 @@ def test_fused_kernel_equals_island_pipeline_on_the_bench_lexem_set(monkeypatch)
     corpus.fill(12, vocab, text, offs)
     ctx = g.create_context()
     rf = ctx.scan(text, offs)
-    assert ctx.counter("fused") == 1
+    assert ctx.counter("second_half") == 4
     ctx.close()
-    monkeypatch.setenv("SP_LEXER_FUSED", "0")
+    monkeypatch.setenv("SP_LEXER_FUSED", "1")
     ctx = g.create_context()
     rl = ctx.scan(text, offs)
-    assert ctx.counter("fused") == 0
+    assert ctx.counter("second_half") == 3
+    ctx.close()
+    _same(rl, rf)
+    monkeypatch.setenv("SP_LEXER_FUSED", "0")
+    monkeypatch.setenv("SP_LEXER_HYBRID", "0")
+    ctx = g.create_context()
+    rl = ctx.scan(text, offs)
+    assert ctx.counter("second_half") == 2
     ctx.close()
     _same(rl, rf)
     o = W.define_lexer(OracleLexer())
@@ -189,7 +202,12 @@ def test_fused_kernel_falls_back_to_the_island_pipeline():
             for d in defs:
                 lx.define_lexem(*d)
             lx.compile()
-        ctx = g.create_context()
-        _same(o.scan(b"".join(docs), offs), ctx.scan(b"".join(docs), offs))
-        assert ctx.counter("fused") == 0 and ctx.counter("fused_fallbacks") == 1
-        ctx.close()
+        for fused in ("0", "1"):
+            os.environ["SP_LEXER_FUSED"] = fused
+            try:
+                ctx = g.create_context()
+                _same(o.scan(b"".join(docs), offs), ctx.scan(b"".join(docs), offs))
+                assert ctx.counter("second_half") == 2 and ctx.counter("fused_fallbacks") == 1
+                ctx.close()
+            finally:
+                del os.environ["SP_LEXER_FUSED"]

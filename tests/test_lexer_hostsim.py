@@ -143,11 +143,13 @@ def test_per_document_loop_still_matches(name):
 # ---------------------------------------------------------------------------------------------------------
 # Fused segment formulation (lexer_fused.cuh, mode 2): the same per-thread functions the kernels k_lex_fused,
 # k_fused_fix, k_fused_docs and k_fused_write run.
+@pytest.mark.parametrize("mode", [2, 3])
 @pytest.mark.parametrize("name", sorted(LEXEM_SETS))
 @pytest.mark.parametrize("chunk,warmup", [(16, 4), (48, 16), (512, 64)])
-def test_fused_segments_match_oracle(name, chunk, warmup):
+def test_fused_segments_match_oracle(name, chunk, warmup, mode):
+    """mode 2: scan + completion + resolution in one thread per chunk; mode 3: chunk resolution over the completed events"""
     o = define_set(OracleLexer(), name)
-    h = define_set(HostSimLexer(chunk=chunk, warmup=warmup, mode=2), name)
+    h = define_set(HostSimLexer(chunk=chunk, warmup=warmup, mode=mode), name)
     assert h.info("cut_states") > 0
     for seed in (1, 2):
         text, offs = make_batch(seed=seed * 7919 + chunk + len(name), ndocs=40, mean_bytes=300)
@@ -172,8 +174,8 @@ def test_fused_leading_predecessor_elements_are_decided_by_the_ranges_in_front()
         o.define_lexem(*d)
     o.compile()
     ro = o.scan(text, offs)
-    for chunk in (8, 16, 32, 512):
-        h = HostSimLexer(chunk=chunk, warmup=4, mode=2)
+    for chunk, mode in [(8, 2), (16, 2), (32, 2), (512, 2), (8, 3), (16, 3), (32, 3), (512, 3)]:
+        h = HostSimLexer(chunk=chunk, warmup=4, mode=mode)
         for d in defs:
             h.define_lexem(*d)
         h.compile()
@@ -185,31 +187,34 @@ def test_fused_leading_predecessor_elements_are_decided_by_the_ranges_in_front()
 
 
 def test_fused_falls_back_where_it_must():
-    """Successor elements in a document without content, long chains of overlapping matches, empty selected sub
-    expressions and oversized terms are answered by the island pipeline (fused_legacy) with the oracle's output."""
+    """Successor elements in a document without content and empty selected sub expressions are answered by the island
+    pipeline (fused_legacy) with the oracle's output; long chains of overlapping matches (one segment with far more
+    open elements than the fast work memory holds) stay on the segment path."""
     cases = [
-        ([(1, r"[a-z]+", 0, 0, 0), (3, r"#", 0, 0, 1)], [b"# # #", b"ab # cd"]),
-        ([(1, r"[a-z]+ [a-z]+", 0, 1, 0), (2, r"[a-z]+", 0, 0, 0), (3, r"[a-z]+ [a-z]+ [a-z]+", 0, 2, 0)], [(b"ab cd ef gh " * 40 + b". ") * 3]),
-        ([(1, r"x([0-9]*)y", 1, 0, 0), (2, r"[a-z]+", 0, 0, 0)], [b"ab xy x12y cd xy"]),
+        ([(1, r"[a-z]+", 0, 0, 0), (3, r"#", 0, 0, 1)], [b"# # #", b"ab # cd"], True),
+        ([(1, r"[a-z]+ [a-z]+", 0, 1, 0), (2, r"[a-z]+", 0, 0, 0), (3, r"[a-z]+ [a-z]+ [a-z]+", 0, 2, 0)], [(b"ab cd ef gh " * 40 + b". ") * 3], False),
+        ([(1, r"x([0-9]*)y", 1, 0, 0), (2, r"[a-z]+", 0, 0, 0)], [b"ab xy x12y cd xy"], True),
     ]
-    for defs, docs in cases:
+    for defs, docs, legacy in cases:
         offs = np.cumsum([0] + [len(d) for d in docs]).astype(np.uint64)
         text = b"".join(docs)
-        o, h = OracleLexer(), HostSimLexer(chunk=32, warmup=8, mode=2)
-        for lx in (o, h):
-            for d in defs:
-                lx.define_lexem(*d)
-            lx.compile()
-        ro, rh = o.scan(text, offs), h.scan(text, offs)
-        assert (ro["offsets"] == rh["offsets"]).all() and (ro["lexems"] == rh["lexems"]).all()
-        assert h.info("fused_legacy") == 1 and h.info("fused") == 0
+        for mode in (2, 3):
+            o, h = OracleLexer(), HostSimLexer(chunk=32, warmup=8, mode=mode)
+            for lx in (o, h):
+                for d in defs:
+                    lx.define_lexem(*d)
+                lx.compile()
+            ro, rh = o.scan(text, offs), h.scan(text, offs)
+            assert (ro["offsets"] == rh["offsets"]).all() and (ro["lexems"] == rh["lexems"]).all()
+            assert h.info("fused_legacy") == (1 if legacy else 0) and h.info("fused") == (0 if legacy else 1)
 
 
 def test_fused_golden_case_and_symbol_quirk():
     case = _golden_cases()[0]
-    lx = build_case(lambda: HostSimLexer(chunk=16, warmup=8, mode=2), case)
-    lx.compile()
-    assert lx.match(case["src_latin1"].encode("latin-1")) == [tuple(r) for r in case["results"]]
+    for mode in (2, 3):
+        lx = build_case(lambda: HostSimLexer(chunk=16, warmup=8, mode=mode), case)
+        lx.compile()
+        assert lx.match(case["src_latin1"].encode("latin-1")) == [tuple(r) for r in case["results"]]
     lx = HostSimLexer(chunk=512, warmup=8, mode=2)
     lx.define_lexem(1, "[a-z]\\b", 0, 0, 0)
     lx.define_lexem(2, "a b c\\b", 0, 0, 0)

@@ -1,0 +1,44 @@
+#!/usr/bin/env python3
+"""Per-kernel CUDA-event times of the lexer on the C2 corpus (device resident text), without the end-to-end leg of
+bench.py: python tools/time_lexer.py [--bytes B] [--steps K]"""
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--bytes", type=int, default=1 << 30)
+    ap.add_argument("--steps", type=int, default=3)
+    args = ap.parse_args()
+    import torch
+    from struspattern_b200 import Lexer
+    from struspattern_b200 import workloads as W
+    lx = W.define_lexer(Lexer())
+    text, offs, keep = bench.make_corpus(args.bytes, 0, pinned=False)
+    dev = torch.from_numpy(text).cuda()
+    ctx = lx.create_context()
+    for _ in range(2):
+        ctx.launch(dev.data_ptr(), offs, on_device=True)
+        ctx.count()
+    ctx.counter("profile:on"); ctx.counter("profile:reset")
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        ctx.launch(dev.data_ptr(), offs, on_device=True)
+        ctx.count()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / args.steps
+    k = {n: ctx.counter("time_us:" + n) / 1000.0 / args.steps for n in bench.KERNELS}
+    print(json.dumps({"ms_per_step": ms, "gbps": args.bytes / ms / 1e6, "second_half": ctx.counter("second_half"),
+                      "lexems": ctx.counter("lexems"), "kernels_ms": {n: v for n, v in k.items() if v}}))
+
+
+if __name__ == "__main__":
+    main()
