@@ -24,7 +24,7 @@ struct sp_matcher_ctx
 	uint64_t* pinned;		// host staging for scalar read backs [8]
 	cudaEvent_t ev_a, ev_b;
 	double kernel_ms; uint64_t kernel_calls;
-	bool profile;
+	bool profile, trace;	// SP_MATCHER_TRACE=1: one line per round of the run loop on stderr
 
 	sp_matcher_ctx( sp_matcher* m_, cudaStream_t stream_)
 		:m(m_),stream(stream_),warps_per_sm(16),cap_growths(0),arena_budget(0),nsm(0),res_per_token(0.5),items_per_token(1.0)
@@ -41,12 +41,13 @@ struct sp_matcher_ctx
 		}
 		if ((e = std::getenv( "SP_MATCHER_WARPS_PER_SM")) != 0 && std::atoi( e) >= 1) warps_per_sm = (uint32_t)std::atoi( e);
 		if (std::getenv( "SP_MATCHER_PROFILE")) profile = true;
+		trace = std::getenv( "SP_MATCHER_TRACE") != 0;
 		int dev = 0;
 		SP_CUDA( cudaGetDevice( &dev));
 		SP_CUDA( cudaDeviceGetAttribute( &nsm, cudaDevAttrMultiProcessorCount, dev));
 		std::size_t freeb = 0, totalb = 0;
 		SP_CUDA( cudaMemGetInfo( &freeb, &totalb));
-		arena_budget = freeb / 4;
+		arena_budget = freeb / 2;	// the lexer context of a pipeline and the result pools need the rest
 		SP_CUDA( cudaMallocHost( (void**)&pinned, 8 * sizeof(uint64_t)));
 		SP_CUDA( cudaEventCreate( &ev_a)); SP_CUDA( cudaEventCreate( &ev_b));
 	}
@@ -97,7 +98,7 @@ struct sp_matcher_ctx
 			uint32_t retry_docs = 0;
 			for (int round=0;; ++round)
 			{
-				if (round > 12) throw std::runtime_error( "matcher arenas keep overflowing (rule set too large for the device memory)");
+				if (round > 40) throw std::runtime_error( "matcher arenas keep overflowing (rule set too large for the device memory)");
 				sp_arena_layout( curcap, P.T.nstopwords, P.layout);
 				uint32_t ntodo = d_list ? nlist : ndocs;
 				uint64_t maxwarps = arena_budget / P.layout.bytes;
@@ -114,9 +115,9 @@ struct sp_matcher_ctx
 				if (!d_list) SP_CUDA( cudaMemsetAsync( d_scalars, 0, 8 * sizeof(uint64_t), stream));
 				else SP_CUDA( cudaMemsetAsync( d_words, 0, 5 * sizeof(uint32_t), stream));
 				uint32_t* d_newlist = (flip ? list_b : list_a).as<uint32_t>( ntodo);
-				if (profile) SP_CUDA( cudaEventRecord( ev_a, stream));
+				if (profile || trace) SP_CUDA( cudaEventRecord( ev_a, stream));
 				k_match_documents<<<nblocks, MatchThreads, 0, stream>>>( P);
-				if (profile) SP_CUDA( cudaEventRecord( ev_b, stream));
+				if (profile || trace) SP_CUDA( cudaEventRecord( ev_b, stream));
 				k_match_collect<<<(ndocs + 255) / 256, 256, 0, stream>>>( P.status, ndocs, d_newlist, d_words + 1, d_words + 2);
 				SP_CUDA( cudaGetLastError());
 				launches += 2;
@@ -125,6 +126,14 @@ struct sp_matcher_ctx
 				{
 					float ms = 0.0f;
 					if (cudaEventElapsedTime( &ms, ev_a, ev_b) == cudaSuccess) {kernel_ms += ms; kernel_calls += 1;}
+				}
+				if (trace)
+				{
+					float ms = 0.0f; cudaEventElapsedTime( &ms, ev_a, ev_b);
+					const uint32_t* w = reinterpret_cast<const uint32_t*>( pinned + 2);
+					fprintf( stderr, "[sp_matcher] round %d: docs %u, warps %llu, arena %llu KB (rules %u triggers %u items %u results %u follow %u dispose %u heap %u), kernel %.1f ms, overflowed docs %u (arena %u output %u depth %u), results %llu items %llu\n",
+						round, ntodo, (unsigned long long)nwarps, (unsigned long long)(P.layout.bytes >> 10), curcap.rules, curcap.triggers, curcap.items, curcap.results,
+						curcap.follow, curcap.dispose, curcap.heap, ms, w[1], w[2], w[3], w[4], (unsigned long long)pinned[0], (unsigned long long)pinned[1]);
 				}
 				uint64_t want_res = pinned[0], want_items = pinned[1];
 				const uint32_t* words = reinterpret_cast<const uint32_t*>( pinned + 2);
@@ -143,13 +152,25 @@ struct sp_matcher_ctx
 				nres = want_res; nitems = want_items;
 				if (!ovfArena) break;
 				++retries;
-				curcap.rules *= 4; curcap.triggers *= 4; curcap.items *= 4; curcap.datarefs *= 4;
-				curcap.results *= 4; curcap.follow *= 4; curcap.dispose *= 4; curcap.heap *= 4;
+				// only the pools that overflowed grow (a document stops at its first overflow, so another pool may follow in
+				// the next round): the arena stays small enough for a full grid of warps (growing all pools together ended
+				// at 400 MB per warp and 113 warps in flight on the C3 rule set)
+				{
+					const uint32_t kinds = words[2];
+					if (kinds & (1u << (SP_MST_OVF_RULES - SP_MST_OVERFLOW))) curcap.rules *= 4;
+					if (kinds & (1u << (SP_MST_OVF_TRIGGERS - SP_MST_OVERFLOW))) curcap.triggers *= 4;
+					if (kinds & (1u << (SP_MST_OVF_ITEMS - SP_MST_OVERFLOW))) curcap.items *= 4;
+					if (kinds & (1u << (SP_MST_OVF_DATAREFS - SP_MST_OVERFLOW))) curcap.datarefs *= 4;
+					if (kinds & (1u << (SP_MST_OVF_RESULTS - SP_MST_OVERFLOW))) curcap.results *= 4;
+					if (kinds & (1u << (SP_MST_OVF_FOLLOW - SP_MST_OVERFLOW))) curcap.follow *= 4;
+					if (kinds & (1u << (SP_MST_OVF_DISPOSE - SP_MST_OVERFLOW))) curcap.dispose *= 4;
+					if (kinds & (1u << (SP_MST_OVF_HEAP - SP_MST_OVERFLOW))) curcap.heap *= 4;
+				}
 				d_list = d_newlist; nlist = listcount; flip = !flip;
 				retry_docs = std::max( retry_docs, listcount);
 			}
 			// documents of the next batch will look like these: start with the arenas that were needed (two growth steps at most)
-			if (curcap.rules > cap.rules && cap_growths < 2 && (uint64_t)retry_docs * 50 >= ndocs) {cap = curcap; ++cap_growths;}
+			if (std::memcmp( &curcap, &cap, sizeof(cap)) != 0 && cap_growths < 4 && (uint64_t)retry_docs * 50 >= ndocs) {cap = curcap; ++cap_growths;}
 			if (ntokens)
 			{
 				res_per_token = std::max( 0.01, (double)nres / (double)ntokens);

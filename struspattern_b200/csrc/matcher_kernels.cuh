@@ -189,7 +189,7 @@ static __global__ void k_match_collect( const uint32_t* status, uint32_t ndocs, 
 	if (st < SP_MST_OVERFLOW) return;
 	if (st == SP_MST_OVF_OUTPUT) atomicOr( kinds + 1, 1u);
 	else if (st == SP_MST_OVF_DEPTH) atomicOr( kinds + 2, 1u);
-	else {atomicOr( kinds + 0, 1u); list[ atomicAdd( count, 1u)] = d;}
+	else {atomicOr( kinds + 0, 1u << (st - SP_MST_OVERFLOW)); list[ atomicAdd( count, 1u)] = d;}	// bit = which pool of the arena
 }
 
 static __global__ void __launch_bounds__(256) k_match_compact( MatchParams P, const uint64_t* res_off, const uint64_t* item_off, sp_result* results, sp_item* items)
