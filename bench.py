@@ -132,8 +132,8 @@ def algorithmic_bytes(kernel, c):
     return {
         "k_lex_count": n_text + 12 * nchunks,                 # text read once, start/end state + count per chunk
         "k_lex_verify": 9 * nchunks,
-        "k_lex_emit": n_text + 16 * nev + 12 * nchunks,       # text read once, one 16 B event record per raw event
-        "k_lex_finish": 32 * nev,                             # event record read + written (text re-reads hit L2)
+        "k_lex_emit": n_text + 16 * nev + 16 * nchunks,       # text read once, one 16 B event record per raw event
+        "k_lex_finish": 36 * nev,                             # event record read + written, document word written (text re-reads hit L2)
         "k_lex_resolve": 16 * nev + 16 * nlex + 16 * ndocs,   # events read, kept match events written
         "k_lex_write": 32 * nlex + 24 * ndocs,                # kept match events read, 16 B lexem records written
         "k_scan": 12 * (nchunks + ndocs),
@@ -150,8 +150,26 @@ def algorithmic_bytes(kernel, c):
         "k_fused_scan": 40 * nchunks + 28 * ndocs,
         "k_fused_write": 32 * nlex + 20 * nchunks,
         # chunk resolution over completed events (default): event + document id + segment flag read, kept elements written
-        "k_lex_resolve_chunks": 21 * nev + 16 * nlex + 42 * nchunks,
+        "k_lex_resolve_chunks": 20 * nev + 16 * nlex + 42 * nchunks,
     }[kernel]
+
+
+# DRAM traffic (dram__bytes_read.sum + dram__bytes_write.sum) of one launch from the ncu --set full capture summarised in
+# profiles/r01_lexer_v7_ncu.txt (256 MiB of the same corpus), as bytes per unit the launch processes; scaled to this run's units
+NCU_TRAFFIC = {
+    "k_lex_count": (0.316906e9 + 0.008481e9, "text_bytes", 268435456),
+    "k_lex_emit": (0.710452e9 + 1.718279e9, "raw_events", 89434349),
+    "k_lex_finish": (1.699632e9 + 1.729988e9, "raw_events", 89434349),
+    "k_lex_resolve_chunks": (2.175288e9 + 1.277061e9, "raw_events", 89434349),
+    "k_fused_write": (1.182156e9 + 1.070511e9, "lexems", 69551577),
+}
+
+
+def ncu_traffic(kernel, c):
+    if kernel not in NCU_TRAFFIC:
+        return None
+    nbytes, unit, units = NCU_TRAFFIC[kernel]
+    return nbytes * c[unit] / units
 
 
 def run_reference(args, rank, world):
@@ -330,7 +348,8 @@ def run_ours(args, rank, world, local_rank):
                 "pipeline": "%d host threads x (context + stream), sub-batches of %d MiB" % (args.e2e_threads, args.e2e_sub_bytes >> 20)},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "peak_kind": peak_kind,
+                     "frac": achieved / peak, "traffic": ncu_traffic(dominant, counters), "algorithmic_bytes": algorithmic_bytes(dominant, counters),
+                     "traffic_source": "profiles/r01_lexer_v7_ncu.txt (ncu --set full, 256 MiB of this corpus, scaled by units)", "peak_kind": peak_kind,
                      "kernel_ms_per_step": {k: ktimes[k][0] / 1000.0 / args.steps for k in KERNELS}},
         "matches_per_s": counters["lexems"] * world * args.steps / (ms_max / 1000.0),
     }

@@ -10,6 +10,7 @@ struct sp_matcher_ctx
 	// configuration
 	SpArenaCaps cap;		// arena capacities of the first round (grown by 4 for documents that overflow)
 	uint32_t warps_per_sm;
+	bool warps_fixed;	// warps per SM set by the caller (SP_MATCHER_WARPS_PER_SM / counter "warps_per_sm="): no automatic choice
 	uint32_t cap_growths;
 	uint64_t arena_budget;		// bytes of HBM the arenas may take
 	int nsm;
@@ -27,7 +28,7 @@ struct sp_matcher_ctx
 	bool profile, trace;	// SP_MATCHER_TRACE=1: one line per round of the run loop on stderr
 
 	sp_matcher_ctx( sp_matcher* m_, cudaStream_t stream_)
-		:m(m_),stream(stream_),warps_per_sm(16),cap_growths(0),arena_budget(0),nsm(0),res_per_token(0.5),items_per_token(1.0)
+		:m(m_),stream(stream_),warps_per_sm(16),warps_fixed(false),cap_growths(0),arena_budget(0),nsm(0),res_per_token(0.5),items_per_token(1.0)
 		,ndocs(0),ntokens(0),nres(0),nitems(0),retries(0),pool_retries(0),launches(0),valid(false),pinned(0),ev_a(0),ev_b(0)
 		,kernel_ms(0.0),kernel_calls(0),profile(false)
 	{
@@ -39,7 +40,7 @@ struct sp_matcher_ctx
 			uint32_t n = (uint32_t)std::atoi( e);
 			cap.rules = cap.triggers = cap.datarefs = cap.results = cap.dispose = n; cap.items = 4*n; cap.follow = n < 64 ? n : n/8; cap.heap = n/2 + 1;
 		}
-		if ((e = std::getenv( "SP_MATCHER_WARPS_PER_SM")) != 0 && std::atoi( e) >= 1) warps_per_sm = (uint32_t)std::atoi( e);
+		if ((e = std::getenv( "SP_MATCHER_WARPS_PER_SM")) != 0 && std::atoi( e) >= 1) {warps_per_sm = (uint32_t)std::atoi( e); warps_fixed = true;}
 		if (std::getenv( "SP_MATCHER_PROFILE")) profile = true;
 		trace = std::getenv( "SP_MATCHER_TRACE") != 0;
 		int dev = 0;
@@ -103,7 +104,9 @@ struct sp_matcher_ctx
 				uint32_t ntodo = d_list ? nlist : ndocs;
 				uint64_t maxwarps = arena_budget / P.layout.bytes;
 				if (maxwarps < 1) throw std::runtime_error( "matcher arena does not fit the device memory");
-				uint64_t nwarps = std::min<uint64_t>( std::min<uint64_t>( ntodo, (uint64_t)nsm * warps_per_sm), maxwarps);
+				const bool wide = !warps_fixed && (uint64_t)ntodo > (uint64_t)nsm * 16 && maxwarps > (uint64_t)nsm * 16;
+				const uint32_t wps = wide ? 32 : warps_per_sm;
+				uint64_t nwarps = std::min<uint64_t>( std::min<uint64_t>( ntodo, (uint64_t)nsm * wps), maxwarps);
 				uint32_t nblocks = (uint32_t)((nwarps + MatchWarpsPerBlock - 1) / MatchWarpsPerBlock);
 				P.arena_base = arenas.as<uint8_t>( (std::size_t)nblocks * MatchWarpsPerBlock * P.layout.bytes);
 				// the stop word log is validated by a per-warp document stamp that restarts with every launch
@@ -116,7 +119,8 @@ struct sp_matcher_ctx
 				else SP_CUDA( cudaMemsetAsync( d_words, 0, 5 * sizeof(uint32_t), stream));
 				uint32_t* d_newlist = (flip ? list_b : list_a).as<uint32_t>( ntodo);
 				if (profile || trace) SP_CUDA( cudaEventRecord( ev_a, stream));
-				k_match_documents<<<nblocks, MatchThreads, 0, stream>>>( P);
+				if (wide || warps_per_sm > 16) k_match_documents<8><<<nblocks, MatchThreads, 0, stream>>>( P);
+				else k_match_documents<4><<<nblocks, MatchThreads, 0, stream>>>( P);
 				if (profile || trace) SP_CUDA( cudaEventRecord( ev_b, stream));
 				k_match_collect<<<(ndocs + 255) / 256, 256, 0, stream>>>( P.status, ndocs, d_newlist, d_words + 1, d_words + 2);
 				SP_CUDA( cudaGetLastError());
@@ -290,7 +294,7 @@ int64_t sp_matcher_ctx_counter( sp_matcher_ctx* ctx, const char* key)
 	if (k == "time_us:k_match_documents") return (int64_t)(ctx->kernel_ms * 1000.0);
 	if (k == "calls:k_match_documents") return (int64_t)ctx->kernel_calls;
 	if (k == "warps_per_sm") return (int64_t)ctx->warps_per_sm;
-	if (k.compare( 0, 13, "warps_per_sm=") == 0) {int v = std::atoi( k.c_str() + 13); if (v >= 1) ctx->warps_per_sm = (uint32_t)v; return ctx->warps_per_sm;}
+	if (k.compare( 0, 13, "warps_per_sm=") == 0) {int v = std::atoi( k.c_str() + 13); if (v >= 1) {ctx->warps_per_sm = (uint32_t)v; ctx->warps_fixed = true;} return ctx->warps_per_sm;}
 	if (k.compare( 0, 6, "arena=") == 0)
 	{
 		int n = std::atoi( k.c_str() + 6);
