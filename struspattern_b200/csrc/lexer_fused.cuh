@@ -79,11 +79,9 @@ typedef struct SpFusedParams
 struct SpStridedEvents
 {
 	SpMatchEvent* base; uint32_t stride;
-	SpSlot* slots; const uint64_t* out;
-	SP_HD SpMatchEvent& operator[]( uint32_t i) const
-	{
-		return i < SP_FUSED_AR ? base[ (size_t)i * stride] : reinterpret_cast<SpMatchEvent*>( slots + *out)[ i];
-	}
+	SpMatchEvent* spill;	/* = slots + out of the thread, kept up to date by sp_fused_set_out (a pointer to the thread's `out`
+				   would force the whole thread state into local memory) */
+	SP_HD SpMatchEvent& operator[]( uint32_t i) const {return i < SP_FUSED_AR ? base[ (size_t)i * stride] : spill[ i];}
 };
 
 typedef struct SpFusedThread
@@ -101,6 +99,9 @@ typedef struct SpFusedThread
 	uint32_t legacy;
 } SpFusedThread;
 
+struct SpFusedThread;
+SP_HD void sp_fused_set_out( const struct SpFusedParams& P, struct SpFusedThread& st, uint64_t out);
+
 SP_HD void sp_store_slot( SpSlot* dst, const SpSlot& s)
 {
 #ifdef __CUDACC__
@@ -108,6 +109,11 @@ SP_HD void sp_store_slot( SpSlot* dst, const SpSlot& s)
 #else
 	*dst = s;
 #endif
+}
+
+SP_HD void sp_fused_set_out( const SpFusedParams& P, SpFusedThread& st, uint64_t out)
+{
+	st.out = out; st.ar.spill = reinterpret_cast<SpMatchEvent*>( P.slots + out);
 }
 
 // Closes the open segment: COUNTS/INC flags (src/patternLexer.cpp:926-934), slot records, the thread's counters.
@@ -123,7 +129,7 @@ SP_HD void sp_fused_finalize( const SpFusedParams& P, SpFusedThread& st)
 			if (k == 0 && st.prevUnknown && bind == SP_BIND_UNIQUE) st.legacy = 1;	// depends on the element in front of the range
 			const uint32_t f = sp_flags_next( fs, bind, e.origpos);
 			SpSlot s; s.id = e.id; s.origpos = e.origpos; s.info = (e.origsize & 0xFFFFu) | (bind << 16) | f; s.doc = st.doc;
-			sp_store_slot( P.slots + st.out + k, s);	// st.out itself stays until the loop is through: the accessor refers to it
+			sp_store_slot( P.slots + st.out + k, s);	// st.out stays until the loop is through: the accessor's spill range starts there
 			if (f & SP_SLOT_INC) {st.inc += 1; st.docinc += 1;}
 			if ((f & SP_SLOT_COUNTS) && st.contentDoc != st.doc) {P.doc_has_content[ st.doc] = 1; st.contentDoc = st.doc;}
 			switch (bind)
@@ -138,7 +144,7 @@ SP_HD void sp_fused_finalize( const SpFusedParams& P, SpFusedThread& st)
 					break;
 			}
 		}
-		st.nkept += st.n; st.out += st.n;
+		st.nkept += st.n; sp_fused_set_out( P, st, st.out + st.n);
 		st.prevBind = fs.prevBind; st.prevUnknown = 0;
 	}
 	st.n = 0; st.minStart = SP_NO_POS;
@@ -209,7 +215,7 @@ SP_HD void sp_fused_arrive( const SpFusedParams& P, SpFusedThread& st, SpFusedWa
 		{
 			// first cut of the chunk: everything reported up to here belongs to the thread in front
 			w.own = 1;
-			st.out = w.region_begin = w.evidx * P.ar_mult;
+			w.region_begin = w.evidx * P.ar_mult; sp_fused_set_out( P, st, w.region_begin);
 			st.prevUnknown = 1; st.docSeenBegin = 0;
 		}
 	}
@@ -234,14 +240,14 @@ SP_HD void sp_fused_set_doc( const SpFusedParams& P, SpFusedThread& st, SpFusedW
 // Start of the work of the thread of chunk j. buf: SP_FUSED_BUF entries, ar: SP_FUSED_AR elements (both strided).
 SP_HD void sp_fused_init( const SpFusedParams& P, uint64_t j, SpFusedThread& st, SpFusedWalk& w, uint32_t* buf, uint32_t bstride, SpStridedEvents ar, SpStartMemo* memo)
 {
-	st.buf = buf; st.bstride = bstride; st.ar = ar; st.ar.slots = P.slots; st.ar.out = &st.out; st.memo = memo;
+	st.buf = buf; st.bstride = bstride; st.ar = ar; st.memo = memo;
 	st.nbuf = 0; st.n = 0; st.minStart = SP_NO_POS;
 	st.prevBind = SP_BIND_CONTENT; st.prevUnknown = 0; st.docinc = 0; st.docSeenBegin = 0;
 	st.inc = st.emit = st.lead = st.nkept = 0; st.legacy = 0; st.contentDoc = 0xFFFFFFFFu;
 	w.begin = j * P.chunk; w.end = w.begin + P.chunk < P.total ? w.begin + P.chunk : P.total; w.pos = w.begin;
 	sp_fused_set_doc( P, st, w, sp_find_doc( P.doc_off, P.ndocs, w.begin));
 	w.state = P.start_state[ j]; w.own = 0; w.overhang = 0; w.done = 0; w.finished = 0; w.docend = 0; w.evidx = P.ev_off[ j];
-	st.out = w.region_begin = w.evidx * P.ar_mult;
+	w.region_begin = w.evidx * P.ar_mult; sp_fused_set_out( P, st, w.region_begin);
 	if (w.dstart == w.begin) {w.state = P.T.fwd_init; w.own = 1; st.docSeenBegin = 1;}
 	w.roomMax = SP_FUSED_BUF - 1 - P.T.fwd_max_acc;
 }
@@ -287,7 +293,7 @@ SP_HD void sp_fused_after( const SpFusedParams& P, uint64_t j, SpFusedThread& st
 		if (w.overhang) {w.finished = 1; return;}
 		// the next document begins here: its first segment belongs to this thread if it lies in this chunk
 		w.state = P.T.fwd_init;
-		if (!w.own) {w.own = 1; st.out = w.region_begin = w.evidx * P.ar_mult;}
+		if (!w.own) {w.own = 1; w.region_begin = w.evidx * P.ar_mult; sp_fused_set_out( P, st, w.region_begin);}
 		st.prevBind = SP_BIND_CONTENT; st.prevUnknown = 0; st.docinc = 0; st.docSeenBegin = 1;
 		uint32_t d = w.d;
 		for (++d; d < P.ndocs; ++d)
@@ -346,7 +352,7 @@ typedef struct SpChunkRange
 
 SP_HD void sp_resolve_begin( const SpFusedParams& P, uint64_t j, SpFusedThread& st, SpChunkRange& R, SpStridedEvents ar)
 {
-	st.buf = 0; st.bstride = 1; st.ar = ar; st.ar.slots = P.slots; st.ar.out = &st.out; st.memo = 0;
+	st.buf = 0; st.bstride = 1; st.ar = ar; st.memo = 0;
 	st.nbuf = 0; st.n = 0; st.minStart = SP_NO_POS;
 	st.prevBind = SP_BIND_CONTENT; st.prevUnknown = 1; st.docinc = 0; st.docSeenBegin = 0;
 	st.inc = st.emit = st.lead = st.nkept = 0; st.legacy = 0; st.contentDoc = 0xFFFFFFFFu;
@@ -360,7 +366,7 @@ SP_HD void sp_resolve_begin( const SpFusedParams& P, uint64_t j, SpFusedThread& 
 		while (k < P.nchunks && P.head[ k] == SP_HEAD_NOCUT) ++k;
 		R.b = (k < P.nchunks) ? P.ev_off[ k] + P.head[ k] : P.nev;
 	}
-	st.out = R.a * P.ar_mult;
+	sp_fused_set_out( P, st, R.a * P.ar_mult);
 	R.curdoc = R.a ? (P.ev_doc[ R.a-1] & ~SP_EVDOC_CUT) : 0xFFFFFFFFu;
 	st.doc = R.curdoc;
 }

@@ -15,6 +15,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--bytes", type=int, default=1 << 30)
     ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--contexts", type=int, default=1, help="cut the batch into that many sub-batches of whole documents, one host thread + context + stream each")
     args = ap.parse_args()
     import torch
     from struspattern_b200 import Lexer
@@ -22,6 +23,8 @@ def main():
     lx = W.define_lexer(Lexer())
     text, offs, keep = bench.make_corpus(args.bytes, 0, pinned=False)
     dev = torch.from_numpy(text).cuda()
+    if args.contexts > 1:
+        return concurrent(args, lx, dev, offs)
     ctx = lx.create_context()
     for _ in range(2):
         ctx.launch(dev.data_ptr(), offs, on_device=True)
@@ -38,6 +41,43 @@ def main():
     k = {n: ctx.counter("time_us:" + n) / 1000.0 / args.steps for n in bench.KERNELS}
     print(json.dumps({"ms_per_step": ms, "gbps": args.bytes / ms / 1e6, "second_half": ctx.counter("second_half"),
                       "lexems": ctx.counter("lexems"), "kernels_ms": {n: v for n, v in k.items() if v}}))
+
+
+def concurrent(args, lx, dev, offs):
+    import threading
+    import numpy as np
+    import torch
+    n = args.contexts
+    ndocs = len(offs) - 1
+    cuts = [int(np.searchsorted(offs, offs[-1] * k // n, side="left")) for k in range(n)] + [ndocs]
+    subs = [(cuts[k], cuts[k + 1]) for k in range(n)]
+    streams = [torch.cuda.Stream() for _ in range(n)]
+    ctxs = [lx.create_context(s.cuda_stream) for s in streams]
+    sub_offs = [np.ascontiguousarray(offs[b:e + 1] - offs[b]) for b, e in subs]
+    counts = [0] * n
+
+    def one_pass():
+        def worker(k):
+            torch.cuda.set_device(0)
+            b, e = subs[k]
+            ctxs[k].launch(dev.data_ptr() + int(offs[b]), sub_offs[k], on_device=True)
+            counts[k] = ctxs[k].count()
+        ts = [threading.Thread(target=worker, args=(k,)) for k in range(n)]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join()
+
+    for _ in range(2):
+        one_pass()
+    torch.cuda.synchronize()
+    import time
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        one_pass()
+    torch.cuda.synchronize()
+    ms = (time.perf_counter() - t0) * 1000.0 / args.steps
+    print(json.dumps({"contexts": n, "ms_per_step": ms, "gbps": args.bytes / ms / 1e6, "lexems": sum(counts)}))
 
 
 if __name__ == "__main__":
