@@ -39,6 +39,26 @@ typedef struct SpMatchEvent	/* = MatchEvent, src/patternLexer.cpp:665-679 */
 	uint32_t meta;		/* level | posbind << 8 */
 } SpMatchEvent;
 
+// 16 byte records move as one vector access on the device (the arrays are 16 byte aligned)
+SP_HD SpRawEvent sp_load_event( const SpRawEvent* p)
+{
+#ifdef __CUDACC__
+	const uint4 v = *reinterpret_cast<const uint4*>( p);
+	SpRawEvent e; e.pat = v.x; e.from = v.y; e.to = v.z; e.aux = v.w;
+	return e;
+#else
+	return *p;
+#endif
+}
+SP_HD void sp_store_event( SpRawEvent* p, const SpRawEvent& e)
+{
+#ifdef __CUDACC__
+	*reinterpret_cast<uint4*>( p) = make_uint4( e.pat, e.from, e.to, e.aux);
+#else
+	*p = e;
+#endif
+}
+
 SP_HD uint32_t sp_kind_of_byte( uint32_t b)
 {
 	if (b == '\n') return 2;
@@ -89,7 +109,7 @@ struct SpEmitSink
 			SpRawEvent ev; ev.pat = SP_LDG( T->fwd_acc_pat + pi); ev.from = pendingCut; ev.to = to; ev.aux = doc;
 			pendingCut = 0;
 			if (!seenCut) ++head;
-			events[ cursor++] = ev;
+			sp_store_event( events + cursor++, ev);
 		}
 	}
 	SP_HD void docBegin( uint32_t doc) {doc_ev_begin[ doc] = cursor;}
@@ -530,12 +550,12 @@ SP_HD void spk_emit_chunk( const SpScanParams& P, uint64_t j)
 
 SP_HD void spk_finish_event( const SpScanParams& P, uint64_t i)
 {
-	SpRawEvent ev = P.events[ i];
+	SpRawEvent ev = sp_load_event( P.events + i);
 	if (P.ev_doc) P.ev_doc[ i] = P.head ? (ev.aux | (ev.from << 31)) : ev.aux;	// chunk resolution: bit 31 = first event behind a cut
 	uint64_t dstart = SP_LDG( P.doc_off + ev.aux);
 	uint32_t doclen = (uint32_t)(SP_LDG( P.doc_off + ev.aux + 1) - dstart);
 	sp_finish_event( P.T, ev, P.text + dstart, doclen);
-	P.events[ i] = ev;
+	sp_store_event( P.events + i, ev);
 }
 
 SP_HD void spk_resolve_doc( const SpScanParams& P, uint32_t d)
