@@ -23,7 +23,7 @@
 #define SP_PAT_DROPPED   0xFFFFFFFFu	/* event removed by the sub expression selection */
 #define SP_PAT_SIZEERROR 0xFFFFFFFEu	/* matched term of 65535 bytes or more: error of the document */
 
-typedef struct SpRawEvent
+typedef struct alignas(16) SpRawEvent
 {
 	uint32_t pat;		/* 0-based definition index (reference: 1-based hyperscan id, src/patternLexer.cpp:390) */
 	uint32_t from;		/* byte offsets relative to the document */
@@ -31,7 +31,7 @@ typedef struct SpRawEvent
 	uint32_t aux;		/* document index until the start is resolved, then symbol id (0 = none) */
 } SpRawEvent;
 
-typedef struct SpMatchEvent	/* = MatchEvent, src/patternLexer.cpp:665-679 */
+typedef struct alignas(16) SpMatchEvent	/* = MatchEvent, src/patternLexer.cpp:665-679 */
 {
 	uint32_t id;
 	uint32_t origpos;
@@ -658,7 +658,7 @@ SP_HD bool sp_ord_decide( uint32_t bind, bool counts, uint32_t cnt, uint32_t& or
 //           islands of the document start strictly in front of this island's first event, so the running
 //           maximum is seeded with that start and no scan over the document is needed.
 // One sum scan over the slots (low word: INC, high word: emitted) then yields ordinal positions and output indices.
-typedef struct SpSlot
+typedef struct alignas(16) SpSlot
 {
 	uint32_t id;
 	uint32_t origpos;
