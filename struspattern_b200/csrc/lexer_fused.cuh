@@ -81,7 +81,7 @@ struct SpStridedEvents
 	SpMatchEvent* base; uint32_t stride;
 	SpMatchEvent* spill;	/* = slots + out of the thread, kept up to date by sp_fused_set_out (a pointer to the thread's `out`
 				   would force the whole thread state into local memory) */
-	SP_HD SpMatchEvent& operator[]( uint32_t i) const {return i < SP_FUSED_AR ? base[ (size_t)i * stride] : spill[ i];}
+	SP_HD SpMatchEvent& operator[]( uint32_t i) const {return i < SP_FUSED_AR ? base[ i * stride] : spill[ i];}
 };
 
 typedef struct SpFusedThread
@@ -157,11 +157,11 @@ SP_HD void sp_fused_drain( const SpFusedParams& P, SpFusedThread& st)
 	const uint32_t M = P.ar_mult;
 	for (uint32_t i=0; i<st.nbuf; ++i)
 	{
-		const uint32_t e = st.buf[ (size_t)i * st.bstride];
+		const uint32_t e = st.buf[ i * st.bstride];
 		if (e & SP_FUSED_CUTMARK) {sp_fused_finalize( P, st); continue;}
 		SpRawEvent ev; ev.pat = e & SP_FUSED_MAXPAT; ev.from = SP_NO_POS; ev.to = (e >> 15) + st.relbase; ev.aux = 0;
 		const SpPatternInfo I = P.T.pat[ ev.pat];
-		SpStartMemo* mp = st.memo + (size_t)(ev.pat & (SP_FUSED_MEMO-1)) * st.bstride;
+		SpStartMemo* mp = st.memo + (ev.pat & (SP_FUSED_MEMO-1)) * st.bstride;
 		SpStartMemo m = *mp;
 		const uint32_t from = sp_leftmost_start_memo( P.T, ev.pat, I, st.docptr, st.doclen, ev.to, m);
 		*mp = m;
@@ -196,11 +196,11 @@ SP_HD void sp_fused_arrive( const SpFusedParams& P, SpFusedThread& st, SpFusedWa
 		{
 			const uint32_t a = w.state - T.fwd_acc_base, rel = (uint32_t)(w.pos - w.begin) << 15;
 			uint32_t pi = SP_LDG( T.fwd_acc_off + a), pe = SP_LDG( T.fwd_acc_off + a + 1);
-			for (; pi < pe; ++pi) st.buf[ (size_t)(st.nbuf++) * st.bstride] = (uint32_t)SP_LDG( T.fwd_acc_pat + pi) | rel;
+			for (; pi < pe; ++pi) st.buf[ (st.nbuf++) * st.bstride] = (uint32_t)SP_LDG( T.fwd_acc_pat + pi) | rel;
 		}
 		if (cut)
 		{
-			st.buf[ (size_t)(st.nbuf++) * st.bstride] = SP_FUSED_CUTMARK;
+			st.buf[ (st.nbuf++) * st.bstride] = SP_FUSED_CUTMARK;
 			if (w.overhang) w.done = 1;
 		}
 	}
@@ -234,7 +234,7 @@ SP_HD void sp_fused_set_doc( const SpFusedParams& P, SpFusedThread& st, SpFusedW
 {
 	w.d = d; w.dstart = SP_LDG( P.doc_off + d); w.dend = SP_LDG( P.doc_off + d + 1);
 	st.doc = d; st.docptr = P.text + w.dstart; st.doclen = (uint32_t)(w.dend - w.dstart); st.relbase = (uint32_t)(w.begin - w.dstart);
-	for (uint32_t k=0; k<SP_FUSED_MEMO; ++k) st.memo[ (size_t)k * st.bstride].pat = SP_NO_POS;	// offsets are document relative
+	for (uint32_t k=0; k<SP_FUSED_MEMO; ++k) st.memo[ k * st.bstride].pat = SP_NO_POS;	// offsets are document relative
 }
 
 // Start of the work of the thread of chunk j. buf: SP_FUSED_BUF entries, ar: SP_FUSED_AR elements (both strided).

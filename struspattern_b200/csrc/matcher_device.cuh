@@ -57,7 +57,7 @@ typedef struct SpEventData
 } SpEventData;
 
 /* Rule (:171) and its ActionSlot (:87) in one record: a rule owns exactly one slot. 64 bytes. */
-typedef struct SpRule
+typedef struct alignas(16) SpRule
 {
 	uint32_t value;
 	uint32_t count;			/* 16 bit counter in the reference */
@@ -77,7 +77,7 @@ typedef struct SpRule
 } SpRule;
 
 /* LinkedTrigger (:118) + the list element that chains the triggers of a rule. 32 bytes. */
-typedef struct SpTrigger
+typedef struct alignas(16) SpTrigger
 {
 	uint32_t link;			/* bucket << 28 | position in the bucket array */
 	uint32_t rule;			/* 1-based */
@@ -96,13 +96,13 @@ typedef struct SpItem
 	uint32_t next;
 } SpItem;
 
-typedef struct SpDataRef		/* EventDataReference, :241 */
+typedef struct alignas(8) SpDataRef		/* EventDataReference, :241 */
 {
 	uint32_t items;			/* head of the item list (1-based) ; free list link */
 	uint32_t refcount;
 } SpDataRef;
 
-typedef struct SpPendingResult		/* Result, :273 */
+typedef struct alignas(16) SpPendingResult		/* Result, :273 */
 {
 	uint32_t resultHandle, formatHandle, dataref, start_ordpos, end_ordpos, start_origseg, end_origseg, start_origpos, end_origpos;
 	uint32_t eliminated;

@@ -15,7 +15,7 @@
 #define SP_SIG_AND          5
 
 /* Program (src/ruleMatcherAutomaton.hpp:319) with its ActionSlotDef (:291) inlined. 32 bytes. */
-typedef struct SpProgram
+typedef struct alignas(16) SpProgram
 {
 	uint32_t initsigval;
 	uint32_t initcount;
@@ -29,7 +29,7 @@ typedef struct SpProgram
 
 /* TriggerDef (src/ruleMatcherAutomaton.hpp:305). Stored per program in the order the reference's LIFO list
  * is iterated: last argument first (src/ruleMatcherAutomaton.cpp:276, podStackPoolBase.hpp:48-62). 16 bytes. */
-typedef struct SpTriggerDef
+typedef struct alignas(16) SpTriggerDef
 {
 	uint32_t event;
 	uint32_t sigval;
@@ -40,14 +40,14 @@ typedef struct SpTriggerDef
 } SpTriggerDef;
 
 /* ProgramTrigger (src/ruleMatcherAutomaton.hpp:331), stored per key event in list iteration order. */
-typedef struct SpProgramTrigger
+typedef struct alignas(8) SpProgramTrigger
 {
 	uint32_t program;		/* 0-based index into programs */
 	uint32_t past_event;		/* original key event of a program moved to an alternative key, else 0 */
 } SpProgramTrigger;
 
 /* Open addressing hash table over every event that is a key event or a stop word. */
-typedef struct SpEventSlot
+typedef struct alignas(16) SpEventSlot
 {
 	uint32_t key;			/* event id + 1; 0 = empty slot */
 	uint32_t prog_begin;		/* program triggers [prog_begin, prog_begin+prog_count) */
