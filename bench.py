@@ -155,13 +155,13 @@ def algorithmic_bytes(kernel, c):
 
 
 # DRAM traffic (dram__bytes_read.sum + dram__bytes_write.sum) of one launch from the ncu --set full capture summarised in
-# profiles/r01_lexer_v7_ncu.txt (256 MiB of the same corpus), as bytes per unit the launch processes; scaled to this run's units
+# profiles/r01_lexer_v9_ncu.txt (256 MiB of the same corpus), as bytes per unit the launch processes; scaled to this run's units
 NCU_TRAFFIC = {
-    "k_lex_count": (0.316906e9 + 0.008481e9, "text_bytes", 268435456),
-    "k_lex_emit": (0.710452e9 + 1.718279e9, "raw_events", 89434349),
-    "k_lex_finish": (1.699632e9 + 1.729988e9, "raw_events", 89434349),
-    "k_lex_resolve_chunks": (2.175288e9 + 1.277061e9, "raw_events", 89434349),
-    "k_fused_write": (1.182156e9 + 1.070511e9, "lexems", 69551577),
+    "k_lex_count": (0.316676e9 + 0.008487e9, "text_bytes", 268435456),
+    "k_lex_emit": (0.552721e9 + 1.588677e9, "raw_events", 89434349),
+    "k_lex_finish": (1.699707e9 + 1.730083e9, "raw_events", 89434349),
+    "k_lex_resolve_chunks": (2.121796e9 + 1.213993e9, "raw_events", 89434349),
+    "k_fused_write": (1.182107e9 + 1.069964e9, "lexems", 69551577),
 }
 
 
@@ -316,6 +316,25 @@ def run_ours(args, rank, world, local_rank):
         assert (ref["offsets"] == out_offs).all() and (ref["lexems"] == out_lex[:nlex]).all(), "pipelined end-to-end output differs from the single batch"
         del whole
 
+    # what the link allows: plain pinned copies of the same sizes, both directions at once (the end-to-end leg is PCIe bound)
+    pc0, pc1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s_up, s_down = torch.cuda.Stream(), torch.cuda.Stream()
+    dev_out = torch.empty(16 * nlex, dtype=torch.uint8, device="cuda")
+    link_ms = None
+    for _ in range(2):
+        torch.cuda.synchronize()
+        pc0.record()
+        s_up.wait_event(pc0); s_down.wait_event(pc0)
+        with torch.cuda.stream(s_up):
+            dev_text[:len(text)].copy_(keep[:len(text)], non_blocking=True)
+        with torch.cuda.stream(s_down):
+            out_keep[:16 * nlex].copy_(dev_out, non_blocking=True)
+        torch.cuda.current_stream().wait_stream(s_up); torch.cuda.current_stream().wait_stream(s_down)
+        pc1.record()
+        torch.cuda.synchronize()
+        link_ms = pc0.elapsed_time(pc1) if link_ms is None else min(link_ms, pc0.elapsed_time(pc1))
+    del dev_out
+
     times = torch.tensor([ms, e2e_s * 1000.0], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
@@ -345,11 +364,13 @@ def run_ours(args, rank, world, local_rank):
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": int(args.bytes + 8 * (ndocs + 1)),
                 "d2h_bytes_per_step": int(16 * nlex + 8 * (ndocs + len(subs)) + 4 * ndocs), "steps": e2e_steps,
-                "pipeline": "%d host threads x (context + stream), sub-batches of %d MiB" % (args.e2e_threads, args.e2e_sub_bytes >> 20)},
+                "pipeline": "%d host threads x (context + stream), sub-batches of %d MiB" % (args.e2e_threads, args.e2e_sub_bytes >> 20),
+                "link_bound": {"value": float(args.bytes) / (link_ms / 1000.0) / 1e9, "unit": "GB/s",
+                               "what": "text bytes / time of plain pinned copies of the same H2D and D2H bytes issued together (rank 0)"}},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": ncu_traffic(dominant, counters), "algorithmic_bytes": algorithmic_bytes(dominant, counters),
-                     "traffic_source": "profiles/r01_lexer_v7_ncu.txt (ncu --set full, 256 MiB of this corpus, scaled by units)", "peak_kind": peak_kind,
+                     "traffic_source": "profiles/r01_lexer_v9_ncu.txt (ncu --set full, 256 MiB of this corpus, scaled by units)", "peak_kind": peak_kind,
                      "kernel_ms_per_step": {k: ktimes[k][0] / 1000.0 / args.steps for k in KERNELS}},
         "matches_per_s": counters["lexems"] * world * args.steps / (ms_max / 1000.0),
     }

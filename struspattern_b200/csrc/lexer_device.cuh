@@ -374,7 +374,7 @@ SP_HD void sp_supersede( const SpLexerTables& T, const SpRawEvent& rev, EventArr
 		if ((old.id == ev.id && old.origpos == ev.origpos && oldLevel == evLevel)
 		||  (oldLevel < evLevel && old.origpos + old.origsize <= evEnd))
 		{
-			for (uint32_t m=k; m<n; ++m) ar[ m-1] = ar[ m];
+			for (uint32_t m=k; m<n; ++m) {const SpMatchEvent moved = ar[ m]; ar[ m-1] = moved;}
 			--n; ++deleted;
 		}
 	}
@@ -391,7 +391,12 @@ SP_HD void sp_supersede( const SpLexerTables& T, const SpRawEvent& rev, EventArr
 	if (!withSymbol)
 	{
 		uint32_t k = n;
-		for (; k>0 && ar[ k-1].origpos > ev.origpos; --k) ar[ k] = ar[ k-1];
+		for (; k>0; --k)
+		{
+			const SpMatchEvent later = ar[ k-1];
+			if (later.origpos <= ev.origpos) break;
+			ar[ k] = later;
+		}
 		ar[ k] = ev;
 		++n;
 	}
@@ -402,7 +407,12 @@ SP_HD void sp_supersede( const SpLexerTables& T, const SpRawEvent& rev, EventArr
 		SpMatchEvent zero; zero.id = 0; zero.origpos = 0; zero.origsize = 0; zero.meta = 0;
 		ar[ n] = zero; ar[ n+1] = zero;
 		uint32_t dst = n + 1, k = n;
-		for (; k>0 && ar[ k-1].origpos > ev.origpos; --k) {ar[ dst] = ar[ k-1]; dst = k-1;}
+		for (; k>0; --k)
+		{
+			const SpMatchEvent later = ar[ k-1];
+			if (later.origpos <= ev.origpos) break;
+			ar[ dst] = later; dst = k-1;
+		}
 		ar[ k] = ev;
 		ar[ k+1] = symev;
 		n += 2;

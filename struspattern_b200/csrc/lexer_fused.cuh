@@ -81,7 +81,19 @@ struct SpStridedEvents
 	SpMatchEvent* base; uint32_t stride;
 	SpMatchEvent* spill;	/* = slots + out of the thread, kept up to date by sp_fused_set_out (a pointer to the thread's `out`
 				   would force the whole thread state into local memory) */
-	SP_HD SpMatchEvent& operator[]( uint32_t i) const {return i < SP_FUSED_AR ? base[ i * stride] : spill[ i];}
+	// element access by value through a proxy: a reference would have to point into either of two address spaces and
+	// make every access a generic one; this way the common case stays a plain shared memory access
+	struct Element
+	{
+		const SpStridedEvents* a; uint32_t i;
+		SP_HD operator SpMatchEvent() const {return i < SP_FUSED_AR ? a->base[ i * a->stride] : a->spill[ i];}
+		SP_HD const Element& operator=( const SpMatchEvent& v) const
+		{
+			if (i < SP_FUSED_AR) a->base[ i * a->stride] = v; else a->spill[ i] = v;
+			return *this;
+		}
+	};
+	SP_HD Element operator[]( uint32_t i) const {Element e; e.a = this; e.i = i; return e;}
 };
 
 typedef struct SpFusedThread
