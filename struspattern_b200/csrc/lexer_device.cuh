@@ -143,7 +143,7 @@ SP_HD uint32_t sp_scan_range( const SpLexerTables& T, const uint8_t* text, const
 					for (int bi=0; bi<4; ++bi)
 					{
 						uint32_t b = (w[wi] >> (8*bi)) & 0xFF;
-						state = SP_LDG( T.fwd_next + state * stride + SP_LDG( T.fwd_class + b));
+						state = SP_LDG( T.fwd_next + state * stride + T.fwd_class[ b]);
 						if (state >= accbase) sink.accept( state, (uint32_t)(pos - dstart), d);
 						if ((state - T.fwd_cut_lo) < T.fwd_cut_n) sink.cut();
 						++pos;
@@ -153,7 +153,7 @@ SP_HD uint32_t sp_scan_range( const SpLexerTables& T, const uint8_t* text, const
 			else
 			{
 				uint32_t b = SP_LDG( text + pos);
-				state = SP_LDG( T.fwd_next + state * stride + SP_LDG( T.fwd_class + b));
+				state = SP_LDG( T.fwd_next + state * stride + T.fwd_class[ b]);
 				if (state >= accbase) sink.accept( state, (uint32_t)(pos - dstart), d);
 						if ((state - T.fwd_cut_lo) < T.fwd_cut_n) sink.cut();
 				++pos;

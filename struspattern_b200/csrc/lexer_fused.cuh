@@ -237,7 +237,7 @@ SP_HD void sp_fused_arrive( const SpFusedParams& P, SpFusedThread& st, SpFusedWa
 SP_HD void sp_fused_step( const SpFusedParams& P, SpFusedThread& st, SpFusedWalk& w, uint32_t b)
 {
 	const SpLexerTables& T = P.T;
-	w.state = SP_LDG( T.fwd_next + w.state * T.fwd_stride + SP_LDG( T.fwd_class + b));
+	w.state = SP_LDG( T.fwd_next + w.state * T.fwd_stride + T.fwd_class[ b]);
 	sp_fused_arrive( P, st, w, (w.state - T.fwd_cut_lo) < T.fwd_cut_n);
 	++w.pos;
 }

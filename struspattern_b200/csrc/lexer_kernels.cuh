@@ -23,8 +23,19 @@ namespace sp {
 
 enum {LexScanThreads = 128, LexEventThreads = 256, LexDocThreads = 64};
 
+// the byte -> column map of the forward automaton is read once per text byte with a different index in every lane:
+// as a global load that is a 32 address gather per byte; a copy in shared memory makes it a (mostly conflict free) LDS
+__device__ __forceinline__ void stageByteClasses( SpScanParams& P, uint8_t* s_class)
+{
+	for (unsigned int i=threadIdx.x; i<64; i+=blockDim.x) reinterpret_cast<uint32_t*>( s_class)[ i] = reinterpret_cast<const uint32_t*>( P.T.fwd_class)[ i];
+	__syncthreads();
+	P.T.fwd_class = s_class;
+}
+
 static __global__ void __launch_bounds__(LexScanThreads) k_lex_count( SpScanParams P, int round)
 {
+	__shared__ __align__(16) uint8_t s_class[ 256];
+	stageByteClasses( P, s_class);
 	uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (j < P.nchunks) spk_count_chunk( P, j, round);
 }
@@ -39,6 +50,8 @@ static __global__ void __launch_bounds__(256) k_lex_verify( SpScanParams P)
 
 static __global__ void __launch_bounds__(LexScanThreads) k_lex_emit( SpScanParams P)
 {
+	__shared__ __align__(16) uint8_t s_class[ 256];
+	stageByteClasses( P, s_class);
 	uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (j < P.nchunks) spk_emit_chunk( P, j);
 }
