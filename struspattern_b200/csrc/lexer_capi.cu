@@ -40,7 +40,7 @@ struct sp_lexer
 		const LexerTablesHost& H = prog.tables();
 		dev = H.view;
 		dev.fwd_next = put( H.fwd_next); dev.fwd_class = put( H.fwd_class);
-		dev.fwd_acc_off = put( H.fwd_acc_off); dev.fwd_acc_pat = put( H.fwd_acc_pat);
+		dev.fwd_acc_off = put( H.fwd_acc_off); dev.fwd_acc_span = put( H.fwd_acc_span); dev.fwd_acc_pat = put( H.fwd_acc_pat);
 		dev.rev_next = put( H.rev_next); dev.rev_classes = put( H.rev_classes);
 		dev.cap_next = put( H.cap_next); dev.cap_classes = put( H.cap_classes); dev.cap = put( H.cap);
 		dev.pat = put( H.pat); dev.sym_slots = put( H.sym_slots); dev.sym_pool = put( H.sym_pool);

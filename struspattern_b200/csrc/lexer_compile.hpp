@@ -26,6 +26,7 @@ struct LexerTablesHost
 	std::vector<uint16_t> fwd_next;
 	std::vector<uint8_t> fwd_class;
 	std::vector<uint32_t> fwd_acc_off;
+	std::vector<SpAccSpan> fwd_acc_span;
 	std::vector<uint16_t> fwd_acc_pat;
 	std::vector<uint32_t> rev_next;
 	std::vector<uint8_t> rev_classes;
@@ -40,7 +41,7 @@ struct LexerTablesHost
 	void pointToHost()
 	{
 		view.fwd_next = fwd_next.data(); view.fwd_class = fwd_class.data();
-		view.fwd_acc_off = fwd_acc_off.data(); view.fwd_acc_pat = fwd_acc_pat.data();
+		view.fwd_acc_off = fwd_acc_off.data(); view.fwd_acc_span = fwd_acc_span.data(); view.fwd_acc_pat = fwd_acc_pat.data();
 		view.rev_next = rev_next.data(); view.rev_classes = rev_classes.data();
 		view.cap_next = cap_next.data(); view.cap_classes = cap_classes.data(); view.cap = cap.data();
 		view.pat = pat.data(); view.sym_slots = sym_slots.data(); view.sym_pool = sym_pool.data();
@@ -304,6 +305,8 @@ private:
 			for (uint32_t p: acc[a]) T.fwd_acc_pat.push_back( (uint16_t)p);	// ascending definition index = canonical event order
 		}
 		T.fwd_acc_off[ acc.size()] = (uint32_t)T.fwd_acc_pat.size();
+		T.fwd_acc_span.resize( acc.size());
+		for (std::size_t a=0; a<acc.size(); ++a) {T.fwd_acc_span[a].off = T.fwd_acc_off[a]; T.fwd_acc_span[a].n = T.fwd_acc_off[a+1] - T.fwd_acc_off[a];}
 		T.view.fwd_max_acc = 0;
 		for (std::size_t a=0; a<acc.size(); ++a) if (acc[a].size() > T.view.fwd_max_acc) T.view.fwd_max_acc = (uint32_t)acc[a].size();
 		T.fwd_class.assign( dfa.byteclass, dfa.byteclass + 256);

@@ -77,14 +77,24 @@ SP_HD uint32_t sp_find_doc( const uint64_t* doc_off, uint32_t ndocs, uint64_t po
 	return lo;
 }
 
+SP_HD SpAccSpan sp_load_span( const SpAccSpan* p)
+{
+#ifdef __CUDACC__
+	const uint2 v = __ldg( reinterpret_cast<const uint2*>( p));
+	SpAccSpan rt; rt.off = v.x; rt.n = v.y;
+	return rt;
+#else
+	return *p;
+#endif
+}
+
 struct SpCountSink
 {
 	const SpLexerTables* T;
 	uint32_t count;
 	SP_HD void accept( uint32_t state, uint32_t, uint32_t)
 	{
-		uint32_t a = state - T->fwd_acc_base;
-		count += SP_LDG( T->fwd_acc_off + a + 1) - SP_LDG( T->fwd_acc_off + a);
+		count += SP_LDG( &T->fwd_acc_span[ state - T->fwd_acc_base].n);
 	}
 	SP_HD void docBegin( uint32_t) {}
 	SP_HD void cut() {}
@@ -101,14 +111,13 @@ struct SpEmitSink
 	uint32_t pendingCut, seenCut, head;	/* a cut lies between the next event and the one in front of it; events in front of the first cut */
 	SP_HD void accept( uint32_t state, uint32_t to, uint32_t doc)
 	{
-		uint32_t a = state - T->fwd_acc_base;
-		uint32_t pi = SP_LDG( T->fwd_acc_off + a), pe = SP_LDG( T->fwd_acc_off + a + 1);
-		for (; pi < pe; ++pi)
+		const SpAccSpan span = sp_load_span( T->fwd_acc_span + (state - T->fwd_acc_base));
+		if (!seenCut) head += span.n;
+		for (uint32_t pi = span.off, pe = span.off + span.n; pi < pe; ++pi)
 		{
 			// until the start is resolved `from` says whether the event is the first one behind a cut
 			SpRawEvent ev; ev.pat = SP_LDG( T->fwd_acc_pat + pi); ev.from = pendingCut; ev.to = to; ev.aux = doc;
 			pendingCut = 0;
-			if (!seenCut) ++head;
 			sp_store_event( events + cursor++, ev);
 		}
 	}

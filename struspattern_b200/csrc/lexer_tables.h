@@ -42,12 +42,19 @@ typedef struct SpSymbolSlot
 	uint16_t symtab;
 } SpSymbolSlot;
 
+/* the events of one accepting state: fwd_acc_pat[off .. off+n) (one 8-byte load instead of two loads of fwd_acc_off) */
+typedef struct alignas(8) SpAccSpan
+{
+	uint32_t off, n;
+} SpAccSpan;
+
 typedef struct SpLexerTables
 {
 	/* forward automaton over all definitions */
 	const uint16_t* fwd_next;	/* [fwd_states][fwd_stride] state ids; column fwd_stride-1 = end of text */
 	const uint8_t* fwd_class;	/* [256] byte -> column */
 	const uint32_t* fwd_acc_off;	/* [fwd_states - fwd_acc_base + 1] */
+	const SpAccSpan* fwd_acc_span;	/* [fwd_states - fwd_acc_base] the same as (offset, count) pairs */
 	const uint16_t* fwd_acc_pat;	/* definition indices (0-based), ascending per state */
 	uint32_t fwd_states;
 	uint32_t fwd_stride;

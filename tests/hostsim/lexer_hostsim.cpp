@@ -66,6 +66,24 @@ int64_t hsim_info( void* h, const char* key)
 	return -1;
 }
 
+// how often the scan reads the row of every forward state (tools/state_histogram.py: which rows are worth a place in shared memory)
+int hsim_state_histogram( void* h, const uint8_t* text, const uint64_t* doc_off, uint32_t ndocs, uint64_t* hist)
+{
+	HostSim* hs = (HostSim*)h;
+	if (!hs->prog.compiled()) {hs->lasterror = "called scan without calling 'compile'"; return -1;}
+	const SpLexerTables& T = hs->prog.tables().view;
+	for (uint32_t d=0; d<ndocs; ++d)
+	{
+		uint32_t state = T.fwd_init;
+		for (uint64_t i=doc_off[d]; i<doc_off[d+1]; ++i)
+		{
+			++hist[ state];
+			state = T.fwd_next[ state * T.fwd_stride + T.fwd_class[ text[i]]];
+		}
+	}
+	return 0;
+}
+
 // text must be 16 byte aligned for the vector path to be exercised (numpy arrays are)
 int hsim_scan_batch( void* h, const uint8_t* text, const uint64_t* doc_off, uint32_t ndocs, uint32_t chunk, uint32_t warmup)
 {

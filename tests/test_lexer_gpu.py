@@ -211,3 +211,62 @@ def test_fused_kernel_falls_back_to_the_island_pipeline():
                 ctx.close()
             finally:
                 del os.environ["SP_LEXER_FUSED"]
+
+
+def test_full_size_corpus_properties(monkeypatch):
+    """BASELINE.json configs[1] at its full size (1 GiB of text, the bench corpus): too large for the oracle as a whole, so the
+    output is checked through properties that do not depend on the size -- documents are closed units
+    (src/patternLexer.cpp:858-950: all state is per match() call), so any split of the batch gives the same lexems; a sample
+    of documents spread over the batch is compared with the oracle bit by bit; the slot pipeline gives the same output."""
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    from struspattern_b200 import workloads as W
+    nbytes = int(os.environ.get("SP_TEST_FULL_BYTES", 1 << 30))
+    text, offs, _ = bench.make_corpus(nbytes, 0, pinned=False)
+    offs = np.ascontiguousarray(offs, dtype=np.uint64)
+    ndocs = len(offs) - 1
+    g = W.define_lexer(_gpu_lexer()())
+    ctx = g.create_context()
+    whole = ctx.scan(text, offs)
+    assert ctx.counter("second_half") == 4 and ctx.counter("fused_fallbacks") == 0
+    lex, lo = whole["lexems"], whole["offsets"]
+    assert (whole["status"] == 0).all() and len(lo) == ndocs + 1 and int(lo[-1]) == len(lex)
+    # structure: positions inside the document, ordinal positions start at 1 and never fall, start offsets never fall
+    doc_of = np.repeat(np.arange(ndocs, dtype=np.int64), np.diff(lo).astype(np.int64))
+    doclen = np.diff(offs).astype(np.int64)
+    assert (lex["origpos"].astype(np.int64) + lex["origsize"] <= doclen[doc_of]).all()
+    first = lo[:-1][np.diff(lo) > 0].astype(np.int64)
+    assert (lex["ordpos"][first] == 1).all()
+    inner = np.ones(len(lex), dtype=bool); inner[first] = False
+    step = np.diff(lex["ordpos"].astype(np.int64), prepend=0)
+    assert ((step == 0) | (step == 1))[inner].all()
+    assert (np.diff(lex["origpos"].astype(np.int64), prepend=0)[inner] >= 0).all()
+    del doc_of, inner, step
+    # any split of the batch at document borders gives the same lexems
+    for cut in (ndocs // 3, ndocs // 2 + 1):
+        a = ctx.scan(text[:int(offs[cut])], offs[:cut + 1])
+        b = ctx.scan(text[int(offs[cut]):], offs[cut:] - offs[cut])
+        assert int(a["offsets"][-1]) + int(b["offsets"][-1]) == len(lex)
+        assert (a["lexems"] == lex[:len(a["lexems"])]).all() and (b["lexems"] == lex[len(a["lexems"]):]).all()
+        assert (a["offsets"] == lo[:cut + 1]).all() and (b["offsets"] + lo[cut] == lo[cut:]).all()
+        assert a["raw_event_count"] + b["raw_event_count"] == whole["raw_event_count"]
+        del a, b
+    ctx.close()
+    # a sample of documents from all over the batch against the oracle
+    o = W.define_lexer(OracleLexer())
+    pick = np.unique(np.linspace(0, ndocs - 1, 48).astype(np.int64))
+    stext = np.concatenate([text[int(offs[d]):int(offs[d + 1])] for d in pick])
+    soffs = np.concatenate([[0], np.cumsum(doclen[pick])]).astype(np.uint64)
+    ro = o.scan(stext, soffs, nthreads=8)
+    for k, d in enumerate(pick):
+        mine = lex[int(lo[d]):int(lo[d + 1])]
+        ref = ro["lexems"][int(ro["offsets"][k]):int(ro["offsets"][k + 1])]
+        assert len(mine) == len(ref) and (mine == ref).all(), "document %d differs from the oracle" % d
+    # the island/slot formulation gives the same bytes
+    monkeypatch.setenv("SP_LEXER_HYBRID", "0")
+    ctx = g.create_context()
+    other = ctx.scan(text, offs)
+    assert ctx.counter("second_half") == 2
+    ctx.close()
+    assert (other["offsets"] == lo).all() and (other["lexems"] == lex).all() and other["raw_event_count"] == whole["raw_event_count"]
