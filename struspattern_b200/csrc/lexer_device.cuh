@@ -373,6 +373,17 @@ SP_HD void sp_supersede( const SpLexerTables& T, const SpRawEvent& rev, EventArr
 		return;
 	}
 	const uint32_t evLevel = ev.meta & 0xFF, evEnd = ev.origpos + ev.origsize;
+	if (!withSymbol)
+	{
+		// the usual case decided with one read: the new element starts behind the last one, so nothing is deleted (the first
+		// loop below stops at once) and it is appended at the end (so does the third); the second loop looks at the last one only
+		const SpMatchEvent last = ar[ n-1];
+		if (last.origpos < ev.origpos)
+		{
+			if (last.origpos + last.origsize < evEnd) {ar[ n++] = ev; return;}
+			if ((last.meta & 0xFF) > evLevel) return;
+		}
+	}
 	// elements replaced by the new one (same lexem at the same place) or covered by it with a lower level
 	uint32_t deleted = 0;
 	for (uint32_t k=n; k>0; --k)

@@ -114,7 +114,7 @@ struct TileSource	/* the lane's column of the warp's event tile: element k at [k
 	__device__ __forceinline__ uint32_t df( uint32_t k) const {return doc_tile[ k * 33];}
 };
 
-static __global__ void __launch_bounds__(LexFusedThreads) k_lex_resolve_chunks( SpFusedParams P)
+static __global__ void __launch_bounds__(LexFusedThreads, 8) k_lex_resolve_chunks( SpFusedParams P)
 {
 	__shared__ uint4 s_ar[ SP_FUSED_AR * LexFusedThreads];
 	// event tiles of the warps, [warp][k][lane]: every lane consumes its own stream of events, which lies 2-3 KB away from

@@ -63,6 +63,8 @@ int64_t hsim_info( void* h, const char* key)
 	if (k == "fused_legacy") return (int64_t)hs->legacy;
 	if (k == "lead_fixed") return (int64_t)hs->leadfixed;
 	if (k == "cut_states") return (int64_t)hs->prog.tables().view.fwd_cut_n;
+	if (k == "cut_lo") return (int64_t)hs->prog.tables().view.fwd_cut_lo;
+	if (k == "acc_base") return (int64_t)hs->prog.tables().view.fwd_acc_base;
 	return -1;
 }
 

@@ -25,3 +25,16 @@ print("states", n, "stride", stride, "row bytes", stride * 2, "visited states", 
 srt = np.sort(hist)[::-1]
 for H in (32, 64, 128, 160, 192, 256, 384, 512, 1024):
     print("H=%4d (%6.1f KB): best rows cover %.4f, lowest ids cover %.4f" % (H, H * stride * 2 / 1024, srt[:H].sum() / tot, hist[:H].sum() / tot))
+
+# by group: [plain][plain,cut][acc,cut][acc]
+accbase, cutlo, cutn = hs.info("acc_base"), hs.info("cut_lo"), hs.info("cut_states")
+groups = [("plain", 0, cutlo), ("plain,cut", cutlo, accbase), ("acc,cut", accbase, cutlo + cutn), ("acc", cutlo + cutn, n)]
+for name, lo, hi in groups:
+    h = np.sort(hist[lo:hi])[::-1]
+    print("%-10s states %6d share of reads %.4f; top 8/16/32/64 rows of the group cover %s of all reads" % (
+        name, hi - lo, h.sum() / tot, " ".join("%.4f" % (h[:k].sum() / tot) for k in (8, 16, 32, 64))))
+# one budget of H rows spent greedily over all groups = the best-rows line above; how many rows per group is that?
+order = np.argsort(hist)[::-1]
+for H in (32, 64, 128):
+    top = order[:H]
+    print("H=%d: rows per group" % H, [int(((top >= lo) & (top < hi)).sum()) for _, lo, hi in groups])
