@@ -100,7 +100,7 @@ static __global__ void __launch_bounds__(LexFusedThreads) k_lex_fused( SpFusedPa
 
 // chunk resolution over completed events (second half of the fused formulation alone): one thread per chunk, open
 // segment elements in shared memory, element i of thread t at [i*LexFusedThreads + t]
-enum {LexResolveTile = 8};	// events per lane and refill
+enum {LexResolveTile = 8};	// events per lane and refill (a power of two up to 32)
 
 struct TileSource	/* the lane's column of the warp's event tile: element k at [k*33] */
 {
@@ -118,8 +118,8 @@ static __global__ void __launch_bounds__(LexFusedThreads, 8) k_lex_resolve_chunk
 {
 	__shared__ uint4 s_ar[ SP_FUSED_AR * LexFusedThreads];
 	// event tiles of the warps, [warp][k][lane]: every lane consumes its own stream of events, which lies 2-3 KB away from
-	// its neighbour's; the warp fetches LexResolveTile events of every stream with coalesced loads (4 streams x 128 bytes
-	// per instruction) instead of 32 scattered 16 byte loads per step
+	// its neighbour's; the warp fetches LexResolveTile events of every stream with coalesced loads (32/LexResolveTile streams
+	// x LexResolveTile events per instruction) instead of 32 scattered 16 byte loads per step
 	__shared__ uint4 s_ev[ LexFusedThreads/32][ LexResolveTile][ 33];
 	__shared__ uint32_t s_doc[ LexFusedThreads/32][ LexResolveTile][ 33];
 	const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -137,7 +137,7 @@ static __global__ void __launch_bounds__(LexFusedThreads, 8) k_lex_resolve_chunk
 		#pragma unroll
 		for (int r=0; r<LexResolveTile; ++r)
 		{
-			const unsigned int s = r * 4 + (lane & 3), k = lane >> 2;
+			const unsigned int s = r * (32/LexResolveTile) + (lane % (32/LexResolveTile)), k = lane / (32/LexResolveTile);
 			const uint64_t p = ((uint64_t)__shfl_sync( 0xFFFFFFFFu, phi, s) << 32) | __shfl_sync( 0xFFFFFFFFu, plo, s);
 			const uint32_t n = __shfl_sync( 0xFFFFFFFFu, left, s);
 			if (k < n)
