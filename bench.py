@@ -155,13 +155,13 @@ def algorithmic_bytes(kernel, c):
 
 
 # DRAM traffic (dram__bytes_read.sum + dram__bytes_write.sum) of one launch from the ncu --set full capture summarised in
-# profiles/r01_lexer_v9_ncu.txt (256 MiB of the same corpus), as bytes per unit the launch processes; scaled to this run's units
+# profiles/r01_lexer_v10_ncu.txt (256 MiB of the same corpus), as bytes per unit the launch processes; scaled to this run's units
 NCU_TRAFFIC = {
-    "k_lex_count": (0.316676e9 + 0.008487e9, "text_bytes", 268435456),
-    "k_lex_emit": (0.552721e9 + 1.588677e9, "raw_events", 89434349),
-    "k_lex_finish": (1.699707e9 + 1.730083e9, "raw_events", 89434349),
-    "k_lex_resolve_chunks": (2.121796e9 + 1.213993e9, "raw_events", 89434349),
-    "k_fused_write": (1.182107e9 + 1.069964e9, "lexems", 69551577),
+    "k_lex_count": (0.323008e9 + 0.010925e9, "text_bytes", 268435456),
+    "k_lex_emit": (0.539853e9 + 1.577043e9, "raw_events", 89434349),
+    "k_lex_finish": (1.699961e9 + 1.731728e9, "raw_events", 89434349),
+    "k_lex_resolve_chunks": (2.123800e9 + 1.211899e9, "raw_events", 89434349),
+    "k_fused_write": (1.182111e9 + 1.070465e9, "lexems", 69551577),
 }
 
 
@@ -370,7 +370,7 @@ def run_ours(args, rank, world, local_rank):
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": ncu_traffic(dominant, counters), "algorithmic_bytes": algorithmic_bytes(dominant, counters),
-                     "traffic_source": "profiles/r01_lexer_v9_ncu.txt (ncu --set full, 256 MiB of this corpus, scaled by units)", "peak_kind": peak_kind,
+                     "traffic_source": "profiles/r01_lexer_v10_ncu.txt (ncu --set full, 256 MiB of this corpus, scaled by units)", "peak_kind": peak_kind,
                      "kernel_ms_per_step": {k: ktimes[k][0] / 1000.0 / args.steps for k in KERNELS}},
         "matches_per_s": counters["lexems"] * world * args.steps / (ms_max / 1000.0),
     }
