@@ -198,6 +198,28 @@ def run_reference(args, rank, world):
     }
 
 
+def bind_to_gpu_numa_node(local_rank):
+    """Run this rank's host threads (and with them its pinned buffers: pages are placed where they are first touched) on the
+    CPU socket its GPU hangs on; without it the copies of half of the ranks cross the socket link. -> what was done"""
+    import torch
+    try:
+        p = torch.cuda.get_device_properties(local_rank)
+        dev = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        node = int(open("/sys/bus/pci/devices/%s/numa_node" % dev).read())
+        if node < 0:
+            return {"gpu": dev, "node": node, "bound": False}
+        cpus = set()
+        for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        usable = cpus & os.sched_getaffinity(0)
+        if usable:
+            os.sched_setaffinity(0, usable)
+        return {"gpu": dev, "node": node, "bound": bool(usable), "cpus": len(usable)}
+    except (OSError, ValueError, AttributeError) as exc:
+        return {"bound": False, "why": str(exc)[:80]}
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
@@ -205,6 +227,7 @@ def run_ours(args, rank, world, local_rank):
     from struspattern_b200 import workloads as W
 
     torch.cuda.set_device(local_rank)
+    numa = bind_to_gpu_numa_node(local_rank) if world > 1 else {"bound": False, "why": "single rank"}
     lx = W.define_lexer(Lexer())
     text, offs, keep = make_corpus(args.bytes, rank, pinned=True)
     ndocs = len(offs) - 1
@@ -321,6 +344,7 @@ def run_ours(args, rank, world, local_rank):
     s_up, s_down = torch.cuda.Stream(), torch.cuda.Stream()
     dev_out = torch.empty(16 * nlex, dtype=torch.uint8, device="cuda")
     link_ms = None
+    barrier()   # all ranks copy at the same time: the bound is what the host gives every rank then
     for _ in range(2):
         torch.cuda.synchronize()
         pc0.record()
@@ -365,6 +389,7 @@ def run_ours(args, rank, world, local_rank):
         "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": int(args.bytes + 8 * (ndocs + 1)),
                 "d2h_bytes_per_step": int(16 * nlex + 8 * (ndocs + len(subs)) + 4 * ndocs), "steps": e2e_steps,
                 "pipeline": "%d host threads x (context + stream), sub-batches of %d MiB" % (args.e2e_threads, args.e2e_sub_bytes >> 20),
+                "numa_rank0": numa, "host_cpus": len(os.sched_getaffinity(0)),
                 "link_bound": {"value": float(args.bytes) / (link_ms / 1000.0) / 1e9, "unit": "GB/s",
                                "what": "text bytes / time of plain pinned copies of the same H2D and D2H bytes issued together (rank 0)"}},
         "gpu_launches": int(launches),
