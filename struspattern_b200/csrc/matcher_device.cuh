@@ -23,13 +23,11 @@
 
 #ifdef __CUDACC__
 #define SP_MHD __device__ __forceinline__
-#define SP_MCOLD __device__ __noinline__	/* rarely taken paths: one copy, out of the per-token loop's instruction stream */
 #define SP_MLDG(p) __ldg(p)
 #define SP_MHOSTDEV __host__ __device__ __forceinline__
 #else
 #define SP_MHOSTDEV inline
 #define SP_MHD inline
-#define SP_MCOLD inline
 #define SP_MLDG(p) (*(p))
 #endif
 
@@ -280,7 +278,7 @@ SP_MHD uint32_t sp_dataref_create( SpArena& A, SpDocState& S)
 	return d;
 }
 
-SP_MCOLD void sp_dataref_release( SpArena& A, SpDocState& S, uint32_t d)
+SP_MHD void sp_dataref_release( SpArena& A, SpDocState& S, uint32_t d)
 {
 	SpDataRef& ref = A.datarefs[ d-1];
 	if (ref.refcount > 1) {--ref.refcount; return;}
