@@ -118,6 +118,14 @@ uint32_t sp_lexer_get_symbol( const sp_lexer* lx, uint32_t lexemid, const char* 
 int sp_lexer_compile( sp_lexer* lx);
 /* Introspection of the compiled tables (DESIGN.md "lexer tables"); values by key name, -1 if unknown. */
 int64_t sp_lexer_table_info( const sp_lexer* lx, const char* key);
+/* Compiled lexer <-> flat byte image (no counterpart in the reference, which calls
+ * hs_compile_ext_multi on every start, src/patternLexer.cpp:1083, and never hs_serialize_database).
+ * sp_lexer_serialize returns the image size (>= 0) and fills `image` if `capacity` is large enough (call with
+ * image = NULL to ask for the size), or a negative SP_ERR_*. sp_lexer_deserialize loads an image into a lexer that
+ * has no definitions yet and uploads the tables, like sp_lexer_compile does; images of another table layout or
+ * damaged images are rejected with SP_ERR_ARGUMENT. */
+int64_t sp_lexer_serialize( const sp_lexer* lx, void* image, uint64_t capacity);
+int sp_lexer_deserialize( sp_lexer* lx, const void* image, uint64_t size);
 
 /* PatternLexerInstance::createContext, src/patternLexer.cpp:1120: scratch + output buffers of one
  * in-flight batch. cuda_stream is a cudaStream_t (NULL = default stream). */

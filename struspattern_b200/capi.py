@@ -48,6 +48,7 @@ def lib():
             "sp_lexer_define_symbol": (C.c_int, [vp, u32, u32, cp, C.c_size_t]),
             "sp_lexer_get_symbol": (u32, [vp, u32, cp, C.c_size_t]),
             "sp_lexer_compile": (C.c_int, [vp]), "sp_lexer_table_info": (C.c_int64, [vp, cp]),
+            "sp_lexer_serialize": (C.c_int64, [vp, vp, C.c_uint64]), "sp_lexer_deserialize": (C.c_int, [vp, vp, C.c_uint64]),
             "sp_lexer_ctx_create": (vp, [vp, vp]), "sp_lexer_ctx_destroy": (None, [vp]),
             "sp_lexer_ctx_last_error": (cp, [vp]),
             "sp_lexer_scan": (C.c_int, [vp, vp, C.c_int, u64p, u32]),
@@ -125,6 +126,21 @@ class Lexer:
 
     def table_info(self, key):
         return int(self.L.sp_lexer_table_info(self.h, key.encode()))
+
+    def serialize(self):
+        """-> bytes: image of the compiled tables (sp_lexer_serialize)"""
+        n = int(self.L.sp_lexer_serialize(self.h, None, 0))
+        if n < 0:
+            self._ck(n)
+        buf = C.create_string_buffer(n)
+        m = int(self.L.sp_lexer_serialize(self.h, buf, n))
+        if m != n:
+            self._ck(m if m < 0 else -1)
+        return buf.raw
+
+    def deserialize(self, image):
+        """loads an image made by serialize() into this (empty) lexer instead of define_* + compile"""
+        self._ck(self.L.sp_lexer_deserialize(self.h, image, len(image)))
 
     def create_context(self, stream=None):
         return LexerContext(self, stream)

@@ -83,6 +83,24 @@ int sp_lexer_compile( sp_lexer* lx)
 		lx->upload();
 	})
 }
+int64_t sp_lexer_serialize( const sp_lexer* lx, void* image, uint64_t capacity)
+{
+	try
+	{
+		std::vector<uint8_t> bytes;
+		lx->prog.serialize( bytes);
+		if (image && capacity >= bytes.size()) std::memcpy( image, bytes.data(), bytes.size());
+		return (int64_t)bytes.size();
+	}
+	catch (const std::exception& e) {return lexerFail( const_cast<sp_lexer*>( lx)->lasterror, e);}
+}
+int sp_lexer_deserialize( sp_lexer* lx, const void* image, uint64_t size)
+{
+	SP_LEXER_TRY( lx, {
+		lx->prog.deserialize( static_cast<const uint8_t*>( image), (std::size_t)size);
+		lx->upload();
+	})
+}
 int64_t sp_lexer_table_info( const sp_lexer* lx, const char* key)
 {
 	std::string k( key);

@@ -9,6 +9,7 @@
 #define SP_LEXER_COMPILE_HPP_INCLUDED
 #include "automaton.hpp"
 #include "lexer_tables.h"
+#include <cstring>
 #include <cstdlib>
 
 namespace sp {
@@ -62,6 +63,96 @@ public:
 	LexerTablesHost& tables() {return m_tables;}
 	uint32_t forwardStates() const {return m_fwdStates;}
 	uint32_t reverseStates() const {return m_revStates;}
+
+	// ---- compiled program <-> flat byte image (the reference recompiles its Hyperscan database on every
+	// start, hs_serialize_database is unused; compiling the C2 set takes seconds here, loading the image milliseconds).
+	// Image: header {magic, version, layout hash, payload bytes, payload FNV-1a} + payload (scalars, definitions, symbols,
+	// every table array as {count, raw elements}). It is tied to this build's table layout (layout hash) and byte order.
+	enum {ImageMagic = 0x584C5053u /*"SPLX"*/, ImageVersion = 1, NofImageScalars = 10};
+
+	void serialize( std::vector<uint8_t>& out) const
+	{
+		if (!m_compiled) throw std::runtime_error( "serialize called before compile");
+		ImageWriter w;
+		w.pod( m_flags); w.pod( (uint32_t)m_bytechar); w.pod( m_fwdStates); w.pod( m_revStates);
+		const SpLexerTables& V = m_tables.view;
+		const uint32_t scalars[ NofImageScalars] = {V.fwd_states, V.fwd_stride, V.fwd_init, V.fwd_acc_base, V.fwd_cut_lo, V.fwd_cut_n, V.fwd_max_acc, V.npat, V.sym_mask, V.has_symbols};
+		w.pod( scalars);
+		w.pod( (uint64_t)m_defs.size());
+		for (const LexemDefinition& d: m_defs)
+		{
+			w.str( d.expression); w.pod( d.id); w.pod( d.level); w.pod( d.posbind); w.pod( d.resultidx); w.pod( d.editdist); w.pod( d.symtab);
+		}
+		w.pod( (uint64_t)m_symtabOfLexem.size());
+		for (const auto& kv: m_symtabOfLexem) {w.pod( kv.first); w.pod( kv.second);}
+		w.pod( (uint64_t)m_symbols.size());
+		for (const auto& kv: m_symbols) {w.pod( kv.first.first); w.str( kv.first.second); w.pod( kv.second);}
+		const LexerTablesHost& T = m_tables;
+		w.vec( T.fwd_next); w.vec( T.fwd_class); w.vec( T.fwd_acc_off); w.vec( T.fwd_acc_span); w.vec( T.fwd_acc_pat);
+		w.vec( T.rev_next); w.vec( T.rev_classes); w.vec( T.cap_next); w.vec( T.cap_classes); w.vec( T.cap);
+		w.vec( T.pat); w.vec( T.sym_slots); w.vec( T.sym_pool);
+		const uint32_t header[ 4] = {(uint32_t)ImageMagic, (uint32_t)ImageVersion, layoutHash(), fnv1a( w.bytes.data(), w.bytes.size())};
+		const uint64_t payload = w.bytes.size();
+		out.clear();
+		out.insert( out.end(), (const uint8_t*)header, (const uint8_t*)header + sizeof(header));
+		out.insert( out.end(), (const uint8_t*)&payload, (const uint8_t*)&payload + sizeof(payload));
+		out.insert( out.end(), w.bytes.begin(), w.bytes.end());
+	}
+
+	void deserialize( const uint8_t* image, std::size_t size)
+	{
+		if (m_compiled || !m_defs.empty()) throw std::runtime_error( "a compiled lexer image can only be loaded into an empty lexer");
+		uint32_t header[ 4]; uint64_t payload;
+		if (size < sizeof(header) + sizeof(payload)) throw std::runtime_error( "lexer image truncated");
+		std::memcpy( header, image, sizeof(header)); std::memcpy( &payload, image + sizeof(header), sizeof(payload));
+		if (header[0] != (uint32_t)ImageMagic) throw std::runtime_error( "not a lexer image");
+		if (header[1] != (uint32_t)ImageVersion || header[2] != layoutHash()) throw std::runtime_error( "lexer image of another version or table layout: compile again");
+		const uint8_t* body = image + sizeof(header) + sizeof(payload);
+		if (payload != size - sizeof(header) - sizeof(payload)) throw std::runtime_error( "lexer image truncated");
+		if (header[3] != fnv1a( body, (std::size_t)payload)) throw std::runtime_error( "lexer image damaged (checksum)");
+		ImageReader r( body, (std::size_t)payload);
+		LexerProgram fresh;
+		uint32_t bytechar;
+		r.pod( fresh.m_flags); r.pod( bytechar); r.pod( fresh.m_fwdStates); r.pod( fresh.m_revStates);
+		fresh.m_bytechar = bytechar != 0;
+		uint32_t scalars[ NofImageScalars];
+		r.pod( scalars);
+		{
+			SpLexerTables& W = fresh.m_tables.view;
+			std::memset( &W, 0, sizeof(W));
+			W.fwd_states = scalars[0]; W.fwd_stride = scalars[1]; W.fwd_init = scalars[2]; W.fwd_acc_base = scalars[3]; W.fwd_cut_lo = scalars[4];
+			W.fwd_cut_n = scalars[5]; W.fwd_max_acc = scalars[6]; W.npat = scalars[7]; W.sym_mask = scalars[8]; W.has_symbols = scalars[9];
+		}
+		uint64_t n;
+		r.pod( n);
+		for (uint64_t i=0; i<n; ++i)
+		{
+			LexemDefinition d;
+			r.str( d.expression); r.pod( d.id); r.pod( d.level); r.pod( d.posbind); r.pod( d.resultidx); r.pod( d.editdist); r.pod( d.symtab);
+			fresh.m_defs.push_back( d);
+		}
+		r.pod( n);
+		for (uint64_t i=0; i<n; ++i) {uint32_t k; uint8_t v; r.pod( k); r.pod( v); fresh.m_symtabOfLexem[ k] = v;}
+		r.pod( n);
+		for (uint64_t i=0; i<n; ++i) {uint32_t lexemid, symid; std::string name; r.pod( lexemid); r.str( name); r.pod( symid); fresh.m_symbols[ std::make_pair( lexemid, name)] = symid;}
+		LexerTablesHost& T = fresh.m_tables;
+		r.vec( T.fwd_next); r.vec( T.fwd_class); r.vec( T.fwd_acc_off); r.vec( T.fwd_acc_span); r.vec( T.fwd_acc_pat);
+		r.vec( T.rev_next); r.vec( T.rev_classes); r.vec( T.cap_next); r.vec( T.cap_classes); r.vec( T.cap);
+		r.vec( T.pat); r.vec( T.sym_slots); r.vec( T.sym_pool);
+		if (!r.atEnd()) throw std::runtime_error( "lexer image has trailing bytes");
+		// the arrays must be as large as the scalars say: a kernel indexes them without further checks
+		const SpLexerTables& V = T.view;
+		if (T.fwd_next.size() != (std::size_t)V.fwd_states * V.fwd_stride || T.fwd_class.size() != 256 || V.fwd_acc_base > V.fwd_states
+		||  T.fwd_acc_off.size() != (std::size_t)(V.fwd_states - V.fwd_acc_base) + 1 || T.fwd_acc_span.size() + 1 != T.fwd_acc_off.size()
+		||  T.fwd_acc_off.back() != T.fwd_acc_pat.size() || T.pat.size() != V.npat || fresh.m_defs.size() != V.npat
+		||  (V.sym_mask && T.sym_slots.size() != (std::size_t)V.sym_mask + 1))
+		{
+			throw std::runtime_error( "lexer image inconsistent");
+		}
+		fresh.m_compiled = true;
+		*this = fresh;
+		m_tables.pointToHost();
+	}
 
 	// PatternLexerInstance::defineOption, src/patternLexer.cpp:1031-1066
 	void defineOption( const std::string& name)
@@ -339,6 +430,47 @@ private:
 			T.sym_pool.insert( T.sym_pool.end(), name.begin(), name.end());
 		}
 		if (T.sym_pool.empty()) T.sym_pool.push_back( 0);
+	}
+	struct ImageWriter
+	{
+		std::vector<uint8_t> bytes;
+		template <typename T> void pod( const T& v) {const uint8_t* p = (const uint8_t*)&v; bytes.insert( bytes.end(), p, p + sizeof(T));}
+		void str( const std::string& v) {pod( (uint64_t)v.size()); bytes.insert( bytes.end(), v.begin(), v.end());}
+		template <typename T> void vec( const std::vector<T>& v)
+		{
+			pod( (uint64_t)v.size());
+			const uint8_t* p = (const uint8_t*)v.data();
+			bytes.insert( bytes.end(), p, p + v.size() * sizeof(T));
+		}
+	};
+	struct ImageReader
+	{
+		const uint8_t* p; std::size_t left;
+		ImageReader( const uint8_t* p_, std::size_t n) :p(p_),left(n){}
+		void need( std::size_t n) {if (n > left) throw std::runtime_error( "lexer image truncated");}
+		template <typename T> void pod( T& v) {need( sizeof(T)); std::memcpy( &v, p, sizeof(T)); p += sizeof(T); left -= sizeof(T);}
+		void str( std::string& v) {uint64_t n; pod( n); need( (std::size_t)n); v.assign( (const char*)p, (std::size_t)n); p += n; left -= (std::size_t)n;}
+		template <typename T> void vec( std::vector<T>& v)
+		{
+			uint64_t n; pod( n);
+			if (n > left / sizeof(T)) throw std::runtime_error( "lexer image truncated");
+			v.resize( (std::size_t)n);
+			if (n) std::memcpy( (void*)v.data(), p, (std::size_t)n * sizeof(T));
+			p += n * sizeof(T); left -= (std::size_t)n * sizeof(T);
+		}
+		bool atEnd() const {return left == 0;}
+	};
+	static uint32_t fnv1a( const uint8_t* s, std::size_t n)
+	{
+		uint32_t h = 2166136261u;
+		for (std::size_t i=0; i<n; ++i) {h ^= s[i]; h *= 16777619u;}
+		return h;
+	}
+	static uint32_t layoutHash()
+	{
+		const uint32_t sizes[] = {(uint32_t)sizeof(SpLexerTables), (uint32_t)sizeof(SpPatternInfo), (uint32_t)sizeof(SpAnchoredDfa),
+					(uint32_t)sizeof(SpSymbolSlot), (uint32_t)sizeof(SpAccSpan), SP_REV_ACCEPT, SP_REV_STOP};
+		return fnv1a( (const uint8_t*)sizes, sizeof(sizes));
 	}
 	static uint32_t symbolHash( const uint8_t* s, uint32_t len, uint32_t symtab)
 	{

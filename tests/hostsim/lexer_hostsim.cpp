@@ -46,6 +46,20 @@ int hsim_define_lexem( void* h, uint32_t id, const char* expr, size_t exprlen, u
 int hsim_define_symbol( void* h, uint32_t symbolid, uint32_t lexemid, const char* name, size_t namelen)
 	{HSIM_TRY( hs->prog.defineSymbol( symbolid, lexemid, std::string( name, namelen)))}
 int hsim_compile( void* h) {HSIM_TRY( hs->prog.compile())}
+// image of the compiled program (LexerProgram::serialize / deserialize)
+int64_t hsim_serialize( void* h, uint8_t* image, uint64_t capacity)
+{
+	HostSim* hs = (HostSim*)h;
+	try
+	{
+		std::vector<uint8_t> bytes;
+		hs->prog.serialize( bytes);
+		if (image && capacity >= bytes.size()) std::memcpy( image, bytes.data(), bytes.size());
+		return (int64_t)bytes.size();
+	}
+	catch (const std::exception& e) {hs->lasterror = e.what(); return -1;}
+}
+int hsim_deserialize( void* h, const uint8_t* image, uint64_t size) {HSIM_TRY( hs->prog.deserialize( image, (std::size_t)size))}
 int hsim_set_mode( void* h, int mode) {((HostSim*)h)->mode = mode; return 0;}
 int64_t hsim_info( void* h, const char* key)
 {

@@ -37,6 +37,7 @@ class HostSimLexer:
             L.hsim_result_count.restype = C.c_uint64
             L.hsim_raw_event_count.restype = C.c_uint64
             L.hsim_info.restype = C.c_int64
+            L.hsim_serialize.restype = C.c_int64
             cls._lib = L
         return cls._lib
 
@@ -72,6 +73,17 @@ class HostSimLexer:
 
     def info(self, key):
         return int(self.L.hsim_info(self.h, key.encode()))
+
+    def serialize(self):
+        n = int(self.L.hsim_serialize(self.h, None, C.c_uint64(0)))
+        if n < 0:
+            self._ck(n)
+        buf = C.create_string_buffer(n)
+        assert int(self.L.hsim_serialize(self.h, buf, C.c_uint64(n))) == n
+        return buf.raw
+
+    def deserialize(self, image):
+        self._ck(self.L.hsim_deserialize(self.h, image, C.c_uint64(len(image))))
 
     def scan(self, text, doc_offsets, nthreads=1, keep_raw=False):
         buf = np.frombuffer(text, dtype=np.uint8) if isinstance(text, (bytes, bytearray)) else np.ascontiguousarray(text, dtype=np.uint8)

@@ -270,3 +270,23 @@ def test_full_size_corpus_properties(monkeypatch):
     assert ctx.counter("second_half") == 2
     ctx.close()
     assert (other["offsets"] == lo).all() and (other["lexems"] == lex).all() and other["raw_event_count"] == whole["raw_event_count"]
+
+
+def test_compiled_image_gives_the_same_lexer():
+    """sp_lexer_serialize / sp_lexer_deserialize: the lexer loaded from an image scans like the one that was compiled."""
+    import time
+    from struspattern_b200 import workloads as W
+    t0 = time.perf_counter()
+    a = W.define_lexer(_gpu_lexer()(), symbols=[(900 + i, W.WORD, w) for i, w in enumerate(("the", "of", "and"))])
+    t_compile = time.perf_counter() - t0
+    image = a.serialize()
+    t0 = time.perf_counter()
+    b = _gpu_lexer()()
+    b.deserialize(image)
+    t_load = time.perf_counter() - t0
+    assert b.serialize() == image and b.table_info("fwd_states") == a.table_info("fwd_states")
+    assert b.get_symbol(W.WORD, "of") == 901 and t_load < t_compile
+    text, offs = make_batch(seed=9, ndocs=200, mean_bytes=3000)
+    _same(a.scan(text, offs), b.scan(text, offs))
+    with pytest.raises(Exception):
+        _gpu_lexer()().deserialize(image[:-3])

@@ -221,3 +221,39 @@ def test_fused_golden_case_and_symbol_quirk():
     lx.define_symbol(9, 2, "a b c")
     lx.compile()
     assert lx.match("a b c") == [(1, 1, 0, 1), (2, 1, 0, 5), (9, 1, 0, 5), (0, 1, 0, 0), (1, 2, 4, 1)]
+
+
+def test_compiled_image_round_trip():
+    """LexerProgram::serialize / deserialize (sp_lexer_serialize / sp_lexer_deserialize): a lexer loaded from the image of a
+    compiled one has the same tables (image of the image is identical) and gives the oracle's output."""
+    for name in sorted(LEXEM_SETS):
+        a = define_set(HostSimLexer(chunk=64, warmup=16, mode=3), name)
+        image = a.serialize()
+        assert image[:4] == b"SPLX" and image == a.serialize()
+        b = HostSimLexer(chunk=64, warmup=16, mode=3)
+        b.deserialize(image)
+        assert b.serialize() == image
+        for key in ("fwd_states", "fwd_stride", "rev_states", "cut_states", "acc_base"):
+            assert a.info(key) == b.info(key)
+        text, offs = make_batch(seed=5, ndocs=40, mean_bytes=600)
+        o = define_set(OracleLexer(), name)
+        ro, rb = o.scan(text, offs), b.scan(text, offs)
+        assert (ro["offsets"] == rb["offsets"]).all() and (ro["lexems"] == rb["lexems"]).all()
+
+
+def test_compiled_image_is_checked():
+    a = define_set(HostSimLexer(), sorted(LEXEM_SETS)[0])
+    image = a.serialize()
+    for bad, what in ((image[:-1], "truncated"), (b"XXXX" + image[4:], "not a lexer image"),
+                      (image[:200] + bytes([image[200] ^ 1]) + image[201:], "checksum"), (image + b"\0", "truncated")):
+        b = HostSimLexer()
+        with pytest.raises(Exception) as err:
+            b.deserialize(bad)
+        assert what in str(err.value)
+    # only an empty lexer takes an image; an uncompiled one has none
+    with pytest.raises(Exception):
+        a.deserialize(image)
+    c = HostSimLexer()
+    c.define_lexem(1, "[a-z]+")
+    with pytest.raises(Exception):
+        c.serialize()
