@@ -25,16 +25,32 @@ def main():
     ap.add_argument("--no-compile", action="store_true")
     ap.add_argument("--no-ref", action="store_true")
     ap.add_argument("--check", action="store_true")
+    ap.add_argument("--c4", action="store_true", help="BASELINE config 3 shape: --rules dictionary style sequence_imm patterns (2-5 terms, Zipf 0.8) "
+                                                       "over a vocabulary of --features terms; --docs token streams of 1000-4000 tokens (Zipf 1.0)")
     args = ap.parse_args()
     import torch
     import matcher_cases as MC
     from oracle_util import RefMatcher
     from struspattern_b200 import Matcher
-    toks, offs = MC.random_documents(4712, args.docs, args.tokens, args.features)
+    from struspattern_b200 import workloads as W
+    if args.c4:
+        toks, offs = W.c4_token_documents(4712, args.docs, args.features)
+
+        def define(m):
+            W.define_c4_patterns(m, 4711, args.rules, args.features)
+    else:
+        toks, offs = MC.random_documents(4712, args.docs, args.tokens, args.features)
+
+        def define(m):
+            MC.define_c1_rules(m, 4711, args.rules, args.features)
     gpu = Matcher()
-    MC.define_c1_rules(gpu, 4711, args.rules, args.features)
+    t0 = time.perf_counter()
+    define(gpu)
+    t_define = time.perf_counter() - t0
+    t0 = time.perf_counter()
     if not args.no_compile:
         gpu.compile()
+    t_compile = time.perf_counter() - t0
     ctx = gpu.create_context()
     if args.warps:
         ctx.counter("warps_per_sm=%d" % args.warps)
@@ -54,14 +70,15 @@ def main():
     dt = (time.perf_counter() - t0) / args.steps
     kms = ctx.counter("time_us:k_match_documents") / 1000.0 / max(1, ctx.counter("calls:k_match_documents"))
     out = ctx.fetch()
-    line = {"tokens": int(len(toks)), "docs": args.docs, "rules": args.rules, "results": int(nres), "items": int(nitems),
+    line = {"workload": "C4 dictionary patterns" if args.c4 else "C1 random rules", "define_s": t_define, "compile_s": t_compile,
+            "tokens": int(len(toks)), "docs": args.docs, "rules": args.rules, "results": int(nres), "items": int(nitems),
             "gpu_ms": dt * 1000.0, "kernel_ms": kms, "gpu_mtok_s": len(toks) / dt / 1e6,
             "installs": int(out["stats"]["nof_programs_installed"].sum()), "signals": int(out["stats"]["nof_signals_fired"].sum()),
             "arena_retries": ctx.counter("arena_retries"), "pool_retries": ctx.counter("pool_retries"), "warps_per_sm": ctx.counter("warps_per_sm"),
             "errors": int((out["status"] != 0).sum())}
     if not args.no_ref:
         ref = RefMatcher()
-        MC.define_c1_rules(ref, 4711, args.rules, args.features)
+        define(ref)
         if not args.no_compile:
             ref.compile()
         nthreads = os.cpu_count() or 1
