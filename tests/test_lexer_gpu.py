@@ -290,3 +290,38 @@ def test_compiled_image_gives_the_same_lexer():
     _same(a.scan(text, offs), b.scan(text, offs))
     with pytest.raises(Exception):
         _gpu_lexer()().deserialize(image[:-3])
+
+
+def test_one_large_document(monkeypatch):
+    """A single document is scanned by as many threads as it has chunks (the reference scans one block
+    below 4 GiB sequentially, src/patternLexer.cpp:866): 4 MiB against the oracle, 128 MiB through two formulations."""
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    from struspattern_b200 import workloads as W
+    text, _, _ = bench.make_corpus(128 << 20, 0, pinned=False)
+    g = W.define_lexer(_gpu_lexer()())
+    o = W.define_lexer(OracleLexer())
+    small = np.array([0, 4 << 20], dtype=np.uint64)
+    _same(o.scan(text[:4 << 20], small), g.scan(text[:4 << 20], small))
+    one = np.array([0, len(text)], dtype=np.uint64)
+    ctx = g.create_context()
+    a = ctx.scan(text, one)
+    assert ctx.counter("second_half") == 4 and int(a["status"][0]) == 0
+    ctx.close()
+    lex = a["lexems"]
+    assert len(lex) > 10_000_000 and int(lex["ordpos"][0]) == 1
+    step = np.diff(lex["ordpos"].astype(np.int64))
+    assert ((step == 0) | (step == 1)).all() and (np.diff(lex["origpos"].astype(np.int64)) >= 0).all()
+    assert int((lex["origpos"].astype(np.int64) + lex["origsize"]).max()) <= len(text)
+    # the first 4 MiB of the large document give the same lexems as the small one up to the last complete match
+    b = g.scan(text[:4 << 20], small)["lexems"]
+    keep = b["origpos"].astype(np.int64) + b["origsize"] < (4 << 20) - 4096
+    n = int(keep.sum())
+    assert keep[:n].all() and (lex[:n] == b[:n]).all()
+    monkeypatch.setenv("SP_LEXER_HYBRID", "0")
+    ctx = g.create_context()
+    c = ctx.scan(text, one)
+    assert ctx.counter("second_half") == 2
+    ctx.close()
+    _same(a, c)
