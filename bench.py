@@ -285,6 +285,11 @@ def run_ours(args, rank, world, local_rank):
     sub_lex_begin = [0] * (len(subs) + 1)     # filled by the untimed first pass (sizes are deterministic)
     streams = [torch.cuda.Stream() for _ in range(args.e2e_threads)]
     ctxs = [lx.create_context(s.cuda_stream) for s in streams]
+    # several ranks on one host: waiting host threads sleep instead of spinning (ranks x threads is about the CPU count)
+    blocking = world * args.e2e_threads * 2 > len(os.sched_getaffinity(0))
+    if blocking:
+        for c in ctxs:
+            c.counter("sync:blocking")
     scratch_offs = [np.zeros(max(e - b for b, e in subs) + 1, dtype=np.uint64) for _ in ctxs]
     errors = []
 
@@ -389,7 +394,7 @@ def run_ours(args, rank, world, local_rank):
         "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": int(args.bytes + 8 * (ndocs + 1)),
                 "d2h_bytes_per_step": int(16 * nlex + 8 * (ndocs + len(subs)) + 4 * ndocs), "steps": e2e_steps,
                 "pipeline": "%d host threads x (context + stream), sub-batches of %d MiB" % (args.e2e_threads, args.e2e_sub_bytes >> 20),
-                "numa_rank0": numa, "host_cpus": len(os.sched_getaffinity(0)),
+                "numa_rank0": numa, "host_cpus": len(os.sched_getaffinity(0)), "blocking_waits": bool(blocking),
                 "link_bound": {"value": float(args.bytes) / (link_ms / 1000.0) / 1e9, "unit": "GB/s",
                                "what": "text bytes / time of plain pinned copies of the same H2D and D2H bytes issued together (rank 0)"}},
         "gpu_launches": int(launches),

@@ -26,6 +26,8 @@ struct sp_lexer_ctx
 	uint64_t total, nchunks, nev, nlex, fixups, rounds;
 	bool valid;
 	uint64_t* pinned;	// [4] host staging for scalar read backs
+	bool blockingSync;	// SP_BLOCKING_SYNC=1 or counter "sync:blocking": host threads sleep in waits instead of spinning (many contexts per host)
+	cudaEvent_t syncEvent;
 	// optional per kernel timing with CUDA events on the context's stream (SP_LEXER_PROFILE=1 or counter "profile:on")
 	enum KernelId {KCount, KVerify, KEmit, KFinish, KResolve, KWrite, KScan, KIslFlags, KIslResolve, KOrdpos, KIslSlots, KSlotScan, KFused, KFusedScan, KFusedWrite, KResolveChunks, NofKernelIds};
 	struct Span {int kernel; cudaEvent_t a, b;};
@@ -64,10 +66,11 @@ struct sp_lexer_ctx
 	}
 
 	sp_lexer_ctx( const sp_lexer* lx_, cudaStream_t stream_)
-		:lx(lx_),stream(stream_),chunk(512),warmup(96),ndocs(0),total(0),nchunks(0),nev(0),nlex(0),fixups(0),rounds(0),valid(false),pinned(0),profile(false),nspans(0)
+		:lx(lx_),stream(stream_),chunk(512),warmup(96),ndocs(0),total(0),nchunks(0),nev(0),nlex(0),fixups(0),rounds(0),valid(false),pinned(0),blockingSync(false),syncEvent(0),profile(false),nspans(0)
 	{
 		std::memset( kernel_ms, 0, sizeof(kernel_ms)); std::memset( kernel_calls, 0, sizeof(kernel_calls));
 		if (std::getenv( "SP_LEXER_PROFILE")) profile = true;
+		if (const char* be = std::getenv( "SP_BLOCKING_SYNC")) blockingSync = be[0] != '0';
 		sequential = std::getenv( "SP_LEXER_SEQUENTIAL") != 0;
 		dense = std::getenv( "SP_LEXER_DENSE") != 0;
 		const char* fe = std::getenv( "SP_LEXER_FUSED");
@@ -86,13 +89,26 @@ struct sp_lexer_ctx
 	{
 		if (pinned) cudaFreeHost( pinned);
 		for (Span& sp: spans) {cudaEventDestroy( sp.a); cudaEventDestroy( sp.b);}
+		if (syncEvent) cudaEventDestroy( syncEvent);
+	}
+
+	cudaError_t waitStream()
+	{
+		if (!blockingSync) return cudaStreamSynchronize( stream);
+		if (!syncEvent)
+		{
+			cudaError_t e = cudaEventCreateWithFlags( &syncEvent, cudaEventBlockingSync | cudaEventDisableTiming);
+			if (e != cudaSuccess) return e;
+		}
+		cudaError_t e = cudaEventRecord( syncEvent, stream);
+		return e != cudaSuccess ? e : cudaEventSynchronize( syncEvent);
 	}
 
 	uint64_t readScalar( const void* devptr, std::size_t bytes)
 	{
 		pinned[0] = 0;
 		SP_CUDA( cudaMemcpyAsync( pinned, devptr, bytes, cudaMemcpyDeviceToHost, stream));
-		SP_CUDA( cudaStreamSynchronize( stream));
+		SP_CUDA( waitStream());
 		return pinned[0];
 	}
 
@@ -162,7 +178,7 @@ struct sp_lexer_ctx
 		k_fused_docs<<<(ndocs + 1 + 255) / 256, 256, 0, stream>>>( F, d_scalars + 1);
 		spanEnd();
 		SP_CUDA( cudaMemcpyAsync( pinned, d_scalars + 1, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, stream));
-		SP_CUDA( cudaStreamSynchronize( stream));
+		SP_CUDA( waitStream());
 		if ((uint32_t)pinned[1]) {++fused_fallbacks; return false;}
 		nlex = pinned[0] >> 32;
 		F.lexems = lexems.as<sp_lexem>( nlex);
@@ -432,7 +448,7 @@ int sp_lexer_scan( sp_lexer_ctx* ctx, const uint8_t* text, int text_on_device, c
 int64_t sp_lexer_result_count( sp_lexer_ctx* ctx)
 {
 	if (!ctx->valid) {ctx->lasterror = "no finished scan"; return SP_ERR_ARGUMENT;}
-	if (cudaStreamSynchronize( ctx->stream) != cudaSuccess) {ctx->lasterror = "kernel failure"; return SP_ERR_CUDA;}
+	if (ctx->waitStream() != cudaSuccess) {ctx->lasterror = "kernel failure"; return SP_ERR_CUDA;}
 	return (int64_t)ctx->nlex;
 }
 const sp_lexem* sp_lexer_result_lexems_device( sp_lexer_ctx* ctx) {return ctx->valid ? (const sp_lexem*)ctx->lexems.ptr() : 0;}
@@ -446,7 +462,7 @@ int sp_lexer_fetch( sp_lexer_ctx* ctx, sp_lexem* lexems, uint64_t* offsets, uint
 		if (lexems && ctx->nlex) SP_CUDA( cudaMemcpyAsync( lexems, ctx->lexems.ptr(), ctx->nlex * sizeof(sp_lexem), cudaMemcpyDeviceToHost, ctx->stream));
 		if (offsets) SP_CUDA( cudaMemcpyAsync( offsets, ctx->lex_off.ptr(), ((std::size_t)ctx->ndocs + 1) * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
 		if (status && ctx->ndocs) SP_CUDA( cudaMemcpyAsync( status, ctx->status.ptr(), (std::size_t)ctx->ndocs * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
-		SP_CUDA( cudaStreamSynchronize( ctx->stream));
+		SP_CUDA( ctx->waitStream());
 	})
 }
 
@@ -468,13 +484,15 @@ int64_t sp_lexer_ctx_counter( sp_lexer_ctx* ctx, const char* key)
 	if (k == "ndocs") return ctx->valid ? (int64_t)ctx->ndocs : -1;
 	if (k == "chunk_bytes") return (int64_t)ctx->chunk;
 	if (k == "profile:on") {ctx->profile = true; return 1;}
+	if (k == "sync:blocking") {ctx->blockingSync = true; return 1;}
+	if (k == "sync:spin") {ctx->blockingSync = false; return 1;}
 	if (k == "profile:off") {ctx->profile = false; return 0;}
 	if (k == "profile:reset") {std::memset( ctx->kernel_ms, 0, sizeof(ctx->kernel_ms)); std::memset( ctx->kernel_calls, 0, sizeof(ctx->kernel_calls)); return 0;}
 	if (k.compare( 0, 8, "time_us:") == 0 || k.compare( 0, 6, "calls:") == 0)
 	{
 		static const char* names[] = {"k_lex_count","k_lex_verify","k_lex_emit","k_lex_finish","k_lex_resolve","k_lex_write","k_scan","k_isl_flags","k_isl_resolve","k_ordpos","k_isl_slots","k_slot_scan","k_lex_fused","k_fused_scan","k_fused_write","k_lex_resolve_chunks"};
 		static_assert( sizeof(names)/sizeof(names[0]) == sp_lexer_ctx::NofKernelIds, "kernel name table out of date");
-		if (cudaStreamSynchronize( ctx->stream) != cudaSuccess) return -1;
+		if (ctx->waitStream() != cudaSuccess) return -1;
 		try {ctx->collectSpans();} catch (...) {return -1;}
 		bool calls = k[0] == 'c';
 		std::string name = k.substr( calls ? 6 : 8);

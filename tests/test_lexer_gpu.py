@@ -47,6 +47,8 @@ def test_device_resident_text_and_context_reuse():
         text, offs = make_batch(seed=seed, ndocs=50 * seed, mean_bytes=700)
         dev = torch.from_numpy(text).cuda()
         _same(o.scan(text, offs, nthreads=8), ctx.scan(dev.data_ptr(), offs, on_device=True))
+        if seed == 2:
+            assert ctx.counter("sync:blocking") == 1     # waits sleep on an event from here on (many contexts per host)
 
 
 def test_speculation_is_repaired():
