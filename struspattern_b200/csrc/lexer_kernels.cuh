@@ -21,7 +21,7 @@
 
 namespace sp {
 
-enum {LexScanThreads = 128, LexEventThreads = 256, LexDocThreads = 64};
+enum {LexScanThreads = 128, LexEventThreads = 128, LexDocThreads = 64};
 
 // the byte -> column map of the forward automaton is read once per text byte with a different index in every lane:
 // as a global load that is a 32 address gather per byte; a copy in shared memory makes it a (mostly conflict free) LDS
