@@ -81,7 +81,7 @@ static __global__ void __launch_bounds__(LexDocThreads) k_lex_write( SpScanParam
 //   AggScan        exclusive scan of the per chunk (advanced | emitted << 32) pairs
 //   k_fused_docs   per document scan base, lexem offsets, late checks
 //   k_fused_write  one warp per chunk: ordinal positions and output indices by ballot scans, 16 byte lexem records
-enum {LexFusedThreads = 128, LexWriteThreads = 256};
+enum {LexFusedThreads = 128, LexWriteThreads = 128};
 
 enum {LexFusedSmem = (SP_FUSED_AR * 16 + SP_FUSED_MEMO * 16 + SP_FUSED_BUF * 4) * LexFusedThreads};
 
