@@ -61,6 +61,9 @@ struct MatcherTablesHost
 	std::vector<SpProgramTrigger> program_triggers;
 	std::vector<SpEventSlot> event_slots;
 	std::vector<uint32_t> stopwords;	// event id per stop word index (0-based)
+	std::vector<SpEvalSlot> eval_slots;	// window evaluator (matcher_eval.cuh): static follow events per event slot
+	std::vector<SpEvalFollow> eval_follows;
+	std::vector<uint32_t> prog_flags;
 	SpMatcherTables view;			// pointers are filled by the owner (host or device addresses)
 };
 
@@ -314,11 +317,98 @@ public:
 		T.view.nstopwords = (uint32_t)T.stopwords.size();
 		T.view.exclusive = m_exclusive ? 1 : 0; T.view.max_result_size = m_maxResultSize;
 		T.view.max_trigger_defs = maxdefs;
+		buildEvalTables( T);
 		m_flattened = true;
 		return T;
 	}
 
 private:
+	// Tables of the window evaluator (matcher_eval.cuh) and the decision whether it reproduces this rule set exactly.
+	// It does when every event that is not a term event and that some program waits for (as key or as trigger) can only
+	// come from programs that emit at their installation: all trigger definitions of type "any" on term events. Other
+	// nested expressions, "and" programs (src/ruleMatcherAutomaton.cpp:807-826), the option "exclusive" (the covered
+	// flags of src/patternMatcher.cpp:192-246 depend on the emission order) and programs with more than 32 trigger
+	// definitions are left to the state machine.
+	void buildEvalTables( MatcherTablesHost& T) const
+	{
+		const uint32_t nslots = (uint32_t)T.event_slots.size();
+		SpEvalSlot noslot; noslot.follow_begin = noslot.follow_count = 0;
+		T.eval_slots.assign( nslots, noslot);
+		T.prog_flags.assign( T.programs.size(), 0);
+		bool capable = !m_exclusive;
+		std::vector<char> anyEmitter( T.programs.size(), 0);
+		std::set<uint32_t> listened;
+		for (std::size_t pi=0; pi<T.programs.size(); ++pi)
+		{
+			const SpProgram& P = T.programs[ pi];
+			if (P.trig_count > 32) capable = false;
+			bool allAny = true, allTerm = true;
+			for (uint32_t d=0; d<P.trig_count; ++d)
+			{
+				const SpTriggerDef& def = T.trigger_defs[ P.trig_begin + d];
+				if (def.sigtype == SP_SIG_AND) capable = false;
+				if (def.sigtype != SP_SIG_ANY) allAny = false;
+				if ((def.event >> 29) != TermEvent) {allTerm = false; listened.insert( def.event); T.prog_flags[ pi] |= SP_PROGFLAG_LISTENS_FOLLOW;}
+			}
+			anyEmitter[ pi] = (allAny && allTerm && (P.initcount & 0xFFFFu) >= 1 && P.trig_count >= 1);
+		}
+		for (const SpEventSlot& slot: T.event_slots)
+		{
+			if (!slot.key || !slot.prog_count) continue;
+			const uint32_t ev = slot.key - 1;
+			if ((ev >> 29) != TermEvent) listened.insert( ev);
+			for (uint32_t k=0; k<slot.prog_count; ++k)
+			{
+				const SpProgramTrigger& pt = T.program_triggers[ slot.prog_begin + k];
+				if (!pt.past_event) continue;
+				// alternative key programs: the replay compares the log times of structure delimiters, which the
+				// evaluator does for term events
+				const SpProgram& P = T.programs[ pt.program];
+				for (uint32_t d=0; d<P.trig_count; ++d)
+				{
+					const SpTriggerDef& def = T.trigger_defs[ P.trig_begin + d];
+					if (def.sigtype == SP_SIG_DEL && (def.event >> 29) != TermEvent) capable = false;
+				}
+				if ((pt.past_event >> 29) != TermEvent) listened.insert( pt.past_event);
+			}
+		}
+		for (std::size_t pi=0; pi<T.programs.size(); ++pi)
+		{
+			if (T.programs[ pi].event && listened.count( T.programs[ pi].event) && !anyEmitter[ pi]) capable = false;
+		}
+		if (capable)
+		{
+			for (uint32_t h=0; h<nslots; ++h)
+			{
+				const SpEventSlot& slot = T.event_slots[ h];
+				if (!slot.key || ((slot.key - 1) >> 29) != TermEvent) continue;
+				T.eval_slots[ h].follow_begin = (uint32_t)T.eval_follows.size();
+				for (uint32_t k=0; k<slot.prog_count; ++k)
+				{
+					const SpProgramTrigger& pt = T.program_triggers[ slot.prog_begin + k];
+					const SpProgram& P = T.programs[ pt.program];
+					if (pt.past_event || !anyEmitter[ pt.program] || !P.event || !listened.count( P.event)) continue;
+					SpEvalFollow F; std::memset( &F, 0, sizeof(F));
+					F.event = P.event; F.qpt = slot.prog_begin + k; F.eslot = 0xFFFFFFFFu; F.format = P.formatHandle;
+					for (uint32_t d=0; d<P.trig_count; ++d)
+					{
+						const SpTriggerDef& def = T.trigger_defs[ P.trig_begin + d];
+						if (def.event == slot.key - 1) {F.sub = def.variable ? 1 : 0; break;}	// the first signal emits
+					}
+					for (uint32_t e = sp_event_slot_hash( F.event) & (nslots-1); T.event_slots[ e].key; e = (e + 1) & (nslots-1))
+					{
+						if (T.event_slots[ e].key == F.event + 1) {F.eslot = e; break;}
+					}
+					T.eval_follows.push_back( F);
+				}
+				T.eval_slots[ h].follow_count = (uint32_t)T.eval_follows.size() - T.eval_slots[ h].follow_begin;
+			}
+		}
+		T.view.eval_slots = T.eval_slots.data(); T.view.eval_follows = T.eval_follows.data(); T.view.prog_flags = T.prog_flags.data();
+		T.view.nfollows = (uint32_t)T.eval_follows.size();
+		T.view.eval_capable = capable ? 1 : 0;
+	}
+
 	struct Node
 	{
 		uint32_t event, program, variable;

@@ -55,6 +55,30 @@ typedef struct alignas(16) SpEventSlot
 	uint32_t stopword;		/* 1-based index into the per document stop word log, 0 = not a stop word */
 } SpEventSlot;
 
+/* ---- tables of the window evaluator (matcher_eval.cuh) ----
+ * Follow events that are known at table build time: a program whose trigger definitions all have the signal type
+ * "any" emits its event when it is installed (fireSignal, src/ruleMatcherAutomaton.cpp:794-806: the first signal on a
+ * fresh slot with count > 0 is a match), so a term event t is always followed by the events of the "any" programs keyed
+ * by t, in the order of the program list of t (installEventPrograms, :1137-1147). One record per such event. 32 bytes. */
+typedef struct alignas(16) SpEvalFollow
+{
+	uint32_t event;			/* the follow event E */
+	uint32_t qpt;			/* index into program_triggers: the entry of the emitting program Q in the list of t */
+	uint32_t eslot;			/* index of the event slot of E (programs keyed by E), 0xFFFFFFFF = none */
+	uint32_t format;		/* format handle of Q (EventData::formathandle of E) */
+	uint32_t sub;			/* 1: E refers to the item list of its rule (the first key definition of Q for t has a variable) */
+	uint32_t reserved[3];
+} SpEvalFollow;
+
+/* per event slot (parallel to event_slots): the static follow events of a term event */
+typedef struct alignas(8) SpEvalSlot
+{
+	uint32_t follow_begin;
+	uint32_t follow_count;
+} SpEvalSlot;
+
+#define SP_PROGFLAG_LISTENS_FOLLOW 1u	/* some trigger definition waits for an event that is not a term event */
+
 typedef struct SpMatcherTables
 {
 	const SpProgram* programs;
@@ -69,6 +93,12 @@ typedef struct SpMatcherTables
 	uint32_t exclusive;		/* option "exclusive" (src/patternMatcher.cpp:632) */
 	uint32_t max_result_size;	/* option "maxResultSize" (:628) */
 	uint32_t max_trigger_defs;	/* largest trig_count */
+	/* window evaluator */
+	const SpEvalSlot* eval_slots;	/* [event_mask+1] */
+	const SpEvalFollow* eval_follows;
+	const uint32_t* prog_flags;	/* [nprograms] SP_PROGFLAG_* */
+	uint32_t nfollows;
+	uint32_t eval_capable;		/* 1: the rule set is inside what the window evaluator reproduces exactly (matcher_program.hpp: evalCapable) */
 } SpMatcherTables;
 
 #ifdef __CUDACC__

@@ -87,19 +87,29 @@ def define_c3_patterns(m, seed, npatterns, nsymbols, lexem_share=0.1):
     """C3: 50 % sequence_imm of 2-4 terms (range = argc), 30 % within of 2-3 terms (range 3-10), 10 % *_struct with the
     sentence delimiter, 10 % any of 2-5 terms nested as first argument of a sequence; cardinality 0 except 5 % of
     within/any with cardinality 2; variables on all leaf terms; terms are symbols of vocabulary words (Zipf 0.8) or,
-    with probability lexem_share, plain lexem ids."""
+    with probability lexem_share, plain lexem ids. The terms of one pattern are distinct: a pattern that names a term
+    twice (within(the, the, x)) binds its variables in the order of the reference's trigger arrays, i.e. depending on
+    the history of the document; such rule sets are valid but run on the state machine, not on the window evaluator."""
     import numpy as np
     rng = np.random.default_rng(seed)
     plain = [NUMBER, DECIMAL, DATE, CAPWORD, ABBREV, AMOUNT]
 
+    used = set()
+
     def term(var):
-        if rng.random() < lexem_share:
-            m.push_term(int(plain[int(rng.integers(0, len(plain)))]))
-        else:
-            m.push_term(SYMBOL_BASE + int(_zipf_ranks(rng, 1, nsymbols, 0.8)[0]))
+        while True:
+            if rng.random() < lexem_share:
+                t = int(plain[int(rng.integers(0, len(plain)))])
+            else:
+                t = SYMBOL_BASE + int(_zipf_ranks(rng, 1, nsymbols, 0.8)[0])
+            if t not in used:
+                break
+        used.add(t)
+        m.push_term(t)
         m.attach_variable("v%d" % var)
 
     for r in range(npatterns):
+        used.clear()
         u = rng.random()
         if u < 0.5:
             n = int(rng.integers(2, 5))

@@ -7,8 +7,11 @@
 #include <cstring>
 #include "matcher_program.hpp"
 #include "matcher_device.cuh"
+#include "matcher_eval.cuh"
 #include <vector>
 #include <string>
+#include <cstdio>
+#include <cstdlib>
 
 namespace {
 struct MatcherSim
@@ -23,13 +26,87 @@ struct MatcherSim
 	std::vector<sp_matcher_stats> stats;
 	std::vector<uint32_t> status;
 	uint64_t retries;
+	int mode;			// 0 = state machine, 1 = window evaluator (documents it flags run on the state machine)
+	uint64_t eval_docs, eval_flagged;
 
-	MatcherSim() :retries(0)
+	MatcherSim() :retries(0),mode(0),eval_docs(0),eval_flagged(0)
 	{
 		cap.rules = 256; cap.triggers = 256; cap.items = 512; cap.datarefs = 256; cap.results = 256;
 		cap.follow = 64; cap.dispose = 256; cap.heap = 64;
 	}
 };
+}
+
+// One document through the window evaluator (matcher_eval.cuh), sites in the order of the CUDA kernels: token by token,
+// the token event first, then its static follow events, every program list in list order. Returns false if the
+// document has to run on the state machine.
+static bool evalDocument( const SpMatcherTables& T, const sp_lexem* tokens, const uint32_t* segs, uint64_t tb, uint64_t te,
+			  std::vector<sp_result>& results, std::vector<sp_item>& items, sp_matcher_stats& st)
+{
+	std::memset( &st, 0, sizeof(st));
+	for (uint64_t i=tb; i<te; ++i)
+	{
+		if (sp_eval_token_irregular( tokens[ i], segs ? segs[ i] : 0, i == tb, i == tb ? 0 : tokens[ i-1].ordpos)) return false;
+	}
+	const std::size_t item_base = items.size();
+	for (uint64_t i=tb; i<te; ++i)
+	{
+		const uint32_t slotidx = sp_find_event_index( T, tokens[ i].id);
+		if (slotidx == SP_EVAL_NOSLOT) continue;
+		SpEvalSite base;
+		sp_eval_site_token( T, tokens[ i], segs ? segs[ i] : 0, i, slotidx, base);
+		for (uint32_t c=0; c<=base.follow_count; ++c)
+		{
+			SpEvalSite site = base;
+			uint32_t listslot = slotidx;
+			if (c > 0)
+			{
+				const SpEvalFollow& F = T.eval_follows[ base.follow_begin + c - 1];
+				if (F.eslot == SP_EVAL_NOSLOT) continue;
+				sp_eval_site_follow( base, c - 1, F, site);
+				listslot = F.eslot;
+			}
+			const SpEventSlot& es = T.event_slots[ listslot];
+			for (uint32_t k=0; k<es.prog_count; ++k)
+			{
+				const SpProgramTrigger pt = T.program_triggers[ es.prog_begin + k];
+				SpEvalRule R;
+				SpEvalTake takes[ SP_EVAL_MAX_TAKES];
+				sp_eval_fold<true,0>( T, tokens, segs, tb, te, site, pt, false, R, takes);
+				if (R.flag)
+				{
+					if (getenv( "SP_EVAL_DEBUG"))
+					{
+						const SpProgram& P = T.programs[ pt.program];
+						fprintf( stderr, "flag: doc token %llu cpos %u program %u past %u range %u initsigval %u count %u defs:", (unsigned long long)(i-tb), site.cpos, pt.program, pt.past_event, P.range, P.initsigval, P.initcount);
+						for (uint32_t d=0; d<P.trig_count; ++d) {const SpTriggerDef& f = T.trigger_defs[ P.trig_begin+d]; fprintf( stderr, " (ev %u sig %u val %u key %u var %u)", f.event, f.sigtype, f.sigval, f.is_key, f.variable);}
+						fprintf( stderr, "\n");
+					}
+					return false;
+				}
+				// the counting instance must agree with the collecting one (the kernels run them in two passes)
+				SpEvalRule C;
+				sp_eval_fold<false,0>( T, tokens, segs, tb, te, site, pt, false, C, 0);
+				if (C.flag || C.nitems != R.nitems || C.ntakes != R.ntakes || C.has_result != R.has_result || C.signals != R.signals || C.open != R.open)
+				{
+					throw std::runtime_error( "count pass and write pass of the evaluator disagree");
+				}
+				st.nof_programs_installed += R.installed; st.nof_altkey_programs_installed += R.altkey;
+				st.nof_signals_fired += R.signals; st.nof_open_patterns += R.open;
+				if (!R.has_result) continue;
+				const uint32_t want = sp_eval_result_items( R);
+				const std::size_t ib = items.size();
+				items.resize( ib + want);
+				const uint32_t got = want ? sp_eval_write_items( T, tokens, segs, tb, te, takes, R.ntakes, items.data() + ib) : 0;
+				if (got != want) throw std::runtime_error( "evaluator item count differs from the items written");
+				sp_result rec;
+				sp_eval_result_record( T.programs[ pt.program], R, (uint32_t)(ib - item_base), want, rec);
+				results.push_back( rec);
+			}
+		}
+	}
+	st.nof_events = te - tb;
+	return true;
 }
 
 #define MSIM_TRY(...) MatcherSim* ms = (MatcherSim*)h; try {__VA_ARGS__; return 0;} \
@@ -57,6 +134,8 @@ int msim_set_caps( void* h, uint32_t rules, uint32_t triggers, uint32_t items, u
 	return 0;
 }
 
+int msim_set_mode( void* h, int mode) {((MatcherSim*)h)->mode = mode; return 0;}
+
 int msim_run_batch( void* h, const sp_lexem* tokens, const uint32_t* origsegs, const uint64_t* tok_offsets, uint32_t ndocs, int, int)
 {
 	MSIM_TRY({
@@ -71,6 +150,22 @@ int msim_run_batch( void* h, const sp_lexem* tokens, const uint32_t* origsegs, c
 		SpArena A; sp_arena_bind( L, mem.data(), A);
 		for (uint32_t d=0; d<ndocs; ++d)
 		{
+			if (ms->mode == 1 && T.eval_capable)
+			{
+				std::size_t rb = ms->results.size(), ib = ms->items.size();
+				sp_matcher_stats est;
+				++ms->eval_docs;
+				if (evalDocument( T, tokens, origsegs, tok_offsets[ d], tok_offsets[ d+1], ms->results, ms->items, est))
+				{
+					ms->stats.push_back( est);
+					ms->status.push_back( 0);
+					ms->result_offsets.push_back( ms->results.size());
+					ms->item_offsets.push_back( ms->items.size());
+					continue;
+				}
+				++ms->eval_flagged;
+				ms->results.resize( rb); ms->items.resize( ib);
+			}
 			uint64_t nevents = 0; uint32_t nres = 0, nitems = 0;
 			for (;;)
 			{
@@ -134,6 +229,10 @@ int64_t msim_info( void* h, const char* key)
 		if (k == "program_triggers") return H.view.nprogram_triggers;
 		if (k == "stopwords") return H.view.nstopwords;
 		if (k == "event_slots") return (int64_t)H.view.event_mask + 1;
+		if (k == "eval_capable") return H.view.eval_capable;
+		if (k == "eval_follows") return H.view.nfollows;
+		if (k == "eval_docs") return (int64_t)ms->eval_docs;
+		if (k == "eval_flagged") return (int64_t)ms->eval_flagged;
 	}
 	catch (...) {}
 	return -1;

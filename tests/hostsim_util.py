@@ -119,7 +119,7 @@ HS_MATCHER_LIB = os.path.join(HS_DIR, "_build", "libsp_hostsim_matcher.so")
 def build_hostsim_matcher(force=False):
     srcs = [os.path.join(HS_DIR, "matcher_hostsim.cpp")] + [
         os.path.join(ROOT, "struspattern_b200", "csrc", f)
-        for f in ("matcher_program.hpp", "matcher_device.cuh", "matcher_tables.h")]
+        for f in ("matcher_program.hpp", "matcher_device.cuh", "matcher_tables.h", "matcher_eval.cuh")]
     if not force and os.path.exists(HS_MATCHER_LIB) and all(os.path.getmtime(HS_MATCHER_LIB) >= os.path.getmtime(s) for s in srcs):
         return
     os.makedirs(os.path.dirname(HS_MATCHER_LIB), exist_ok=True)
@@ -146,9 +146,10 @@ class HostSimMatcher:
             cls._lib = L
         return cls._lib
 
-    def __init__(self, caps=None):
+    def __init__(self, caps=None, mode=0):
         self.L = self.lib()
         self.h = C.c_void_p(self.L.msim_create())
+        self.L.msim_set_mode(self.h, C.c_int(mode))
         if caps:
             self.L.msim_set_caps(self.h, *[C.c_uint32(c) for c in caps])
 
