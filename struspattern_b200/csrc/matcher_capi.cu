@@ -4,6 +4,7 @@
 #include "strus_pattern_b200.h"
 #include "matcher_program.hpp"
 #include "matcher_kernels.cuh"
+#include "matcher_eval_kernels.cuh"
 #include "device_util.cuh"
 #include <vector>
 #include <string>
@@ -48,6 +49,8 @@ struct sp_matcher
 		dev = H.view;
 		dev.programs = put( H.programs); dev.trigger_defs = put( H.trigger_defs);
 		dev.program_triggers = put( H.program_triggers); dev.event_slots = put( H.event_slots);
+		dev.eval_slots = put( H.eval_slots); dev.eval_follows = put( H.eval_follows); dev.prog_flags = put( H.prog_flags);
+		dev.eval_entries = put( H.eval_entries);
 		uploaded = true;
 	}
 };
@@ -104,6 +107,8 @@ int64_t sp_matcher_table_info( const sp_matcher* m, const char* key)
 		if (k == "table_bytes") return (int64_t)(H.programs.size() * sizeof(SpProgram) + H.trigger_defs.size() * sizeof(SpTriggerDef)
 							+ H.program_triggers.size() * sizeof(SpProgramTrigger) + H.event_slots.size() * sizeof(SpEventSlot));
 		if (k == "uploaded") return m->uploaded ? 1 : 0;
+		if (k == "eval_capable") return H.view.eval_capable;
+		if (k == "eval_follows") return H.view.nfollows;
 	}
 	catch (...) {}
 	return -1;

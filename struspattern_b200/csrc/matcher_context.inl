@@ -16,7 +16,12 @@ struct sp_matcher_ctx
 	int nsm;
 	// device buffers (grow only)
 	DeviceBuffer tokens, origsegs, tok_off, arenas, res_pool, item_pool, scalars, doc_res_begin, doc_res_count, doc_item_begin,
-		     doc_item_count, stats, status, list_a, list_b, res_off, item_off, results, items, scantmp;
+		     doc_item_count, stats, status, list_a, list_b, res_off, item_off, results, items, scantmp,
+		     tok_nres, tok_nitems, tok_res_off, tok_item_off, flags, flag_list, tok_slot, tok_work, tok_work_off, resbits, queue;
+	uint64_t queue_cap, eval_queued, eval_items;
+	int mode;			// 0 = automatic (window evaluator if the rule set allows it), 1 = state machine (emission order), 2 = evaluator required
+	uint64_t eval_docs, eval_flagged, eval_runs;
+	double eval_count_ms, eval_write_ms;
 	double res_per_token, items_per_token;	// output pool sizing, learned from the last run
 	// last batch
 	uint32_t ndocs;
@@ -30,7 +35,7 @@ struct sp_matcher_ctx
 	sp_matcher_ctx( sp_matcher* m_, cudaStream_t stream_)
 		:m(m_),stream(stream_),warps_per_sm(16),warps_fixed(false),cap_growths(0),arena_budget(0),nsm(0),res_per_token(0.5),items_per_token(1.0)
 		,ndocs(0),ntokens(0),nres(0),nitems(0),retries(0),pool_retries(0),launches(0),valid(false),pinned(0),ev_a(0),ev_b(0)
-		,kernel_ms(0.0),kernel_calls(0),profile(false)
+		,kernel_ms(0.0),kernel_calls(0),profile(false),mode(0),eval_docs(0),eval_flagged(0),eval_runs(0),eval_count_ms(0.0),eval_write_ms(0.0),queue_cap(0),eval_queued(0),eval_items(0)
 	{
 		cap.rules = 2048; cap.triggers = 2048; cap.items = 8192; cap.datarefs = 4096; cap.results = 4096;
 		cap.follow = 256; cap.dispose = 2048; cap.heap = 1024;
@@ -42,6 +47,7 @@ struct sp_matcher_ctx
 		}
 		if ((e = std::getenv( "SP_MATCHER_WARPS_PER_SM")) != 0 && std::atoi( e) >= 1) {warps_per_sm = (uint32_t)std::atoi( e); warps_fixed = true;}
 		if (std::getenv( "SP_MATCHER_PROFILE")) profile = true;
+		if ((e = std::getenv( "SP_MATCHER_MODE")) != 0) mode = !std::strcmp( e, "statemachine") ? 1 : !std::strcmp( e, "eval") ? 2 : 0;
 		trace = std::getenv( "SP_MATCHER_TRACE") != 0;
 		int dev = 0;
 		SP_CUDA( cudaGetDevice( &dev));
@@ -65,6 +71,101 @@ struct sp_matcher_ctx
 		SP_CUDA( cudaStreamSynchronize( stream));
 	}
 
+	// The per-document state machine (k_match_documents) over all documents (init_list == 0) or over the listed ones:
+	// fills the pools and the per document descriptors (doc_res_begin/count, doc_item_begin/count, stats, status).
+	void runStateMachine( MatchParams& P, uint32_t* init_list, uint32_t init_nlist)
+	{
+		uint64_t* d_scalars = scalars.as<uint64_t>( 8);
+		P.cursors = reinterpret_cast<unsigned long long*>( d_scalars);
+		uint32_t* d_words = reinterpret_cast<uint32_t*>( d_scalars + 2);	// [0] next_doc [1] list count [2..4] overflow kinds
+		P.next_doc = d_words;
+		const uint64_t ntok_run = init_list ? std::max<uint64_t>( 1, ntokens * init_nlist / std::max<uint32_t>( ndocs, 1)) : ntokens;
+		uint64_t res_cap = (uint64_t)(res_per_token * 1.25 * (double)ntok_run) + 4096;
+		uint64_t item_cap = (uint64_t)(items_per_token * 1.25 * (double)ntok_run) + 8192;
+		SpArenaCaps curcap = cap;
+		uint32_t* d_list = init_list; uint32_t nlist = init_nlist;
+		bool flip = false, fresh = true;
+		uint32_t retry_docs = 0;
+		for (int round=0;; ++round)
+		{
+			if (round > 40) throw std::runtime_error( "matcher arenas keep overflowing (rule set too large for the device memory)");
+			sp_arena_layout( curcap, P.T.nstopwords, P.layout);
+			uint32_t ntodo = d_list ? nlist : ndocs;
+			uint64_t maxwarps = arena_budget / P.layout.bytes;
+			if (maxwarps < 1) throw std::runtime_error( "matcher arena does not fit the device memory");
+			const bool wide = !warps_fixed && (uint64_t)ntodo > (uint64_t)nsm * 16 && maxwarps > (uint64_t)nsm * 16;
+			const uint32_t wps = wide ? 32 : warps_per_sm;
+			uint64_t nwarps = std::min<uint64_t>( std::min<uint64_t>( ntodo, (uint64_t)nsm * wps), maxwarps);
+			uint32_t nblocks = (uint32_t)((nwarps + MatchWarpsPerBlock - 1) / MatchWarpsPerBlock);
+			P.arena_base = arenas.as<uint8_t>( (std::size_t)nblocks * MatchWarpsPerBlock * P.layout.bytes);
+			// the stop word log is validated by a per-warp document stamp that restarts with every launch
+			SP_CUDA( cudaMemset2DAsync( P.arena_base + P.layout.stoplog, P.layout.bytes, 0, ((std::size_t)P.T.nstopwords + 1) * sizeof(SpStopLog),
+						    (std::size_t)nblocks * MatchWarpsPerBlock, stream));
+			P.res_pool = res_pool.as<sp_result>( res_cap); P.item_pool = item_pool.as<sp_item>( item_cap);
+			P.res_cap = res_cap; P.item_cap = item_cap;
+			P.doc_list = d_list; P.nlist = nlist;
+			if (fresh) SP_CUDA( cudaMemsetAsync( d_scalars, 0, 8 * sizeof(uint64_t), stream));
+			else SP_CUDA( cudaMemsetAsync( d_words, 0, 5 * sizeof(uint32_t), stream));
+			fresh = false;
+			uint32_t* d_newlist = (flip ? list_b : list_a).as<uint32_t>( ntodo);
+			if (profile || trace) SP_CUDA( cudaEventRecord( ev_a, stream));
+			if (wide || warps_per_sm > 16) k_match_documents<8><<<nblocks, MatchThreads, 0, stream>>>( P);
+			else k_match_documents<4><<<nblocks, MatchThreads, 0, stream>>>( P);
+			if (profile || trace) SP_CUDA( cudaEventRecord( ev_b, stream));
+			k_match_collect<<<(ndocs + 255) / 256, 256, 0, stream>>>( P.status, ndocs, d_newlist, d_words + 1, d_words + 2);
+			SP_CUDA( cudaGetLastError());
+			launches += 2;
+			readScalars( d_scalars, 8 * sizeof(uint64_t));
+			if (profile)
+			{
+				float ms = 0.0f;
+				if (cudaEventElapsedTime( &ms, ev_a, ev_b) == cudaSuccess) {kernel_ms += ms; kernel_calls += 1;}
+			}
+			if (trace)
+			{
+				float ms = 0.0f; cudaEventElapsedTime( &ms, ev_a, ev_b);
+				const uint32_t* w = reinterpret_cast<const uint32_t*>( pinned + 2);
+				fprintf( stderr, "[sp_matcher] round %d: docs %u, warps %llu, arena %llu KB (rules %u triggers %u items %u results %u follow %u dispose %u heap %u), kernel %.1f ms, overflowed docs %u (arena %u output %u depth %u), results %llu items %llu\n",
+					round, ntodo, (unsigned long long)nwarps, (unsigned long long)(P.layout.bytes >> 10), curcap.rules, curcap.triggers, curcap.items, curcap.results,
+					curcap.follow, curcap.dispose, curcap.heap, ms, w[1], w[2], w[3], w[4], (unsigned long long)pinned[0], (unsigned long long)pinned[1]);
+			}
+			uint64_t want_res = pinned[0], want_items = pinned[1];
+			const uint32_t* words = reinterpret_cast<const uint32_t*>( pinned + 2);
+			uint32_t listcount = words[1];
+			bool ovfArena = words[2] != 0, ovfOutput = words[3] != 0, ovfDepth = words[4] != 0;
+			if (ovfDepth) throw std::runtime_error( "nesting of result items too deep");
+			if (ovfOutput)
+			{
+				// output pools too small: size them from what this round asked for and run everything again
+				++pool_retries;
+				res_cap = std::max<uint64_t>( res_cap * 2, want_res + want_res / 4 + 4096);
+				item_cap = std::max<uint64_t>( item_cap * 2, want_items + want_items / 4 + 8192);
+				d_list = init_list; nlist = init_nlist; fresh = true;
+				continue;
+			}
+			if (!ovfArena) break;
+			++retries;
+			// only the pools that overflowed grow (a document stops at its first overflow, so another pool may follow in
+			// the next round): the arena stays small enough for a full grid of warps (growing all pools together ended
+			// at 400 MB per warp and 113 warps in flight on the C3 rule set)
+			{
+				const uint32_t kinds = words[2];
+				if (kinds & (1u << (SP_MST_OVF_RULES - SP_MST_OVERFLOW))) curcap.rules *= 4;
+				if (kinds & (1u << (SP_MST_OVF_TRIGGERS - SP_MST_OVERFLOW))) curcap.triggers *= 4;
+				if (kinds & (1u << (SP_MST_OVF_ITEMS - SP_MST_OVERFLOW))) curcap.items *= 4;
+				if (kinds & (1u << (SP_MST_OVF_DATAREFS - SP_MST_OVERFLOW))) curcap.datarefs *= 4;
+				if (kinds & (1u << (SP_MST_OVF_RESULTS - SP_MST_OVERFLOW))) curcap.results *= 4;
+				if (kinds & (1u << (SP_MST_OVF_FOLLOW - SP_MST_OVERFLOW))) curcap.follow *= 4;
+				if (kinds & (1u << (SP_MST_OVF_DISPOSE - SP_MST_OVERFLOW))) curcap.dispose *= 4;
+				if (kinds & (1u << (SP_MST_OVF_HEAP - SP_MST_OVERFLOW))) curcap.heap *= 4;
+			}
+			d_list = d_newlist; nlist = listcount; flip = !flip;
+			retry_docs = std::max( retry_docs, listcount);
+		}
+		// documents of the next batch will look like these: start with the arenas that were needed (two growth steps at most)
+		if (std::memcmp( &curcap, &cap, sizeof(cap)) != 0 && cap_growths < 4 && (uint64_t)retry_docs * 50 >= (init_list ? init_nlist : ndocs)) {cap = curcap; ++cap_growths;}
+	}
+
 	// tokens / origsegs / tok_offsets already on the device; ntokens known
 	void runDevice( const sp_lexem* d_tokens, const uint32_t* d_origsegs, const uint64_t* d_tok_off, uint32_t ndocs_, uint64_t ntokens_)
 	{
@@ -82,118 +183,112 @@ struct sp_matcher_ctx
 		P.doc_res_begin = doc_res_begin.as<uint64_t>( ndocs); P.doc_res_count = doc_res_count.as<uint32_t>( ndocs);
 		P.doc_item_begin = doc_item_begin.as<uint64_t>( ndocs); P.doc_item_count = doc_item_count.as<uint32_t>( ndocs);
 		P.stats = stats.as<sp_matcher_stats>( ndocs); P.status = status.as<uint32_t>( ndocs);
-		uint64_t* d_scalars = scalars.as<uint64_t>( 8);
-		P.cursors = reinterpret_cast<unsigned long long*>( d_scalars);
-		uint32_t* d_words = reinterpret_cast<uint32_t*>( d_scalars + 2);	// [0] next_doc [1] list count [2..4] overflow kinds
-		P.next_doc = d_words;
 		uint64_t* d_res_off = res_off.as<uint64_t>( (std::size_t)ndocs + 1);
 		uint64_t* d_item_off = item_off.as<uint64_t>( (std::size_t)ndocs + 1);
+		if (mode == 2 && !P.T.eval_capable) throw std::runtime_error( "the rule set is outside of what the window evaluator reproduces (mode eval)");
+		const bool useEval = mode != 1 && P.T.eval_capable && ndocs && ntokens;
 
-		if (ndocs)
+		if (!useEval)
 		{
-			uint64_t res_cap = (uint64_t)(res_per_token * 1.25 * (double)ntokens) + 4096;
-			uint64_t item_cap = (uint64_t)(items_per_token * 1.25 * (double)ntokens) + 8192;
-			SpArenaCaps curcap = cap;
-			uint32_t* d_list = 0; uint32_t nlist = 0;
-			bool flip = false;
-			uint32_t retry_docs = 0;
-			for (int round=0;; ++round)
+			if (ndocs) runStateMachine( P, 0, 0);
+			// document order: offsets by prefix sum, then one warp per document copies its records
+			exclusiveScan( P.doc_res_count, ndocs, d_res_off, scantmp, stream);
+			exclusiveScan( P.doc_item_count, ndocs, d_item_off, scantmp, stream);
+			launches += 6;
+			readScalars( d_res_off + ndocs, sizeof(uint64_t)); nres = pinned[0];
+			readScalars( d_item_off + ndocs, sizeof(uint64_t)); nitems = pinned[0];
+			sp_result* d_results = results.as<sp_result>( nres);
+			sp_item* d_items = items.as<sp_item>( nitems);
+			if (ndocs)
 			{
-				if (round > 40) throw std::runtime_error( "matcher arenas keep overflowing (rule set too large for the device memory)");
-				sp_arena_layout( curcap, P.T.nstopwords, P.layout);
-				uint32_t ntodo = d_list ? nlist : ndocs;
-				uint64_t maxwarps = arena_budget / P.layout.bytes;
-				if (maxwarps < 1) throw std::runtime_error( "matcher arena does not fit the device memory");
-				const bool wide = !warps_fixed && (uint64_t)ntodo > (uint64_t)nsm * 16 && maxwarps > (uint64_t)nsm * 16;
-				const uint32_t wps = wide ? 32 : warps_per_sm;
-				uint64_t nwarps = std::min<uint64_t>( std::min<uint64_t>( ntodo, (uint64_t)nsm * wps), maxwarps);
-				uint32_t nblocks = (uint32_t)((nwarps + MatchWarpsPerBlock - 1) / MatchWarpsPerBlock);
-				P.arena_base = arenas.as<uint8_t>( (std::size_t)nblocks * MatchWarpsPerBlock * P.layout.bytes);
-				// the stop word log is validated by a per-warp document stamp that restarts with every launch
-				SP_CUDA( cudaMemset2DAsync( P.arena_base + P.layout.stoplog, P.layout.bytes, 0, ((std::size_t)P.T.nstopwords + 1) * sizeof(SpStopLog),
-							    (std::size_t)nblocks * MatchWarpsPerBlock, stream));
-				P.res_pool = res_pool.as<sp_result>( res_cap); P.item_pool = item_pool.as<sp_item>( item_cap);
-				P.res_cap = res_cap; P.item_cap = item_cap;
-				P.doc_list = d_list; P.nlist = nlist;
-				if (!d_list) SP_CUDA( cudaMemsetAsync( d_scalars, 0, 8 * sizeof(uint64_t), stream));
-				else SP_CUDA( cudaMemsetAsync( d_words, 0, 5 * sizeof(uint32_t), stream));
-				uint32_t* d_newlist = (flip ? list_b : list_a).as<uint32_t>( ntodo);
-				if (profile || trace) SP_CUDA( cudaEventRecord( ev_a, stream));
-				if (wide || warps_per_sm > 16) k_match_documents<8><<<nblocks, MatchThreads, 0, stream>>>( P);
-				else k_match_documents<4><<<nblocks, MatchThreads, 0, stream>>>( P);
-				if (profile || trace) SP_CUDA( cudaEventRecord( ev_b, stream));
-				k_match_collect<<<(ndocs + 255) / 256, 256, 0, stream>>>( P.status, ndocs, d_newlist, d_words + 1, d_words + 2);
+				k_match_compact<<<(ndocs + 7) / 8, 256, 0, stream>>>( P, d_res_off, d_item_off, d_results, d_items);
 				SP_CUDA( cudaGetLastError());
-				launches += 2;
-				readScalars( d_scalars, 8 * sizeof(uint64_t));
-				if (profile)
-				{
-					float ms = 0.0f;
-					if (cudaEventElapsedTime( &ms, ev_a, ev_b) == cudaSuccess) {kernel_ms += ms; kernel_calls += 1;}
-				}
-				if (trace)
-				{
-					float ms = 0.0f; cudaEventElapsedTime( &ms, ev_a, ev_b);
-					const uint32_t* w = reinterpret_cast<const uint32_t*>( pinned + 2);
-					fprintf( stderr, "[sp_matcher] round %d: docs %u, warps %llu, arena %llu KB (rules %u triggers %u items %u results %u follow %u dispose %u heap %u), kernel %.1f ms, overflowed docs %u (arena %u output %u depth %u), results %llu items %llu\n",
-						round, ntodo, (unsigned long long)nwarps, (unsigned long long)(P.layout.bytes >> 10), curcap.rules, curcap.triggers, curcap.items, curcap.results,
-						curcap.follow, curcap.dispose, curcap.heap, ms, w[1], w[2], w[3], w[4], (unsigned long long)pinned[0], (unsigned long long)pinned[1]);
-				}
-				uint64_t want_res = pinned[0], want_items = pinned[1];
-				const uint32_t* words = reinterpret_cast<const uint32_t*>( pinned + 2);
-				uint32_t listcount = words[1];
-				bool ovfArena = words[2] != 0, ovfOutput = words[3] != 0, ovfDepth = words[4] != 0;
-				if (ovfDepth) throw std::runtime_error( "nesting of result items too deep");
-				if (ovfOutput)
-				{
-					// output pools too small: size them from what this round asked for and run everything again
-					++pool_retries;
-					res_cap = std::max<uint64_t>( res_cap * 2, want_res + want_res / 4 + 4096);
-					item_cap = std::max<uint64_t>( item_cap * 2, want_items + want_items / 4 + 8192);
-					d_list = 0; nlist = 0;
-					continue;
-				}
-				nres = want_res; nitems = want_items;
-				if (!ovfArena) break;
-				++retries;
-				// only the pools that overflowed grow (a document stops at its first overflow, so another pool may follow in
-				// the next round): the arena stays small enough for a full grid of warps (growing all pools together ended
-				// at 400 MB per warp and 113 warps in flight on the C3 rule set)
-				{
-					const uint32_t kinds = words[2];
-					if (kinds & (1u << (SP_MST_OVF_RULES - SP_MST_OVERFLOW))) curcap.rules *= 4;
-					if (kinds & (1u << (SP_MST_OVF_TRIGGERS - SP_MST_OVERFLOW))) curcap.triggers *= 4;
-					if (kinds & (1u << (SP_MST_OVF_ITEMS - SP_MST_OVERFLOW))) curcap.items *= 4;
-					if (kinds & (1u << (SP_MST_OVF_DATAREFS - SP_MST_OVERFLOW))) curcap.datarefs *= 4;
-					if (kinds & (1u << (SP_MST_OVF_RESULTS - SP_MST_OVERFLOW))) curcap.results *= 4;
-					if (kinds & (1u << (SP_MST_OVF_FOLLOW - SP_MST_OVERFLOW))) curcap.follow *= 4;
-					if (kinds & (1u << (SP_MST_OVF_DISPOSE - SP_MST_OVERFLOW))) curcap.dispose *= 4;
-					if (kinds & (1u << (SP_MST_OVF_HEAP - SP_MST_OVERFLOW))) curcap.heap *= 4;
-				}
-				d_list = d_newlist; nlist = listcount; flip = !flip;
-				retry_docs = std::max( retry_docs, listcount);
-			}
-			// documents of the next batch will look like these: start with the arenas that were needed (two growth steps at most)
-			if (std::memcmp( &curcap, &cap, sizeof(cap)) != 0 && cap_growths < 4 && (uint64_t)retry_docs * 50 >= ndocs) {cap = curcap; ++cap_growths;}
-			if (ntokens)
-			{
-				res_per_token = std::max( 0.01, (double)nres / (double)ntokens);
-				items_per_token = std::max( 0.01, (double)nitems / (double)ntokens);
+				launches += 1;
 			}
 		}
-		// document order: offsets by prefix sum, then one warp per document copies its records
-		exclusiveScan( P.doc_res_count, ndocs, d_res_off, scantmp, stream);
-		exclusiveScan( P.doc_item_count, ndocs, d_item_off, scantmp, stream);
-		launches += 6;
-		readScalars( d_res_off + ndocs, sizeof(uint64_t)); nres = pinned[0];
-		readScalars( d_item_off + ndocs, sizeof(uint64_t)); nitems = pinned[0];
-		sp_result* d_results = results.as<sp_result>( nres);
-		sp_item* d_items = items.as<sp_item>( nitems);
-		if (ndocs)
+		else
 		{
-			k_match_compact<<<(ndocs + 7) / 8, 256, 0, stream>>>( P, d_res_off, d_item_off, d_results, d_items);
+			// window evaluator: work items per token, count pass, prefix sums, write pass; flagged documents go through
+			// the state machine
+			EvalParams E; std::memset( &E, 0, sizeof(E));
+			E.T = P.T; E.tokens = d_tokens; E.origsegs = d_origsegs; E.tok_off = d_tok_off; E.ndocs = ndocs; E.ntokens = ntokens;
+			E.tok_slot = tok_slot.as<uint32_t>( ntokens); E.tok_work = tok_work.as<uint32_t>( ntokens);
+			uint64_t* d_tok_work_off = tok_work_off.as<uint64_t>( ntokens + 1);
+			E.tok_work_off = d_tok_work_off;
+			E.tok_nres = tok_nres.as<uint32_t>( ntokens); E.tok_nitems = tok_nitems.as<uint32_t>( ntokens);
+			uint64_t* d_tok_res_off = tok_res_off.as<uint64_t>( ntokens + 1);
+			uint64_t* d_tok_item_off = tok_item_off.as<uint64_t>( ntokens + 1);
+			E.tok_res_off = d_tok_res_off; E.tok_item_off = d_tok_item_off;
+			E.stats = P.stats; E.flags = flags.as<uint32_t>( ndocs);
+			uint32_t* d_flag_list = flag_list.as<uint32_t>( ndocs);
+			uint64_t* d_escalars = scalars.as<uint64_t>( 16) + 8;	// [0] results [1] items of evaluator documents [2] flagged documents [3] queued items
+			E.queue_count = reinterpret_cast<unsigned long long*>( d_escalars + 3);
+			SP_CUDA( cudaMemsetAsync( E.flags, 0, (std::size_t)ndocs * sizeof(uint32_t), stream));
+			const uint32_t nblocks = (uint32_t)(((ntokens + EvalRun - 1) / EvalRun + EvalWarpsPerBlock - 1) / EvalWarpsPerBlock);
+			if (profile) SP_CUDA( cudaEventRecord( ev_a, stream));
+			k_eval_prepare<<<(unsigned int)((ntokens + 255) / 256), 256, 0, stream>>>( E);
+			exclusiveScan( E.tok_work, ntokens, d_tok_work_off, scantmp, stream);
 			SP_CUDA( cudaGetLastError());
-			launches += 1;
+			launches += 4;
+			readScalars( d_tok_work_off + ntokens, sizeof(uint64_t));
+			const uint64_t nwork = pinned[0];
+			E.resbits = resbits.as<uint32_t>( nwork / 32 + 2);
+			for (int attempt=0;; ++attempt)
+			{
+				if (queue_cap < 65536) queue_cap = 65536;
+				E.queue = reinterpret_cast<unsigned long long*>( queue.as<uint64_t>( queue_cap)); E.queue_cap = queue_cap;
+				SP_CUDA( cudaMemsetAsync( P.stats, 0, (std::size_t)ndocs * sizeof(sp_matcher_stats), stream));
+				SP_CUDA( cudaMemsetAsync( d_escalars, 0, 4 * sizeof(uint64_t), stream));
+				SP_CUDA( cudaMemsetAsync( E.resbits, 0, (nwork / 32 + 2) * sizeof(uint32_t), stream));
+				k_eval_count<<<nblocks, EvalThreads, 0, stream>>>( E);
+				k_eval_count_full<<<(unsigned int)nsm * 8, 128, 0, stream>>>( E);
+				if (profile) SP_CUDA( cudaEventRecord( ev_b, stream));
+				exclusiveScan( E.tok_nres, ntokens, d_tok_res_off, scantmp, stream);
+				exclusiveScan( E.tok_nitems, ntokens, d_tok_item_off, scantmp, stream);
+				k_eval_docs<<<(ndocs + 255) / 256, 256, 0, stream>>>( E, P.doc_res_count, P.doc_item_count, P.status, d_flag_list,
+										     reinterpret_cast<uint32_t*>( d_escalars + 2), reinterpret_cast<unsigned long long*>( d_escalars));
+				SP_CUDA( cudaGetLastError());
+				launches += 9;
+				readScalars( d_escalars, 4 * sizeof(uint64_t));
+				if (pinned[3] <= queue_cap) break;
+				if (attempt) throw std::runtime_error( "work queue of the evaluator keeps overflowing");
+				queue_cap = pinned[3] + pinned[3] / 4;		// the flags of this attempt are kept: they can only be set again
+			}
+			eval_queued += pinned[3];
+			if (profile)
+			{
+				float ms = 0.0f;
+				if (cudaEventElapsedTime( &ms, ev_a, ev_b) == cudaSuccess) {eval_count_ms += ms;}
+			}
+			const uint32_t nflagged = (uint32_t)(pinned[2] & 0xFFFFFFFFu);
+			++eval_runs; eval_docs += ndocs; eval_flagged += nflagged; eval_items += nwork;
+			if (trace) fprintf( stderr, "[sp_matcher] evaluator: docs %u, tokens %llu, rules %llu (queued for the full fold %llu), results %llu items %llu, flagged docs %u\n", ndocs,
+					     (unsigned long long)ntokens, (unsigned long long)nwork, (unsigned long long)pinned[3], (unsigned long long)pinned[0], (unsigned long long)pinned[1], nflagged);
+			if (nflagged) runStateMachine( P, d_flag_list, nflagged);
+			exclusiveScan( P.doc_res_count, ndocs, d_res_off, scantmp, stream);
+			exclusiveScan( P.doc_item_count, ndocs, d_item_off, scantmp, stream);
+			launches += 6;
+			readScalars( d_res_off + ndocs, sizeof(uint64_t)); nres = pinned[0];
+			readScalars( d_item_off + ndocs, sizeof(uint64_t)); nitems = pinned[0];
+			E.doc_res_off = d_res_off; E.doc_item_off = d_item_off;
+			E.results = results.as<sp_result>( nres); E.items = items.as<sp_item>( nitems);
+			if (profile) SP_CUDA( cudaEventRecord( ev_a, stream));
+			k_eval_write<<<nblocks, EvalThreads, 0, stream>>>( E);
+			if (profile) SP_CUDA( cudaEventRecord( ev_b, stream));
+			if (nflagged) k_eval_place<<<(nflagged + 7) / 8, 256, 0, stream>>>( d_flag_list, nflagged, P, d_res_off, d_item_off, E.results, E.items);
+			SP_CUDA( cudaGetLastError());
+			launches += nflagged ? 2 : 1;
+			if (profile)
+			{
+				SP_CUDA( cudaStreamSynchronize( stream));
+				float ms = 0.0f;
+				if (cudaEventElapsedTime( &ms, ev_a, ev_b) == cudaSuccess) {eval_write_ms += ms;}
+			}
+		}
+		if (ntokens)
+		{
+			res_per_token = std::max( 0.01, (double)nres / (double)ntokens);
+			items_per_token = std::max( 0.01, (double)nitems / (double)ntokens);
 		}
 		valid = true;
 	}
@@ -290,7 +385,19 @@ int64_t sp_matcher_ctx_counter( sp_matcher_ctx* ctx, const char* key)
 	if (k == "launches:reset") {ctx->launches = 0; return 0;}
 	if (k == "profile:on") {ctx->profile = true; return 1;}
 	if (k == "profile:off") {ctx->profile = false; return 0;}
-	if (k == "profile:reset") {ctx->kernel_ms = 0.0; ctx->kernel_calls = 0; return 0;}
+	if (k == "profile:reset") {ctx->kernel_ms = 0.0; ctx->kernel_calls = 0; ctx->eval_count_ms = ctx->eval_write_ms = 0.0; return 0;}
+	if (k == "time_us:k_eval_count") return (int64_t)(ctx->eval_count_ms * 1000.0);
+	if (k == "time_us:k_eval_write") return (int64_t)(ctx->eval_write_ms * 1000.0);
+	if (k == "eval_docs") return (int64_t)ctx->eval_docs;
+	if (k == "eval_flagged") return (int64_t)ctx->eval_flagged;
+	if (k == "eval_runs") return (int64_t)ctx->eval_runs;
+	if (k == "eval_queued") return (int64_t)ctx->eval_queued;
+	if (k == "eval_rules") return (int64_t)ctx->eval_items;
+	if (k == "eval_capable") return (int64_t)ctx->m->dev.eval_capable;
+	if (k == "mode") return ctx->mode;
+	if (k == "mode=auto") return ctx->mode = 0;
+	if (k == "mode=statemachine") return ctx->mode = 1;
+	if (k == "mode=eval") return ctx->mode = 2;
 	if (k == "time_us:k_match_documents") return (int64_t)(ctx->kernel_ms * 1000.0);
 	if (k == "calls:k_match_documents") return (int64_t)ctx->kernel_calls;
 	if (k == "warps_per_sm") return (int64_t)ctx->warps_per_sm;

@@ -488,6 +488,121 @@ SP_MHD void sp_eval_fold( const SpMatcherTables& T, const sp_lexem* toks, const 
 	}
 }
 
+/* A rule instance followed through its window from its compiled list entry alone (matcher_tables.h: SpEvalEntry): no
+ * loads of the program or its trigger definitions, a handful of registers of state. Gives the counters and whether the
+ * rule has a result and how many items it delivers; the result record and the items themselves are produced by the
+ * full fold (write pass). */
+typedef struct SpEvalLite
+{
+	uint32_t value, count, endpos;	/* slot */
+	uint32_t flags;			/* SP_LITE_* */
+	uint32_t nitems, signals, alive_tokens;
+} SpEvalLite;
+#define SP_LITE_ALIVE     1u
+#define SP_LITE_DONE      2u
+#define SP_LITE_DATAREF   4u
+#define SP_LITE_RESULT    8u
+#define SP_LITE_DREFEMIT 16u
+#define SP_LITE_FULL     32u	/* an event hit two live triggers: the full fold decides (and may flag the document) */
+
+SP_MHD void sp_eval_lite_init( const SpEvalEntry& en, uint32_t site_ordpos, SpEvalLite& L)
+{
+	L.value = en.value0; L.count = SP_EVAL_M2_COUNT( en.meta2);
+	L.endpos = (en.meta2 & SP_EVAL_M2_END0) ? site_ordpos + 1 : 0;
+	L.flags = (en.meta & SP_EVAL_META_DEAD) ? 0u : SP_LITE_ALIVE;
+	if (en.meta2 & SP_EVAL_M2_DONE0) L.flags |= SP_LITE_DONE;
+	if (en.meta2 & SP_EVAL_M2_DATAREF0) L.flags |= SP_LITE_DATAREF;
+	if (en.meta2 & SP_EVAL_M2_RESULT0) L.flags |= SP_LITE_RESULT;
+	if (en.meta2 & SP_EVAL_M2_DREFEMIT0) L.flags |= SP_LITE_DREFEMIT;
+	L.nitems = SP_EVAL_M2_NITEMS( en.meta2); L.signals = SP_EVAL_META_NKEY( en.meta); L.alive_tokens = 0;
+}
+
+/* fireSignal of live trigger j (:772-979) for a token at `pos` */
+SP_MHD void sp_eval_lite_fire( const SpEvalEntry& en, uint32_t j, uint32_t pos, SpEvalLite& L)
+{
+	const uint32_t code = (en.codes >> (8 * j)) & 0xFFu, type = code >> 5, sig = code & 31u;
+	bool take = false, match = false, finished = false;
+	L.signals += 1;
+	if (type == SP_SIG_ANY)
+	{
+		take = true;
+		if (L.count > 0)
+		{
+			match = true; L.count -= 1; finished = (L.count == 0);
+			if (L.endpos < pos + 1) L.endpos = pos + 1;
+		}
+	}
+	else if (type == SP_SIG_DEL)
+	{
+		L.count = 0; L.value = 0; L.flags &= ~SP_LITE_ALIVE;
+		return;
+	}
+	else
+	{
+		bool accept;
+		if (type == SP_SIG_WITHIN) accept = ((1u << sig) & L.value) != 0 && L.endpos <= pos;
+		else if (type == SP_SIG_SEQUENCE) accept = sig + 1 == L.value && L.endpos <= pos;
+		else accept = sig + 1 == L.value && L.endpos == pos;
+		if (accept)
+		{
+			L.endpos = pos + 1;
+			if (type == SP_SIG_WITHIN) L.value &= ~(1u << sig); else L.value = sig;
+			if (L.count > 0) {L.count -= 1; match = (L.count == 0);} else match = true;
+			finished = (L.value == 0);
+			take = true;
+		}
+	}
+	if (take && ((SP_EVAL_M2_VARMASK( en.meta2) >> j) & 1u)) {L.nitems += 1; L.flags |= SP_LITE_DATAREF;}
+	if (match)
+	{
+		if (!(L.flags & SP_LITE_DONE))
+		{
+			if (en.meta2 & SP_EVAL_M2_HASRES) L.flags |= SP_LITE_RESULT | ((L.flags & SP_LITE_DATAREF) ? SP_LITE_DREFEMIT : 0u);
+			L.flags |= SP_LITE_DONE;
+		}
+		if (finished) L.flags &= ~SP_LITE_ALIVE;
+	}
+}
+
+/* one window token for the rule: expiry, live trigger count sample (:992), signals */
+SP_MHD void sp_eval_lite_step( const SpEvalEntry& en, uint32_t expiry, uint32_t id, uint32_t pos, SpEvalLite& L)
+{
+	if (!(L.flags & SP_LITE_ALIVE)) return;
+	if (pos > expiry) {L.flags &= ~SP_LITE_ALIVE; return;}
+	L.alive_tokens += 1;
+	const uint32_t m = (id == en.ev[0] ? 1u : 0u) | (id == en.ev[1] ? 2u : 0u) | (id == en.ev[2] ? 4u : 0u) | (id == en.ev[3] ? 8u : 0u);
+	if (!m) return;
+	if (m & (m - 1)) {L.flags = (L.flags | SP_LITE_FULL) & ~SP_LITE_ALIVE; return;}
+	sp_eval_lite_fire( en, (uint32_t)sp_ctz( m), pos, L);
+}
+
+SP_MHD void sp_eval_lite_result( const SpEvalEntry& en, const SpEvalLite& L, SpEvalRule& R)
+{
+	sp_eval_rule_init( R);
+	R.installed = 1; R.signals = L.signals;
+	R.open = (uint64_t)L.alive_tokens * SP_EVAL_META_NTRIG( en.meta);
+	R.has_result = (L.flags & SP_LITE_RESULT) ? 1 : 0;
+	R.dataref_at_emit = (L.flags & SP_LITE_DREFEMIT) ? 1 : 0;
+	R.nitems = L.nitems;
+}
+
+/* per entry form of what k_eval_pass does for 32 entries at a time (tests/hostsim). Returns false if the rule needs the full fold. */
+SP_MHD bool sp_eval_entry_run( const SpEvalEntry& en, const sp_lexem* toks, uint64_t te, const SpEvalSite& site, SpEvalRule& R)
+{
+	if (en.meta & SP_EVAL_META_GENERIC) return false;
+	SpEvalLite L;
+	sp_eval_lite_init( en, site.data.start_ordpos, L);
+	const uint32_t expiry = site.data.start_ordpos + SP_EVAL_META_RANGE( en.meta);
+	for (uint64_t k=site.tok+1; k<te && (L.flags & SP_LITE_ALIVE); ++k)
+	{
+		sp_eval_lite_step( en, expiry, SP_MLDG( &toks[ k].id), SP_MLDG( &toks[ k].ordpos), L);
+	}
+	if (L.flags & SP_LITE_FULL) return false;
+	if ((L.flags & SP_LITE_RESULT) && (en.meta & SP_EVAL_META_ITEMSFULL)) return false;
+	sp_eval_lite_result( en, L, R);
+	return true;
+}
+
 SP_MHD void sp_eval_item_record( const sp_lexem& tok, uint32_t origseg, uint32_t variable, uint32_t format, sp_item& o)
 {
 	o.variable = variable; o.format = format;

@@ -1,0 +1,538 @@
+// CUDA kernels of the window evaluator (matcher_eval.cuh) for sm_100a.
+//
+// A "work item" is one rule instance: (key token, site, entry of the site's program list). The items of a batch are
+// numbered in document order (token, then the token event before its follow events, then list order); that order
+// is also the order of the results inside a document.
+//
+//   k_eval_prepare      per token: event slot and number of work items; irregular tokens flag their document.
+//   (prefix sum: first work item of every token)
+//   k_eval_count        one warp per run of 256 tokens. The tokens of the run (+ 64 behind it) are staged in shared
+//                       memory as (id, ordinal position). Every lane owns a contiguous block of the run's work items and
+//                       follows one rule at a time through its window from the compiled list entry (sp_eval_lite_step:
+//                       32 bytes per rule, no program / trigger definition loads); a lane whose rule has ended takes its
+//                       next item at once, so the lanes stay busy whatever the lengths of lists and windows are. Output:
+//                       results / items per token, one bit per work item that has a result, the statistics counters per
+//                       document; the few items the entry cannot decide are queued.
+//   k_eval_count_full   the queued items, one per thread, by the full fold (sp_eval_fold).
+//   (prefix sums over the per token counts, k_eval_docs, prefix sums over the per document counts)
+//   k_eval_write        one warp per run: walks the result bits of the run, 32 results at a time: full fold with the
+//                       taken events recorded, result record and items written at their final place.
+//   k_eval_docs         per document: counts, status, list of flagged documents (they run on the state machine of
+//                       matcher_kernels.cuh and are copied into place by k_eval_place).
+// No arena and no inter-thread dependency; atomics only for the per document counters and the result bits.
+#ifndef SP_MATCHER_EVAL_KERNELS_CUH_INCLUDED
+#define SP_MATCHER_EVAL_KERNELS_CUH_INCLUDED
+#include "matcher_eval.cuh"
+#include "matcher_kernels.cuh"
+
+namespace sp {
+
+enum {EvalWarpsPerBlock = 4, EvalThreads = EvalWarpsPerBlock * 32, EvalRun = 256, EvalLook = 64, EvalPerLane = EvalRun / 32};
+
+#define SP_EVALQ_STATS_DONE (1ull << 63)	/* queued item whose counters are already added: only result, items and bit are missing */
+
+struct EvalParams
+{
+	SpMatcherTables T;
+	const sp_lexem* tokens;
+	const uint32_t* origsegs;		// may be 0
+	const uint64_t* tok_off;		// [ndocs+1]
+	uint32_t ndocs;
+	uint64_t ntokens;
+	uint32_t* tok_slot; uint32_t* tok_work;				// [ntokens] k_eval_prepare
+	const uint64_t* tok_work_off;					// [ntokens+1] first work item of a token
+	uint32_t* tok_nres; uint32_t* tok_nitems;			// [ntokens] count pass output
+	const uint64_t* tok_res_off; const uint64_t* tok_item_off;	// [ntokens+1] prefix sums of the above
+	const uint64_t* doc_res_off; const uint64_t* doc_item_off;	// [ndocs+1] final places of the documents
+	uint32_t* resbits;			// one bit per work item: the rule has a result
+	unsigned long long* queue; uint64_t queue_cap; unsigned long long* queue_count;
+	sp_result* results; sp_item* items;
+	sp_matcher_stats* stats;
+	uint32_t* flags;			// [ndocs] 1 = run the document on the state machine
+};
+
+// document that owns token i: last d with tok_off[d] <= i
+__device__ __forceinline__ uint32_t evalFindDoc( const uint64_t* __restrict__ tok_off, uint32_t ndocs, uint64_t i)
+{
+	uint32_t lo = 0, hi = ndocs;	// invariant: tok_off[lo] <= i < tok_off[hi]
+	while (hi - lo > 1)
+	{
+		uint32_t mid = lo + (hi - lo) / 2;
+		if (__ldg( &tok_off[ mid]) <= i) lo = mid; else hi = mid;
+	}
+	return lo;
+}
+
+__device__ __forceinline__ void evalAddStats( sp_matcher_stats* st, uint32_t installed, uint32_t altkey, uint64_t signals, uint64_t open)
+{
+	if (installed) atomicAdd( (unsigned long long*)&st->nof_programs_installed, (unsigned long long)installed);
+	if (altkey) atomicAdd( (unsigned long long*)&st->nof_altkey_programs_installed, (unsigned long long)altkey);
+	if (signals) atomicAdd( (unsigned long long*)&st->nof_signals_fired, (unsigned long long)signals);
+	if (open) atomicAdd( (unsigned long long*)&st->nof_open_patterns, (unsigned long long)open);
+}
+
+// number of work items of a token with event slot `slotidx`
+__device__ __forceinline__ uint32_t evalTokenWork( const SpMatcherTables& T, uint32_t slotidx)
+{
+	if (slotidx == SP_EVAL_NOSLOT) return 0;
+	uint32_t work = __ldg( &T.event_slots[ slotidx].prog_count);
+	const uint32_t fb = __ldg( &T.eval_slots[ slotidx].follow_begin), fc = __ldg( &T.eval_slots[ slotidx].follow_count);
+	for (uint32_t c=0; c<fc; ++c)
+	{
+		const uint32_t es = __ldg( &T.eval_follows[ fb + c].eslot);
+		if (es != SP_EVAL_NOSLOT) work += __ldg( &T.event_slots[ es].prog_count);
+	}
+	return work;
+}
+
+static __global__ void __launch_bounds__(256) k_eval_prepare( EvalParams P)
+{
+	__shared__ uint32_t sdoc;
+	const uint64_t b0 = (uint64_t)blockIdx.x * 256;
+	if (threadIdx.x == 0) sdoc = evalFindDoc( P.tok_off, P.ndocs, b0);
+	__syncthreads();
+	const uint64_t i = b0 + threadIdx.x;
+	if (i >= P.ntokens) return;
+	uint32_t d = sdoc;
+	while (__ldg( &P.tok_off[ d+1]) <= i) ++d;
+	const uint64_t tb = __ldg( &P.tok_off[ d]);
+	uint32_t slotidx = SP_EVAL_NOSLOT, work = 0;
+	if (i >= tb)	// tokens in front of the first document belong to nobody
+	{
+		const sp_lexem tok = P.tokens[ i];
+		const uint32_t prev = i > tb ? __ldg( &P.tokens[ i-1].ordpos) : 0;
+		if (sp_eval_token_irregular( tok, P.origsegs ? P.origsegs[ i] : 0, i == tb, prev)) P.flags[ d] = 1;
+		slotidx = sp_find_event_index( P.T, tok.id);
+		work = evalTokenWork( P.T, slotidx);
+	}
+	P.tok_slot[ i] = slotidx; P.tok_work[ i] = work;
+}
+
+// Position inside the work items of a token: site and entry.
+struct EvalCursor
+{
+	uint32_t c;			// 0 = token event, else follow event number c-1
+	uint32_t k;			// entry inside the list
+	uint32_t lbegin, lcount;	// program list of the site
+	uint32_t fb, fc;		// static follow events of the token
+};
+
+// the list of site cur.c of the token with event slot `slotidx`; false if the site has no list
+__device__ __forceinline__ bool evalSiteList( const SpMatcherTables& T, uint32_t slotidx, EvalCursor& cur)
+{
+	uint32_t es = slotidx;
+	if (cur.c) es = __ldg( &T.eval_follows[ cur.fb + cur.c - 1].eslot);
+	cur.lbegin = 0; cur.lcount = 0;
+	if (es == SP_EVAL_NOSLOT) return false;
+	cur.lbegin = __ldg( &T.event_slots[ es].prog_begin); cur.lcount = __ldg( &T.event_slots[ es].prog_count);
+	return cur.lcount != 0;
+}
+
+// cursor at item `rem` of a token (rem < work items of the token)
+__device__ __forceinline__ void evalCursorSeek( const SpMatcherTables& T, uint32_t slotidx, uint32_t rem, EvalCursor& cur)
+{
+	cur.c = 0; cur.k = 0;
+	cur.fb = __ldg( &T.eval_slots[ slotidx].follow_begin); cur.fc = __ldg( &T.eval_slots[ slotidx].follow_count);
+	for (;;)
+	{
+		evalSiteList( T, slotidx, cur);
+		if (rem < cur.lcount) {cur.k = rem; return;}
+		rem -= cur.lcount;
+		if (cur.c >= cur.fc) {cur.k = 0; cur.lcount = 0; return;}	// not reached for rem < work
+		++cur.c;
+	}
+}
+
+__device__ __forceinline__ void evalQueuePush( const EvalParams& P, uint64_t item)
+{
+	const unsigned long long q = atomicAdd( P.queue_count, 1ull);
+	if (q < P.queue_cap) P.queue[ q] = item;
+}
+
+static __global__ void __launch_bounds__(EvalThreads) k_eval_count( EvalParams P)
+{
+	__shared__ uint2 s_tok[ EvalWarpsPerBlock][ EvalRun + EvalLook];		// id, ordinal position
+	__shared__ uint32_t s_work[ EvalWarpsPerBlock][ EvalRun + 1];			// first work item of a token, relative to the run
+	__shared__ uint32_t s_slot[ EvalWarpsPerBlock][ EvalRun];
+	__shared__ uint32_t s_te[ EvalWarpsPerBlock][ EvalRun];				// end of the token's document, relative to the run
+	__shared__ uint32_t s_doc[ EvalWarpsPerBlock][ EvalRun];
+	__shared__ uint32_t s_nres[ EvalWarpsPerBlock][ EvalRun];
+	__shared__ uint32_t s_nitems[ EvalWarpsPerBlock][ EvalRun];
+	const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	uint2* stok = s_tok[ warp]; uint32_t* swork = s_work[ warp]; uint32_t* sslot = s_slot[ warp];
+	uint32_t* ste = s_te[ warp]; uint32_t* sdoc = s_doc[ warp]; uint32_t* snres = s_nres[ warp]; uint32_t* snitems = s_nitems[ warp];
+
+	const uint64_t run = (uint64_t)blockIdx.x * EvalWarpsPerBlock + warp;
+	const uint64_t r0 = run * EvalRun;
+	if (r0 >= P.ntokens) return;
+	const uint32_t nrun = (uint32_t)min( (uint64_t)EvalRun, P.ntokens - r0);
+	const uint32_t nstaged = (uint32_t)min( (uint64_t)(EvalRun + EvalLook), P.ntokens - r0);
+	// ---- stage the run: every lane owns EvalPerLane consecutive tokens
+	uint32_t dbase = 0;
+	if (lane == 0) dbase = evalFindDoc( P.tok_off, P.ndocs, r0);
+	dbase = __shfl_sync( SP_FULL, dbase, 0);
+	for (uint32_t j=lane; j<nstaged; j+=32) stok[ j] = __ldg( reinterpret_cast<const uint2*>( P.tokens + r0 + j));
+	uint32_t mywork = 0;
+	{
+		uint32_t d = dbase;
+		for (uint32_t q=0; q<EvalPerLane; ++q)
+		{
+			const uint32_t j = lane * EvalPerLane + q;
+			uint32_t w = 0;
+			if (j < nrun)
+			{
+				const uint64_t i = r0 + j;
+				while (__ldg( &P.tok_off[ d+1]) <= i) ++d;
+				const uint64_t te = __ldg( &P.tok_off[ d+1]);
+				sdoc[ j] = d;
+				ste[ j] = (uint32_t)min( te - r0, (uint64_t)0xFFFFFFFFu);
+				sslot[ j] = P.tok_slot[ i];
+				w = P.tok_work[ i];
+			}
+			snres[ j] = 0; snitems[ j] = 0;
+			swork[ j] = w;		// turned into the prefix sum below
+			mywork += w;
+		}
+	}
+	uint32_t incl = mywork;
+	#pragma unroll
+	for (int ofs=1; ofs<32; ofs<<=1)
+	{
+		uint32_t up = __shfl_up_sync( SP_FULL, incl, ofs);
+		if (lane >= (unsigned int)ofs) incl += up;
+	}
+	const uint32_t W = __shfl_sync( SP_FULL, incl, 31);
+	{
+		uint32_t run_sum = incl - mywork;
+		for (uint32_t q=0; q<EvalPerLane; ++q)
+		{
+			const uint32_t j = lane * EvalPerLane + q;
+			const uint32_t w = swork[ j];
+			swork[ j] = run_sum;
+			run_sum += w;
+		}
+		if (lane == 31) swork[ EvalRun] = W;
+	}
+	__syncwarp();
+	if (W == 0)
+	{
+		for (uint32_t j=lane; j<nrun; j+=32) {P.tok_nres[ r0 + j] = 0; P.tok_nitems[ r0 + j] = 0;}
+		return;
+	}
+	const uint64_t wbase = __ldg( &P.tok_work_off[ r0]);	// number of the run's first work item
+
+	// ---- every lane follows the rules of its block of work items
+	const uint32_t B = (W + 31) / 32;
+	uint32_t w = min( lane * B, W);
+	const uint32_t wend = min( w + B, W);
+	uint32_t t = 0;				// token of the run the cursor is in
+	EvalCursor cur; cur.c = cur.k = cur.lbegin = cur.lcount = cur.fb = cur.fc = 0;
+	if (w < wend)
+	{
+		uint32_t lo = 0, hi = EvalRun;		// last token with swork[t] <= w
+		while (hi - lo > 1) {uint32_t mid = (lo + hi) / 2; if (swork[ mid] <= w) lo = mid; else hi = mid;}
+		t = lo;
+		evalCursorSeek( P.T, sslot[ t], w - swork[ t], cur);
+	}
+	// counters of the document the lane is in
+	uint32_t accdoc = (w < wend) ? sdoc[ t] : 0xFFFFFFFFu, acc_installed = 0;
+	uint64_t acc_signals = 0, acc_open = 0;
+	// the rule the lane follows
+	bool have = false;
+	SpEvalEntry en; SpEvalLite L;
+	uint32_t expiry = 0, wpos = 0, wte = 0;
+	en.ev[0] = en.ev[1] = en.ev[2] = en.ev[3] = 0xFFFFFFFFu; en.codes = en.value0 = en.meta = en.meta2 = 0;
+	L.value = L.count = L.endpos = L.flags = L.nitems = L.signals = L.alive_tokens = 0;
+
+	while (__any_sync( SP_FULL, w < wend))
+	{
+		if (w >= wend) continue;
+		bool consumed = false;
+		if (!have)
+		{
+			// take the item the cursor stands on
+			const uint4* ep = reinterpret_cast<const uint4*>( P.T.eval_entries + cur.lbegin + cur.k);
+			const uint4 a = __ldg( ep), b = __ldg( ep + 1);
+			en.ev[0] = a.x; en.ev[1] = a.y; en.ev[2] = a.z; en.ev[3] = a.w; en.codes = b.x; en.value0 = b.y; en.meta = b.z; en.meta2 = b.w;
+			const uint32_t d = sdoc[ t];
+			if (d != accdoc)
+			{
+				evalAddStats( P.stats + accdoc, acc_installed, 0, acc_signals, acc_open);
+				accdoc = d; acc_installed = 0; acc_signals = 0; acc_open = 0;
+			}
+			if (en.meta & SP_EVAL_META_GENERIC)
+			{
+				evalQueuePush( P, wbase + w);
+				consumed = true;
+			}
+			else
+			{
+				const uint32_t spos = stok[ t].y;
+				sp_eval_lite_init( en, spos, L);
+				expiry = spos + SP_EVAL_META_RANGE( en.meta);
+				wpos = t + 1; wte = ste[ t];
+				have = true;
+			}
+		}
+		if (have)
+		{
+			// one token of the window
+			if ((L.flags & SP_LITE_ALIVE) && wpos < wte)
+			{
+				uint2 tk;
+				if (wpos < EvalRun + EvalLook) tk = stok[ wpos];
+				else tk = __ldg( reinterpret_cast<const uint2*>( P.tokens + r0 + wpos));
+				sp_eval_lite_step( en, expiry, tk.x, tk.y, L);
+				++wpos;
+			}
+			else L.flags &= ~SP_LITE_ALIVE;
+			if (!(L.flags & SP_LITE_ALIVE))
+			{
+				// the rule has ended
+				if (L.flags & SP_LITE_FULL) evalQueuePush( P, wbase + w);
+				else
+				{
+					acc_installed += 1; acc_signals += L.signals;
+					acc_open += (uint64_t)L.alive_tokens * SP_EVAL_META_NTRIG( en.meta);
+					if (L.flags & SP_LITE_RESULT)
+					{
+						if (en.meta & SP_EVAL_META_ITEMSFULL) evalQueuePush( P, (wbase + w) | SP_EVALQ_STATS_DONE);
+						else
+						{
+							atomicAdd( &snres[ t], 1u);
+							if (L.flags & SP_LITE_DREFEMIT) atomicAdd( &snitems[ t], L.nitems);
+							const uint64_t bit = wbase + w;
+							atomicOr( P.resbits + (bit >> 5), 1u << (bit & 31));
+						}
+					}
+				}
+				have = false;
+				consumed = true;
+			}
+		}
+		if (consumed)
+		{
+			++w; ++cur.k;
+			if (cur.k >= cur.lcount && w < wend)
+			{
+				cur.k = 0;
+				for (;;)
+				{
+					if (cur.c < cur.fc) ++cur.c;
+					else
+					{
+						++t;
+						while (swork[ t+1] == swork[ t]) ++t;		// w < wend: there is a token with work
+						cur.c = 0;
+						cur.fb = __ldg( &P.T.eval_slots[ sslot[ t]].follow_begin); cur.fc = __ldg( &P.T.eval_slots[ sslot[ t]].follow_count);
+					}
+					if (evalSiteList( P.T, sslot[ t], cur)) break;
+				}
+			}
+		}
+	}
+	if (accdoc != 0xFFFFFFFFu) evalAddStats( P.stats + accdoc, acc_installed, 0, acc_signals, acc_open);
+	__syncwarp();
+	for (uint32_t j=lane; j<nrun; j+=32) {P.tok_nres[ r0 + j] = snres[ j]; P.tok_nitems[ r0 + j] = snitems[ j];}
+}
+
+// work item number -> token (binary search over the first items of the tokens), site and list entry
+__device__ __forceinline__ void evalDecodeItem( const EvalParams& P, uint64_t item, uint64_t& tok, uint32_t& slotidx, EvalCursor& cur)
+{
+	uint64_t lo = 0, hi = P.ntokens;	// last token with tok_work_off[t] <= item
+	while (hi - lo > 1)
+	{
+		uint64_t mid = lo + (hi - lo) / 2;
+		if (__ldg( &P.tok_work_off[ mid]) <= item) lo = mid; else hi = mid;
+	}
+	tok = lo;
+	slotidx = P.tok_slot[ lo];
+	evalCursorSeek( P.T, slotidx, (uint32_t)(item - __ldg( &P.tok_work_off[ lo])), cur);
+}
+
+__device__ __forceinline__ void evalItemSite( const EvalParams& P, uint64_t tok, uint32_t slotidx, const EvalCursor& cur, SpEvalSite& site)
+{
+	SpEvalSite base;
+	sp_eval_site_token( P.T, P.tokens[ tok], P.origsegs ? P.origsegs[ tok] : 0, tok, slotidx, base);
+	if (cur.c) sp_eval_site_follow( base, cur.c - 1, P.T.eval_follows[ cur.fb + cur.c - 1], site);
+	else site = base;
+}
+
+// The queued items of the count pass by the full fold, one per thread.
+static __global__ void __launch_bounds__(128) k_eval_count_full( EvalParams P)
+{
+	const uint64_t nq = min( (uint64_t)*P.queue_count, P.queue_cap);
+	for (uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; q < nq; q += (uint64_t)gridDim.x * blockDim.x)
+	{
+		const uint64_t entry = P.queue[ q];
+		const uint64_t item = entry & ~SP_EVALQ_STATS_DONE;
+		uint64_t tok; uint32_t slotidx; EvalCursor cur;
+		evalDecodeItem( P, item, tok, slotidx, cur);
+		const uint32_t d = evalFindDoc( P.tok_off, P.ndocs, tok);
+		SpEvalSite site;
+		evalItemSite( P, tok, slotidx, cur, site);
+		SpEvalRule R;
+		sp_eval_fold<false,0>( P.T, P.tokens, P.origsegs, __ldg( &P.tok_off[ d]), __ldg( &P.tok_off[ d+1]), site, P.T.program_triggers[ cur.lbegin + cur.k], false, R, 0);
+		if (R.flag) P.flags[ d] = 1;
+		if (!(entry & SP_EVALQ_STATS_DONE)) evalAddStats( P.stats + d, R.installed, R.altkey, R.signals, R.open);
+		if (R.has_result)
+		{
+			atomicAdd( P.tok_nres + tok, 1u);
+			const uint32_t nit = sp_eval_result_items( R);
+			if (nit) atomicAdd( P.tok_nitems + tok, nit);
+			atomicOr( P.resbits + (item >> 5), 1u << (item & 31));
+		}
+	}
+}
+
+// Write pass: the result bits of a run of tokens, 32 results at a time.
+static __global__ void __launch_bounds__(EvalThreads) k_eval_write( EvalParams P)
+{
+	__shared__ uint32_t s_work[ EvalWarpsPerBlock][ EvalRun + 1];
+	__shared__ uint32_t s_word[ EvalWarpsPerBlock][ 32];
+	__shared__ uint32_t s_pre[ EvalWarpsPerBlock][ 33];
+	const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	uint32_t* swork = s_work[ warp]; uint32_t* sword = s_word[ warp]; uint32_t* spre = s_pre[ warp];
+	const uint64_t run = (uint64_t)blockIdx.x * EvalWarpsPerBlock + warp;
+	const uint64_t r0 = run * EvalRun;
+	if (r0 >= P.ntokens) return;
+	const uint32_t nrun = (uint32_t)min( (uint64_t)EvalRun, P.ntokens - r0);
+	const uint64_t res0 = __ldg( &P.tok_res_off[ r0]);
+	const uint32_t nres_run = (uint32_t)(__ldg( &P.tok_res_off[ r0 + nrun]) - res0);
+	if (nres_run == 0) return;
+	const uint64_t wbase = __ldg( &P.tok_work_off[ r0]);
+	const uint32_t W = (uint32_t)(__ldg( &P.tok_work_off[ r0 + nrun]) - wbase);
+	for (uint32_t j=lane; j<=EvalRun; j+=32) swork[ j] = (uint32_t)(__ldg( &P.tok_work_off[ r0 + min( j, nrun)]) - wbase);
+	__syncwarp();
+	uint64_t res_done = 0;				// results of the run in front of the current group of words
+	uint64_t carry_tok = ~0ull; uint32_t carry_items = 0;	// items of the results of the last token seen so far
+	const uint64_t firstword = wbase >> 5, lastword = (wbase + W - 1) >> 5;
+	for (uint64_t wordbase=firstword; wordbase<=lastword; wordbase+=32)
+	{
+		// 32 words of the bit map, restricted to the items of the run
+		const uint64_t wi = wordbase + lane;
+		uint32_t word = 0;
+		if (wi <= lastword)
+		{
+			word = P.resbits[ wi];
+			if (wi == firstword) word &= 0xFFFFFFFFu << (wbase & 31);
+			if (wi == lastword && ((wbase + W) & 31)) word &= 0xFFFFFFFFu >> (32 - ((wbase + W) & 31));
+		}
+		uint32_t cnt = __popc( word), incl = cnt;
+		#pragma unroll
+		for (int ofs=1; ofs<32; ofs<<=1)
+		{
+			uint32_t up = __shfl_up_sync( SP_FULL, incl, ofs);
+			if (lane >= (unsigned int)ofs) incl += up;
+		}
+		const uint32_t total = __shfl_sync( SP_FULL, incl, 31);
+		if (!total) continue;
+		__syncwarp();
+		sword[ lane] = word; spre[ lane] = incl - cnt;
+		if (lane == 31) spre[ 32] = total;
+		__syncwarp();
+		for (uint32_t j0=0; j0<total; j0+=32)
+		{
+			const uint32_t j = j0 + lane;
+			const bool valid = j < total;
+			SpEvalRule R; sp_eval_rule_init( R);
+			SpEvalTake takes[ SP_EVAL_MAX_TAKES];
+			uint64_t tok = ~0ull - 1 - lane, tb = 0, te = 0;
+			uint32_t d = 0, program = 0;
+			bool live = false;
+			if (valid)
+			{
+				uint32_t lo = 0, hi = 32;	// word that holds result j: last word with spre <= j
+				while (hi - lo > 1) {uint32_t mid = (lo + hi) / 2; if (spre[ mid] <= j) lo = mid; else hi = mid;}
+				const uint32_t bit = __fns( sword[ lo], 0, (int)(j - spre[ lo]) + 1);
+				const uint32_t wl = (uint32_t)(((wordbase + lo) << 5) + bit - wbase);		// item of the run
+				uint32_t tlo = 0, thi = EvalRun;
+				while (thi - tlo > 1) {uint32_t mid = (tlo + thi) / 2; if (swork[ mid] <= wl) tlo = mid; else thi = mid;}
+				tok = r0 + tlo;
+				const uint32_t slotidx = P.tok_slot[ tok];
+				EvalCursor cur;
+				evalCursorSeek( P.T, slotidx, wl - swork[ tlo], cur);
+				d = evalFindDoc( P.tok_off, P.ndocs, tok);
+				tb = __ldg( &P.tok_off[ d]); te = __ldg( &P.tok_off[ d+1]);
+				live = !P.flags[ d];	// the results of flagged documents come from the state machine
+				if (live)
+				{
+					SpEvalSite site;
+					evalItemSite( P, tok, slotidx, cur, site);
+					const SpProgramTrigger pt = P.T.program_triggers[ cur.lbegin + cur.k];
+					program = pt.program;
+					sp_eval_fold<true,0>( P.T, P.tokens, P.origsegs, tb, te, site, pt, false, R, takes);
+				}
+			}
+			// items of the earlier results of the same token (the results of a token are neighbours)
+			const uint32_t nit = live ? sp_eval_result_items( R) : 0;
+			uint32_t seg = nit;
+			#pragma unroll
+			for (int ofs=1; ofs<32; ofs<<=1)
+			{
+				const uint32_t up = __shfl_up_sync( SP_FULL, seg, ofs);
+				const uint64_t uptok = __shfl_up_sync( SP_FULL, tok, ofs);
+				if (lane >= (unsigned int)ofs && uptok == tok) seg += up;
+			}
+			const uint32_t before = seg - nit + (tok == carry_tok ? carry_items : 0u);
+			if (live && R.has_result)
+			{
+				const uint64_t res_in_doc = (res0 + res_done + j) - __ldg( &P.tok_res_off[ tb]);
+				const uint64_t item_in_doc = (__ldg( &P.tok_item_off[ tok]) - __ldg( &P.tok_item_off[ tb])) + before;
+				if (nit) sp_eval_write_items( P.T, P.tokens, P.origsegs, tb, te, takes, R.ntakes, P.items + __ldg( &P.doc_item_off[ d]) + item_in_doc);
+				sp_eval_result_record( P.T.programs[ program], R, (uint32_t)item_in_doc, nit, P.results[ __ldg( &P.doc_res_off[ d]) + res_in_doc]);
+			}
+			const int last = (int)min( total - j0, 32u) - 1;
+			const uint64_t ltok = __shfl_sync( SP_FULL, tok, last);
+			const uint32_t lseg = __shfl_sync( SP_FULL, seg, last);
+			carry_items = lseg + (ltok == carry_tok ? carry_items : 0u);
+			carry_tok = ltok;
+		}
+		res_done += total;
+	}
+}
+
+// Per document: counts from the token prefix sums, status, number of events; flagged documents are listed.
+// totals[0] results, [1] items of the documents that stay on the evaluator; nflagged = length of the list.
+static __global__ void k_eval_docs( EvalParams P, uint32_t* doc_res_count, uint32_t* doc_item_count, uint32_t* status,
+				    uint32_t* list, uint32_t* nflagged, unsigned long long* totals)
+{
+	const uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
+	if (d >= P.ndocs) return;
+	const uint64_t tb = P.tok_off[ d], te = P.tok_off[ d+1];
+	status[ d] = 0;
+	if (P.flags[ d])
+	{
+		doc_res_count[ d] = 0; doc_item_count[ d] = 0;
+		list[ atomicAdd( nflagged, 1u)] = d;
+		return;
+	}
+	const uint64_t nr = P.tok_res_off[ te] - P.tok_res_off[ tb], ni = P.tok_item_off[ te] - P.tok_item_off[ tb];
+	doc_res_count[ d] = (uint32_t)nr; doc_item_count[ d] = (uint32_t)ni;
+	P.stats[ d].nof_events = te - tb;
+	if (nr) atomicAdd( totals + 0, (unsigned long long)nr);
+	if (ni) atomicAdd( totals + 1, (unsigned long long)ni);
+}
+
+// Results of the documents that ran on the state machine: from its pools to their place (one warp per listed document).
+static __global__ void __launch_bounds__(256) k_eval_place( const uint32_t* list, uint32_t nlist, MatchParams M, const uint64_t* res_off, const uint64_t* item_off,
+							   sp_result* results, sp_item* items)
+{
+	const unsigned int lane = threadIdx.x & 31;
+	const uint32_t w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	if (w >= nlist) return;
+	const uint32_t d = list[ w];
+	{
+		const uint4* src = reinterpret_cast<const uint4*>( M.item_pool + M.doc_item_begin[ d]);
+		uint4* dst = reinterpret_cast<uint4*>( items + item_off[ d]);
+		for (uint64_t i=lane, n=2ull*M.doc_item_count[ d]; i<n; i+=32) dst[ i] = src[ i];
+	}
+	{
+		const uint2* src = reinterpret_cast<const uint2*>( M.res_pool + M.doc_res_begin[ d]);
+		uint2* dst = reinterpret_cast<uint2*>( results + res_off[ d]);
+		for (uint64_t i=lane, n=5ull*M.doc_res_count[ d]; i<n; i+=32) dst[ i] = src[ i];
+	}
+}
+
+} // namespace sp
+#endif

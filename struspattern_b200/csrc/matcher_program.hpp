@@ -64,6 +64,7 @@ struct MatcherTablesHost
 	std::vector<SpEvalSlot> eval_slots;	// window evaluator (matcher_eval.cuh): static follow events per event slot
 	std::vector<SpEvalFollow> eval_follows;
 	std::vector<uint32_t> prog_flags;
+	std::vector<SpEvalEntry> eval_entries;
 	SpMatcherTables view;			// pointers are filled by the owner (host or device addresses)
 };
 
@@ -404,9 +405,118 @@ private:
 				T.eval_slots[ h].follow_count = (uint32_t)T.eval_follows.size() - T.eval_slots[ h].follow_begin;
 			}
 		}
+		// list entries: live trigger events and the outcome of the installation signals
+		SpEvalEntry noentry; std::memset( &noentry, 0, sizeof(noentry)); noentry.meta = SP_EVAL_META_GENERIC;
+		T.eval_entries.assign( T.program_triggers.size(), noentry);
+		for (const SpEventSlot& slot: T.event_slots)
+		{
+			if (!slot.key) continue;
+			for (uint32_t k=0; k<slot.prog_count; ++k) T.eval_entries[ slot.prog_begin + k] = evalEntry( T, T.program_triggers[ slot.prog_begin + k], slot.key - 1);
+		}
+		T.view.eval_entries = T.eval_entries.data();
 		T.view.eval_slots = T.eval_slots.data(); T.view.eval_follows = T.eval_follows.data(); T.view.prog_flags = T.prog_flags.data();
 		T.view.nfollows = (uint32_t)T.eval_follows.size();
 		T.view.eval_capable = capable ? 1 : 0;
+	}
+
+	// Installation of program pt.program by `keyevent` on an event at position S (any S >= 1) without sub data: which
+	// definitions become live triggers (installProgram, src/ruleMatcherAutomaton.cpp:1204-1250) and what the direct signals
+	// of the key definitions (:1259-1269, fireSignal :772-979 on a fresh slot) leave behind. With end_ordpos in {0, S+1}
+	// the position tests of fireSignal do not depend on S. `termKey`: the key event is a term event (no sub data).
+	static SpEvalEntry evalEntry( const MatcherTablesHost& T, const SpProgramTrigger& pt, uint32_t keyevent)
+	{
+		SpEvalEntry en; std::memset( &en, 0, sizeof(en));
+		for (int e=0; e<SP_EVAL_NEV; ++e) en.ev[ e] = 0xFFFFFFFFu;
+		const SpProgram& P = T.programs[ pt.program];
+		uint32_t count = P.initcount & 0xFFFFu, value = P.initsigval;
+		bool generic = pt.past_event != 0 || P.range >= 0xFFFFu || P.trig_count > 32;
+		uint32_t nev = 0, ntrig = 0, nkey = 0, varmask = 0;
+		bool hasKeyEvent = false;
+		std::vector<uint32_t> keydefs;
+		for (uint32_t d=0; d<P.trig_count && d<32; ++d)
+		{
+			const SpTriggerDef& def = T.trigger_defs[ P.trig_begin + d];
+			bool install = true;
+			if (def.event == keyevent)
+			{
+				keydefs.push_back( d);
+				const bool needsInstall = (def.sigtype == SP_SIG_ANY && count > 1);
+				if (def.is_key && !hasKeyEvent) {hasKeyEvent = true; install = needsInstall;}
+				else if (def.sigtype == SP_SIG_DEL) install = needsInstall;
+			}
+			if (!install) continue;
+			++ntrig;
+			uint32_t sig = 0;
+			switch (def.sigtype)
+			{
+				case SP_SIG_SEQUENCE: case SP_SIG_SEQUENCE_IMM:
+					if (def.sigval < 1 || def.sigval > 32) generic = true; else sig = def.sigval - 1;
+					break;
+				case SP_SIG_WITHIN:
+					if (!def.sigval || (def.sigval & (def.sigval - 1))) generic = true; else sig = (uint32_t)__builtin_ctz( def.sigval);
+					break;
+				case SP_SIG_ANY: case SP_SIG_DEL: break;
+				default: generic = true; break;
+			}
+			if ((def.event >> 29) != TermEvent || nev >= SP_EVAL_NEV) {generic = true; continue;}
+			en.ev[ nev] = def.event;
+			en.codes |= (((uint32_t)def.sigtype << 5) | sig) << (8 * nev);
+			if (def.variable) varmask |= 1u << nev;
+			++nev;
+		}
+		bool endSet = false, done = false, disposed = false, result = false, dataref = false, drefEmit = false;
+		uint32_t nitems = 0;
+		for (uint32_t d: keydefs)
+		{
+			const SpTriggerDef& def = T.trigger_defs[ P.trig_begin + d];
+			bool match = false, finished = false, take = false;
+			++nkey;
+			switch (def.sigtype)
+			{
+				case SP_SIG_ANY:
+					take = true;
+					if (count > 0) {match = true; --count; finished = (count == 0); endSet = true;}
+					break;
+				case SP_SIG_SEQUENCE: case SP_SIG_SEQUENCE_IMM: case SP_SIG_WITHIN:
+				{
+					bool accept;
+					if (def.sigtype == SP_SIG_WITHIN) accept = (def.sigval & value) != 0 && !endSet;
+					else if (def.sigtype == SP_SIG_SEQUENCE) accept = def.sigval == value && !endSet;
+					else accept = false;	// end_ordpos == start_ordpos: neither 0 nor S+1 equals S
+					if (accept)
+					{
+						endSet = true;
+						if (def.sigtype == SP_SIG_WITHIN) value &= ~def.sigval; else value = def.sigval - 1;
+						if (count > 0) {--count; match = (count == 0);} else match = true;
+						finished = (value == 0);
+						take = true;
+					}
+					break;
+				}
+				case SP_SIG_DEL: count = 0; value = 0; disposed = true; continue;
+				default: generic = true; break;
+			}
+			if (take && def.variable) {dataref = true; ++nitems;}
+			if (match)
+			{
+				if (!done) {if (P.resultHandle) {result = true; drefEmit = dataref;} done = true;}
+				if (finished) disposed = true;
+			}
+		}
+		if (nkey > 63 || ntrig > 63 || nitems > 63) generic = true;
+		en.value0 = value;
+		en.meta = (P.range & 0xFFFFu) | ((ntrig & 0x3Fu) << 16) | ((nkey & 0x3Fu) << 22);
+		en.meta2 = (count & 0xFFFFu) | ((nitems & 0x3Fu) << 16) | (varmask << 22);
+		if (P.resultHandle) en.meta2 |= SP_EVAL_M2_HASRES;
+		if (done) en.meta2 |= SP_EVAL_M2_DONE0;
+		if (endSet) en.meta2 |= SP_EVAL_M2_END0;
+		if (dataref) en.meta2 |= SP_EVAL_M2_DATAREF0;
+		if (result) en.meta2 |= SP_EVAL_M2_RESULT0;
+		if (drefEmit) en.meta2 |= SP_EVAL_M2_DREFEMIT0;
+		if ((keyevent >> 29) != TermEvent) en.meta |= SP_EVAL_META_ITEMSFULL;
+		if (generic) en.meta |= SP_EVAL_META_GENERIC;
+		else if (disposed || ntrig == 0) en.meta |= SP_EVAL_META_DEAD;
+		return en;
 	}
 
 	struct Node

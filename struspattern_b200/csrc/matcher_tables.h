@@ -77,6 +77,36 @@ typedef struct alignas(8) SpEvalSlot
 	uint32_t follow_count;
 } SpEvalSlot;
 
+/* Per program list entry (parallel to program_triggers): the rule instance this entry creates, compiled for the window
+ * evaluator (matcher_eval.cuh: sp_eval_entry_step). The signals of the installation (key definitions fired on the fresh
+ * slot, src/ruleMatcherAutomaton.cpp:1259-1269) do not depend on the document, so the slot they leave behind is stored
+ * here (value0, count0, flags), next to the live triggers: event, signal type and signal value of up to 4 of them. A
+ * rule is then followed through its window without reading the program or its trigger definitions. 32 bytes. */
+#define SP_EVAL_NEV 4
+typedef struct alignas(16) SpEvalEntry
+{
+	uint32_t ev[ SP_EVAL_NEV];	/* events of the live triggers, 0xFFFFFFFF = unused */
+	uint32_t codes;			/* 8 bits per live trigger: signal type << 5 | (sequence: signal value - 1, within: bit number) */
+	uint32_t value0;		/* slot value behind the installation */
+	uint32_t meta;			/* range | ntrig << 16 | nkey << 22 | SP_EVAL_META_* */
+	uint32_t meta2;			/* count0 | nitems0 << 16 | varmask << 22 | SP_EVAL_M2_* */
+} SpEvalEntry;
+#define SP_EVAL_META_RANGE( m)  ((m) & 0xFFFFu)
+#define SP_EVAL_META_NTRIG( m)  (((m) >> 16) & 0x3Fu)
+#define SP_EVAL_META_NKEY( m)   (((m) >> 22) & 0x3Fu)
+#define SP_EVAL_META_GENERIC    (1u << 28)	/* not compiled: evaluated by the full fold (alternative key, more than 4 live triggers, ...) */
+#define SP_EVAL_META_DEAD       (1u << 29)	/* finished by the signals of its installation */
+#define SP_EVAL_META_ITEMSFULL  (1u << 30)	/* the key event is a follow event: the items of a result are counted by the full fold */
+#define SP_EVAL_M2_COUNT( m)    ((m) & 0xFFFFu)
+#define SP_EVAL_M2_NITEMS( m)   (((m) >> 16) & 0x3Fu)
+#define SP_EVAL_M2_VARMASK( m)  (((m) >> 22) & 0xFu)	/* live triggers that have a variable */
+#define SP_EVAL_M2_HASRES       (1u << 26)	/* the program has a result handle */
+#define SP_EVAL_M2_DONE0        (1u << 27)	/* the rule has matched at its installation */
+#define SP_EVAL_M2_END0         (1u << 28)	/* end_ordpos = position of the key event + 1 (else 0) */
+#define SP_EVAL_M2_DATAREF0     (1u << 29)	/* the rule has an item list behind the installation */
+#define SP_EVAL_M2_RESULT0      (1u << 30)	/* result emitted at the installation */
+#define SP_EVAL_M2_DREFEMIT0    (1u << 31)	/* ... and the rule had its item list then */
+
 #define SP_PROGFLAG_LISTENS_FOLLOW 1u	/* some trigger definition waits for an event that is not a term event */
 
 typedef struct SpMatcherTables
@@ -97,6 +127,7 @@ typedef struct SpMatcherTables
 	const SpEvalSlot* eval_slots;	/* [event_mask+1] */
 	const SpEvalFollow* eval_follows;
 	const uint32_t* prog_flags;	/* [nprograms] SP_PROGFLAG_* */
+	const SpEvalEntry* eval_entries;	/* [nprogram_triggers] */
 	uint32_t nfollows;
 	uint32_t eval_capable;		/* 1: the rule set is inside what the window evaluator reproduces exactly (matcher_program.hpp: evalCapable) */
 } SpMatcherTables;

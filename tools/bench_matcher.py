@@ -88,7 +88,7 @@ def main():
         line.update({"cpu_ms": rdt * 1000.0, "cpu_threads": nthreads, "cpu_mtok_s": len(toks) / rdt / 1e6, "speedup": rdt / dt,
                      "cpu_results": int(ro["result_offsets"][-1])})
         if args.check:
-            MC.compare_outputs(ref, ro, gpu, out, check_order=True)
+            MC.compare_outputs(ref, ro, gpu, out, check_order=False)
             line["parity"] = "ok"
     print(json.dumps(line))
 
