@@ -586,8 +586,32 @@ SP_MHD void sp_eval_lite_result( const SpEvalEntry& en, const SpEvalLite& L, SpE
 	R.nitems = L.nitems;
 }
 
-/* per entry form of what k_eval_pass does for 32 entries at a time (tests/hostsim). Returns false if the rule needs the full fold. */
-SP_MHD bool sp_eval_entry_run( const SpEvalEntry& en, const sp_lexem* toks, uint64_t te, const SpEvalSite& site, SpEvalRule& R)
+/* A rule keyed by follow event F has taken F with a variable `nkv` times at its installation (SP_EVAL_M2_NITEMS of an
+ * entry with SP_EVAL_META_ITEMSFULL): each of these items refers to the item list of the rule Q that emitted F, and
+ * the items of that list follow it in the result (gatherResultItems, src/patternMatcher.cpp:185-188) unless F has a
+ * format. `extra` = number of those items: Q followed to its end from its own list entry. False: the full fold decides. */
+SP_MHD bool sp_eval_lite_follow_items( const SpMatcherTables& T, const sp_lexem* toks, uint64_t tok, uint64_t te, const SpEvalEntry& en, const SpEvalFollow& F, uint32_t& extra)
+{
+	extra = 0;
+	const uint32_t nkv = SP_EVAL_M2_NITEMS( en.meta2);
+	if (!nkv || !F.sub || F.format) return true;
+	const SpEvalEntry q = T.eval_entries[ F.qpt];
+	if (q.meta & SP_EVAL_META_GENERIC) return false;
+	SpEvalLite Q;
+	const uint32_t spos = SP_MLDG( &toks[ tok].ordpos);
+	sp_eval_lite_init( q, spos, Q);
+	const uint32_t expiry = spos + SP_EVAL_META_RANGE( q.meta);
+	for (uint64_t k=tok+1; k<te && (Q.flags & SP_LITE_ALIVE); ++k)
+	{
+		sp_eval_lite_step( q, expiry, SP_MLDG( &toks[ k].id), SP_MLDG( &toks[ k].ordpos), Q);
+	}
+	if (Q.flags & SP_LITE_FULL) return false;
+	extra = nkv * Q.nitems;
+	return true;
+}
+
+/* per entry form of what k_eval_count does with 32 rules in lock step (tests/hostsim). Returns false if the rule needs the full fold. */
+SP_MHD bool sp_eval_entry_run( const SpMatcherTables& T, const SpEvalEntry& en, const sp_lexem* toks, uint64_t te, const SpEvalSite& site, SpEvalRule& R)
 {
 	if (en.meta & SP_EVAL_META_GENERIC) return false;
 	SpEvalLite L;
@@ -598,8 +622,13 @@ SP_MHD bool sp_eval_entry_run( const SpEvalEntry& en, const sp_lexem* toks, uint
 		sp_eval_lite_step( en, expiry, SP_MLDG( &toks[ k].id), SP_MLDG( &toks[ k].ordpos), L);
 	}
 	if (L.flags & SP_LITE_FULL) return false;
-	if ((L.flags & SP_LITE_RESULT) && (en.meta & SP_EVAL_META_ITEMSFULL)) return false;
+	uint32_t extra = 0;
+	if ((L.flags & SP_LITE_RESULT) && (en.meta & SP_EVAL_META_ITEMSFULL))
+	{
+		if (!site.cpos || !sp_eval_lite_follow_items( T, toks, site.tok, te, en, T.eval_follows[ site.follow_begin + site.cpos - 1], extra)) return false;
+	}
 	sp_eval_lite_result( en, L, R);
+	R.nitems += extra;
 	return true;
 }
 

@@ -27,7 +27,7 @@
 
 namespace sp {
 
-enum {EvalWarpsPerBlock = 4, EvalThreads = EvalWarpsPerBlock * 32, EvalRun = 256, EvalLook = 64, EvalPerLane = EvalRun / 32};
+enum {EvalWarpsPerBlock = 4, EvalThreads = EvalWarpsPerBlock * 32, EvalRun = 256, EvalLook = 64, EvalPerLane = EvalRun / 32, EvalSteps = 4};
 
 #define SP_EVALQ_STATS_DONE (1ull << 63)	/* queued item whose counters are already added: only result, items and bit are missing */
 
@@ -244,90 +244,91 @@ static __global__ void __launch_bounds__(EvalThreads) k_eval_count( EvalParams P
 	en.ev[0] = en.ev[1] = en.ev[2] = en.ev[3] = 0xFFFFFFFFu; en.codes = en.value0 = en.meta = en.meta2 = 0;
 	L.value = L.count = L.endpos = L.flags = L.nitems = L.signals = L.alive_tokens = 0;
 
-	while (__any_sync( SP_FULL, w < wend))
+	// The lanes step their rules in lock step (EvalSteps window tokens per round, one uniform instruction stream); ended
+	// rules are accounted and replaced at the begin of a round. A lane waits at most EvalSteps-1 steps for its next rule.
+	auto advance = [&]()
 	{
-		if (w >= wend) continue;
-		bool consumed = false;
-		if (!have)
+		++w; ++cur.k;
+		if (cur.k >= cur.lcount && w < wend)
 		{
-			// take the item the cursor stands on
-			const uint4* ep = reinterpret_cast<const uint4*>( P.T.eval_entries + cur.lbegin + cur.k);
-			const uint4 a = __ldg( ep), b = __ldg( ep + 1);
-			en.ev[0] = a.x; en.ev[1] = a.y; en.ev[2] = a.z; en.ev[3] = a.w; en.codes = b.x; en.value0 = b.y; en.meta = b.z; en.meta2 = b.w;
-			const uint32_t d = sdoc[ t];
-			if (d != accdoc)
+			cur.k = 0;
+			for (;;)
 			{
-				evalAddStats( P.stats + accdoc, acc_installed, 0, acc_signals, acc_open);
-				accdoc = d; acc_installed = 0; acc_signals = 0; acc_open = 0;
+				if (cur.c < cur.fc) ++cur.c;
+				else
+				{
+					++t;
+					while (swork[ t+1] == swork[ t]) ++t;		// w < wend: there is a token with work
+					cur.c = 0;
+					cur.fb = __ldg( &P.T.eval_slots[ sslot[ t]].follow_begin); cur.fc = __ldg( &P.T.eval_slots[ sslot[ t]].follow_count);
+				}
+				if (evalSiteList( P.T, sslot[ t], cur)) break;
 			}
-			if (en.meta & SP_EVAL_META_GENERIC)
+		}
+	};
+	auto account = [&]()
+	{
+		if (L.flags & SP_LITE_FULL) {evalQueuePush( P, wbase + w); return;}
+		acc_installed += 1; acc_signals += L.signals;
+		acc_open += (uint64_t)L.alive_tokens * SP_EVAL_META_NTRIG( en.meta);
+		if (L.flags & SP_LITE_RESULT)
+		{
+			uint32_t extra = 0;
+			if ((en.meta & SP_EVAL_META_ITEMSFULL)
+			    && !sp_eval_lite_follow_items( P.T, P.tokens, r0 + t, r0 + ste[ t], en, P.T.eval_follows[ cur.fb + cur.c - 1], extra))
 			{
-				evalQueuePush( P, wbase + w);
-				consumed = true;
+				evalQueuePush( P, (wbase + w) | SP_EVALQ_STATS_DONE);
 			}
 			else
 			{
+				atomicAdd( &snres[ t], 1u);
+				if (L.flags & SP_LITE_DREFEMIT) atomicAdd( &snitems[ t], L.nitems + extra);
+				const uint64_t bit = wbase + w;
+				atomicOr( P.resbits + (bit >> 5), 1u << (bit & 31));
+			}
+		}
+	};
+	while (__any_sync( SP_FULL, have || w < wend))
+	{
+		if (!(L.flags & SP_LITE_ALIVE))
+		{
+			if (have) {account(); have = false; advance();}
+			while (w < wend)
+			{
+				// take the item the cursor stands on
+				const uint4* ep = reinterpret_cast<const uint4*>( P.T.eval_entries + cur.lbegin + cur.k);
+				const uint4 a = __ldg( ep), b = __ldg( ep + 1);
+				en.ev[0] = a.x; en.ev[1] = a.y; en.ev[2] = a.z; en.ev[3] = a.w; en.codes = b.x; en.value0 = b.y; en.meta = b.z; en.meta2 = b.w;
+				const uint32_t d = sdoc[ t];
+				if (d != accdoc)
+				{
+					evalAddStats( P.stats + accdoc, acc_installed, 0, acc_signals, acc_open);
+					accdoc = d; acc_installed = 0; acc_signals = 0; acc_open = 0;
+				}
+				if (en.meta & SP_EVAL_META_GENERIC) {evalQueuePush( P, wbase + w); advance(); continue;}
 				const uint32_t spos = stok[ t].y;
 				sp_eval_lite_init( en, spos, L);
+				if (!(L.flags & SP_LITE_ALIVE)) {account(); advance(); continue;}	// ended by its installation
 				expiry = spos + SP_EVAL_META_RANGE( en.meta);
 				wpos = t + 1; wte = ste[ t];
 				have = true;
+				break;
 			}
 		}
-		if (have)
+		#pragma unroll
+		for (int step=0; step<EvalSteps; ++step)
 		{
-			// one token of the window
-			if ((L.flags & SP_LITE_ALIVE) && wpos < wte)
+			if (L.flags & SP_LITE_ALIVE)
 			{
-				uint2 tk;
-				if (wpos < EvalRun + EvalLook) tk = stok[ wpos];
-				else tk = __ldg( reinterpret_cast<const uint2*>( P.tokens + r0 + wpos));
-				sp_eval_lite_step( en, expiry, tk.x, tk.y, L);
-				++wpos;
-			}
-			else L.flags &= ~SP_LITE_ALIVE;
-			if (!(L.flags & SP_LITE_ALIVE))
-			{
-				// the rule has ended
-				if (L.flags & SP_LITE_FULL) evalQueuePush( P, wbase + w);
-				else
+				if (wpos < wte)
 				{
-					acc_installed += 1; acc_signals += L.signals;
-					acc_open += (uint64_t)L.alive_tokens * SP_EVAL_META_NTRIG( en.meta);
-					if (L.flags & SP_LITE_RESULT)
-					{
-						if (en.meta & SP_EVAL_META_ITEMSFULL) evalQueuePush( P, (wbase + w) | SP_EVALQ_STATS_DONE);
-						else
-						{
-							atomicAdd( &snres[ t], 1u);
-							if (L.flags & SP_LITE_DREFEMIT) atomicAdd( &snitems[ t], L.nitems);
-							const uint64_t bit = wbase + w;
-							atomicOr( P.resbits + (bit >> 5), 1u << (bit & 31));
-						}
-					}
+					uint2 tk;
+					if (wpos < EvalRun + EvalLook) tk = stok[ wpos];
+					else tk = __ldg( reinterpret_cast<const uint2*>( P.tokens + r0 + wpos));
+					sp_eval_lite_step( en, expiry, tk.x, tk.y, L);
+					++wpos;
 				}
-				have = false;
-				consumed = true;
-			}
-		}
-		if (consumed)
-		{
-			++w; ++cur.k;
-			if (cur.k >= cur.lcount && w < wend)
-			{
-				cur.k = 0;
-				for (;;)
-				{
-					if (cur.c < cur.fc) ++cur.c;
-					else
-					{
-						++t;
-						while (swork[ t+1] == swork[ t]) ++t;		// w < wend: there is a token with work
-						cur.c = 0;
-						cur.fb = __ldg( &P.T.eval_slots[ sslot[ t]].follow_begin); cur.fc = __ldg( &P.T.eval_slots[ sslot[ t]].follow_count);
-					}
-					if (evalSiteList( P.T, sslot[ t], cur)) break;
-				}
+				else L.flags &= ~SP_LITE_ALIVE;
 			}
 		}
 	}

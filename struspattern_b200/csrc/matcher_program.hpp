@@ -497,6 +497,8 @@ private:
 				default: generic = true; break;
 			}
 			if (take && def.variable) {dataref = true; ++nitems;}
+			// a follow event taken without a variable joins the items of its rule (:911-918): left to the full fold
+			if (take && !def.variable && (keyevent >> 29) != TermEvent) generic = true;
 			if (match)
 			{
 				if (!done) {if (P.resultHandle) {result = true; drefEmit = dataref;} done = true;}

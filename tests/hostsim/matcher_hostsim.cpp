@@ -89,7 +89,7 @@ static bool evalDocument( const SpMatcherTables& T, const sp_lexem* tokens, cons
 				sp_eval_fold<false,0>( T, tokens, segs, tb, te, site, pt, false, C, 0);
 				// the compiled list entry must give the same answer whenever it claims to know it
 				SpEvalRule Qt;
-				if (sp_eval_entry_run( T.eval_entries[ es.prog_begin + k], tokens, te, site, Qt)
+				if (sp_eval_entry_run( T, T.eval_entries[ es.prog_begin + k], tokens, te, site, Qt)
 				    && (Qt.installed != R.installed || Qt.signals != R.signals || Qt.open != R.open || Qt.has_result != R.has_result
 					|| (R.has_result && sp_eval_result_items( Qt) != sp_eval_result_items( R)) || R.altkey || R.flag))
 				{
