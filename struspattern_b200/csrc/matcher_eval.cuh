@@ -517,8 +517,10 @@ SP_MHD void sp_eval_lite_init( const SpEvalEntry& en, uint32_t site_ordpos, SpEv
 	L.nitems = SP_EVAL_M2_NITEMS( en.meta2); L.signals = SP_EVAL_META_NKEY( en.meta); L.alive_tokens = 0;
 }
 
-/* fireSignal of live trigger j (:772-979) for a token at `pos` */
-SP_MHD void sp_eval_lite_fire( const SpEvalEntry& en, uint32_t j, uint32_t pos, SpEvalLite& L)
+/* fireSignal of live trigger j (:772-979) for a token at `pos`. Returns SP_LITE_TOOK | SP_LITE_EMITTED bits. */
+#define SP_LITE_TOOK    1u	/* the rule has taken the event */
+#define SP_LITE_EMITTED 2u	/* the rule has emitted its result with this event */
+SP_MHD uint32_t sp_eval_lite_fire( const SpEvalEntry& en, uint32_t j, uint32_t pos, SpEvalLite& L)
 {
 	const uint32_t code = (en.codes >> (8 * j)) & 0xFFu, type = code >> 5, sig = code & 31u;
 	bool take = false, match = false, finished = false;
@@ -535,7 +537,7 @@ SP_MHD void sp_eval_lite_fire( const SpEvalEntry& en, uint32_t j, uint32_t pos, 
 	else if (type == SP_SIG_DEL)
 	{
 		L.count = 0; L.value = 0; L.flags &= ~SP_LITE_ALIVE;
-		return;
+		return 0;
 	}
 	else
 	{
@@ -552,28 +554,32 @@ SP_MHD void sp_eval_lite_fire( const SpEvalEntry& en, uint32_t j, uint32_t pos, 
 			take = true;
 		}
 	}
+	uint32_t what = take ? SP_LITE_TOOK : 0u;
 	if (take && ((SP_EVAL_M2_VARMASK( en.meta2) >> j) & 1u)) {L.nitems += 1; L.flags |= SP_LITE_DATAREF;}
 	if (match)
 	{
 		if (!(L.flags & SP_LITE_DONE))
 		{
-			if (en.meta2 & SP_EVAL_M2_HASRES) L.flags |= SP_LITE_RESULT | ((L.flags & SP_LITE_DATAREF) ? SP_LITE_DREFEMIT : 0u);
+			if (en.meta2 & SP_EVAL_M2_HASRES) {L.flags |= SP_LITE_RESULT | ((L.flags & SP_LITE_DATAREF) ? SP_LITE_DREFEMIT : 0u); what |= SP_LITE_EMITTED;}
 			L.flags |= SP_LITE_DONE;
 		}
 		if (finished) L.flags &= ~SP_LITE_ALIVE;
 	}
+	return what;
 }
 
-/* one window token for the rule: expiry, live trigger count sample (:992), signals */
-SP_MHD void sp_eval_lite_step( const SpEvalEntry& en, uint32_t expiry, uint32_t id, uint32_t pos, SpEvalLite& L)
+/* one window token for the rule: expiry, live trigger count sample (:992), signals.
+ * Returns (SP_LITE_TOOK | SP_LITE_EMITTED bits) | live trigger << 4 if a live trigger was signalled, else 0. */
+SP_MHD uint32_t sp_eval_lite_step( const SpEvalEntry& en, uint32_t expiry, uint32_t id, uint32_t pos, SpEvalLite& L)
 {
-	if (!(L.flags & SP_LITE_ALIVE)) return;
-	if (pos > expiry) {L.flags &= ~SP_LITE_ALIVE; return;}
+	if (!(L.flags & SP_LITE_ALIVE)) return 0;
+	if (pos > expiry) {L.flags &= ~SP_LITE_ALIVE; return 0;}
 	L.alive_tokens += 1;
+	if (id != en.ev[0] && id != en.ev[1] && id != en.ev[2] && id != en.ev[3]) return 0;
 	const uint32_t m = (id == en.ev[0] ? 1u : 0u) | (id == en.ev[1] ? 2u : 0u) | (id == en.ev[2] ? 4u : 0u) | (id == en.ev[3] ? 8u : 0u);
-	if (!m) return;
-	if (m & (m - 1)) {L.flags = (L.flags | SP_LITE_FULL) & ~SP_LITE_ALIVE; return;}
-	sp_eval_lite_fire( en, (uint32_t)sp_ctz( m), pos, L);
+	if (m & (m - 1)) {L.flags = (L.flags | SP_LITE_FULL) & ~SP_LITE_ALIVE; return 0;}
+	const uint32_t j = (uint32_t)sp_ctz( m);
+	return sp_eval_lite_fire( en, j, pos, L) | (j << 4);
 }
 
 SP_MHD void sp_eval_lite_result( const SpEvalEntry& en, const SpEvalLite& L, SpEvalRule& R)
@@ -630,6 +636,118 @@ SP_MHD bool sp_eval_entry_run( const SpMatcherTables& T, const SpEvalEntry& en, 
 	sp_eval_lite_result( en, L, R);
 	R.nitems += extra;
 	return true;
+}
+
+/* ---- write pass from the compiled list entry: the rule is followed once more with the taken events recorded ---- */
+#define SP_LITE_MAXTAKES 8
+typedef struct SpEvalTrace
+{
+	uint32_t flags;				/* SP_LITE_* of the ended rule */
+	uint32_t ntakes;			/* live triggers that took an event with a variable */
+	uint32_t take_rel[ SP_LITE_MAXTAKES];	/* token of the event, relative to the first token of the document */
+	uint32_t take_var[ SP_LITE_MAXTAKES];
+	uint32_t first_rel, emit_rel;		/* token of the first event taken / of the event that emitted the result */
+	uint32_t emit_end;			/* end_ordpos of the slot at the emission */
+	uint32_t nitems;			/* items of the rule's list without the items of referenced lists */
+} SpEvalTrace;
+
+/* Follows the rule of list entry `en` (variables V) installed at `site` and records what the result needs.
+ * False: not a rule the entry describes completely (the full fold does it). */
+SP_MHD bool sp_eval_lite_trace( const SpEvalEntry& en, const SpEvalVars& V, const sp_lexem* toks, uint64_t tb, uint64_t te, const SpEvalSite& site, SpEvalTrace& tr)
+{
+	if ((en.meta & SP_EVAL_META_GENERIC) || V.nkeyvar > SP_EVAL_NKEYVAR) return false;
+	SpEvalLite L;
+	const uint32_t spos = site.data.start_ordpos;
+	sp_eval_lite_init( en, spos, L);
+	const uint32_t expiry = spos + SP_EVAL_META_RANGE( en.meta);
+	const uint32_t none = 0xFFFFFFFFu;
+	tr.ntakes = 0;
+	tr.first_rel = (en.meta2 & SP_EVAL_M2_END0) ? (uint32_t)(site.tok - tb) : none;
+	tr.emit_rel = (uint32_t)(site.tok - tb); tr.emit_end = spos + 1;
+	bool overflow = false;
+	for (uint64_t k=site.tok+1; k<te && (L.flags & SP_LITE_ALIVE); ++k)
+	{
+		const uint32_t what = sp_eval_lite_step( en, expiry, SP_MLDG( &toks[ k].id), SP_MLDG( &toks[ k].ordpos), L);
+		if (what & SP_LITE_TOOK)
+		{
+			const uint32_t var = V.livevar[ (what >> 4) & 3u];
+			if (tr.first_rel == none) tr.first_rel = (uint32_t)(k - tb);
+			if (var)
+			{
+				if (tr.ntakes < SP_LITE_MAXTAKES) {tr.take_rel[ tr.ntakes] = (uint32_t)(k - tb); tr.take_var[ tr.ntakes] = var; tr.ntakes += 1;}
+				else overflow = true;
+			}
+		}
+		if (what & SP_LITE_EMITTED) {tr.emit_rel = (uint32_t)(k - tb); tr.emit_end = L.endpos;}
+	}
+	tr.flags = L.flags; tr.nitems = L.nitems;
+	return !overflow && !(L.flags & SP_LITE_FULL) && (L.flags & SP_LITE_RESULT) && tr.first_rel != none;
+}
+
+SP_MHD void sp_eval_item_record( const sp_lexem& tok, uint32_t origseg, uint32_t variable, uint32_t format, sp_item& o);
+
+/* Items of a traced rule in reading order (last appended first, src/patternMatcher.cpp:164-190): the events taken by live
+ * triggers, latest first, then the key event once per key definition that took it with a variable; a key event that is
+ * a follow event (F != 0) is followed by the items of the rule that emitted it. Returns the number of items written;
+ * `ok` = false if the emitting rule is not one its list entry describes (nothing usable written). */
+SP_MHD uint32_t sp_eval_lite_write_items( const SpMatcherTables& T, const sp_lexem* toks, const uint32_t* segs, uint64_t tb, uint64_t te,
+					  const SpEvalSite& site, const SpEvalVars& V, const SpEvalTrace& tr, const SpEvalFollow* F, sp_item* out, bool& ok)
+{
+	uint32_t n = 0;
+	ok = true;
+	for (uint32_t i=tr.ntakes; i>0; --i)
+	{
+		const uint64_t k = tb + tr.take_rel[ i-1];
+		sp_eval_item_record( toks[ k], segs ? segs[ k] : 0, tr.take_var[ i-1], 0, out[ n++]);
+	}
+	const uint32_t siteseg = segs ? segs[ site.tok] : 0;
+	for (uint32_t i=V.nkeyvar; i>0; --i)
+	{
+		sp_eval_item_record( toks[ site.tok], siteseg, V.keyvar[ i-1], F ? F->format : 0, out[ n++]);
+		if (F && F->sub && !F->format)
+		{
+			const SpEvalEntry qen = T.eval_entries[ F->qpt];
+			const SpEvalVars qv = T.eval_vars[ F->qpt];
+			SpEvalSite qsite = site;
+			qsite.cpos = 0; qsite.keyevent = SP_MLDG( &toks[ site.tok].id);
+			SpEvalLite Q;
+			if ((qen.meta & SP_EVAL_META_GENERIC) || qv.nkeyvar > SP_EVAL_NKEYVAR) {ok = false; return n;}
+			// the rule that emitted the follow event, to its end: its live takes (latest first) ...
+			const uint32_t spos = site.data.start_ordpos, expiry = spos + SP_EVAL_META_RANGE( qen.meta);
+			sp_eval_lite_init( qen, spos, Q);
+			uint32_t qrel[ SP_LITE_MAXTAKES], qvar[ SP_LITE_MAXTAKES], qn = 0;
+			for (uint64_t k=site.tok+1; k<te && (Q.flags & SP_LITE_ALIVE); ++k)
+			{
+				const uint32_t what = sp_eval_lite_step( qen, expiry, SP_MLDG( &toks[ k].id), SP_MLDG( &toks[ k].ordpos), Q);
+				const uint32_t var = (what & SP_LITE_TOOK) ? qv.livevar[ (what >> 4) & 3u] : 0;
+				if (var)
+				{
+					if (qn >= SP_LITE_MAXTAKES) {ok = false; return n;}
+					qrel[ qn] = (uint32_t)(k - tb); qvar[ qn] = var; ++qn;
+				}
+			}
+			if (Q.flags & SP_LITE_FULL) {ok = false; return n;}
+			for (uint32_t q=qn; q>0; --q)
+			{
+				const uint64_t k = tb + qrel[ q-1];
+				sp_eval_item_record( toks[ k], segs ? segs[ k] : 0, qvar[ q-1], 0, out[ n++]);
+			}
+			// ... and its key event
+			for (uint32_t q=qv.nkeyvar; q>0; --q) sp_eval_item_record( toks[ site.tok], siteseg, qv.keyvar[ q-1], 0, out[ n++]);
+		}
+	}
+	return n;
+}
+
+SP_MHD void sp_eval_lite_result_record( const SpProgram& P, const sp_lexem* toks, const uint32_t* segs, uint64_t tb, const SpEvalTrace& tr, uint32_t item_begin, uint32_t item_count, sp_result& o)
+{
+	const uint64_t kf = tb + tr.first_rel, ke = tb + tr.emit_rel;
+	const sp_lexem first = toks[ kf], last = toks[ ke];
+	o.name = P.resultHandle; o.format = P.formatHandle;
+	o.ordpos = first.ordpos; o.ordend = tr.emit_end;
+	o.origseg = segs ? segs[ kf] : 0; o.origpos = first.origpos;
+	o.endseg = segs ? segs[ ke] : 0; o.endpos = last.origpos + last.origsize;
+	o.item_begin = item_begin; o.item_count = item_count;
 }
 
 SP_MHD void sp_eval_item_record( const sp_lexem& tok, uint32_t origseg, uint32_t variable, uint32_t format, sp_item& o)

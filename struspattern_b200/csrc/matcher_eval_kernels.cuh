@@ -27,7 +27,7 @@
 
 namespace sp {
 
-enum {EvalWarpsPerBlock = 4, EvalThreads = EvalWarpsPerBlock * 32, EvalRun = 256, EvalLook = 64, EvalPerLane = EvalRun / 32, EvalSteps = 4};
+enum {EvalWarpsPerBlock = 4, EvalThreads = EvalWarpsPerBlock * 32, EvalRun = 256, EvalLook = 64, EvalPerLane = EvalRun / 32, EvalSteps = 4, EvalRefill = 8};
 
 #define SP_EVALQ_STATS_DONE (1ull << 63)	/* queued item whose counters are already added: only result, items and bit are missing */
 
@@ -153,14 +153,12 @@ static __global__ void __launch_bounds__(EvalThreads) k_eval_count( EvalParams P
 {
 	__shared__ uint2 s_tok[ EvalWarpsPerBlock][ EvalRun + EvalLook];		// id, ordinal position
 	__shared__ uint32_t s_work[ EvalWarpsPerBlock][ EvalRun + 1];			// first work item of a token, relative to the run
-	__shared__ uint32_t s_slot[ EvalWarpsPerBlock][ EvalRun];
-	__shared__ uint32_t s_te[ EvalWarpsPerBlock][ EvalRun];				// end of the token's document, relative to the run
-	__shared__ uint32_t s_doc[ EvalWarpsPerBlock][ EvalRun];
+	__shared__ uint16_t s_doc[ EvalWarpsPerBlock][ EvalRun];			// document of a token, relative to the first document of the run
 	__shared__ uint32_t s_nres[ EvalWarpsPerBlock][ EvalRun];
 	__shared__ uint32_t s_nitems[ EvalWarpsPerBlock][ EvalRun];
 	const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-	uint2* stok = s_tok[ warp]; uint32_t* swork = s_work[ warp]; uint32_t* sslot = s_slot[ warp];
-	uint32_t* ste = s_te[ warp]; uint32_t* sdoc = s_doc[ warp]; uint32_t* snres = s_nres[ warp]; uint32_t* snitems = s_nitems[ warp];
+	uint2* stok = s_tok[ warp]; uint32_t* swork = s_work[ warp];
+	uint16_t* sdoc = s_doc[ warp]; uint32_t* snres = s_nres[ warp]; uint32_t* snitems = s_nitems[ warp];
 
 	const uint64_t run = (uint64_t)blockIdx.x * EvalWarpsPerBlock + warp;
 	const uint64_t r0 = run * EvalRun;
@@ -183,10 +181,7 @@ static __global__ void __launch_bounds__(EvalThreads) k_eval_count( EvalParams P
 			{
 				const uint64_t i = r0 + j;
 				while (__ldg( &P.tok_off[ d+1]) <= i) ++d;
-				const uint64_t te = __ldg( &P.tok_off[ d+1]);
-				sdoc[ j] = d;
-				ste[ j] = (uint32_t)min( te - r0, (uint64_t)0xFFFFFFFFu);
-				sslot[ j] = P.tok_slot[ i];
+				sdoc[ j] = (uint16_t)min( d - dbase, 0xFFFFu);
 				w = P.tok_work[ i];
 			}
 			snres[ j] = 0; snitems[ j] = 0;
@@ -225,17 +220,18 @@ static __global__ void __launch_bounds__(EvalThreads) k_eval_count( EvalParams P
 	const uint32_t B = (W + 31) / 32;
 	uint32_t w = min( lane * B, W);
 	const uint32_t wend = min( w + B, W);
-	uint32_t t = 0;				// token of the run the cursor is in
+	uint32_t t = 0, tslot = SP_EVAL_NOSLOT;	// token of the run the cursor is in, its event slot
 	EvalCursor cur; cur.c = cur.k = cur.lbegin = cur.lcount = cur.fb = cur.fc = 0;
 	if (w < wend)
 	{
 		uint32_t lo = 0, hi = EvalRun;		// last token with swork[t] <= w
 		while (hi - lo > 1) {uint32_t mid = (lo + hi) / 2; if (swork[ mid] <= w) lo = mid; else hi = mid;}
 		t = lo;
-		evalCursorSeek( P.T, sslot[ t], w - swork[ t], cur);
+		tslot = P.tok_slot[ r0 + t];
+		evalCursorSeek( P.T, tslot, w - swork[ t], cur);
 	}
 	// counters of the document the lane is in
-	uint32_t accdoc = (w < wend) ? sdoc[ t] : 0xFFFFFFFFu, acc_installed = 0;
+	uint32_t accdoc = (w < wend) ? dbase + sdoc[ t] : 0xFFFFFFFFu, acc_installed = 0;
 	uint64_t acc_signals = 0, acc_open = 0;
 	// the rule the lane follows
 	bool have = false;
@@ -259,10 +255,11 @@ static __global__ void __launch_bounds__(EvalThreads) k_eval_count( EvalParams P
 				{
 					++t;
 					while (swork[ t+1] == swork[ t]) ++t;		// w < wend: there is a token with work
+					tslot = P.tok_slot[ r0 + t];
 					cur.c = 0;
-					cur.fb = __ldg( &P.T.eval_slots[ sslot[ t]].follow_begin); cur.fc = __ldg( &P.T.eval_slots[ sslot[ t]].follow_count);
+					cur.fb = __ldg( &P.T.eval_slots[ tslot].follow_begin); cur.fc = __ldg( &P.T.eval_slots[ tslot].follow_count);
 				}
-				if (evalSiteList( P.T, sslot[ t], cur)) break;
+				if (evalSiteList( P.T, tslot, cur)) break;
 			}
 		}
 	};
@@ -275,7 +272,7 @@ static __global__ void __launch_bounds__(EvalThreads) k_eval_count( EvalParams P
 		{
 			uint32_t extra = 0;
 			if ((en.meta & SP_EVAL_META_ITEMSFULL)
-			    && !sp_eval_lite_follow_items( P.T, P.tokens, r0 + t, r0 + ste[ t], en, P.T.eval_follows[ cur.fb + cur.c - 1], extra))
+			    && !sp_eval_lite_follow_items( P.T, P.tokens, r0 + t, __ldg( &P.tok_off[ accdoc + 1]), en, P.T.eval_follows[ cur.fb + cur.c - 1], extra))
 			{
 				evalQueuePush( P, (wbase + w) | SP_EVALQ_STATS_DONE);
 			}
@@ -290,7 +287,10 @@ static __global__ void __launch_bounds__(EvalThreads) k_eval_count( EvalParams P
 	};
 	while (__any_sync( SP_FULL, have || w < wend))
 	{
-		if (!(L.flags & SP_LITE_ALIVE))
+		// rules are replaced when enough lanes wait for one (the replacement code runs for the waiting lanes only)
+		const unsigned int waiting = __ballot_sync( SP_FULL, !(L.flags & SP_LITE_ALIVE) && (have || w < wend));
+		const unsigned int running = __ballot_sync( SP_FULL, (L.flags & SP_LITE_ALIVE) != 0);
+		if (!(L.flags & SP_LITE_ALIVE) && (__popc( waiting) >= EvalRefill || !running))
 		{
 			if (have) {account(); have = false; advance();}
 			while (w < wend)
@@ -299,7 +299,7 @@ static __global__ void __launch_bounds__(EvalThreads) k_eval_count( EvalParams P
 				const uint4* ep = reinterpret_cast<const uint4*>( P.T.eval_entries + cur.lbegin + cur.k);
 				const uint4 a = __ldg( ep), b = __ldg( ep + 1);
 				en.ev[0] = a.x; en.ev[1] = a.y; en.ev[2] = a.z; en.ev[3] = a.w; en.codes = b.x; en.value0 = b.y; en.meta = b.z; en.meta2 = b.w;
-				const uint32_t d = sdoc[ t];
+				const uint32_t d = dbase + sdoc[ t];
 				if (d != accdoc)
 				{
 					evalAddStats( P.stats + accdoc, acc_installed, 0, acc_signals, acc_open);
@@ -310,7 +310,7 @@ static __global__ void __launch_bounds__(EvalThreads) k_eval_count( EvalParams P
 				sp_eval_lite_init( en, spos, L);
 				if (!(L.flags & SP_LITE_ALIVE)) {account(); advance(); continue;}	// ended by its installation
 				expiry = spos + SP_EVAL_META_RANGE( en.meta);
-				wpos = t + 1; wte = ste[ t];
+				wpos = t + 1; wte = (uint32_t)min( __ldg( &P.tok_off[ d + 1]) - r0, (uint64_t)0xFFFFFFFFu);
 				have = true;
 				break;
 			}
@@ -438,9 +438,12 @@ static __global__ void __launch_bounds__(EvalThreads) k_eval_write( EvalParams P
 			const bool valid = j < total;
 			SpEvalRule R; sp_eval_rule_init( R);
 			SpEvalTake takes[ SP_EVAL_MAX_TAKES];
+			SpEvalTrace tr; tr.flags = 0; tr.ntakes = 0; tr.nitems = 0; tr.first_rel = tr.emit_rel = tr.emit_end = 0;
+			SpEvalSite site;
 			uint64_t tok = ~0ull - 1 - lane, tb = 0, te = 0;
-			uint32_t d = 0, program = 0;
-			bool live = false;
+			uint32_t d = 0, ptidx = 0, nit = 0;
+			bool live = false, lite = false;
+			const SpEvalFollow* F = 0;
 			if (valid)
 			{
 				uint32_t lo = 0, hi = 32;	// word that holds result j: last word with spre <= j
@@ -458,15 +461,27 @@ static __global__ void __launch_bounds__(EvalThreads) k_eval_write( EvalParams P
 				live = !P.flags[ d];	// the results of flagged documents come from the state machine
 				if (live)
 				{
-					SpEvalSite site;
 					evalItemSite( P, tok, slotidx, cur, site);
-					const SpProgramTrigger pt = P.T.program_triggers[ cur.lbegin + cur.k];
-					program = pt.program;
-					sp_eval_fold<true,0>( P.T, P.tokens, P.origsegs, tb, te, site, pt, false, R, takes);
+					ptidx = cur.lbegin + cur.k;
+					if (cur.c) F = P.T.eval_follows + cur.fb + cur.c - 1;
 				}
 			}
+			// the rule once more, with the taken events recorded: from its compiled list entry (all lanes run the same short
+			// loop) or, where the entry is not enough, by the full fold
+			if (live)
+			{
+				const SpEvalEntry en = P.T.eval_entries[ ptidx];
+				lite = sp_eval_lite_trace( en, P.T.eval_vars[ ptidx], P.tokens, tb, te, site, tr);
+				uint32_t extra = 0;
+				if (lite && F && !sp_eval_lite_follow_items( P.T, P.tokens, tok, te, en, *F, extra)) lite = false;
+				if (lite) nit = (tr.flags & SP_LITE_DREFEMIT) ? tr.nitems + extra : 0;
+			}
+			if (live && !lite)
+			{
+				sp_eval_fold<true,0>( P.T, P.tokens, P.origsegs, tb, te, site, P.T.program_triggers[ ptidx], false, R, takes);
+				nit = sp_eval_result_items( R);
+			}
 			// items of the earlier results of the same token (the results of a token are neighbours)
-			const uint32_t nit = live ? sp_eval_result_items( R) : 0;
 			uint32_t seg = nit;
 			#pragma unroll
 			for (int ofs=1; ofs<32; ofs<<=1)
@@ -476,12 +491,24 @@ static __global__ void __launch_bounds__(EvalThreads) k_eval_write( EvalParams P
 				if (lane >= (unsigned int)ofs && uptok == tok) seg += up;
 			}
 			const uint32_t before = seg - nit + (tok == carry_tok ? carry_items : 0u);
-			if (live && R.has_result)
+			if (live && (lite || R.has_result))
 			{
 				const uint64_t res_in_doc = (res0 + res_done + j) - __ldg( &P.tok_res_off[ tb]);
 				const uint64_t item_in_doc = (__ldg( &P.tok_item_off[ tok]) - __ldg( &P.tok_item_off[ tb])) + before;
-				if (nit) sp_eval_write_items( P.T, P.tokens, P.origsegs, tb, te, takes, R.ntakes, P.items + __ldg( &P.doc_item_off[ d]) + item_in_doc);
-				sp_eval_result_record( P.T.programs[ program], R, (uint32_t)item_in_doc, nit, P.results[ __ldg( &P.doc_res_off[ d]) + res_in_doc]);
+				sp_item* iout = P.items + __ldg( &P.doc_item_off[ d]) + item_in_doc;
+				sp_result& rout = P.results[ __ldg( &P.doc_res_off[ d]) + res_in_doc];
+				const SpProgram prog = P.T.programs[ P.T.program_triggers[ ptidx].program];
+				if (lite)
+				{
+					bool ok = true;
+					if (nit) sp_eval_lite_write_items( P.T, P.tokens, P.origsegs, tb, te, site, P.T.eval_vars[ ptidx], tr, F, iout, ok);
+					sp_eval_lite_result_record( prog, P.tokens, P.origsegs, tb, tr, (uint32_t)item_in_doc, nit, rout);
+				}
+				else
+				{
+					if (nit) sp_eval_write_items( P.T, P.tokens, P.origsegs, tb, te, takes, R.ntakes, iout);
+					sp_eval_result_record( prog, R, (uint32_t)item_in_doc, nit, rout);
+				}
 			}
 			const int last = (int)min( total - j0, 32u) - 1;
 			const uint64_t ltok = __shfl_sync( SP_FULL, tok, last);

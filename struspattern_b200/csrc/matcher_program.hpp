@@ -65,6 +65,7 @@ struct MatcherTablesHost
 	std::vector<SpEvalFollow> eval_follows;
 	std::vector<uint32_t> prog_flags;
 	std::vector<SpEvalEntry> eval_entries;
+	std::vector<SpEvalVars> eval_vars;
 	SpMatcherTables view;			// pointers are filled by the owner (host or device addresses)
 };
 
@@ -408,12 +409,17 @@ private:
 		// list entries: live trigger events and the outcome of the installation signals
 		SpEvalEntry noentry; std::memset( &noentry, 0, sizeof(noentry)); noentry.meta = SP_EVAL_META_GENERIC;
 		T.eval_entries.assign( T.program_triggers.size(), noentry);
+		SpEvalVars novars; std::memset( &novars, 0, sizeof(novars));
+		T.eval_vars.assign( T.program_triggers.size(), novars);
 		for (const SpEventSlot& slot: T.event_slots)
 		{
 			if (!slot.key) continue;
-			for (uint32_t k=0; k<slot.prog_count; ++k) T.eval_entries[ slot.prog_begin + k] = evalEntry( T, T.program_triggers[ slot.prog_begin + k], slot.key - 1);
+			for (uint32_t k=0; k<slot.prog_count; ++k)
+			{
+				T.eval_entries[ slot.prog_begin + k] = evalEntry( T, T.program_triggers[ slot.prog_begin + k], slot.key - 1, T.eval_vars[ slot.prog_begin + k]);
+			}
 		}
-		T.view.eval_entries = T.eval_entries.data();
+		T.view.eval_entries = T.eval_entries.data(); T.view.eval_vars = T.eval_vars.data();
 		T.view.eval_slots = T.eval_slots.data(); T.view.eval_follows = T.eval_follows.data(); T.view.prog_flags = T.prog_flags.data();
 		T.view.nfollows = (uint32_t)T.eval_follows.size();
 		T.view.eval_capable = capable ? 1 : 0;
@@ -423,8 +429,9 @@ private:
 	// definitions become live triggers (installProgram, src/ruleMatcherAutomaton.cpp:1204-1250) and what the direct signals
 	// of the key definitions (:1259-1269, fireSignal :772-979 on a fresh slot) leave behind. With end_ordpos in {0, S+1}
 	// the position tests of fireSignal do not depend on S. `termKey`: the key event is a term event (no sub data).
-	static SpEvalEntry evalEntry( const MatcherTablesHost& T, const SpProgramTrigger& pt, uint32_t keyevent)
+	static SpEvalEntry evalEntry( const MatcherTablesHost& T, const SpProgramTrigger& pt, uint32_t keyevent, SpEvalVars& vars)
 	{
+		std::memset( &vars, 0, sizeof(vars));
 		SpEvalEntry en; std::memset( &en, 0, sizeof(en));
 		for (int e=0; e<SP_EVAL_NEV; ++e) en.ev[ e] = 0xFFFFFFFFu;
 		const SpProgram& P = T.programs[ pt.program];
@@ -462,6 +469,7 @@ private:
 			en.ev[ nev] = def.event;
 			en.codes |= (((uint32_t)def.sigtype << 5) | sig) << (8 * nev);
 			if (def.variable) varmask |= 1u << nev;
+			vars.livevar[ nev] = def.variable;
 			++nev;
 		}
 		bool endSet = false, done = false, disposed = false, result = false, dataref = false, drefEmit = false;
@@ -496,7 +504,12 @@ private:
 				case SP_SIG_DEL: count = 0; value = 0; disposed = true; continue;
 				default: generic = true; break;
 			}
-			if (take && def.variable) {dataref = true; ++nitems;}
+			if (take && def.variable)
+			{
+				dataref = true; ++nitems;
+				if (vars.nkeyvar < SP_EVAL_NKEYVAR) vars.keyvar[ vars.nkeyvar] = def.variable;
+				++vars.nkeyvar;
+			}
 			// a follow event taken without a variable joins the items of its rule (:911-918): left to the full fold
 			if (take && !def.variable && (keyevent >> 29) != TermEvent) generic = true;
 			if (match)

@@ -107,6 +107,16 @@ typedef struct alignas(16) SpEvalEntry
 #define SP_EVAL_M2_RESULT0      (1u << 30)	/* result emitted at the installation */
 #define SP_EVAL_M2_DREFEMIT0    (1u << 31)	/* ... and the rule had its item list then */
 
+/* Variables of a compiled list entry (parallel to eval_entries; read by the write pass only): of the key definitions that
+ * take the key event with a variable (in firing order) and of the live triggers (same order as SpEvalEntry::ev). 32 bytes. */
+#define SP_EVAL_NKEYVAR 3
+typedef struct alignas(16) SpEvalVars
+{
+	uint32_t keyvar[ SP_EVAL_NKEYVAR];
+	uint32_t nkeyvar;		/* number of key takes with a variable; > SP_EVAL_NKEYVAR: not tabulated (full fold) */
+	uint32_t livevar[ SP_EVAL_NEV];
+} SpEvalVars;
+
 #define SP_PROGFLAG_LISTENS_FOLLOW 1u	/* some trigger definition waits for an event that is not a term event */
 
 typedef struct SpMatcherTables
@@ -128,6 +138,7 @@ typedef struct SpMatcherTables
 	const SpEvalFollow* eval_follows;
 	const uint32_t* prog_flags;	/* [nprograms] SP_PROGFLAG_* */
 	const SpEvalEntry* eval_entries;	/* [nprogram_triggers] */
+	const SpEvalVars* eval_vars;	/* [nprogram_triggers] */
 	uint32_t nfollows;
 	uint32_t eval_capable;		/* 1: the rule set is inside what the window evaluator reproduces exactly (matcher_program.hpp: evalCapable) */
 } SpMatcherTables;

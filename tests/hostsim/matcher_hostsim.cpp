@@ -37,6 +37,8 @@ struct MatcherSim
 };
 }
 
+static uint64_t g_lite_written = 0, g_results_written = 0;
+
 // One document through the window evaluator (matcher_eval.cuh), sites in the order of the CUDA kernels: token by token,
 // the token event first, then its static follow events, every program list in list order. Returns false if the
 // document has to run on the state machine.
@@ -110,6 +112,34 @@ static bool evalDocument( const SpMatcherTables& T, const sp_lexem* tokens, cons
 				sp_result rec;
 				sp_eval_result_record( T.programs[ pt.program], R, (uint32_t)(ib - item_base), want, rec);
 				results.push_back( rec);
+				// the write pass from the compiled list entry must produce the same record and items
+				{
+					const SpEvalEntry& en = T.eval_entries[ es.prog_begin + k];
+					const SpEvalVars& V = T.eval_vars[ es.prog_begin + k];
+					SpEvalTrace tr;
+					if (sp_eval_lite_trace( en, V, tokens, tb, te, site, tr))
+					{
+						const SpEvalFollow* F = site.cpos ? &T.eval_follows[ site.follow_begin + site.cpos - 1] : 0;
+						uint32_t extra = 0;
+						bool ok = !F || sp_eval_lite_follow_items( T, tokens, site.tok, te, en, *F, extra);
+						const uint32_t lwant = (tr.flags & SP_LITE_DREFEMIT) ? tr.nitems + extra : 0;
+						std::vector<sp_item> litems( lwant + 64);
+						uint32_t lgot = 0;
+						if (ok && lwant) lgot = sp_eval_lite_write_items( T, tokens, segs, tb, te, site, V, tr, F, litems.data(), ok);
+						if (ok)
+						{
+							sp_result lrec;
+							sp_eval_lite_result_record( T.programs[ pt.program], tokens, segs, tb, tr, (uint32_t)(ib - item_base), lwant, lrec);
+							if (lwant != want || lgot != lwant || std::memcmp( &lrec, &rec, sizeof(rec)) != 0
+							    || (want && std::memcmp( litems.data(), items.data() + ib, want * sizeof(sp_item)) != 0))
+							{
+								throw std::runtime_error( "write pass from the list entry differs from the full fold");
+							}
+							++g_lite_written;
+						}
+					}
+					++g_results_written;
+				}
 			}
 		}
 	}
@@ -241,6 +271,8 @@ int64_t msim_info( void* h, const char* key)
 		if (k == "eval_follows") return H.view.nfollows;
 		if (k == "eval_docs") return (int64_t)ms->eval_docs;
 		if (k == "eval_flagged") return (int64_t)ms->eval_flagged;
+		if (k == "lite_written") return (int64_t)g_lite_written;
+		if (k == "results_written") return (int64_t)g_results_written;
 	}
 	catch (...) {}
 	return -1;
