@@ -1,31 +1,40 @@
 #!/usr/bin/env python3
-"""Benchmark of the strusPattern hot path on B200 (BASELINE.json metric: GB/s of UTF-8 text lexed).
+"""Benchmark of the strusPattern hot path on B200 (BASELINE.json metric: GB/s of UTF-8 text lexed+matched).
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--bytes B]
 
-A step = one pass of the lexer over one batch of synthetic text (workload C2 of SURVEY.md 8d: ~100 lexem
-regexes over 1 GiB of UTF-8 text in documents of 4-64 KiB), per GPU (weak scaling: every rank owns its own
-shard generated from (seed, rank)). `value` is measured with the text resident in HBM, `e2e` through the
-C ABI with pinned host buffers (H2D of the text and D2H of the lexems inside the timed region).
---impl reference times the reference's CPU path of level 1; Hyperscan is not available here, so this is the
-CPU restatement (oracle/lexer_oracle.cpp, kind "port") on all host cores over a bounded sample.
-Prints ONE JSON line on rank 0."""
+A step = one pass of the two-level hot path over one batch of synthetic text per GPU: workload C3 of SURVEY.md 8d
+(186 lexem definitions + 5000 symbols, 10 000 token patterns: sequence_imm / within / *_struct / any nested in sequence)
+over B bytes (default 256 MiB) of the multilingual synthetic corpus in documents of 4-64 KiB. Level 1 (sp_lexer_scan)
+-> level 2 on the lexems still in HBM (sp_matcher_run_lexer_output) -> result and item counts. Weak scaling: every
+rank owns its own shard generated from (seed, rank); there is no collective on the data path.
+`value` is measured with the text resident in HBM (CUDA events), `e2e` through the C ABI with pinned host buffers: H2D
+of the text and D2H of results, items, offsets, statistics and status inside the timed region.
+After the timed region a sample of the timed output is compared with the CPU oracle (level-1 restatement + the
+reference's own automaton): lexems element by element, results with their items as multisets per document, the cascade
+counters exactly. A mismatch fails the run; the number of compared results is in the line (`parity_checked`).
+--impl reference times the CPU path (level-1 oracle + oracle/_ref/libsp_ref_matcher.so, all host threads) on a bounded
+sample of the same workload. Prints ONE JSON line on rank 0."""
 import argparse
 import json
 import os
 import subprocess
 import sys
 import tempfile
+import threading
 import time
 
 import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 METRIC = "GB/s UTF-8 text lexed+matched at 1/2/4/8 B200 vs same-box hyperscan CPU path"
-SEED = 0x5354525553000002
-FIXED_WORDS = None
+SEED = 0x5354525553000003
+NPATTERNS, NSYMBOLS, NPHRASES, PATTERN_SEED = 10000, 5000, 140, 33
+# DRAM traffic of the dominant kernel (dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full launch), per token
+NCU_TRAFFIC = {"k_eval_count": {"bytes_per_token": (360.648192e6 + 131.5456e6) / 11341930, "source": "profiles/r02_eval_v3_ncu_raw.csv (32 MiB of this corpus)"}}
 
 
 def fixed_words():
@@ -33,11 +42,15 @@ def fixed_words():
     return W.PHRASE_FIRST + W.PHRASE_SECOND + W.ABBREVIATIONS + ["the", "of", "and", "to", "in", "a", "is", "that", "for", "it"]
 
 
-def make_corpus(nbytes, rank, pinned):
+def vocabulary():
+    from bench_util import corpus
+    return corpus.vocabulary(SEED, 50000, fixed_words())
+
+
+def make_corpus(nbytes, rank, pinned, vocab):
     """-> (host uint8 array, offsets, keepalive)"""
     from bench_util import corpus
-    vocab = corpus.vocabulary(SEED, 50000, fixed_words())
-    offs = corpus.layout(SEED + 1000 * rank, nbytes)
+    offs = corpus.layout(SEED + 1 + 1000 * rank, nbytes)
     keep = None
     if pinned:
         import torch
@@ -45,8 +58,17 @@ def make_corpus(nbytes, rank, pinned):
         text = keep.numpy()[:nbytes]
     else:
         text = np.zeros(int(nbytes), dtype=np.uint8)
-    corpus.fill(SEED + 1000 * rank, vocab, text, offs)
+    corpus.fill(SEED + 1 + 1000 * rank, vocab, text, offs)
     return text, offs, keep
+
+
+def define_workload(lexer_cls, matcher_cls, vocab):
+    from struspattern_b200 import workloads as W
+    lx = W.define_lexer(lexer_cls(), nphrases=NPHRASES, symbols=W.symbol_table(vocab, NSYMBOLS))
+    mt = matcher_cls()
+    W.define_c3_patterns(mt, PATTERN_SEED, NPATTERNS, NSYMBOLS)
+    mt.compile()
+    return lx, mt
 
 
 class ClockSampler:
@@ -92,112 +114,6 @@ class ClockSampler:
         return out
 
 
-def measured_peak():
-    try:
-        d = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        return float(d["hbm_gbs"]), "measured"
-    except Exception:
-        return 6650.0, "fallback"
-
-
-def cpu_lexer_rate(text, offs, seconds_target, nthreads):
-    """Oracle (CPU restatement of level 1) on a bounded prefix of the corpus -> (GB/s, sample bytes, seconds)."""
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    from oracle_util import OracleLexer
-    from struspattern_b200 import workloads as W
-    o = W.define_lexer(OracleLexer())
-    # probe on ~1 MiB, then size the sample for the target duration
-    nd = int(np.searchsorted(offs, 1 << 20, side="right"))
-    nd = max(1, min(nd, len(offs) - 1))
-    t = time.perf_counter()
-    o.scan(text[:int(offs[nd])], offs[:nd + 1], nthreads=nthreads)
-    dt = time.perf_counter() - t
-    rate = float(offs[nd]) / max(dt, 1e-9)
-    want = rate * seconds_target
-    nd2 = int(np.searchsorted(offs, want, side="right"))
-    nd2 = max(nd, min(nd2, len(offs) - 1))
-    t = time.perf_counter()
-    o.scan(text[:int(offs[nd2])], offs[:nd2 + 1], nthreads=nthreads)
-    dt = time.perf_counter() - t
-    return float(offs[nd2]) / dt / 1e9, int(offs[nd2]), dt
-
-
-KERNELS = ["k_lex_count", "k_lex_verify", "k_lex_emit", "k_lex_finish", "k_lex_resolve", "k_lex_write", "k_scan",
-           "k_isl_flags", "k_isl_resolve", "k_ordpos", "k_isl_slots", "k_slot_scan", "k_lex_fused", "k_fused_scan", "k_fused_write", "k_lex_resolve_chunks"]
-
-
-def algorithmic_bytes(kernel, c):
-    """Bytes one launch of `kernel` has to move by the algorithm (DESIGN.md 'kernels'), c = batch counters."""
-    n_text, nev, nlex, ndocs, nchunks = c["text_bytes"], c["raw_events"], c["lexems"], c["ndocs"], c["chunks"]
-    return {
-        "k_lex_count": n_text + 12 * nchunks,                 # text read once, start/end state + count per chunk
-        "k_lex_verify": 9 * nchunks,
-        "k_lex_emit": n_text + 16 * nev + 16 * nchunks,       # text read once, one 16 B event record per raw event
-        "k_lex_finish": 36 * nev,                             # event record read + written, document word written (text re-reads hit L2)
-        "k_lex_resolve": 16 * nev + 16 * nlex + 16 * ndocs,   # events read, kept match events written
-        "k_lex_write": 32 * nlex + 24 * ndocs,                # kept match events read, 16 B lexem records written
-        "k_scan": 12 * (nchunks + ndocs),
-        # island pipeline (per step totals of the kernel group; divided by its launches by the caller)
-        "k_isl_flags": 20 * nev + nev + 4 * c.get("islands", 0),       # events + document ids read, flags + island starts written
-        "k_isl_resolve": 2 * 20 * nev + 20 * c.get("elements", 0),    # events read by both passes, dense elements written
-        "k_ordpos": 20 * c.get("elements", 0) + 16 * nlex,           # dense elements read once, lexem records written
-        # slot pipeline (default): events + document ids read once, one 16 B slot per event written; slots read once, lexems written
-        "k_isl_slots": 20 * nev + 16 * nev * c.get("ar_mult", 1),
-        "k_slot_scan": 16 * nev * c.get("ar_mult", 1) + 16 * nlex + 16 * ndocs,
-        # fused segment pipeline (default): text read once, one 16 B record per kept element (>= lexems) written, per chunk
-        # start state + event offset read and 30 B of counters written; then kept elements read once, 16 B lexem records written
-        "k_lex_fused": n_text + 16 * nlex + 42 * nchunks,
-        "k_fused_scan": 40 * nchunks + 28 * ndocs,
-        "k_fused_write": 32 * nlex + 20 * nchunks,
-        # chunk resolution over completed events (default): event + document id + segment flag read, kept elements written
-        "k_lex_resolve_chunks": 20 * nev + 16 * nlex + 42 * nchunks,
-    }[kernel]
-
-
-# DRAM traffic (dram__bytes_read.sum + dram__bytes_write.sum) of one launch from the ncu --set full capture summarised in
-# profiles/r01_lexer_v10_ncu.txt (256 MiB of the same corpus), as bytes per unit the launch processes; scaled to this run's units
-NCU_TRAFFIC = {
-    "k_lex_count": (0.323008e9 + 0.010925e9, "text_bytes", 268435456),
-    "k_lex_emit": (0.539853e9 + 1.577043e9, "raw_events", 89434349),
-    "k_lex_finish": (1.699961e9 + 1.731728e9, "raw_events", 89434349),
-    "k_lex_resolve_chunks": (2.123800e9 + 1.211899e9, "raw_events", 89434349),
-    "k_fused_write": (1.182111e9 + 1.070465e9, "lexems", 69551577),
-}
-
-
-def ncu_traffic(kernel, c):
-    if kernel not in NCU_TRAFFIC:
-        return None
-    nbytes, unit, units = NCU_TRAFFIC[kernel]
-    return nbytes * c[unit] / units
-
-
-def run_reference(args, rank, world):
-    if rank != 0:
-        return None
-    nthreads = os.cpu_count() or 1
-    text, offs, _ = make_corpus(min(args.bytes, 256 << 20), 0, pinned=False)
-    per_step = max(2.0, 60.0 / max(1, args.steps + args.warmup))
-    rates = []
-    sample = 0
-    for i in range(args.warmup + args.steps):
-        r, sample, dt = cpu_lexer_rate(text, offs, per_step, nthreads)
-        if i >= args.warmup:
-            rates.append((r, dt))
-    total_t = sum(dt for _, dt in rates)
-    value = sample * len(rates) / total_t / 1e9
-    return {
-        "impl": "reference", "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1000.0 * total_t / len(rates), "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "C2 lexer only: %d lexem definitions, CPU sample of the 1 GiB corpus" % args.ndefs,
-                   "sample_bytes": sample},
-        "cpu_baseline": {"value": value, "unit": "GB/s", "cores": nthreads, "kind": "port",
-                         "sample": "first %d bytes of the C2 corpus per step; level-1 CPU restatement (Hyperscan/libtre not installable here)" % sample},
-        "e2e": {"value": value, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }
-
-
 def bind_to_gpu_numa_node(local_rank):
     """Run this rank's host threads (and with them its pinned buffers: pages are placed where they are first touched) on the
     CPU socket its GPU hangs on; without it the copies of half of the ranks cross the socket link. -> what was done"""
@@ -220,77 +136,168 @@ def bind_to_gpu_numa_node(local_rank):
         return {"bound": False, "why": str(exc)[:80]}
 
 
+def measured_peak():
+    try:
+        d = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(d["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class CpuPipeline:
+    """The CPU arm: level-1 oracle (CPU restatement; Hyperscan/libtre cannot be installed here) + the reference's own
+    automaton compiled from its sources (oracle/_ref/libsp_ref_matcher.so), both on all host threads."""
+
+    def __init__(self, vocab):
+        from oracle_util import OracleLexer, RefMatcher
+        self.lx, self.mt = define_workload(OracleLexer, RefMatcher, vocab)
+        self.nthreads = os.cpu_count() or 1
+
+    def run(self, text, offs, nd, with_results):
+        t0 = time.perf_counter()
+        ro = self.lx.scan(text[:int(offs[nd])], offs[:nd + 1], nthreads=self.nthreads)
+        t1 = time.perf_counter()
+        rm = self.mt.run(ro["lexems"], ro["offsets"], nthreads=self.nthreads, with_results=with_results)
+        t2 = time.perf_counter()
+        return ro, rm, t1 - t0, t2 - t1
+
+    def sample_docs(self, text, offs, seconds):
+        """number of leading documents that take about `seconds` (probe on ~1 MiB first)"""
+        nd = max(1, min(int(np.searchsorted(offs, 1 << 20, side="right")) - 1, len(offs) - 1))
+        _, _, tl, tm = self.run(text, offs, nd, False)
+        want = float(offs[nd]) / max(tl + tm, 1e-9) * seconds
+        return max(nd, min(int(np.searchsorted(offs, want, side="right")) - 1, len(offs) - 1))
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return None
+    vocab = vocabulary()
+    cpu = CpuPipeline(vocab)
+    text, offs, _ = make_corpus(min(args.bytes, 64 << 20), 0, False, vocab)
+    per_step = max(2.0, 90.0 / max(1, args.steps + args.warmup))
+    nd = cpu.sample_docs(text, offs, per_step)
+    times, ntok = [], 0
+    for i in range(args.warmup + args.steps):
+        ro, rm, tl, tm = cpu.run(text, offs, nd, False)
+        ntok = len(ro["lexems"])
+        if i >= args.warmup:
+            times.append((tl, tm))
+    total = sum(a + b for a, b in times)
+    sample = int(offs[nd])
+    value = sample * len(times) / total / 1e9
+    return {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1000.0 * total / len(times), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "C3 lexer+matcher: %d lexem definitions + %d symbols, %d token patterns; CPU sample of the corpus" % (
+            cpu.lx.table_info("definitions") if hasattr(cpu.lx, "table_info") else 186, NSYMBOLS, NPATTERNS), "sample_bytes": sample},
+        "cpu_baseline": {"value": value, "unit": "GB/s", "cores": cpu.nthreads, "kind": "port+reference",
+                         "sample": "first %d bytes (%d documents, %d tokens) of the C3 corpus per step: level-1 CPU restatement %.2f s + the reference's automaton %.2f s "
+                                   "(Hyperscan/libtre are not installable here)" % (sample, nd, ntok, times[-1][0], times[-1][1]),
+                         "matcher_mtokens_per_s": ntok / times[-1][1] / 1e6},
+        "e2e": {"value": value, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+
+
+def parity_check(cpu, text, offs, nd, lexer_out, matcher_out, gpu_matcher):
+    """GPU output of the first nd documents against the CPU oracle -> number of results compared (raises on a mismatch)."""
+    import matcher_cases as MC
+    ro, rm, tl, tm = cpu.run(text, offs, nd, True)
+    assert (ro["offsets"] == lexer_out["offsets"]).all() and (ro["lexems"] == lexer_out["lexems"]).all(), "lexer output differs from the oracle"
+    n = MC.compare_outputs_fast(cpu.mt, rm, gpu_matcher, matcher_out)
+    return n, len(ro["lexems"]), tl, tm
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
-    from struspattern_b200 import LEXEM_DT, Lexer
-    from struspattern_b200 import workloads as W
+    from struspattern_b200 import ITEM_DT, RESULT_DT, STATS_DT, Lexer, Matcher
 
     torch.cuda.set_device(local_rank)
     numa = bind_to_gpu_numa_node(local_rank) if world > 1 else {"bound": False, "why": "single rank"}
-    lx = W.define_lexer(Lexer())
-    text, offs, keep = make_corpus(args.bytes, rank, pinned=True)
+    vocab = vocabulary()
+    lx, mt = define_workload(Lexer, Matcher, vocab)
+    text, offs, keep = make_corpus(args.bytes, rank, True, vocab)
     ndocs = len(offs) - 1
     dev_text = torch.empty(len(text) + 64, dtype=torch.uint8, device="cuda")
     dev_text[:len(text)].copy_(keep[:len(text)], non_blocking=False)
-    ctx = lx.create_context()
+    lctx, mctx = lx.create_context(), mt.create_context()
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
+    def step():
+        lctx.launch(dev_text.data_ptr(), offs, on_device=True)
+        nlex = lctx.count()
+        mctx.launch_lexer_output(lctx)
+        nres, nitems = mctx.count()
+        return nlex, nres, nitems
+
     # ---- device resident
     sampler = ClockSampler(local_rank)
     sampler.start()
     for _ in range(args.warmup):
-        ctx.launch(dev_text.data_ptr(), offs, on_device=True)
-        ctx.count()
-    counters = {k: ctx.counter(k) for k in ("raw_events", "lexems", "chunks", "fixup_chunks", "fixup_rounds", "text_bytes", "kernel_launches", "islands", "elements", "fused", "fused_fallbacks", "second_half")}
-    counters["ndocs"] = ndocs
-    counters["ar_mult"] = 2 if lx.table_info("symbols") else 1
-    ctx.counter("profile:on"); ctx.counter("profile:reset")
+        nlex, nres, nitems = step()
+    mctx.counter("profile:on"); mctx.counter("profile:reset"); mctx.counter("launches:reset")
+    lctx.counter("profile:on"); lctx.counter("profile:reset")
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()
-    launches = 0
+    launches, t_lex = 0, 0.0
     for _ in range(args.steps):
-        ctx.launch(dev_text.data_ptr(), offs, on_device=True)
-        ctx.count()
-        launches += ctx.counter("kernel_launches")
+        nlex, nres, nitems = step()
+        launches += lctx.counter("kernel_launches")
     e1.record()
     barrier()
+    launches += mctx.counter("kernel_launches")
     clocks = sampler.stop()
     ms = e0.elapsed_time(e1)
-    ktimes = {k: (ctx.counter("time_us:" + k), ctx.counter("calls:" + k)) for k in KERNELS}
-    ctx.counter("profile:off")
+    kern_ms = {k: mctx.counter("time_us:" + k) / 1000.0 / args.steps for k in ("k_eval_count", "k_eval_write", "k_match_documents")}
+    lex_ms = sum(lctx.counter("time_us:" + k) for k in ("k_lex_count", "k_lex_verify", "k_lex_emit", "k_lex_finish", "k_lex_resolve_chunks", "k_fused_scan", "k_fused_write")) / 1000.0 / args.steps
+    mctx.counter("profile:off"); lctx.counter("profile:off")
+    nrules = mctx.counter("eval_rules") // max(1, mctx.counter("eval_runs"))
+    info = {"eval_capable": mctx.counter("eval_capable"), "eval_flagged_docs": mctx.counter("eval_flagged") // max(1, mctx.counter("eval_runs")),
+            "rule_instances_per_step": nrules, "rules_by_full_fold_per_step": mctx.counter("eval_queued") // max(1, mctx.counter("eval_runs"))}
+    stats = mctx.fetch()["stats"] if args.bytes <= (64 << 20) else None
 
-    # ---- end to end through the C ABI with pinned host buffers: the batch is cut into sub-batches of whole documents
-    # that several host threads (one context + CUDA stream each) push through scan + fetch, so that the H2D copy of one
-    # sub-batch, the kernels of another and the D2H copy of a third overlap (PCIe is full duplex)
-    import threading
-    nlex = counters["lexems"]
-    del ctx
-    out_keep = torch.empty((nlex + 1024) * 16, dtype=torch.uint8, pin_memory=True)
-    out_lex = out_keep.numpy().view(LEXEM_DT)
-    out_offs = torch.empty(ndocs + 1, dtype=torch.int64, pin_memory=True).numpy().view(np.uint64)
-    out_status = torch.empty(ndocs, dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)
-    e2e_steps = max(1, min(args.steps, 3))
+    # ---- parity gate on the timed output: the first documents of the batch against the CPU oracle
+    parity = None
+    cpu_line = None
+    if rank == 0 and not args.no_parity:
+        cpu = CpuPipeline(vocab)
+        seconds = args.cpu_seconds if (world == 1 and not args.no_cpu) else 2.0
+        nd = cpu.sample_docs(text, offs, seconds)
+        # the first nd documents of the output of the last timed step, as it lies in HBM
+        lo, mo = lctx.fetch_docs(0, nd), mctx.fetch_docs(0, nd)
+        n, ntok, tl, tm = parity_check(cpu, text, offs, nd, lo, mo, mt)
+        parity = {"results": n, "documents": nd, "tokens": ntok}
+        if world == 1 and not args.no_cpu:
+            cpu_line = {"value": float(offs[nd]) / (tl + tm) / 1e9, "unit": "GB/s", "cores": cpu.nthreads, "kind": "port+reference",
+                        "sample": "first %d bytes (%d documents) of the same corpus: level-1 CPU restatement %.2f s + the reference's automaton %.2f s" % (int(offs[nd]), nd, tl, tm),
+                        "matcher_mtokens_per_s": ntok / tm / 1e6}
+
+    # ---- end to end through the C ABI with pinned host buffers: sub-batches of whole documents go through (lexer context,
+    # matcher context, stream) pairs on several host threads, so that the copies of one sub-batch overlap the kernels of another
+    del lctx, mctx
+    e2e_steps = max(1, min(args.steps, 2))
     cuts = [0]
     while cuts[-1] < ndocs:
         nxt = int(np.searchsorted(offs, offs[cuts[-1]] + np.uint64(args.e2e_sub_bytes), side="right")) - 1
         cuts.append(min(ndocs, max(nxt, cuts[-1] + 1)))
     subs = [(cuts[i], cuts[i + 1]) for i in range(len(cuts) - 1)]
     sub_offs = [np.ascontiguousarray(offs[b:e + 1] - offs[b]) for b, e in subs]
-    sub_lex_begin = [0] * (len(subs) + 1)     # filled by the untimed first pass (sizes are deterministic)
+    res_begin, item_begin = [0] * (len(subs) + 1), [0] * (len(subs) + 1)
     streams = [torch.cuda.Stream() for _ in range(args.e2e_threads)]
-    ctxs = [lx.create_context(s.cuda_stream) for s in streams]
-    # several ranks on one host: waiting host threads sleep instead of spinning (ranks x threads is about the CPU count)
-    blocking = world * args.e2e_threads * 2 > len(os.sched_getaffinity(0))
-    if blocking:
-        for c in ctxs:
-            c.counter("sync:blocking")
-    scratch_offs = [np.zeros(max(e - b for b, e in subs) + 1, dtype=np.uint64) for _ in ctxs]
+    pairs = [(lx.create_context(s.cuda_stream), mt.create_context(s.cuda_stream)) for s in streams]
+    out_res = torch.empty((nres + 4096) * RESULT_DT.itemsize, dtype=torch.uint8, pin_memory=True).numpy().view(RESULT_DT)
+    out_items = torch.empty((nitems + 4096) * ITEM_DT.itemsize, dtype=torch.uint8, pin_memory=True).numpy().view(ITEM_DT)
+    out_roffs = torch.empty(ndocs + len(subs) + 1, dtype=torch.int64, pin_memory=True).numpy().view(np.uint64)
+    out_ioffs = torch.empty(ndocs + len(subs) + 1, dtype=torch.int64, pin_memory=True).numpy().view(np.uint64)
+    out_stats = torch.empty(ndocs * STATS_DT.itemsize, dtype=torch.uint8, pin_memory=True).numpy().view(STATS_DT)
+    out_status = torch.empty(ndocs, dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)
     errors = []
 
     def e2e_pass(measure_only):
@@ -300,6 +307,7 @@ def run_ours(args, rank, world, local_rank):
         def worker(w):
             try:
                 torch.cuda.set_device(local_rank)
+                lc, mc = pairs[w]
                 while True:
                     with lock:
                         k = nxt[0]
@@ -307,17 +315,18 @@ def run_ours(args, rank, world, local_rank):
                     if k >= len(subs):
                         return
                     b, e = subs[k]
-                    ctxs[w].launch(text[int(offs[b]):int(offs[e])], sub_offs[k], on_device=False)
+                    lc.launch(text[int(offs[b]):int(offs[e])], sub_offs[k], on_device=False)
+                    mc.launch_lexer_output(lc)
                     if measure_only:
-                        sub_lex_begin[k + 1] = ctxs[w].count()
+                        res_begin[k + 1], item_begin[k + 1] = mc.count()
                     else:
-                        lb = sub_lex_begin[k]
-                        ctxs[w].fetch_into(out_lex[lb:sub_lex_begin[k + 1] + 1], scratch_offs[w], out_status[b:e])
-                        out_offs[b:e + 1] = scratch_offs[w][:e - b + 1] + np.uint64(lb)
+                        rb, ib = res_begin[k], item_begin[k]
+                        mc.fetch_into(out_res[rb:res_begin[k + 1] + 1], out_roffs[b + k:e + k + 1], out_items[ib:item_begin[k + 1] + 1],
+                                      out_ioffs[b + k:e + k + 1], out_stats[b:e], out_status[b:e])
             except Exception as exc:  # surfaced after the join
                 errors.append(exc)
 
-        threads = [threading.Thread(target=worker, args=(w,)) for w in range(len(ctxs))]
+        threads = [threading.Thread(target=worker, args=(w,)) for w in range(len(pairs))]
         for t in threads:
             t.start()
         for t in threads:
@@ -327,8 +336,9 @@ def run_ours(args, rank, world, local_rank):
 
     e2e_pass(True)
     for k in range(len(subs)):
-        sub_lex_begin[k + 1] += sub_lex_begin[k]
-    assert sub_lex_begin[-1] == nlex, "sub-batches give another lexem count than the whole batch"
+        res_begin[k + 1] += res_begin[k]
+        item_begin[k + 1] += item_begin[k]
+    assert res_begin[-1] == nres and item_begin[-1] == nitems, "sub-batches give other counts than the whole batch"
     e2e_pass(False)
     barrier()
     t0 = time.perf_counter()
@@ -337,32 +347,8 @@ def run_ours(args, rank, world, local_rank):
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     if int(out_status.max(initial=0)) != 0:
-        raise RuntimeError("lexer reported document errors on the synthetic corpus")
-    if args.verify_e2e:
-        whole = lx.create_context()
-        ref = whole.scan(dev_text.data_ptr(), offs, on_device=True)
-        assert (ref["offsets"] == out_offs).all() and (ref["lexems"] == out_lex[:nlex]).all(), "pipelined end-to-end output differs from the single batch"
-        del whole
-
-    # what the link allows: plain pinned copies of the same sizes, both directions at once (the end-to-end leg is PCIe bound)
-    pc0, pc1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    s_up, s_down = torch.cuda.Stream(), torch.cuda.Stream()
-    dev_out = torch.empty(16 * nlex, dtype=torch.uint8, device="cuda")
-    link_ms = None
-    barrier()   # all ranks copy at the same time: the bound is what the host gives every rank then
-    for _ in range(2):
-        torch.cuda.synchronize()
-        pc0.record()
-        s_up.wait_event(pc0); s_down.wait_event(pc0)
-        with torch.cuda.stream(s_up):
-            dev_text[:len(text)].copy_(keep[:len(text)], non_blocking=True)
-        with torch.cuda.stream(s_down):
-            out_keep[:16 * nlex].copy_(dev_out, non_blocking=True)
-        torch.cuda.current_stream().wait_stream(s_up); torch.cuda.current_stream().wait_stream(s_down)
-        pc1.record()
-        torch.cuda.synchronize()
-        link_ms = pc0.elapsed_time(pc1) if link_ms is None else min(link_ms, pc0.elapsed_time(pc1))
-    del dev_out
+        raise RuntimeError("document errors on the synthetic corpus")
+    d2h = int(RESULT_DT.itemsize * nres + ITEM_DT.itemsize * nitems + 16 * (ndocs + len(subs)) + (STATS_DT.itemsize + 4) * ndocs)
 
     times = torch.tensor([ms, e2e_s * 1000.0], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -373,41 +359,47 @@ def run_ours(args, rank, world, local_rank):
     total_bytes = float(args.bytes) * world
     value = total_bytes * args.steps / (ms_max / 1000.0) / 1e9
     e2e_value = total_bytes * e2e_steps / (e2e_ms_max / 1000.0) / 1e9
-    dominant = max(KERNELS, key=lambda k: ktimes[k][0])
-    dom_us, dom_calls = ktimes[dominant]
     peak, peak_kind = measured_peak()
-    # timed groups may cover several launches per step: algorithmic bytes of the group per step / its time per step
-    achieved = algorithmic_bytes(dominant, counters) / (dom_us / args.steps * 1e-6) / 1e9 if dom_us else 0.0
+    step_s = ms_max / 1000.0 / args.steps
+    # fused pipeline (lexems never leave the device): text + result records + item records + document offsets
+    b_step = args.bytes + RESULT_DT.itemsize * nres + ITEM_DT.itemsize * nitems + 8 * ndocs
+    dominant = max(kern_ms, key=lambda k: kern_ms[k])
+    # algorithmic bytes of the dominant kernel per launch: count pass = token record (16 B) + event slot and
+    # work count (8 B) read, result/item counts (8 B) written per token, one bit per rule instance
+    b_dom = {"k_eval_count": 32.0 * nlex + nrules / 8.0, "k_eval_write": 16.0 * nlex + RESULT_DT.itemsize * nres + ITEM_DT.itemsize * nitems + nrules / 8.0,
+             "k_match_documents": 16.0 * nlex + RESULT_DT.itemsize * nres + ITEM_DT.itemsize * nitems}[dominant]
+    achieved = b_dom / (kern_ms[dominant] / 1000.0) / 1e9 if kern_ms[dominant] else 0.0
+    traffic = NCU_TRAFFIC.get(dominant)
     line = {
         "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "C2 lexer only: %d lexem definitions over %d bytes of synthetic UTF-8 text per GPU in %d documents (4-64 KiB)"
-                               % (lx.table_info("definitions"), args.bytes, ndocs),
-                   "l2": "input (%.0f MiB) larger than L2, no flush needed" % (args.bytes / 2**20),
-                   "lexems_per_step": counters["lexems"], "raw_events_per_step": counters["raw_events"],
-                   "fwd_states": lx.table_info("fwd_states"), "fwd_table_bytes": lx.table_info("fwd_table_bytes"),
-                   "fixup_chunks": counters["fixup_chunks"], "chunks": counters["chunks"],
-                   "second_half": {0: "per document loop", 1: "dense island pipeline", 2: "island/slot pipeline", 3: "fused segment kernel",
-                                   4: "chunk resolution over completed events"}.get(counters["second_half"], "?")},
+        "dtype": "u32", "data": "synthetic",
+        "config": {"workload": "C3 lexer+matcher: %d lexem definitions + %d symbols, %d token patterns over %d bytes of synthetic multilingual UTF-8 text per GPU in %d documents "
+                               "(4-64 KiB); one batch of the 4 GiB corpus of BASELINE config 3" % (lx.table_info("definitions"), NSYMBOLS, NPATTERNS, args.bytes, ndocs),
+                   "l2": "input (%.0f MiB text, %.0f MiB lexems) larger than L2, no flush needed" % (args.bytes / 2**20, 16.0 * nlex / 2**20),
+                   "lexems_per_step": int(nlex), "results_per_step": int(nres), "items_per_step": int(nitems), "matcher": info},
         "clocks": clocks,
-        "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": int(args.bytes + 8 * (ndocs + 1)),
-                "d2h_bytes_per_step": int(16 * nlex + 8 * (ndocs + len(subs)) + 4 * ndocs), "steps": e2e_steps,
-                "pipeline": "%d host threads x (context + stream), sub-batches of %d MiB" % (args.e2e_threads, args.e2e_sub_bytes >> 20),
-                "numa_rank0": numa, "host_cpus": len(os.sched_getaffinity(0)), "blocking_waits": bool(blocking),
-                "link_bound": {"value": float(args.bytes) / (link_ms / 1000.0) / 1e9, "unit": "GB/s",
-                               "what": "text bytes / time of plain pinned copies of the same H2D and D2H bytes issued together (rank 0)"}},
+        "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": int(args.bytes + 8 * (ndocs + len(subs))), "d2h_bytes_per_step": d2h, "steps": e2e_steps,
+                "pipeline": "%d host threads x (lexer context + matcher context + stream), sub-batches of %d MiB" % (args.e2e_threads, args.e2e_sub_bytes >> 20),
+                "numa_rank0": numa, "host_cpus": len(os.sched_getaffinity(0))},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": ncu_traffic(dominant, counters), "algorithmic_bytes": algorithmic_bytes(dominant, counters),
-                     "traffic_source": "profiles/r01_lexer_v10_ncu.txt (ncu --set full, 256 MiB of this corpus, scaled by units)", "peak_kind": peak_kind,
-                     "kernel_ms_per_step": {k: ktimes[k][0] / 1000.0 / args.steps for k in KERNELS}},
-        "matches_per_s": counters["lexems"] * world * args.steps / (ms_max / 1000.0),
+        "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": (traffic["bytes_per_token"] * nlex) if traffic else None, "traffic_source": traffic["source"] if traffic else None,
+                     "algorithmic_bytes": b_dom, "peak_kind": peak_kind,
+                     "step": {"algorithmic_bytes": b_step, "achieved": b_step / step_s / 1e9, "frac": b_step / step_s / 1e9 / peak,
+                              "what": "SURVEY 8d fused form: text + result records + item records + document offsets over the whole step"},
+                     "kernel_ms_per_step": dict(kern_ms, lexer_kernels=lex_ms)},
+        "matches_per_s": nres * world * args.steps / (ms_max / 1000.0),
+        "mtokens_per_s": nlex * world * args.steps / (ms_max / 1000.0) / 1e6,
+        "lexer_only": {"value": args.bytes / (lex_ms / 1000.0) / 1e9 if lex_ms else None, "unit": "GB/s", "what": "level-1 kernels of the same step (C3 lexem set), per GPU"},
     }
-    if world == 1 and not args.no_cpu:
-        r, sample, dt = cpu_lexer_rate(text, offs, args.cpu_seconds, os.cpu_count() or 1)
-        line["cpu_baseline"] = {"value": r, "unit": "GB/s", "cores": os.cpu_count() or 1, "kind": "port",
-                                "sample": "first %d bytes of the same corpus, %.1f s; level-1 CPU restatement (Hyperscan not installable here)" % (sample, dt)}
+    if parity:
+        line["parity_checked"] = parity["results"]
+        line["parity"] = parity
+    if stats is not None:
+        line["config"]["installs_per_step"] = int(stats["nof_programs_installed"].sum())
+    if cpu_line:
+        line["cpu_baseline"] = cpu_line
     return line
 
 
@@ -417,14 +409,13 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--bytes", type=int, default=1 << 30)
+    ap.add_argument("--bytes", type=int, default=256 << 20)
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--e2e-threads", type=int, default=4)
-    ap.add_argument("--e2e-sub-bytes", type=int, default=64 << 20)
-    ap.add_argument("--verify-e2e", action="store_true")
+    ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--e2e-threads", type=int, default=3)
+    ap.add_argument("--e2e-sub-bytes", type=int, default=32 << 20)
     args = ap.parse_args()
-    args.ndefs = 86
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -148,6 +148,10 @@ const uint64_t* sp_lexer_result_offsets_device( sp_lexer_ctx* ctx);   /* ndocs+1
 const uint32_t* sp_lexer_result_status_device( sp_lexer_ctx* ctx);    /* ndocs, 0 = ok else SP_ERR_* (positive) */
 /* Copy results to host arrays: lexems[count], offsets[ndocs+1], status[ndocs] (each may be NULL). */
 int sp_lexer_fetch( sp_lexer_ctx* ctx, sp_lexem* lexems, uint64_t* offsets, uint32_t* status);
+/* The same for the documents [first_doc, first_doc + ndocs) of the last scan: offsets[ndocs+1] are the stored (absolute)
+ * offsets, lexems receives offsets[ndocs] - offsets[0] records (capacity = room in `lexems`). Pages through a large batch. */
+int sp_lexer_fetch_range( sp_lexer_ctx* ctx, uint32_t first_doc, uint32_t ndocs, sp_lexem* lexems, uint64_t capacity,
+			  uint64_t* offsets, uint32_t* status);
 /* Counters of the last scan (for roofline accounting): "raw_events", "lexems", "chunks",
  * "fixup_chunks", "text_bytes". */
 int64_t sp_lexer_ctx_counter( sp_lexer_ctx* ctx, const char* key);
@@ -200,6 +204,13 @@ const sp_item* sp_matcher_items_device( sp_matcher_ctx* ctx);
  * stats[ndocs], status[ndocs]; each may be NULL. */
 int sp_matcher_fetch( sp_matcher_ctx* ctx, sp_result* results, uint64_t* result_offsets,
 		      sp_item* items, uint64_t* item_offsets, sp_matcher_stats* stats, uint32_t* status);
+
+/* The same for the documents [first_doc, first_doc + ndocs) of the last run (fetchResults of a slice of the batch):
+ * result_offsets / item_offsets (required) receive the stored (absolute) offsets, results / items the records between
+ * offsets[0] and offsets[ndocs]. */
+int sp_matcher_fetch_range( sp_matcher_ctx* ctx, uint32_t first_doc, uint32_t ndocs, sp_result* results, uint64_t result_capacity,
+			    uint64_t* result_offsets, sp_item* items, uint64_t item_capacity, uint64_t* item_offsets,
+			    sp_matcher_stats* stats, uint32_t* status);
 
 /* Counters of the last run ("results", "items", "tokens", "arena_retries", "pool_retries", "kernel_launches", ...)
  * and tuning knobs ("arena=N", "warps_per_sm=N"); -1 if unknown. */

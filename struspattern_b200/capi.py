@@ -56,6 +56,7 @@ def lib():
             "sp_lexer_result_lexems_device": (vp, [vp]), "sp_lexer_result_offsets_device": (vp, [vp]),
             "sp_lexer_result_status_device": (vp, [vp]),
             "sp_lexer_fetch": (C.c_int, [vp, vp, vp, vp]), "sp_lexer_ctx_counter": (C.c_int64, [vp, cp]),
+            "sp_lexer_fetch_range": (C.c_int, [vp, u32, u32, vp, C.c_uint64, vp, vp]),
             "sp_version": (cp, []), "sp_device_count": (C.c_int, []),
         }
         msigs = {
@@ -77,6 +78,7 @@ def lib():
             "sp_matcher_results_device": (vp, [vp]), "sp_matcher_items_device": (vp, [vp]),
             "sp_matcher_fetch": (C.c_int, [vp, vp, vp, vp, vp, vp, vp]),
             "sp_matcher_run_lexer_output": (C.c_int, [vp, vp]),
+            "sp_matcher_fetch_range": (C.c_int, [vp, u32, u32, vp, C.c_uint64, vp, vp, C.c_uint64, vp, vp, vp]),
         }
         for table in (sigs, msigs):
             for name, (res, args) in table.items():
@@ -204,6 +206,16 @@ class LexerContext:
         self._ck(self.L.sp_lexer_fetch(self.h, _ptr(out["lexems"]) if n else None, _ptr(out["offsets"]),
                                        _ptr(out["status"]) if self.ndocs else None))
         out["raw_event_count"] = self.counter("raw_events")
+        return out
+
+    def fetch_docs(self, first, ndocs):
+        """Lexems of the documents [first, first+ndocs) of the last scan; offsets rebased to the slice."""
+        offs = np.zeros(ndocs + 1, dtype=np.uint64)
+        self._ck(self.L.sp_lexer_fetch_range(self.h, first, ndocs, None, C.c_uint64(0), _ptr(offs), None))
+        n = int(offs[-1] - offs[0])
+        out = {"lexems": np.zeros(n, dtype=LEXEM_DT), "offsets": offs, "status": np.zeros(ndocs, dtype=np.uint32)}
+        self._ck(self.L.sp_lexer_fetch_range(self.h, first, ndocs, _ptr(out["lexems"]) if n else None, C.c_uint64(n), _ptr(offs), _ptr(out["status"]) if ndocs else None))
+        out["offsets"] = offs - offs[0]
         return out
 
     def fetch_into(self, lexems, offsets, status):
@@ -336,6 +348,19 @@ class MatcherContext:
         self._ck(self.L.sp_matcher_fetch(self.h, _ptr(out["results"]) if nres else None, _ptr(out["result_offsets"]),
                                          _ptr(out["items"]) if nitems else None, _ptr(out["item_offsets"]),
                                          _ptr(out["stats"]) if nd else None, _ptr(out["status"]) if nd else None))
+        return out
+
+    def fetch_docs(self, first, ndocs):
+        """Results of the documents [first, first+ndocs) of the last run; offsets rebased to the slice."""
+        ro, io = np.zeros(ndocs + 1, dtype=np.uint64), np.zeros(ndocs + 1, dtype=np.uint64)
+        self._ck(self.L.sp_matcher_fetch_range(self.h, first, ndocs, None, C.c_uint64(0), _ptr(ro), None, C.c_uint64(0), _ptr(io), None, None))
+        nres, nitems = int(ro[-1] - ro[0]), int(io[-1] - io[0])
+        out = {"results": np.zeros(nres, dtype=RESULT_DT), "items": np.zeros(nitems, dtype=ITEM_DT),
+               "stats": np.zeros(ndocs, dtype=STATS_DT), "status": np.zeros(ndocs, dtype=np.uint32)}
+        self._ck(self.L.sp_matcher_fetch_range(self.h, first, ndocs, _ptr(out["results"]) if nres else None, C.c_uint64(nres), _ptr(ro),
+                                               _ptr(out["items"]) if nitems else None, C.c_uint64(nitems), _ptr(io),
+                                               _ptr(out["stats"]) if ndocs else None, _ptr(out["status"]) if ndocs else None))
+        out["result_offsets"], out["item_offsets"] = ro - ro[0], io - io[0]
         return out
 
     def fetch_into(self, results, result_offsets, items, item_offsets, stats, status):

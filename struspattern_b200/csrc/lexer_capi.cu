@@ -57,7 +57,7 @@ static int lexerFail( std::string& lasterror, const std::exception& e)
 	if (dynamic_cast<const std::bad_alloc*>( &e)) return SP_ERR_NOMEM;
 	return SP_ERR_ARGUMENT;
 }
-#define SP_LEXER_TRY( obj, stmt) try {stmt; return SP_OK;} catch (const std::exception& e) {return lexerFail( (obj)->lasterror, e);}
+#define SP_LEXER_TRY( obj, ...) try {__VA_ARGS__; return SP_OK;} catch (const std::exception& e) {return lexerFail( (obj)->lasterror, e);}
 
 extern "C" {
 

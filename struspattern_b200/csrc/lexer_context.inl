@@ -466,6 +466,24 @@ int sp_lexer_fetch( sp_lexer_ctx* ctx, sp_lexem* lexems, uint64_t* offsets, uint
 	})
 }
 
+int sp_lexer_fetch_range( sp_lexer_ctx* ctx, uint32_t first_doc, uint32_t ndocs, sp_lexem* lexems, uint64_t capacity, uint64_t* offsets, uint32_t* status)
+{
+	SP_LEXER_TRY( ctx, {
+		if (!ctx->valid) throw std::runtime_error( "no finished scan");
+		if ((uint64_t)first_doc + ndocs > ctx->ndocs || !offsets) throw std::runtime_error( "document range out of bounds");
+		SP_CUDA( cudaMemcpyAsync( offsets, static_cast<const uint64_t*>( ctx->lex_off.ptr()) + first_doc, ((std::size_t)ndocs + 1) * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+		SP_CUDA( ctx->waitStream());
+		const uint64_t b = offsets[ 0], n = offsets[ ndocs] - b;
+		if (lexems)
+		{
+			if (n > capacity) throw std::runtime_error( "lexem buffer too small for the document range");
+			if (n) SP_CUDA( cudaMemcpyAsync( lexems, static_cast<const sp_lexem*>( ctx->lexems.ptr()) + b, n * sizeof(sp_lexem), cudaMemcpyDeviceToHost, ctx->stream));
+		}
+		if (status && ndocs) SP_CUDA( cudaMemcpyAsync( status, static_cast<const uint32_t*>( ctx->status.ptr()) + first_doc, (std::size_t)ndocs * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+		SP_CUDA( ctx->waitStream());
+	})
+}
+
 int64_t sp_lexer_ctx_counter( sp_lexer_ctx* ctx, const char* key)
 {
 	std::string k( key);

@@ -372,6 +372,26 @@ int sp_matcher_fetch( sp_matcher_ctx* ctx, sp_result* results, uint64_t* result_
 	})
 }
 
+int sp_matcher_fetch_range( sp_matcher_ctx* ctx, uint32_t first_doc, uint32_t ndocs, sp_result* results, uint64_t result_capacity, uint64_t* result_offsets,
+			    sp_item* items, uint64_t item_capacity, uint64_t* item_offsets, sp_matcher_stats* stats, uint32_t* status)
+{
+	SP_MATCHER_TRY( ctx, {
+		if (!ctx->valid) throw std::runtime_error( "no finished run");
+		if ((uint64_t)first_doc + ndocs > ctx->ndocs || !result_offsets || !item_offsets) throw std::runtime_error( "document range out of bounds");
+		cudaStream_t st = ctx->stream;
+		SP_CUDA( cudaMemcpyAsync( result_offsets, static_cast<const uint64_t*>( ctx->res_off.ptr()) + first_doc, ((std::size_t)ndocs + 1) * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+		SP_CUDA( cudaMemcpyAsync( item_offsets, static_cast<const uint64_t*>( ctx->item_off.ptr()) + first_doc, ((std::size_t)ndocs + 1) * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+		SP_CUDA( cudaStreamSynchronize( st));
+		const uint64_t rb = result_offsets[ 0], rn = result_offsets[ ndocs] - rb, ib = item_offsets[ 0], in = item_offsets[ ndocs] - ib;
+		if ((results && rn > result_capacity) || (items && in > item_capacity)) throw std::runtime_error( "result buffers too small for the document range");
+		if (results && rn) SP_CUDA( cudaMemcpyAsync( results, static_cast<const sp_result*>( ctx->results.ptr()) + rb, rn * sizeof(sp_result), cudaMemcpyDeviceToHost, st));
+		if (items && in) SP_CUDA( cudaMemcpyAsync( items, static_cast<const sp_item*>( ctx->items.ptr()) + ib, in * sizeof(sp_item), cudaMemcpyDeviceToHost, st));
+		if (stats && ndocs) SP_CUDA( cudaMemcpyAsync( stats, static_cast<const sp_matcher_stats*>( ctx->stats.ptr()) + first_doc, (std::size_t)ndocs * sizeof(sp_matcher_stats), cudaMemcpyDeviceToHost, st));
+		if (status && ndocs) SP_CUDA( cudaMemcpyAsync( status, static_cast<const uint32_t*>( ctx->status.ptr()) + first_doc, (std::size_t)ndocs * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+		SP_CUDA( cudaStreamSynchronize( st));
+	})
+}
+
 int64_t sp_matcher_ctx_counter( sp_matcher_ctx* ctx, const char* key)
 {
 	std::string k( key);

@@ -142,3 +142,73 @@ def compare_outputs(ref_m, ref_out, got_m, got_out, check_stats=True, check_orde
                 assert int(ref_out["stats"][f][d]) == int(got_out["stats"][f][d]), "%s of document %d: ref %d got %d" % (
                     f, d, int(ref_out["stats"][f][d]), int(got_out["stats"][f][d]))
     return sum(len(rc[d]) for d in ok)
+
+
+def _mix(h, v):
+    """64 bit mixing step (splitmix64 finaliser) of numpy uint64 arrays; wraps around on purpose"""
+    with np.errstate(over="ignore"):
+        h = (h ^ v.astype(np.uint64)) * np.uint64(0x9E3779B97F4A7C15)
+        h ^= h >> np.uint64(29)
+        h = h * np.uint64(0xBF58476D1CE4E5B9)
+        h ^= h >> np.uint64(32)
+    return h
+
+
+def _name_hashes(name_of, handles):
+    import zlib
+    top = int(handles.max(initial=0)) + 1
+    table = np.zeros(top, dtype=np.uint64)
+    for h in np.unique(handles):
+        table[int(h)] = zlib.crc32(name_of(int(h)).encode()) + 1
+    return table[handles]
+
+
+def multiset_hashes(m, out):
+    """Per document: (number of results, order independent 64 bit hash of the complete result records with their items
+    in order). Vectorised form of canonical_results for samples of millions of results."""
+    res, items = out["results"], out["items"]
+    ro, io = out["result_offsets"].astype(np.int64), out["item_offsets"].astype(np.int64)
+    ndocs = len(ro) - 1
+    ih = _name_hashes(m.item_name, items["variable"]) if len(items) else np.zeros(0, dtype=np.uint64)
+    for f in ("ordpos", "ordend", "origseg", "origpos", "endseg", "endpos"):
+        ih = _mix(ih, items[f])
+    doc_of_res = np.repeat(np.arange(ndocs), np.diff(ro))
+    first_item = io[doc_of_res] + res["item_begin"].astype(np.int64)        # absolute index of the first item of a result
+    cnt = res["item_count"].astype(np.int64)
+    rh = _name_hashes(m.result_name, res["name"]) if len(res) else np.zeros(0, dtype=np.uint64)
+    for f in ("ordpos", "ordend", "origseg", "origpos", "endseg", "endpos", "item_count"):
+        rh = _mix(rh, res[f])
+    if len(items) and len(res):
+        owner = np.repeat(np.arange(len(res)), cnt)                         # result of every item, in result order
+        idx = np.repeat(first_item, cnt) + (np.arange(int(cnt.sum())) - np.repeat(np.cumsum(cnt) - cnt, cnt))
+        pos = (idx - np.repeat(first_item, cnt)).astype(np.uint64)
+        with np.errstate(over="ignore"):
+            contrib = _mix(ih[idx], pos + np.uint64(1))                     # position dependent: the item order is part of the record
+        isum = np.zeros(len(res), dtype=np.uint64)
+        np.add.at(isum, owner, contrib)
+        rh = _mix(rh, isum)
+    dh = np.zeros(ndocs, dtype=np.uint64)
+    with np.errstate(over="ignore"):
+        np.add.at(dh, doc_of_res, rh)
+    return np.diff(ro), dh
+
+
+def compare_outputs_fast(ref_m, ref_out, got_m, got_out, exact_docs=32):
+    """compare_outputs for large samples: the first `exact_docs` documents record by record, all documents by result count,
+    multiset hash and the exact cascade counters. Returns the number of results compared."""
+    rs, gs = ref_out["status"], got_out["status"]
+    assert ((rs != 0) == (gs != 0)).all(), "document status differs"
+    ok = rs == 0
+    nd = min(exact_docs, len(rs))
+    sub = lambda o: {"results": o["results"][:int(o["result_offsets"][nd])], "result_offsets": o["result_offsets"][:nd + 1],
+                     "items": o["items"][:int(o["item_offsets"][nd])], "item_offsets": o["item_offsets"][:nd + 1],
+                     "stats": o["stats"][:nd], "status": o["status"][:nd]}
+    compare_outputs(ref_m, sub(ref_out), got_m, sub(got_out), check_order=False)
+    rc, rh = multiset_hashes(ref_m, ref_out)
+    gc, gh = multiset_hashes(got_m, got_out)
+    bad = np.nonzero(ok & ((rc != gc) | (rh != gh)))[0]
+    assert len(bad) == 0, "results of document %d differ (%d vs %d results)" % (int(bad[0]), int(rc[bad[0]]), int(gc[bad[0]]))
+    for f in ("nof_programs_installed", "nof_altkey_programs_installed", "nof_signals_fired", "nof_open_patterns", "nof_events"):
+        diff = np.nonzero(ok & (ref_out["stats"][f] != got_out["stats"][f]))[0]
+        assert len(diff) == 0, "%s of document %d: ref %d got %d" % (f, int(diff[0]), int(ref_out["stats"][f][diff[0]]), int(got_out["stats"][f][diff[0]]))
+    return int(rc[ok].sum())
