@@ -49,7 +49,7 @@ struct sp_matcher
 		dev = H.view;
 		dev.programs = put( H.programs); dev.trigger_defs = put( H.trigger_defs);
 		dev.program_triggers = put( H.program_triggers); dev.event_slots = put( H.event_slots);
-		dev.eval_slots = put( H.eval_slots); dev.eval_follows = put( H.eval_follows); dev.prog_flags = put( H.prog_flags);
+		dev.eval_slots = put( H.eval_slots); dev.eval_follows = put( H.eval_follows); dev.eval_xlist = put( H.eval_xlist); dev.prog_flags = put( H.prog_flags);
 		dev.eval_entries = put( H.eval_entries); dev.eval_vars = put( H.eval_vars);
 		uploaded = true;
 	}

@@ -17,8 +17,9 @@ struct sp_matcher_ctx
 	// device buffers (grow only)
 	DeviceBuffer tokens, origsegs, tok_off, arenas, res_pool, item_pool, scalars, doc_res_begin, doc_res_count, doc_item_begin,
 		     doc_item_count, stats, status, list_a, list_b, res_off, item_off, results, items, scantmp,
-		     tok_nres, tok_nitems, tok_res_off, tok_item_off, flags, flag_list, tok_slot, tok_work, tok_work_off, resbits, queue;
+		     tok_nres, tok_nitems, tok_res_off, tok_item_off, flags, flag_list, tok_slot, tok_work, tok_docs, tok_work_off, resbits, queue;
 	uint64_t queue_cap, eval_queued, eval_items;
+	bool count_by_steps;	// SP_EVAL_COUNT=step: the count pass that follows every rule token by token (k_eval_count_step), for A/B runs
 	int mode;			// 0 = automatic (window evaluator if the rule set allows it), 1 = state machine (emission order), 2 = evaluator required
 	uint64_t eval_docs, eval_flagged, eval_runs;
 	double eval_count_ms, eval_write_ms;
@@ -35,7 +36,7 @@ struct sp_matcher_ctx
 	sp_matcher_ctx( sp_matcher* m_, cudaStream_t stream_)
 		:m(m_),stream(stream_),warps_per_sm(16),warps_fixed(false),cap_growths(0),arena_budget(0),nsm(0),res_per_token(0.5),items_per_token(1.0)
 		,ndocs(0),ntokens(0),nres(0),nitems(0),retries(0),pool_retries(0),launches(0),valid(false),pinned(0),ev_a(0),ev_b(0)
-		,kernel_ms(0.0),kernel_calls(0),profile(false),mode(0),eval_docs(0),eval_flagged(0),eval_runs(0),eval_count_ms(0.0),eval_write_ms(0.0),queue_cap(0),eval_queued(0),eval_items(0)
+		,kernel_ms(0.0),kernel_calls(0),profile(false),mode(0),eval_docs(0),eval_flagged(0),eval_runs(0),eval_count_ms(0.0),eval_write_ms(0.0),queue_cap(0),eval_queued(0),eval_items(0),count_by_steps(false)
 	{
 		cap.rules = 2048; cap.triggers = 2048; cap.items = 8192; cap.datarefs = 4096; cap.results = 4096;
 		cap.follow = 256; cap.dispose = 2048; cap.heap = 1024;
@@ -47,6 +48,7 @@ struct sp_matcher_ctx
 		}
 		if ((e = std::getenv( "SP_MATCHER_WARPS_PER_SM")) != 0 && std::atoi( e) >= 1) {warps_per_sm = (uint32_t)std::atoi( e); warps_fixed = true;}
 		if (std::getenv( "SP_MATCHER_PROFILE")) profile = true;
+		if ((e = std::getenv( "SP_EVAL_COUNT")) != 0) count_by_steps = !std::strcmp( e, "step");
 		if ((e = std::getenv( "SP_MATCHER_MODE")) != 0) mode = !std::strcmp( e, "statemachine") ? 1 : !std::strcmp( e, "eval") ? 2 : 0;
 		trace = std::getenv( "SP_MATCHER_TRACE") != 0;
 		int dev = 0;
@@ -212,7 +214,7 @@ struct sp_matcher_ctx
 			// the state machine
 			EvalParams E; std::memset( &E, 0, sizeof(E));
 			E.T = P.T; E.tokens = d_tokens; E.origsegs = d_origsegs; E.tok_off = d_tok_off; E.ndocs = ndocs; E.ntokens = ntokens;
-			E.tok_slot = tok_slot.as<uint32_t>( ntokens); E.tok_work = tok_work.as<uint32_t>( ntokens);
+			E.tok_slot = tok_slot.as<uint32_t>( ntokens); E.tok_work = tok_work.as<uint32_t>( ntokens); E.tok_doc = tok_docs.as<uint32_t>( ntokens);
 			uint64_t* d_tok_work_off = tok_work_off.as<uint64_t>( ntokens + 1);
 			E.tok_work_off = d_tok_work_off;
 			E.tok_nres = tok_nres.as<uint32_t>( ntokens); E.tok_nitems = tok_nitems.as<uint32_t>( ntokens);
@@ -240,7 +242,12 @@ struct sp_matcher_ctx
 				SP_CUDA( cudaMemsetAsync( P.stats, 0, (std::size_t)ndocs * sizeof(sp_matcher_stats), stream));
 				SP_CUDA( cudaMemsetAsync( d_escalars, 0, 4 * sizeof(uint64_t), stream));
 				SP_CUDA( cudaMemsetAsync( E.resbits, 0, (nwork / 32 + 2) * sizeof(uint32_t), stream));
-				k_eval_count<<<nblocks, EvalThreads, 0, stream>>>( E);
+				if (count_by_steps) k_eval_count_step<<<nblocks, EvalThreads, 0, stream>>>( E);
+				else
+				{
+					const uint64_t ntiles = (ntokens + EvalTile - 1) / EvalTile;
+					k_eval_count_join<<<(unsigned int)((ntiles + EvalWarpsPerBlock - 1) / EvalWarpsPerBlock), EvalThreads, 0, stream>>>( E);
+				}
 				k_eval_count_full<<<(unsigned int)nsm * 8, 128, 0, stream>>>( E);
 				if (profile) SP_CUDA( cudaEventRecord( ev_b, stream));
 				exclusiveScan( E.tok_nres, ntokens, d_tok_res_off, scantmp, stream);
@@ -418,6 +425,8 @@ int64_t sp_matcher_ctx_counter( sp_matcher_ctx* ctx, const char* key)
 	if (k == "mode=auto") return ctx->mode = 0;
 	if (k == "mode=statemachine") return ctx->mode = 1;
 	if (k == "mode=eval") return ctx->mode = 2;
+	if (k == "count=step") {ctx->count_by_steps = true; return 1;}
+	if (k == "count=join") {ctx->count_by_steps = false; return 0;}
 	if (k == "time_us:k_match_documents") return (int64_t)(ctx->kernel_ms * 1000.0);
 	if (k == "calls:k_match_documents") return (int64_t)ctx->kernel_calls;
 	if (k == "warps_per_sm") return (int64_t)ctx->warps_per_sm;

@@ -39,7 +39,7 @@ struct EvalParams
 	const uint64_t* tok_off;		// [ndocs+1]
 	uint32_t ndocs;
 	uint64_t ntokens;
-	uint32_t* tok_slot; uint32_t* tok_work;				// [ntokens] k_eval_prepare
+	uint32_t* tok_slot; uint32_t* tok_work; uint32_t* tok_doc;	// [ntokens] k_eval_prepare: event slot, work items, document
 	const uint64_t* tok_work_off;					// [ntokens+1] first work item of a token
 	uint32_t* tok_nres; uint32_t* tok_nitems;			// [ntokens] count pass output
 	const uint64_t* tok_res_off; const uint64_t* tok_item_off;	// [ntokens+1] prefix sums of the above
@@ -74,15 +74,7 @@ __device__ __forceinline__ void evalAddStats( sp_matcher_stats* st, uint32_t ins
 // number of work items of a token with event slot `slotidx`
 __device__ __forceinline__ uint32_t evalTokenWork( const SpMatcherTables& T, uint32_t slotidx)
 {
-	if (slotidx == SP_EVAL_NOSLOT) return 0;
-	uint32_t work = __ldg( &T.event_slots[ slotidx].prog_count);
-	const uint32_t fb = __ldg( &T.eval_slots[ slotidx].follow_begin), fc = __ldg( &T.eval_slots[ slotidx].follow_count);
-	for (uint32_t c=0; c<fc; ++c)
-	{
-		const uint32_t es = __ldg( &T.eval_follows[ fb + c].eslot);
-		if (es != SP_EVAL_NOSLOT) work += __ldg( &T.event_slots[ es].prog_count);
-	}
-	return work;
+	return slotidx == SP_EVAL_NOSLOT ? 0u : __ldg( &T.eval_slots[ slotidx].xcount);
 }
 
 static __global__ void __launch_bounds__(256) k_eval_prepare( EvalParams P)
@@ -105,7 +97,7 @@ static __global__ void __launch_bounds__(256) k_eval_prepare( EvalParams P)
 		slotidx = sp_find_event_index( P.T, tok.id);
 		work = evalTokenWork( P.T, slotidx);
 	}
-	P.tok_slot[ i] = slotidx; P.tok_work[ i] = work;
+	P.tok_slot[ i] = slotidx; P.tok_work[ i] = work; P.tok_doc[ i] = d;
 }
 
 // Position inside the work items of a token: site and entry.
@@ -117,30 +109,13 @@ struct EvalCursor
 	uint32_t fb, fc;		// static follow events of the token
 };
 
-// the list of site cur.c of the token with event slot `slotidx`; false if the site has no list
-__device__ __forceinline__ bool evalSiteList( const SpMatcherTables& T, uint32_t slotidx, EvalCursor& cur)
-{
-	uint32_t es = slotidx;
-	if (cur.c) es = __ldg( &T.eval_follows[ cur.fb + cur.c - 1].eslot);
-	cur.lbegin = 0; cur.lcount = 0;
-	if (es == SP_EVAL_NOSLOT) return false;
-	cur.lbegin = __ldg( &T.event_slots[ es].prog_begin); cur.lcount = __ldg( &T.event_slots[ es].prog_count);
-	return cur.lcount != 0;
-}
-
-// cursor at item `rem` of a token (rem < work items of the token)
+// cursor at work item `rem` of a token with event slot `slotidx` (rem < work items of the token): one load of the flattened list
 __device__ __forceinline__ void evalCursorSeek( const SpMatcherTables& T, uint32_t slotidx, uint32_t rem, EvalCursor& cur)
 {
-	cur.c = 0; cur.k = 0;
-	cur.fb = __ldg( &T.eval_slots[ slotidx].follow_begin); cur.fc = __ldg( &T.eval_slots[ slotidx].follow_count);
-	for (;;)
-	{
-		evalSiteList( T, slotidx, cur);
-		if (rem < cur.lcount) {cur.k = rem; return;}
-		rem -= cur.lcount;
-		if (cur.c >= cur.fc) {cur.k = 0; cur.lcount = 0; return;}	// not reached for rem < work
-		++cur.c;
-	}
+	const uint4 es = __ldg( reinterpret_cast<const uint4*>( T.eval_slots + slotidx));	// follow_begin, follow_count, xbegin, xcount
+	const uint2 it = __ldg( reinterpret_cast<const uint2*>( T.eval_xlist + es.z + rem));
+	cur.fb = es.x; cur.fc = es.y;
+	cur.c = it.y; cur.k = 0; cur.lbegin = it.x; cur.lcount = 1;
 }
 
 __device__ __forceinline__ void evalQueuePush( const EvalParams& P, uint64_t item)
@@ -149,7 +124,7 @@ __device__ __forceinline__ void evalQueuePush( const EvalParams& P, uint64_t ite
 	if (q < P.queue_cap) P.queue[ q] = item;
 }
 
-static __global__ void __launch_bounds__(EvalThreads) k_eval_count( EvalParams P)
+static __global__ void __launch_bounds__(EvalThreads) k_eval_count_step( EvalParams P)
 {
 	__shared__ uint2 s_tok[ EvalWarpsPerBlock][ EvalRun + EvalLook];		// id, ordinal position
 	__shared__ uint32_t s_work[ EvalWarpsPerBlock][ EvalRun + 1];			// first work item of a token, relative to the run
@@ -244,23 +219,11 @@ static __global__ void __launch_bounds__(EvalThreads) k_eval_count( EvalParams P
 	// rules are accounted and replaced at the begin of a round. A lane waits at most EvalSteps-1 steps for its next rule.
 	auto advance = [&]()
 	{
-		++w; ++cur.k;
-		if (cur.k >= cur.lcount && w < wend)
+		++w;
+		if (w < wend)
 		{
-			cur.k = 0;
-			for (;;)
-			{
-				if (cur.c < cur.fc) ++cur.c;
-				else
-				{
-					++t;
-					while (swork[ t+1] == swork[ t]) ++t;		// w < wend: there is a token with work
-					tslot = P.tok_slot[ r0 + t];
-					cur.c = 0;
-					cur.fb = __ldg( &P.T.eval_slots[ tslot].follow_begin); cur.fc = __ldg( &P.T.eval_slots[ tslot].follow_count);
-				}
-				if (evalSiteList( P.T, tslot, cur)) break;
-			}
+			while (swork[ t+1] <= w) ++t;		// w < wend: there is a token that owns item w
+			evalCursorSeek( P.T, P.tok_slot[ r0 + t], w - swork[ t], cur);
 		}
 	};
 	auto account = [&]()
@@ -337,6 +300,334 @@ static __global__ void __launch_bounds__(EvalThreads) k_eval_count( EvalParams P
 	for (uint32_t j=lane; j<nrun; j+=32) {P.tok_nres[ r0 + j] = snres[ j]; P.tok_nitems[ r0 + j] = snitems[ j];}
 }
 
+// ---- count pass as a hash join (default) ------------------------------------------------------------------------------
+// A rule instance that never gets a signal after its installation (the fate of more than nine rules out of ten) is known as
+// such as soon as none of the events of its live triggers occurs among the tokens of its window. All rules installed by
+// one token share that window, so the warp builds, once per key token, a small hash table in shared memory: token id ->
+// distance (in ordinal positions) of its first occurrence behind the key token, for the tokens up to EvalJoinRange
+// positions away, plus the number of window tokens per distance. A rule then costs one 32 byte list entry and at most four
+// probes; the rules that can get a signal (and rules with a longer range, and the windows that do not fit the table) are
+// queued in shared memory and followed token by token, 32 at a time (sp_eval_lite_step).
+enum {EvalTile = 8, EvalTileLook = 88, EvalJoinSlots = 128, EvalJoinCap = 64, EvalJoinRange = 15, EvalStepQueue = 96};
+#define SP_JOIN_EMPTY 0xFFFFFFFFFFFFFFFFull
+
+struct EvalLaneAcc		// statistics of the document a lane is in
+{
+	uint32_t doc, installed;
+	uint64_t signals, open;
+};
+
+__device__ __forceinline__ void evalAccDoc( const EvalParams& P, EvalLaneAcc& acc, uint32_t d)
+{
+	if (d == acc.doc) return;
+	if (acc.doc != 0xFFFFFFFFu) evalAddStats( P.stats + acc.doc, acc.installed, 0, acc.signals, acc.open);
+	acc.doc = d; acc.installed = 0; acc.signals = 0; acc.open = 0;
+}
+
+// what an ended rule leaves behind: counters, result count / item count / result bit, or a place in the queue of the full fold
+__device__ __forceinline__ void evalAccount( const EvalParams& P, const SpEvalEntry& en, const SpEvalLite& L, uint64_t item, uint64_t tok, uint64_t te,
+						const SpEvalFollow* F, uint32_t* snres, uint32_t* snitems, EvalLaneAcc& acc)
+{
+	if (L.flags & SP_LITE_FULL) {evalQueuePush( P, item); return;}
+	acc.installed += 1; acc.signals += L.signals;
+	acc.open += (uint64_t)L.alive_tokens * SP_EVAL_META_NTRIG( en.meta);
+	if (!(L.flags & SP_LITE_RESULT)) return;
+	uint32_t extra = 0;
+	if ((en.meta & SP_EVAL_META_ITEMSFULL) && !sp_eval_lite_follow_items( P.T, P.tokens, tok, te, en, *F, extra))
+	{
+		evalQueuePush( P, item | SP_EVALQ_STATS_DONE);
+		return;
+	}
+	atomicAdd( snres, 1u);
+	if (L.flags & SP_LITE_DREFEMIT) atomicAdd( snitems, L.nitems + extra);
+	atomicOr( P.resbits + (item >> 5), 1u << (item & 31));
+}
+
+__device__ __forceinline__ uint32_t evalJoinHash( uint32_t id) {return (id * 0x9E3779B1u) >> 25;}	// 7 bits: EvalJoinSlots
+
+static __global__ void __launch_bounds__(EvalThreads, 8) k_eval_count_join( EvalParams P)
+{
+	__shared__ uint32_t s_key[ EvalWarpsPerBlock][ EvalTile][ EvalJoinSlots];		// token id, 0xFFFFFFFF = empty
+	__shared__ uint8_t s_dist[ EvalWarpsPerBlock][ EvalTile][ EvalJoinSlots];		// distance of its first occurrence
+	__shared__ uint8_t s_cnt[ EvalWarpsPerBlock][ EvalTile][ EvalJoinRange + 1];		// window tokens up to a distance
+	__shared__ uint32_t s_queue[ EvalWarpsPerBlock][ EvalStepQueue];			// items of the tile to follow token by token
+	__shared__ uint2 s_tok[ EvalWarpsPerBlock][ EvalTile + EvalTileLook];
+	__shared__ uint32_t s_nres[ EvalWarpsPerBlock][ EvalTile], s_nitems[ EvalWarpsPerBlock][ EvalTile];
+	const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	uint32_t (*skey)[ EvalJoinSlots] = s_key[ warp];
+	uint8_t (*sdist)[ EvalJoinSlots] = s_dist[ warp];
+	uint8_t (*scnt)[ EvalJoinRange + 1] = s_cnt[ warp];
+	uint32_t* squeue = s_queue[ warp]; uint32_t* snres = s_nres[ warp]; uint32_t* snitems = s_nitems[ warp];
+	uint2* stok = s_tok[ warp];
+
+	const uint64_t tile = (uint64_t)blockIdx.x * EvalWarpsPerBlock + warp;
+	const uint64_t r0 = tile * EvalTile;
+	if (r0 >= P.ntokens) return;
+	const uint32_t ntile = (uint32_t)min( (uint64_t)EvalTile, P.ntokens - r0);
+	// ---- the tokens of the tile: lane j < EvalTile holds token j
+	uint32_t my_work = 0, my_slot = SP_EVAL_NOSLOT, my_doc = 0, my_pos = 0;
+	uint32_t my_lbegin = 0, my_pbegin = 0, my_lcount = 0, my_fb = 0, my_fc = 0;	// work item list, program list of the token event, static follow events
+	uint64_t my_te = 0;
+	if (lane < ntile)
+	{
+		my_work = P.tok_work[ r0 + lane];
+		my_slot = P.tok_slot[ r0 + lane];
+		if (my_work)
+		{
+			my_lbegin = __ldg( &P.T.eval_slots[ my_slot].xbegin);
+			my_pbegin = __ldg( &P.T.event_slots[ my_slot].prog_begin); my_lcount = __ldg( &P.T.event_slots[ my_slot].prog_count);
+			my_fb = __ldg( &P.T.eval_slots[ my_slot].follow_begin); my_fc = __ldg( &P.T.eval_slots[ my_slot].follow_count);
+		}
+	}
+	const unsigned int workmask = __ballot_sync( SP_FULL, my_work != 0);
+	if (lane < EvalTile) {snres[ lane] = 0; snitems[ lane] = 0;}
+	if (!workmask)
+	{
+		if (lane < ntile) {P.tok_nres[ r0 + lane] = 0; P.tok_nitems[ r0 + lane] = 0;}
+		return;
+	}
+	if (lane < ntile)
+	{
+		my_doc = P.tok_doc[ r0 + lane]; my_te = __ldg( &P.tok_off[ my_doc + 1]);
+	}
+	// the tokens of the tile and behind it, (id, ordinal position): the windows of the rules that are followed step by step
+	for (uint32_t j=lane; j<EvalTile+EvalTileLook; j+=32)
+	{
+		stok[ j] = (r0 + j < P.ntokens) ? __ldg( reinterpret_cast<const uint2*>( P.tokens + r0 + j)) : make_uint2( 0, 0);
+	}
+	__syncwarp();
+	if (lane < ntile) my_pos = stok[ lane].y;
+	// prefix sums of the work items over the tile (lanes 0..EvalTile)
+	uint32_t pre = my_work;
+	#pragma unroll
+	for (int ofs=1; ofs<EvalTile; ofs<<=1)
+	{
+		uint32_t up = __shfl_up_sync( SP_FULL, pre, ofs);
+		if (lane >= (unsigned int)ofs) pre += up;
+	}
+	const uint32_t Wt = __shfl_sync( SP_FULL, pre, EvalTile - 1);
+	pre -= my_work;		// exclusive
+	const uint64_t wbase = __ldg( &P.tok_work_off[ r0]);
+	// ---- hash tables of the windows of the tokens that install something
+	const uint32_t joinrange = P.T.eval_join_range;		// <= EvalJoinRange
+	unsigned int bigwindow = 0;	// tokens whose window does not fit: all their rules are followed token by token
+	for (unsigned int m=workmask; m; m &= m - 1)
+	{
+		const int t = __ffs( m) - 1;
+		const uint64_t i = r0 + t, te = __shfl_sync( SP_FULL, my_te, t);
+		const uint32_t spos = __shfl_sync( SP_FULL, my_pos, t);
+		for (uint32_t h=lane; h<EvalJoinSlots; h+=32) skey[ t][ h] = 0xFFFFFFFFu;
+		uint32_t cnt = 0;	// lane r: window tokens with distance <= r
+		__syncwarp();
+		bool more = true;
+		for (uint32_t round=0; more; ++round)
+		{
+			const uint64_t k = i + 1 + round * 32 + lane;
+			uint2 tk = make_uint2( 0, 0);
+			bool in = false;
+			if (k < te)
+			{
+				tk = (k - r0 < EvalTile + EvalTileLook) ? stok[ k - r0] : __ldg( reinterpret_cast<const uint2*>( P.tokens + k));
+				in = tk.y <= spos + joinrange && tk.y >= spos;
+			}
+			const unsigned int inmask = __ballot_sync( SP_FULL, in);
+			// positions ascend with the lanes and with the rounds: the first occurrence of an id is its lowest lane in the
+			// first round that has it; that lane alone inserts the id, an id that is already there keeps its distance
+			const unsigned int same = __match_any_sync( SP_FULL, in ? tk.x : 0xFFFFFFFFu - lane);
+			if (in && (unsigned int)(__ffs( same) - 1) == lane)
+			{
+				for (uint32_t h = evalJoinHash( tk.x);; h = (h + 1) & (EvalJoinSlots - 1))
+				{
+					const uint32_t old = atomicCAS( &skey[ t][ h], 0xFFFFFFFFu, tk.x);
+					if (old == 0xFFFFFFFFu) {sdist[ t][ h] = (uint8_t)(tk.y - spos); break;}
+					if (old == tk.x) break;
+				}
+			}
+			__syncwarp();
+			#pragma unroll
+			for (int r=0; r<=EvalJoinRange; ++r)
+			{
+				const unsigned int c = __popc( __ballot_sync( SP_FULL, in && tk.y - spos <= (uint32_t)r));
+				if (lane == (unsigned int)r) cnt += c;
+			}
+			more = inmask == SP_FULL;		// positions ascend: the window ends inside this round otherwise
+			if (more && (round + 1) * 32 >= EvalJoinCap) {bigwindow |= 1u << t; more = false;}
+		}
+		if (lane <= EvalJoinRange) scnt[ t][ lane] = (uint8_t)min( cnt, 255u);
+	}
+	__syncwarp();
+
+	// ---- the rules of the tile, 32 per round
+	EvalLaneAcc acc; acc.doc = 0xFFFFFFFFu; acc.installed = 0; acc.signals = 0; acc.open = 0;
+	uint32_t nqueue = 0;		// uniform
+	auto decode = [&]( uint32_t wl, uint32_t& t, EvalCursor& cur)
+	{
+		uint32_t best = 0;	// last token of the tile that has work and whose first item is not behind wl (all lanes call)
+		#pragma unroll
+		for (int j=0; j<EvalTile; ++j)
+		{
+			const uint32_t pj = __shfl_sync( SP_FULL, pre, j), wj = __shfl_sync( SP_FULL, my_work, j);
+			if (wj && wl >= pj) best = j;
+		}
+		t = best;
+		const uint32_t rem = wl - __shfl_sync( SP_FULL, pre, t);
+		const uint32_t xbegin = __shfl_sync( SP_FULL, my_lbegin, t), direct = __shfl_sync( SP_FULL, my_lcount, t), pbegin = __shfl_sync( SP_FULL, my_pbegin, t);
+		cur.fb = __shfl_sync( SP_FULL, my_fb, t); cur.fc = __shfl_sync( SP_FULL, my_fc, t);
+		cur.c = 0; cur.k = 0; cur.lbegin = pbegin + rem; cur.lcount = 1;
+		if (rem >= direct)	// an item of a follow event of the token
+		{
+			const uint2 it = __ldg( reinterpret_cast<const uint2*>( P.T.eval_xlist + xbegin + rem));
+			cur.c = it.y; cur.lbegin = it.x;
+		}
+	};
+	auto follow_steps = [&]( uint32_t nbatch)
+	{
+		// the first nbatch queued items, one per lane: followed token by token in lock step
+		const bool valid = lane < nbatch;
+		const uint32_t wl = valid ? squeue[ lane] : 0;
+		uint32_t t; EvalCursor cur;
+		decode( wl, t, cur);
+		const uint32_t d = __shfl_sync( SP_FULL, my_doc, t);
+		const uint64_t te = __shfl_sync( SP_FULL, my_te, t);
+		const uint32_t spos = __shfl_sync( SP_FULL, my_pos, t);
+		SpEvalEntry en; SpEvalLite L;
+		en.ev[0] = en.ev[1] = en.ev[2] = en.ev[3] = 0xFFFFFFFFu; en.codes = en.value0 = en.meta = en.meta2 = 0;
+		L.value = L.count = L.endpos = L.flags = L.nitems = L.signals = L.alive_tokens = 0;
+		uint32_t expiry = 0;
+		uint64_t k = r0 + t + 1;
+		if (valid)
+		{
+			const uint4* ep = reinterpret_cast<const uint4*>( P.T.eval_entries + cur.lbegin + cur.k);
+			const uint4 a = __ldg( ep), b = __ldg( ep + 1);
+			en.ev[0] = a.x; en.ev[1] = a.y; en.ev[2] = a.z; en.ev[3] = a.w; en.codes = b.x; en.value0 = b.y; en.meta = b.z; en.meta2 = b.w;
+			sp_eval_lite_init( en, spos, L);
+			expiry = spos + SP_EVAL_META_RANGE( en.meta);
+		}
+		while (__any_sync( SP_FULL, (L.flags & SP_LITE_ALIVE) != 0))
+		{
+			#pragma unroll
+			for (int step=0; step<4; ++step)
+			{
+				if (L.flags & SP_LITE_ALIVE)
+				{
+					if (k < te)
+					{
+						const uint2 tk = (k - r0 < EvalTile + EvalTileLook) ? stok[ k - r0] : __ldg( reinterpret_cast<const uint2*>( P.tokens + k));
+						sp_eval_lite_step( en, expiry, tk.x, tk.y, L);
+						++k;
+					}
+					else L.flags &= ~SP_LITE_ALIVE;
+				}
+			}
+		}
+		if (valid)
+		{
+			evalAccDoc( P, acc, d);
+			evalAccount( P, en, L, wbase + wl, r0 + t, te, cur.c ? P.T.eval_follows + cur.fb + cur.c - 1 : 0, snres + t, snitems + t, acc);
+		}
+		__syncwarp();
+		// the rest of the queue moves to the front
+		const uint32_t rest = nqueue - nbatch;
+		uint32_t mv[ EvalStepQueue / 32];
+		#pragma unroll
+		for (int q=0; q<EvalStepQueue/32; ++q) mv[ q] = (q * 32 + lane < rest) ? squeue[ nbatch + q * 32 + lane] : 0;
+		__syncwarp();
+		#pragma unroll
+		for (int q=0; q<EvalStepQueue/32; ++q) if (q * 32 + lane < rest) squeue[ q * 32 + lane] = mv[ q];
+		nqueue = rest;
+		__syncwarp();
+	};
+	// the list entries of a round are loaded one round ahead
+	uint32_t nt = 0; EvalCursor ncur; uint4 na = make_uint4( 0, 0, 0, 0), nb = make_uint4( 0, 0, 0, 0);
+	decode( lane < Wt ? lane : 0, nt, ncur);
+	if (lane < Wt)
+	{
+		const uint4* ep = reinterpret_cast<const uint4*>( P.T.eval_entries + ncur.lbegin);
+		na = __ldg( ep); nb = __ldg( ep + 1);
+	}
+	for (uint32_t base=0; base<Wt; base+=32)
+	{
+		const uint32_t wl = base + lane;
+		const bool valid = wl < Wt;
+		const uint32_t t = nt; const EvalCursor cur = ncur; const uint4 a = na, b = nb;
+		if (base + 32 < Wt)
+		{
+			const uint32_t nwl = base + 32 + lane;
+			decode( nwl < Wt ? nwl : 0, nt, ncur);
+			if (nwl < Wt)
+			{
+				const uint4* ep = reinterpret_cast<const uint4*>( P.T.eval_entries + ncur.lbegin);
+				na = __ldg( ep); nb = __ldg( ep + 1);
+			}
+		}
+		const uint32_t tpos = __shfl_sync( SP_FULL, my_pos, t), tdoc = __shfl_sync( SP_FULL, my_doc, t);
+		const uint64_t tte = __shfl_sync( SP_FULL, my_te, t);
+		bool tostep = false;
+		if (valid)
+		{
+			SpEvalEntry en;
+			en.ev[0] = a.x; en.ev[1] = a.y; en.ev[2] = a.z; en.ev[3] = a.w; en.codes = b.x; en.value0 = b.y; en.meta = b.z; en.meta2 = b.w;
+			if (en.meta & SP_EVAL_META_GENERIC) evalQueuePush( P, wbase + wl);
+			else
+			{
+				const uint32_t range = SP_EVAL_META_RANGE( en.meta);
+				bool quiet = true;
+				if (!(en.meta & SP_EVAL_META_DEAD))
+				{
+					if (range > joinrange || ((bigwindow >> t) & 1u)) quiet = false;
+					else
+					{
+						#pragma unroll
+						for (int e=0; e<SP_EVAL_NEV; ++e)
+						{
+							const uint32_t ev = en.ev[ e];
+							if (ev == 0xFFFFFFFFu) continue;
+							for (uint32_t h = evalJoinHash( ev);; h = (h + 1) & (EvalJoinSlots - 1))
+							{
+								const uint32_t key = skey[ t][ h];
+								if (key == 0xFFFFFFFFu) break;
+								if (key == ev) {if (sdist[ t][ h] <= range) quiet = false; break;}
+							}
+						}
+					}
+				}
+				if (quiet)
+				{
+					SpEvalLite L;
+					sp_eval_lite_init( en, tpos, L);
+					if (L.flags & SP_LITE_ALIVE) L.alive_tokens = scnt[ t][ range];
+					evalAccDoc( P, acc, tdoc);
+					evalAccount( P, en, L, wbase + wl, r0 + t, tte, cur.c ? P.T.eval_follows + cur.fb + cur.c - 1 : 0, snres + t, snitems + t, acc);
+				}
+				else tostep = true;
+			}
+		}
+		// queue the rules that can get a signal
+		const unsigned int sm = __ballot_sync( SP_FULL, tostep);
+		if (tostep) squeue[ nqueue + __popc( sm & laneLt( lane))] = wl;
+		nqueue += __popc( sm);
+		__syncwarp();
+		while (nqueue >= 32) follow_steps( 32);		// full batches; what stays (< 32) waits for the next round (at most 32 more)
+	}
+	while (nqueue) follow_steps( min( nqueue, 32u));
+	// the counters of the lanes: one set of atomics per warp when all lanes are in the same document (the usual case)
+	{
+		const uint32_t d0 = __shfl_sync( SP_FULL, my_doc, __ffs( workmask) - 1);
+		if (__all_sync( SP_FULL, acc.doc == d0 || acc.doc == 0xFFFFFFFFu))
+		{
+			const uint32_t inst = __reduce_add_sync( SP_FULL, acc.doc == d0 ? acc.installed : 0u);
+			uint64_t sig = acc.doc == d0 ? acc.signals : 0, open = acc.doc == d0 ? acc.open : 0;
+			#pragma unroll
+			for (int ofs=16; ofs>0; ofs>>=1) {sig += __shfl_xor_sync( SP_FULL, sig, ofs); open += __shfl_xor_sync( SP_FULL, open, ofs);}
+			if (lane == 0) evalAddStats( P.stats + d0, inst, 0, sig, open);
+			acc.doc = 0xFFFFFFFFu;
+		}
+	}
+	evalAccDoc( P, acc, 0xFFFFFFFFu);
+	__syncwarp();
+	if (lane < ntile) {P.tok_nres[ r0 + lane] = snres[ lane]; P.tok_nitems[ r0 + lane] = snitems[ lane];}
+}
+
 // work item number -> token (binary search over the first items of the tokens), site and list entry
 __device__ __forceinline__ void evalDecodeItem( const EvalParams& P, uint64_t item, uint64_t& tok, uint32_t& slotidx, EvalCursor& cur)
 {
@@ -369,7 +660,7 @@ static __global__ void __launch_bounds__(128) k_eval_count_full( EvalParams P)
 		const uint64_t item = entry & ~SP_EVALQ_STATS_DONE;
 		uint64_t tok; uint32_t slotidx; EvalCursor cur;
 		evalDecodeItem( P, item, tok, slotidx, cur);
-		const uint32_t d = evalFindDoc( P.tok_off, P.ndocs, tok);
+		const uint32_t d = P.tok_doc[ tok];
 		SpEvalSite site;
 		evalItemSite( P, tok, slotidx, cur, site);
 		SpEvalRule R;
@@ -456,7 +747,7 @@ static __global__ void __launch_bounds__(EvalThreads) k_eval_write( EvalParams P
 				const uint32_t slotidx = P.tok_slot[ tok];
 				EvalCursor cur;
 				evalCursorSeek( P.T, slotidx, wl - swork[ tlo], cur);
-				d = evalFindDoc( P.tok_off, P.ndocs, tok);
+				d = P.tok_doc[ tok];
 				tb = __ldg( &P.tok_off[ d]); te = __ldg( &P.tok_off[ d+1]);
 				live = !P.flags[ d];	// the results of flagged documents come from the state machine
 				if (live)

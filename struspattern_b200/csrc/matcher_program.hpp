@@ -63,6 +63,7 @@ struct MatcherTablesHost
 	std::vector<uint32_t> stopwords;	// event id per stop word index (0-based)
 	std::vector<SpEvalSlot> eval_slots;	// window evaluator (matcher_eval.cuh): static follow events per event slot
 	std::vector<SpEvalFollow> eval_follows;
+	std::vector<SpEvalItem> eval_xlist;
 	std::vector<uint32_t> prog_flags;
 	std::vector<SpEvalEntry> eval_entries;
 	std::vector<SpEvalVars> eval_vars;
@@ -334,7 +335,7 @@ private:
 	void buildEvalTables( MatcherTablesHost& T) const
 	{
 		const uint32_t nslots = (uint32_t)T.event_slots.size();
-		SpEvalSlot noslot; noslot.follow_begin = noslot.follow_count = 0;
+		SpEvalSlot noslot; noslot.follow_begin = noslot.follow_count = noslot.xbegin = noslot.xcount = 0;
 		T.eval_slots.assign( nslots, noslot);
 		T.prog_flags.assign( T.programs.size(), 0);
 		bool capable = !m_exclusive;
@@ -419,7 +420,30 @@ private:
 				T.eval_entries[ slot.prog_begin + k] = evalEntry( T, T.program_triggers[ slot.prog_begin + k], slot.key - 1, T.eval_vars[ slot.prog_begin + k]);
 			}
 		}
+		uint32_t joinrange = 0;
+		for (const SpEvalEntry& en: T.eval_entries)
+		{
+			if (!(en.meta & (SP_EVAL_META_GENERIC | SP_EVAL_META_DEAD)) && SP_EVAL_META_RANGE( en.meta) <= 15) joinrange = std::max( joinrange, SP_EVAL_META_RANGE( en.meta));
+		}
+		T.view.eval_join_range = joinrange;
 		T.view.eval_entries = T.eval_entries.data(); T.view.eval_vars = T.eval_vars.data();
+		// the work items of a term event, flattened
+		for (uint32_t h=0; h<nslots; ++h)
+		{
+			const SpEventSlot& slot = T.event_slots[ h];
+			if (!slot.key || ((slot.key - 1) >> 29) != TermEvent) continue;
+			T.eval_slots[ h].xbegin = (uint32_t)T.eval_xlist.size();
+			for (uint32_t k=0; k<slot.prog_count; ++k) {SpEvalItem it; it.ptidx = slot.prog_begin + k; it.cpos = 0; T.eval_xlist.push_back( it);}
+			for (uint32_t c=0; c<T.eval_slots[ h].follow_count; ++c)
+			{
+				const SpEvalFollow& F = T.eval_follows[ T.eval_slots[ h].follow_begin + c];
+				if (F.eslot == 0xFFFFFFFFu) continue;
+				const SpEventSlot& fs = T.event_slots[ F.eslot];
+				for (uint32_t k=0; k<fs.prog_count; ++k) {SpEvalItem it; it.ptidx = fs.prog_begin + k; it.cpos = c + 1; T.eval_xlist.push_back( it);}
+			}
+			T.eval_slots[ h].xcount = (uint32_t)T.eval_xlist.size() - T.eval_slots[ h].xbegin;
+		}
+		T.view.eval_xlist = T.eval_xlist.data();
 		T.view.eval_slots = T.eval_slots.data(); T.view.eval_follows = T.eval_follows.data(); T.view.prog_flags = T.prog_flags.data();
 		T.view.nfollows = (uint32_t)T.eval_follows.size();
 		T.view.eval_capable = capable ? 1 : 0;

@@ -71,11 +71,20 @@ typedef struct alignas(16) SpEvalFollow
 } SpEvalFollow;
 
 /* per event slot (parallel to event_slots): the static follow events of a term event */
-typedef struct alignas(8) SpEvalSlot
+typedef struct alignas(16) SpEvalSlot
 {
 	uint32_t follow_begin;
 	uint32_t follow_count;
+	uint32_t xbegin;		/* work items of a token with this event (eval_xlist range): the programs keyed by the event, */
+	uint32_t xcount;		/* then the programs keyed by its follow events, in the order of the follow events */
 } SpEvalSlot;
+
+/* One work item of a term event: entry of a program list and the site it is installed at. */
+typedef struct alignas(8) SpEvalItem
+{
+	uint32_t ptidx;			/* index into program_triggers / eval_entries / eval_vars */
+	uint32_t cpos;			/* 0 = installed by the token event, c = by follow event number c-1 of the token */
+} SpEvalItem;
 
 /* Per program list entry (parallel to program_triggers): the rule instance this entry creates, compiled for the window
  * evaluator (matcher_eval.cuh: sp_eval_entry_step). The signals of the installation (key definitions fired on the fresh
@@ -136,10 +145,12 @@ typedef struct SpMatcherTables
 	/* window evaluator */
 	const SpEvalSlot* eval_slots;	/* [event_mask+1] */
 	const SpEvalFollow* eval_follows;
+	const SpEvalItem* eval_xlist;
 	const uint32_t* prog_flags;	/* [nprograms] SP_PROGFLAG_* */
 	const SpEvalEntry* eval_entries;	/* [nprogram_triggers] */
 	const SpEvalVars* eval_vars;	/* [nprogram_triggers] */
 	uint32_t nfollows;
+	uint32_t eval_join_range;	/* largest position range of a compiled list entry, at most 15: window of the hash join (k_eval_count_join) */
 	uint32_t eval_capable;		/* 1: the rule set is inside what the window evaluator reproduces exactly (matcher_program.hpp: evalCapable) */
 } SpMatcherTables;
 

@@ -119,3 +119,26 @@ def test_long_ranges_and_many_tokens_per_position():
     toks["ordpos"] = toks["ordpos"] * 3 + (toks["ordpos"] // 50) * 100
     ctx, go = run_eval(gpu, toks, offs)
     MC.compare_outputs(ref, ref.run(toks, offs, nthreads=4), gpu, go, check_order=False)
+
+
+def test_both_count_formulations_give_the_same_output():
+    """k_eval_count_join (hash join over the window of a key token) and k_eval_count_step (every rule followed token by
+    token) must agree bit for bit, also for long ranges, many tokens per position and windows that overflow the hash table."""
+    def define(m):
+        MC.define_c1_rules(m, 9, 600, 60, nterms=(2, 4))
+        rng = np.random.default_rng(5)
+        for r in range(60):
+            terms = rng.integers(1, 40, size=int(rng.integers(2, 4)))
+            MC.define_term_rule(m, MC.OP_SEQUENCE if r % 2 else MC.OP_WITHIN, terms, int(rng.integers(12, 90)), 0)
+            m.define_pattern("L%u" % r, "", True)
+    ref, gpu = both(define, True)
+    toks, offs = MC.random_documents(77, 60, 400, 60, tokens_per_pos=0.15)     # about 7 tokens per position: big windows
+    outs = []
+    for key in ("count=join", "count=step"):
+        ctx = gpu.create_context()
+        ctx.counter("mode=eval")
+        ctx.counter(key)
+        outs.append(ctx.run(toks, offs))
+    for f in ("results", "items", "result_offsets", "item_offsets", "stats", "status"):
+        assert (outs[0][f] == outs[1][f]).all(), f
+    MC.compare_outputs(ref, ref.run(toks, offs, nthreads=4), gpu, outs[0], check_order=False)
