@@ -4,6 +4,8 @@
 
   charRegexMatch.json          <- tests/charRegexMatch/src/testCharRegexMatch.cpp:105-209 (g_tests)
   simpleTokenPatternMatch.json <- tests/simpleTokenPatternMatch/src/testSimpleTokenPatternMatch.cpp:79-97, 179-218
+  worked_example.json          <- doc/webpage/introduction_struspattern.htm:82-102 (rules), :171-176 (input),
+                                  :188-226 (tokens with ordinal positions), :232-236 (results with their items)
 """
 import json
 import os
@@ -35,6 +37,21 @@ def c_string(lit):
             out += {"n": b"\n", "t": b"\t", "\\": b"\\", '"': b'"', "0": b"\0"}.get(n, n.encode())
             i += 2
     return bytes(out)
+
+
+def worked_example():
+    """The published two-level example: rule file, input document, token listing and result listing, verbatim."""
+    import html
+    lines = open(os.path.join(REF, "doc", "webpage", "introduction_struspattern.htm"), encoding="utf-8").read().split("\n")
+    unesc = lambda ls: html.unescape("\n".join(ls))
+    rules = unesc(lines[81:102])                    # :82-102
+    xml = unesc(lines[170:176]) + "\n"             # :171-176
+    tokens = [ln.strip() for ln in lines[187:226] if re.match(r"\d+: ", ln.strip())]       # :188-226
+    results = [html.unescape(ln.strip()) for ln in lines[231:236] if "[" in ln]             # :232-236
+    begin = xml.index("<text>") + len("<text>")
+    end = xml.index("</text>")
+    return {"source": "doc/webpage/introduction_struspattern.htm:82-102, 171-176, 188-226, 232-236",
+            "rules": rules, "xml": xml, "text": xml[begin:end], "text_offset": begin, "tokens": tokens, "results": results}
 
 
 def char_regex_match():
@@ -80,6 +97,7 @@ def simple_token_pattern_match():
 
 
 if __name__ == "__main__":
+    json.dump(worked_example(), open(os.path.join(HERE, "worked_example.json"), "w"), indent=1, ensure_ascii=False)
     json.dump(char_regex_match(), open(os.path.join(HERE, "charRegexMatch.json"), "w"), indent=1)
     json.dump(simple_token_pattern_match(), open(os.path.join(HERE, "simpleTokenPatternMatch.json"), "w"), indent=1)
     print("written")
