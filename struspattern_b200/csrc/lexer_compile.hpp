@@ -149,6 +149,39 @@ public:
 		{
 			throw std::runtime_error( "lexer image inconsistent");
 		}
+		// ... and every index stored inside them must stay inside: a crafted or stale image (the checksum guards against
+		// neither) would otherwise make the kernels read out of bounds, which ends the process with a sticky CUDA error
+		{
+			bool ok = V.fwd_init < V.fwd_states && V.fwd_stride >= 2 && (uint64_t)V.fwd_cut_lo + V.fwd_cut_n <= V.fwd_states
+				&& (V.sym_mask == 0 || ((V.sym_mask + 1) & V.sym_mask) == 0);
+			for (std::size_t i=0; ok && i<T.fwd_next.size(); ++i) ok = T.fwd_next[ i] < V.fwd_states;
+			for (std::size_t i=0; ok && i<256; ++i) ok = (uint32_t)T.fwd_class[ i] + 1 < V.fwd_stride;
+			for (std::size_t i=0; ok && i<T.fwd_acc_pat.size(); ++i) ok = T.fwd_acc_pat[ i] < V.npat;
+			for (std::size_t i=0; ok && i+1<T.fwd_acc_off.size(); ++i)
+			{
+				ok = T.fwd_acc_off[ i] <= T.fwd_acc_off[ i+1] && T.fwd_acc_span[ i].off == T.fwd_acc_off[ i]
+					&& T.fwd_acc_span[ i].n == T.fwd_acc_off[ i+1] - T.fwd_acc_off[ i] && T.fwd_acc_span[ i].n <= V.fwd_max_acc;
+			}
+			for (std::size_t i=0; ok && i<T.rev_next.size(); ++i) ok = (T.rev_next[ i] & SP_REV_ROWMASK) < T.rev_next.size() || (T.rev_next[ i] & SP_REV_STOP);
+			for (std::size_t i=0; ok && i<T.cap_next.size(); ++i) ok = (T.cap_next[ i] & SP_REV_ROWMASK) < T.cap_next.size() || (T.cap_next[ i] & SP_REV_STOP);
+			for (std::size_t i=0; ok && i<T.pat.size(); ++i)
+			{
+				const SpPatternInfo& pi = T.pat[ i];
+				ok = pi.rev_stride >= 1 && (uint64_t)pi.rev_class + 256 <= T.rev_classes.size() && pi.posbind <= 3
+					&& (!pi.resultidx || (uint64_t)pi.cap_first + 5 <= T.cap.size());
+				for (int k=0; ok && k<4; ++k) ok = (uint64_t)pi.rev_init[ k] + pi.rev_stride <= T.rev_next.size();
+				for (std::size_t b=0; ok && b<256; ++b) ok = (uint32_t)T.rev_classes[ pi.rev_class + b] < pi.rev_stride;
+			}
+			for (std::size_t i=0; ok && i<T.cap.size(); ++i)
+			{
+				const SpAnchoredDfa& c = T.cap[ i];
+				ok = c.stride >= 1 && (uint64_t)c.classes + 256 <= T.cap_classes.size();
+				for (int k=0; ok && k<4; ++k) ok = (uint64_t)c.init[ k] + c.stride <= T.cap_next.size();
+				for (std::size_t b=0; ok && b<256; ++b) ok = (uint32_t)T.cap_classes[ c.classes + b] < c.stride;
+			}
+			for (std::size_t i=0; ok && i<T.sym_slots.size(); ++i) ok = !T.sym_slots[ i].hash || (uint64_t)T.sym_slots[ i].str + T.sym_slots[ i].len <= T.sym_pool.size();
+			if (!ok) throw std::runtime_error( "lexer image inconsistent: an index inside the tables is out of range");
+		}
 		fresh.m_compiled = true;
 		*this = fresh;
 		m_tables.pointToHost();
@@ -363,7 +396,18 @@ private:
 		DfaOptions opt; opt.unanchored = true; opt.allowEmpty = false; opt.maxStates = 65000; opt.markCuts = true;
 		Dfa dfa;
 		try {dfa = DfaBuilder( nfa, entries, opt).build();}
-		catch (const DfaTooLarge&) {opt.markCuts = false; dfa = DfaBuilder( nfa, entries, opt).build();}
+		catch (const DfaTooLarge&)
+		{
+			opt.markCuts = false;
+			try {dfa = DfaBuilder( nfa, entries, opt).build();}
+			catch (const DfaTooLarge&)
+			{
+				// all definitions share one forward automaton with 16 bit state numbers (limits)
+				throw UnsupportedError( "the " + std::to_string( m_defs.size()) + " lexem definitions together need more than "
+							+ std::to_string( opt.maxStates) + " automaton states (counted repeats or '.*' in front of long tails multiply states); "
+							"split the set over several lexer instances");
+			}
+		}
 		// renumber: [plain][plain, cut][reporting, cut][reporting] so that the scan loop tests `state >= fwd_acc_base`
 		// for matches and `state - fwd_cut_lo < fwd_cut_n` for cuts
 		std::vector<uint32_t> newid( dfa.nstates);

@@ -141,6 +141,8 @@ struct sp_lexer_ctx
 	bool resolveFused( const SpScanParams& P, uint64_t* d_lex_off, bool overEvents=false)
 	{
 		const uint32_t M = P.ar_mult;
+		// positions advanced and lexems emitted are packed as (low, high) halves of one 64 bit word per chunk and summed together
+		if (nev * M >= 0xFFFFFFFFull) throw std::runtime_error( "batch too large: more than 2^32 event slots (split the batch)");
 		SpFusedParams F; std::memset( &F, 0, sizeof(F));
 		F.T = P.T; F.text = P.text; F.doc_off = P.doc_off; F.ndocs = ndocs; F.total = total; F.chunk = chunk; F.nchunks = nchunks;
 		F.start_state = P.start_state; F.ev_off = P.ev_off; F.ar_mult = M;

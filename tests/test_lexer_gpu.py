@@ -225,7 +225,7 @@ def test_full_size_corpus_properties(monkeypatch):
     import bench
     from struspattern_b200 import workloads as W
     nbytes = int(os.environ.get("SP_TEST_FULL_BYTES", 1 << 30))
-    text, offs, _ = bench.make_corpus(nbytes, 0, pinned=False)
+    text, offs, _ = bench.make_corpus(nbytes, 0, False, bench.vocabulary())
     offs = np.ascontiguousarray(offs, dtype=np.uint64)
     ndocs = len(offs) - 1
     g = W.define_lexer(_gpu_lexer()())
@@ -301,7 +301,7 @@ def test_one_large_document(monkeypatch):
     sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     import bench
     from struspattern_b200 import workloads as W
-    text, _, _ = bench.make_corpus(128 << 20, 0, pinned=False)
+    text, _, _ = bench.make_corpus(128 << 20, 0, False, bench.vocabulary())
     g = W.define_lexer(_gpu_lexer()())
     o = W.define_lexer(OracleLexer())
     small = np.array([0, 4 << 20], dtype=np.uint64)

@@ -257,3 +257,15 @@ def test_compiled_image_is_checked():
     c.define_lexem(1, "[a-z]+")
     with pytest.raises(Exception):
         c.serialize()
+
+
+def test_too_large_definition_sets_are_reported_as_unsupported():
+    """One forward automaton for all definitions, 16 bit state numbers: a set that needs more states is refused with a message
+    that says so (it used to surface as a bare "automaton has too many states" argument error)."""
+    from hostsim_util import HostSimLexer
+    lx = HostSimLexer()
+    for i in range(12):
+        lx.define_lexem(i + 1, r"[a-c]*%s[a-c]{%d}x" % ("abc"[i % 3], 9 + i), 0, 1, 0)
+    with pytest.raises(RuntimeError) as exc:
+        lx.compile()
+    assert "automaton states" in str(exc.value) and "12 lexem definitions" in str(exc.value)
