@@ -8,6 +8,9 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(PKG)
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libstrus_pattern_b200.so")
+# the artefact names of the reference build (src/CMakeLists.txt:48-57, 72-74): SONAME 0.17 of libstrus_pattern and the
+# analyzer module that strusModule's loader opens; both are this library under the names a strus installation looks for
+ALIASES = ["libstrus_pattern.so.0.17", "modstrus_analyzer_pattern.so"]
 SOURCES = ["lexer_capi.cu", "matcher_capi.cu", "strus_iface.cpp"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC,-fvisibility=default", "-shared", "-cudart", "shared"]
@@ -32,9 +35,19 @@ def up_to_date():
     return all(os.path.getmtime(d) <= t for d in deps)
 
 
+def link_aliases():
+    for name in ALIASES:
+        path = os.path.join(PKG, name)
+        if os.path.lexists(path):
+            os.unlink(path)
+        os.symlink(os.path.basename(LIB), path)
+
+
 def build(force=False, verbose=False):
     """Compile every CUDA source into libstrus_pattern_b200.so (skipped when it is newer than its sources)."""
     if not force and up_to_date():
+        if not all(os.path.lexists(os.path.join(PKG, a)) for a in ALIASES):
+            link_aliases()
         return LIB
     nvcc = nvcc_path()
     if nvcc is None:
@@ -48,6 +61,7 @@ def build(force=False, verbose=False):
         raise RuntimeError("nvcc failed:\n" + res.stdout)
     if verbose:
         print(res.stdout)
+    link_aliases()
     return LIB
 
 

@@ -38,3 +38,18 @@ def test_definition_calls_work_without_a_device():
         assert False, "expected an error"
     except PatternError as e:
         assert e.code == -1
+
+
+def test_reference_artefact_names_load_and_export_the_strus_symbols():
+    """libstrus_pattern.so.0.17 and modstrus_analyzer_pattern.so (reference src/CMakeLists.txt:48-57) are build targets: they
+    load under those names and export the two factory functions (src/libstrus_pattern.cpp:21-47) and the module entry point
+    (src/modstrus_analyzer_pattern.cpp:59-61)."""
+    from struspattern_b200 import build
+    build.build()
+    for name in build.ALIASES:
+        path = os.path.join(build.PKG, name)
+        assert os.path.exists(path), name
+        L = ctypes.CDLL(path)
+        for sym in ("entryPoint", "_ZN5strus22createPatternLexer_stdEPNS_20ErrorBufferInterfaceE",
+                    "_ZN5strus24createPatternMatcher_stdEPNS_20ErrorBufferInterfaceE"):
+            assert hasattr(L, sym), "%s lacks %s" % (name, sym)
