@@ -19,6 +19,7 @@ struct sp_lexer_ctx
 	uint64_t fused_batches, fused_fallbacks;
 	bool last_fused, fusedGaveUp;
 	bool dense;		// SP_LEXER_DENSE=1: first island pipeline (two resolution passes, dense elements, three scans)
+	bool tma;		// SP_LEXER_TMA=0: the scans read their chunks from global memory instead of TMA-staged shared memory tiles
 	bool sequential;	// SP_LEXER_SEQUENTIAL=1: one thread per document for resolution and ordinal positions (A/B check)
 	uint64_t nisl, nelem;
 	// last batch
@@ -72,6 +73,13 @@ struct sp_lexer_ctx
 		if (std::getenv( "SP_LEXER_PROFILE")) profile = true;
 		if (const char* be = std::getenv( "SP_BLOCKING_SYNC")) blockingSync = be[0] != '0';
 		sequential = std::getenv( "SP_LEXER_SEQUENTIAL") != 0;
+		{
+			const char* te = std::getenv( "SP_LEXER_TMA");
+			tma = !te || te[0] != '0';
+			// 66 KB of dynamic shared memory per block: above the default limit of 48 KB
+			if (cudaFuncSetAttribute( k_lex_count<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LexTileBytes) != cudaSuccess
+			||  cudaFuncSetAttribute( k_lex_emit<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LexTileBytes) != cudaSuccess) {cudaGetLastError(); tma = false;}
+		}
 		dense = std::getenv( "SP_LEXER_DENSE") != 0;
 		const char* fe = std::getenv( "SP_LEXER_FUSED");
 		fused = (fe && fe[0] == '1');	// the fully fused scan kernel is correct but slower than emit + finish + chunk resolution
@@ -329,7 +337,10 @@ struct sp_lexer_ctx
 		if (nchunks)
 		{
 			unsigned int grid = (unsigned int)((nchunks + LexScanThreads - 1) / LexScanThreads);
-			spanBegin( KEmit); k_lex_emit<<<grid, LexScanThreads, 0, stream>>>( P); spanEnd();
+			spanBegin( KEmit);
+			if (useTma( P)) k_lex_emit<true><<<grid, LexScanThreads, LexTileBytes, stream>>>( P);
+			else k_lex_emit<false><<<grid, LexScanThreads, 0, stream>>>( P);
+			spanEnd();
 		}
 		P.ev_doc = ev_doc.as<uint32_t>( nev);
 		if (nev)
@@ -363,6 +374,9 @@ struct sp_lexer_ctx
 			resolveSlots( P, d_lex_off); last_path = 2;
 		}
 	}
+
+	// bulk copies need 16 byte aligned sources: the text pointer (chunks are 512 bytes)
+	bool useTma( const SpScanParams& P) const {return tma && chunk == 512 && (reinterpret_cast<uintptr_t>( P.text) & 15) == 0;}
 
 	void scan( const uint8_t* text_in, int text_on_device, const uint64_t* doc_offsets, uint32_t ndocs_)
 	{
@@ -410,7 +424,10 @@ struct sp_lexer_ctx
 		{
 			unsigned int grid = (unsigned int)((nchunks + LexScanThreads - 1) / LexScanThreads);
 			unsigned int vgrid = (unsigned int)((nchunks + 255) / 256);
-			spanBegin( KCount); k_lex_count<<<grid, LexScanThreads, 0, stream>>>( P, 0); spanEnd();
+			spanBegin( KCount);
+			if (useTma( P)) k_lex_count<true><<<grid, LexScanThreads, LexTileBytes, stream>>>( P, 0);
+			else k_lex_count<false><<<grid, LexScanThreads, 0, stream>>>( P, 0);
+			spanEnd();
 			for (;;)
 			{
 				SP_CUDA( cudaMemsetAsync( P.nbad, 0, sizeof(uint32_t), stream));
@@ -419,7 +436,7 @@ struct sp_lexer_ctx
 				uint32_t nbad = (uint32_t)readScalar( P.nbad, sizeof(uint32_t));
 				if (!nbad) break;
 				fixups += nbad; ++rounds;
-				spanBegin( KCount); k_lex_count<<<grid, LexScanThreads, 0, stream>>>( P, 1); spanEnd();
+				spanBegin( KCount); k_lex_count<false><<<grid, LexScanThreads, 0, stream>>>( P, 1); spanEnd();
 			}
 		}
 		spanBegin( KScan); exclusiveScan( P.ev_count, nchunks, d_ev_off, scantmp, stream); spanEnd();
@@ -490,6 +507,9 @@ int64_t sp_lexer_ctx_counter( sp_lexer_ctx* ctx, const char* key)
 {
 	std::string k( key);
 	if (k == "raw_events") return (int64_t)ctx->nev;
+	if (k == "tma") return ctx->tma ? 1 : 0;
+	if (k == "tma=0") {ctx->tma = false; return 0;}
+	if (k == "tma=1") {ctx->tma = true; return 1;}
 	if (k == "lexems") return (int64_t)ctx->nlex;
 	if (k == "chunks") return (int64_t)ctx->nchunks;
 	if (k == "fixup_chunks") return (int64_t)ctx->fixups;

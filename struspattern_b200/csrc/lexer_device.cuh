@@ -527,7 +527,8 @@ struct SpNullSink
 	SP_HD void cut() {}
 };
 
-SP_HD void spk_count_chunk( const SpScanParams& P, uint64_t j, int round)
+// scan_text: where the bytes [begin, end) of the chunk are read from (P.text, or a staged copy addressed like P.text)
+SP_HD void spk_count_chunk( const SpScanParams& P, uint64_t j, int round, const uint8_t* scan_text)
 {
 	uint64_t begin = j * P.chunk, end = begin + P.chunk < P.total ? begin + P.chunk : P.total;
 	uint32_t state;
@@ -553,7 +554,7 @@ SP_HD void spk_count_chunk( const SpScanParams& P, uint64_t j, int round)
 		state = P.start_state[ j];
 	}
 	SpCountSink sink; sink.T = &P.T; sink.count = 0;
-	P.end_state[ j] = sp_scan_range( P.T, P.text, P.doc_off, P.ndocs, begin, end, state, sink);
+	P.end_state[ j] = sp_scan_range( P.T, scan_text, P.doc_off, P.ndocs, begin, end, state, sink);
 	P.ev_count[ j] = sink.count;
 }
 
@@ -568,13 +569,13 @@ SP_HD int spk_verify_chunk( const SpScanParams& P, uint64_t j)
 	return 1;
 }
 
-SP_HD void spk_emit_chunk( const SpScanParams& P, uint64_t j)
+SP_HD void spk_emit_chunk( const SpScanParams& P, uint64_t j, const uint8_t* scan_text)
 {
 	uint64_t begin = j * P.chunk, end = begin + P.chunk < P.total ? begin + P.chunk : P.total;
 	SpEmitSink sink; sink.T = &P.T; sink.events = P.events; sink.cursor = P.ev_off[ j]; sink.doc_ev_begin = P.doc_ev_begin;
 	sink.head = 0;
 	sink.pendingCut = sink.seenCut = P.known[ j] ? 1 : 0;	// a chunk that starts with a document starts with a cut
-	sp_scan_range( P.T, P.text, P.doc_off, P.ndocs, begin, end, P.start_state[ j], sink);
+	sp_scan_range( P.T, scan_text, P.doc_off, P.ndocs, begin, end, P.start_state[ j], sink);
 	if (P.head) P.head[ j] = sink.seenCut ? sink.head : SP_HEAD_NOCUT;
 }
 

@@ -18,6 +18,7 @@
 #include "lexer_device.cuh"
 #include "lexer_fused.cuh"
 #include "tile_scan.cuh"
+#include <cuda/barrier>
 
 namespace sp {
 
@@ -32,12 +33,43 @@ __device__ __forceinline__ void stageByteClasses( SpScanParams& P, uint8_t* s_cl
 	P.T.fwd_class = s_class;
 }
 
+// TMA-staged text tiles (north_star kernel 1): the 128 chunks of a block are 64 KiB of consecutive text. Every thread asks the
+// bulk copy engine for its own 512 byte chunk (cp.async.bulk global -> shared, completion counted in bytes on one mbarrier)
+// into a row of LexTilePitch = 528 bytes: with that pitch the 16 byte vector reads of the lanes of a quarter warp fall into
+// different banks (row r starts at bank 4r mod 32), where a pitch of 512 would put all 32 lanes on the same banks. The scan
+// then reads its chunk from shared memory through a pointer that is addressed like the text itself (tile row - begin).
+// A chunk that is not a full, 16 byte aligned 512 bytes (the last one of the batch) is read from global memory as before.
+enum {LexTilePitch = 528, LexTileBytes = LexScanThreads * LexTilePitch};
+
+__device__ __forceinline__ const uint8_t* stageTextTile( const SpScanParams& P, uint64_t j, uint8_t* s_tile, cuda::barrier<cuda::thread_scope_block>& bar)
+{
+	const uint64_t begin = j * P.chunk;
+	const bool staged = j < P.nchunks && P.chunk == 512 && begin + 512 <= P.total;
+	if (threadIdx.x == 0)
+	{
+		init( &bar, blockDim.x);
+		cuda::device::experimental::fence_proxy_async_shared_cta();
+	}
+	__syncthreads();
+	uint8_t* row = s_tile + (size_t)threadIdx.x * LexTilePitch;
+	cuda::barrier<cuda::thread_scope_block>::arrival_token token = staged
+		? (cuda::device::memcpy_async_tx( row, P.text + begin, cuda::aligned_size_t<16>( 512), bar), cuda::device::barrier_arrive_tx( bar, 1, 512))
+		: bar.arrive();
+	bar.wait( std::move( token));
+	return staged ? row - begin : P.text;
+}
+
+template <bool TMA>
 static __global__ void __launch_bounds__(LexScanThreads) k_lex_count( SpScanParams P, int round)
 {
 	__shared__ __align__(16) uint8_t s_class[ 256];
+	extern __shared__ __align__(128) uint8_t s_tile[];
+	__shared__ cuda::barrier<cuda::thread_scope_block> bar;
 	stageByteClasses( P, s_class);
 	uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (j < P.nchunks) spk_count_chunk( P, j, round);
+	const uint8_t* scan_text = P.text;
+	if (TMA) scan_text = stageTextTile( P, j, s_tile, bar);
+	if (j < P.nchunks) spk_count_chunk( P, j, round, scan_text);
 }
 
 static __global__ void __launch_bounds__(256) k_lex_verify( SpScanParams P)
@@ -48,12 +80,17 @@ static __global__ void __launch_bounds__(256) k_lex_verify( SpScanParams P)
 	if ((threadIdx.x & 31) == 0 && ballot) atomicAdd( P.nbad, (uint32_t)__popc( ballot));
 }
 
+template <bool TMA>
 static __global__ void __launch_bounds__(LexScanThreads) k_lex_emit( SpScanParams P)
 {
 	__shared__ __align__(16) uint8_t s_class[ 256];
+	extern __shared__ __align__(128) uint8_t s_tile[];
+	__shared__ cuda::barrier<cuda::thread_scope_block> bar;
 	stageByteClasses( P, s_class);
 	uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (j < P.nchunks) spk_emit_chunk( P, j);
+	const uint8_t* scan_text = P.text;
+	if (TMA) scan_text = stageTextTile( P, j, s_tile, bar);
+	if (j < P.nchunks) spk_emit_chunk( P, j, scan_text);
 }
 
 static __global__ void __launch_bounds__(LexEventThreads) k_lex_finish( SpScanParams P, uint64_t nev)

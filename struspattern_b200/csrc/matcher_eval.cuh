@@ -293,8 +293,24 @@ SP_MHD void sp_eval_hits( const SpMatcherTables& T, const sp_lexem* toks, const 
 	}
 	if (nhits > 2)
 	{
-		R.flag = 1;
-		R.signals += nhits;
+		// more than two hits: order independent if they are all sequence triggers (signal values of one rule are distinct, so
+		// at most one of them is due, and the one accepted moves end_ordpos past the event: the others change nothing)
+		bool sequences = true;
+		for (uint32_t m = installed_mask; m; m &= m - 1)
+		{
+			const SpTriggerDef def = T.trigger_defs[ P.trig_begin + (uint32_t)sp_ctz( m)];
+			if (def.event == event && def.sigtype != SP_SIG_SEQUENCE && def.sigtype != SP_SIG_SEQUENCE_IMM) sequences = false;
+		}
+		if (!sequences) {R.flag = 1; R.signals += nhits; return;}
+		for (uint32_t m = installed_mask; m; m &= m - 1)
+		{
+			const SpTriggerDef def = T.trigger_defs[ P.trig_begin + (uint32_t)sp_ctz( m)];
+			if (def.event != event) continue;
+			if (sp_eval_fire( R, P, def.sigtype, def.sigval, def.variable, data, false))
+			{
+				sp_eval_take<COLLECT,DEPTH>( T, toks, segs, tb, te, R, takes, def.variable, tok, follow, data);
+			}
+		}
 		return;
 	}
 	const SpTriggerDef defA = T.trigger_defs[ P.trig_begin + d1], defB = T.trigger_defs[ P.trig_begin + d2];

@@ -353,7 +353,11 @@ static __global__ void __launch_bounds__(EvalThreads, 8) k_eval_count_join( Eval
 	__shared__ uint32_t s_queue[ EvalWarpsPerBlock][ EvalStepQueue];			// items of the tile to follow token by token
 	__shared__ uint2 s_tok[ EvalWarpsPerBlock][ EvalTile + EvalTileLook];
 	__shared__ uint32_t s_nres[ EvalWarpsPerBlock][ EvalTile], s_nitems[ EvalWarpsPerBlock][ EvalTile];
+	__shared__ uint4 s_info[ EvalWarpsPerBlock][ EvalTile][ 2];	// per token: (first item, work list, program list, direct items), (follow begin, document, position, -)
+	__shared__ unsigned long long s_te[ EvalWarpsPerBlock][ EvalTile];
 	const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	uint4 (*sinfo)[ 2] = s_info[ warp];
+	unsigned long long* ste = s_te[ warp];
 	uint32_t (*skey)[ EvalJoinSlots] = s_key[ warp];
 	uint8_t (*sdist)[ EvalJoinSlots] = s_dist[ warp];
 	uint8_t (*scnt)[ EvalJoinRange + 1] = s_cnt[ warp];
@@ -417,7 +421,8 @@ static __global__ void __launch_bounds__(EvalThreads, 8) k_eval_count_join( Eval
 		const uint64_t i = r0 + t, te = __shfl_sync( SP_FULL, my_te, t);
 		const uint32_t spos = __shfl_sync( SP_FULL, my_pos, t);
 		for (uint32_t h=lane; h<EvalJoinSlots; h+=32) skey[ t][ h] = 0xFFFFFFFFu;
-		uint32_t cnt = 0;	// lane r: window tokens with distance <= r
+		uint32_t cnt = 0;	// window tokens of the rounds done
+		if (lane <= EvalJoinRange) scnt[ t][ lane] = 0;
 		__syncwarp();
 		bool more = true;
 		for (uint32_t round=0; more; ++round)
@@ -444,39 +449,50 @@ static __global__ void __launch_bounds__(EvalThreads, 8) k_eval_count_join( Eval
 				}
 			}
 			__syncwarp();
-			#pragma unroll
-			for (int r=0; r<=EvalJoinRange; ++r)
+			// window tokens up to a distance: the distances ascend with the lanes, so lane L knows the count for every distance
+			// from its own up to (not including) its neighbour's: base + L + 1
 			{
-				const unsigned int c = __popc( __ballot_sync( SP_FULL, in && tk.y - spos <= (uint32_t)r));
-				if (lane == (unsigned int)r) cnt += c;
+				const uint32_t dist = tk.y - spos;
+				const uint32_t nextdist = __shfl_down_sync( SP_FULL, in ? dist : 0xFFFFu, 1);
+				const uint32_t upto = (lane == 31 || !((inmask >> (lane + 1)) & 1u)) ? joinrange + 1 : nextdist;
+				if (in) for (uint32_t r=dist; r<upto; ++r) scnt[ t][ r] = (uint8_t)min( cnt + lane + 1, 255u);
+				cnt += __popc( inmask);
 			}
 			more = inmask == SP_FULL;		// positions ascend: the window ends inside this round otherwise
 			if (more && (round + 1) * 32 >= EvalJoinCap) {bigwindow |= 1u << t; more = false;}
 		}
-		if (lane <= EvalJoinRange) scnt[ t][ lane] = (uint8_t)min( cnt, 255u);
 	}
 	__syncwarp();
 
 	// ---- the rules of the tile, 32 per round
 	EvalLaneAcc acc; acc.doc = 0xFFFFFFFFu; acc.installed = 0; acc.signals = 0; acc.open = 0;
 	uint32_t nqueue = 0;		// uniform
+	// first items of the tokens, in registers of every lane
+	uint32_t pfx[ EvalTile];
+	#pragma unroll
+	for (int j=0; j<EvalTile; ++j) pfx[ j] = __shfl_sync( SP_FULL, pre, j);
+	if (lane < EvalTile)
+	{
+		sinfo[ lane][ 0] = make_uint4( pre, my_lbegin, my_pbegin, my_lcount);
+		sinfo[ lane][ 1] = make_uint4( my_fb, my_doc, my_pos, my_fc);
+		ste[ lane] = my_te;
+	}
+	__syncwarp();
 	auto decode = [&]( uint32_t wl, uint32_t& t, EvalCursor& cur)
 	{
-		uint32_t best = 0;	// last token of the tile that has work and whose first item is not behind wl (all lanes call)
+		// the token of item wl: the last one whose first item is not behind wl (tokens without items share their first item
+		// with the token behind them, and wl < Wt)
+		uint32_t n = 0;
 		#pragma unroll
-		for (int j=0; j<EvalTile; ++j)
+		for (int j=1; j<EvalTile; ++j) n += (wl >= pfx[ j]) ? 1u : 0u;
+		t = n;
+		const uint4 a = sinfo[ t][ 0], b = sinfo[ t][ 1];
+		const uint32_t rem = wl - a.x;
+		cur.fb = b.x; cur.fc = b.w;
+		cur.c = 0; cur.k = 0; cur.lbegin = a.z + rem; cur.lcount = 1;
+		if (rem >= a.w)	// an item of a follow event of the token
 		{
-			const uint32_t pj = __shfl_sync( SP_FULL, pre, j), wj = __shfl_sync( SP_FULL, my_work, j);
-			if (wj && wl >= pj) best = j;
-		}
-		t = best;
-		const uint32_t rem = wl - __shfl_sync( SP_FULL, pre, t);
-		const uint32_t xbegin = __shfl_sync( SP_FULL, my_lbegin, t), direct = __shfl_sync( SP_FULL, my_lcount, t), pbegin = __shfl_sync( SP_FULL, my_pbegin, t);
-		cur.fb = __shfl_sync( SP_FULL, my_fb, t); cur.fc = __shfl_sync( SP_FULL, my_fc, t);
-		cur.c = 0; cur.k = 0; cur.lbegin = pbegin + rem; cur.lcount = 1;
-		if (rem >= direct)	// an item of a follow event of the token
-		{
-			const uint2 it = __ldg( reinterpret_cast<const uint2*>( P.T.eval_xlist + xbegin + rem));
+			const uint2 it = __ldg( reinterpret_cast<const uint2*>( P.T.eval_xlist + a.y + rem));
 			cur.c = it.y; cur.lbegin = it.x;
 		}
 	};
@@ -487,9 +503,8 @@ static __global__ void __launch_bounds__(EvalThreads, 8) k_eval_count_join( Eval
 		const uint32_t wl = valid ? squeue[ lane] : 0;
 		uint32_t t; EvalCursor cur;
 		decode( wl, t, cur);
-		const uint32_t d = __shfl_sync( SP_FULL, my_doc, t);
-		const uint64_t te = __shfl_sync( SP_FULL, my_te, t);
-		const uint32_t spos = __shfl_sync( SP_FULL, my_pos, t);
+		const uint32_t d = sinfo[ t][ 1].y, spos = sinfo[ t][ 1].z;
+		const uint64_t te = ste[ t];
 		SpEvalEntry en; SpEvalLite L;
 		en.ev[0] = en.ev[1] = en.ev[2] = en.ev[3] = 0xFFFFFFFFu; en.codes = en.value0 = en.meta = en.meta2 = 0;
 		L.value = L.count = L.endpos = L.flags = L.nitems = L.signals = L.alive_tokens = 0;
@@ -560,8 +575,8 @@ static __global__ void __launch_bounds__(EvalThreads, 8) k_eval_count_join( Eval
 				na = __ldg( ep); nb = __ldg( ep + 1);
 			}
 		}
-		const uint32_t tpos = __shfl_sync( SP_FULL, my_pos, t), tdoc = __shfl_sync( SP_FULL, my_doc, t);
-		const uint64_t tte = __shfl_sync( SP_FULL, my_te, t);
+		const uint32_t tpos = sinfo[ t][ 1].z, tdoc = sinfo[ t][ 1].y;
+		const uint64_t tte = ste[ t];
 		bool tostep = false;
 		if (valid)
 		{

@@ -217,8 +217,9 @@ public:
 		:m_errorhnd(errorhnd_),m_matcher(matcher_),m_ctx(sp_matcher_ctx_create( matcher_, 0)),m_curPosition(0),m_dirty(true)
 	{
 		if (!m_ctx) throw CallError( SP_ERR_CUDA, sp_matcher_last_error( matcher_));
-		// one document at a time: the state machine, i.e. fetchResults() in the reference's emission order
-		sp_matcher_ctx_counter( m_ctx, "mode=statemachine");
+		// the same automatic choice as the batch interface: a document of a few thousand tokens under a large rule
+		// set takes milliseconds on the window evaluator and the better part of a second on one warp of the state machine;
+		// SP_MATCHER_MODE=statemachine gives the reference's emission order
 		std::memset( &m_stats, 0, sizeof(m_stats));
 	}
 	virtual ~MatcherContext() {sp_matcher_ctx_destroy( m_ctx);}

@@ -116,14 +116,14 @@ int hsim_scan_batch( void* h, const uint8_t* text, const uint64_t* doc_off, uint
 	P.start_state = start_state.data(); P.end_state = end_state.data(); P.ev_count = ev_count.data();
 	P.known = known.data(); P.redo = redo.data();
 	hs->fixups = 0; hs->rounds = 0;
-	for (uint64_t j=0; j<P.nchunks; ++j) spk_count_chunk( P, j, 0);
+	for (uint64_t j=0; j<P.nchunks; ++j) spk_count_chunk( P, j, 0, P.text);
 	for (;;)
 	{
 		uint64_t nbad = 0;
 		for (uint64_t j=0; j<P.nchunks; ++j) nbad += spk_verify_chunk( P, j);
 		if (!nbad) break;
 		hs->fixups += nbad; hs->rounds += 1;
-		for (uint64_t j=0; j<P.nchunks; ++j) spk_count_chunk( P, j, 1);
+		for (uint64_t j=0; j<P.nchunks; ++j) spk_count_chunk( P, j, 1, P.text);
 	}
 	for (uint64_t j=0; j<P.nchunks; ++j) ev_off[ j+1] = ev_off[ j] + ev_count[ j];
 	P.ev_off = ev_off.data();
@@ -134,7 +134,7 @@ int hsim_scan_batch( void* h, const uint8_t* text, const uint64_t* doc_off, uint
 	P.events = hs->events.data(); P.doc_ev_begin = hs->doc_ev_begin.data();
 	std::vector<uint32_t> head( P.nchunks + 1, 0), ev_docflag( nev + 1, 0);
 	P.head = head.data(); P.ev_doc = ev_docflag.data();
-	for (uint64_t j=0; j<P.nchunks; ++j) spk_emit_chunk( P, j);
+	for (uint64_t j=0; j<P.nchunks; ++j) spk_emit_chunk( P, j, P.text);
 	hs->events.resize( nev);
 	for (uint64_t i=0; i<nev; ++i) spk_finish_event( P, i);
 	P.ar_mult = P.T.has_symbols ? 2 : 1;

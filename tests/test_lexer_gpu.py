@@ -327,3 +327,26 @@ def test_one_large_document(monkeypatch):
     assert ctx.counter("second_half") == 2
     ctx.close()
     _same(a, c)
+
+
+@pytest.mark.parametrize("name", ["words_numbers", "unicode_case"])
+def test_tma_staged_text_tiles_give_the_same_output(name):
+    """k_lex_count<true> / k_lex_emit<true> read their chunks from shared memory tiles filled by the bulk copy engine
+    (cp.async.bulk + mbarrier); with SP_LEXER_TMA=0 / counter "tma=0" they read global memory. Same output, also for batches
+    whose last chunk is partial, for text at an unaligned device address (no staging) and for tiny batches."""
+    import torch
+    o = define_set(OracleLexer(), name)
+    g = define_set(_gpu_lexer()(), name)
+    for seed, ndocs, mean in ((5, 400, 3000), (6, 3, 90), (7, 1, 511), (8, 1, 512), (9, 700, 700)):
+        text, offs = make_batch(seed=seed, ndocs=ndocs, mean_bytes=mean)
+        ro = o.scan(text, offs, nthreads=8)
+        outs = []
+        for key in ("tma=1", "tma=0"):
+            ctx = g.create_context()
+            assert ctx.counter(key) == int(key[-1])
+            outs.append(ctx.scan(text, offs))
+        _same(ro, outs[0]); _same(ro, outs[1])
+        dev = torch.zeros(len(text) + 64, dtype=torch.uint8, device="cuda")
+        dev[3:3 + len(text)] = torch.from_numpy(text).cuda()
+        ctx = g.create_context()
+        _same(ro, ctx.scan(dev.data_ptr() + 3, offs, on_device=True))      # unaligned: falls back to global reads

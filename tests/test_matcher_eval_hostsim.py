@@ -209,3 +209,19 @@ def test_c3_style_patterns():
     cnt, so = check(ref, sim, toks, offs)
     assert cnt > 0 and len(so["items"]) > 0
     assert sim.info("eval_flagged") < ndocs
+
+
+def test_sequences_that_name_a_term_several_times_stay_on_the_evaluator():
+    """sequence(a, b, a, a): one token hits up to three live triggers of a rule, but only the one whose signal value is due
+    accepts it, whatever the order of the reference's trigger array: no document is handed to the state machine."""
+    def define(m):
+        rng = np.random.default_rng(17)
+        for r in range(200):
+            terms = rng.integers(1, 6, size=int(rng.integers(3, 6)))
+            MC.define_term_rule(m, MC.OP_SEQUENCE if r % 2 else MC.OP_SEQUENCE_IMM, terms, int(rng.integers(3, 9)), 0)
+            m.define_pattern("S%u" % r, "", True)
+    for compile_ in (False, True):
+        ref, sim = both(define, compile_)
+        toks, offs = MC.random_documents(18, 8, 300, 6)
+        n, _ = check(ref, sim, toks, offs, max_flagged=0)
+        assert n > 0

@@ -21,7 +21,7 @@ def main():
     from struspattern_b200 import Lexer
     from struspattern_b200 import workloads as W
     lx = W.define_lexer(Lexer())
-    text, offs, keep = bench.make_corpus(args.bytes, 0, pinned=False)
+    text, offs, keep = bench.make_corpus(args.bytes, 0, False, bench.vocabulary())
     dev = torch.from_numpy(text).cuda()
     if args.contexts > 1:
         return concurrent(args, lx, dev, offs)
