@@ -413,8 +413,8 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
-    ap.add_argument("--e2e-threads", type=int, default=3)
-    ap.add_argument("--e2e-sub-bytes", type=int, default=32 << 20)
+    ap.add_argument("--e2e-threads", type=int, default=4)
+    ap.add_argument("--e2e-sub-bytes", type=int, default=64 << 20)
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -19,7 +19,7 @@ struct sp_lexer_ctx
 	uint64_t fused_batches, fused_fallbacks;
 	bool last_fused, fusedGaveUp;
 	bool dense;		// SP_LEXER_DENSE=1: first island pipeline (two resolution passes, dense elements, three scans)
-	bool tma;		// SP_LEXER_TMA=0: the scans read their chunks from global memory instead of TMA-staged shared memory tiles
+	bool tma;		// SP_LEXER_TMA=1: the scans read their chunks from TMA-staged shared memory tiles instead of global memory
 	bool sequential;	// SP_LEXER_SEQUENTIAL=1: one thread per document for resolution and ordinal positions (A/B check)
 	uint64_t nisl, nelem;
 	// last batch
@@ -75,7 +75,7 @@ struct sp_lexer_ctx
 		sequential = std::getenv( "SP_LEXER_SEQUENTIAL") != 0;
 		{
 			const char* te = std::getenv( "SP_LEXER_TMA");
-			tma = !te || te[0] != '0';
+			tma = te && te[0] == '1';	// off by default: measured slower, 66 KB of tile per block cost the scan its occupancy
 			// 66 KB of dynamic shared memory per block: above the default limit of 48 KB
 			if (cudaFuncSetAttribute( k_lex_count<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LexTileBytes) != cudaSuccess
 			||  cudaFuncSetAttribute( k_lex_emit<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LexTileBytes) != cudaSuccess) {cudaGetLastError(); tma = false;}

@@ -161,7 +161,7 @@ SP_HD uint32_t sp_scan_range( const SpLexerTables& T, const uint8_t* text, const
 			}
 			else
 			{
-				uint32_t b = SP_LDG( text + pos);
+				uint32_t b = text[ pos];	// generic load: `text` may be a shared memory tile addressed like the text (k_lex_count<true>)
 				state = SP_LDG( T.fwd_next + state * stride + T.fwd_class[ b]);
 				if (state >= accbase) sink.accept( state, (uint32_t)(pos - dstart), d);
 						if ((state - T.fwd_cut_lo) < T.fwd_cut_n) sink.cut();

@@ -592,18 +592,19 @@ static __global__ void __launch_bounds__(EvalThreads, 8) k_eval_count_join( Eval
 					if (range > joinrange || ((bigwindow >> t) & 1u)) quiet = false;
 					else
 					{
+						// four probes with the same instruction stream in all lanes (an unused trigger slot probes for 0xFFFFFFFF, which
+						// is the empty mark and never a key); a probe only loops on a collision
+						bool hit = false;
 						#pragma unroll
 						for (int e=0; e<SP_EVAL_NEV; ++e)
 						{
 							const uint32_t ev = en.ev[ e];
-							if (ev == 0xFFFFFFFFu) continue;
-							for (uint32_t h = evalJoinHash( ev);; h = (h + 1) & (EvalJoinSlots - 1))
-							{
-								const uint32_t key = skey[ t][ h];
-								if (key == 0xFFFFFFFFu) break;
-								if (key == ev) {if (sdist[ t][ h] <= range) quiet = false; break;}
-							}
+							uint32_t h = evalJoinHash( ev);
+							uint32_t key = skey[ t][ h];
+							while (key != 0xFFFFFFFFu && key != ev) {h = (h + 1) & (EvalJoinSlots - 1); key = skey[ t][ h];}
+							hit |= (key == ev) & (ev != 0xFFFFFFFFu) & (sdist[ t][ h] <= range);
 						}
+						quiet = !hit;
 					}
 				}
 				if (quiet)

@@ -332,7 +332,7 @@ def test_one_large_document(monkeypatch):
 @pytest.mark.parametrize("name", ["words_numbers", "unicode_case"])
 def test_tma_staged_text_tiles_give_the_same_output(name):
     """k_lex_count<true> / k_lex_emit<true> read their chunks from shared memory tiles filled by the bulk copy engine
-    (cp.async.bulk + mbarrier); with SP_LEXER_TMA=0 / counter "tma=0" they read global memory. Same output, also for batches
+    (cp.async.bulk + mbarrier) with SP_LEXER_TMA=1 / counter "tma=1"; by default they read global memory. Same output, also for batches
     whose last chunk is partial, for text at an unaligned device address (no staging) and for tiny batches."""
     import torch
     o = define_set(OracleLexer(), name)

@@ -10,6 +10,9 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import bench  # noqa: E402
 
+KERNELS = ["k_lex_count", "k_lex_verify", "k_lex_emit", "k_lex_finish", "k_lex_resolve", "k_lex_write", "k_scan", "k_isl_flags", "k_isl_resolve",
+           "k_ordpos", "k_isl_slots", "k_slot_scan", "k_lex_fused", "k_fused_scan", "k_fused_write", "k_lex_resolve_chunks"]
+
 
 def main():
     ap = argparse.ArgumentParser()
@@ -38,7 +41,7 @@ def main():
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / args.steps
-    k = {n: ctx.counter("time_us:" + n) / 1000.0 / args.steps for n in bench.KERNELS}
+    k = {n: ctx.counter("time_us:" + n) / 1000.0 / args.steps for n in KERNELS}
     print(json.dumps({"ms_per_step": ms, "gbps": args.bytes / ms / 1e6, "second_half": ctx.counter("second_half"),
                       "lexems": ctx.counter("lexems"), "kernels_ms": {n: v for n, v in k.items() if v}}))
 
