@@ -14,13 +14,11 @@ struct sp_lexer_ctx
 		     doc_elem_begin, aggmax, aggmin, aggord, slots, doc_first_content, fix_list, doc_base,
 		     f_region, f_kept, f_agg, f_lead, f_inctail, f_docstart, f_prefix, f_doc_chunk, f_doc_local, f_succ, head;
 	bool hybrid;		// SP_LEXER_HYBRID=0: never resolve per chunk over the completed events (island/slot pipeline instead)
-	int last_path;		// second half of the last batch: 0 sequential, 1 dense islands, 2 slots, 3 fused, 4 chunk resolution
+	int last_path;		// second half of the last batch: 2 island/slot pipeline, 3 fused scan kernel, 4 chunk resolution over completed events (default)
 	bool fused;		// SP_LEXER_FUSED=0 switches the fused segment kernel off (island/slot pipeline for every batch)
 	uint64_t fused_batches, fused_fallbacks;
 	bool last_fused, fusedGaveUp;
-	bool dense;		// SP_LEXER_DENSE=1: first island pipeline (two resolution passes, dense elements, three scans)
 	bool tma;		// SP_LEXER_TMA=1: the scans read their chunks from TMA-staged shared memory tiles instead of global memory
-	bool sequential;	// SP_LEXER_SEQUENTIAL=1: one thread per document for resolution and ordinal positions (A/B check)
 	uint64_t nisl, nelem;
 	// last batch
 	uint32_t ndocs;
@@ -72,7 +70,6 @@ struct sp_lexer_ctx
 		std::memset( kernel_ms, 0, sizeof(kernel_ms)); std::memset( kernel_calls, 0, sizeof(kernel_calls));
 		if (std::getenv( "SP_LEXER_PROFILE")) profile = true;
 		if (const char* be = std::getenv( "SP_BLOCKING_SYNC")) blockingSync = be[0] != '0';
-		sequential = std::getenv( "SP_LEXER_SEQUENTIAL") != 0;
 		{
 			const char* te = std::getenv( "SP_LEXER_TMA");
 			tma = te && te[0] == '1';	// off by default: measured slower, 66 KB of tile per block cost the scan its occupancy
@@ -80,7 +77,6 @@ struct sp_lexer_ctx
 			if (cudaFuncSetAttribute( k_lex_count<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LexTileBytes) != cudaSuccess
 			||  cudaFuncSetAttribute( k_lex_emit<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LexTileBytes) != cudaSuccess) {cudaGetLastError(); tma = false;}
 		}
-		dense = std::getenv( "SP_LEXER_DENSE") != 0;
 		const char* fe = std::getenv( "SP_LEXER_FUSED");
 		fused = (fe && fe[0] == '1');	// the fully fused scan kernel is correct but slower than emit + finish + chunk resolution
 		const char* he = std::getenv( "SP_LEXER_HYBRID");
@@ -258,79 +254,12 @@ struct sp_lexer_ctx
 		SP_CUDA( cudaGetLastError());
 	}
 
-	// island-parallel resolution + scan based ordinal positions (lexer_islands.cuh)
-	void resolveIslands( const SpScanParams& P, uint64_t* d_lex_off)
-	{
-		nisl = nelem = nlex = 0;
-		SP_CUDA( cudaMemsetAsync( P.status, 0, (std::size_t)ndocs * sizeof(uint32_t) + 4, stream));
-		if (!nev)
-		{
-			SP_CUDA( cudaMemsetAsync( d_lex_off, 0, ((std::size_t)ndocs + 1) * sizeof(uint64_t), stream));
-			(void)lexems.as<sp_lexem>( 1);
-			return;
-		}
-		if (nev >= 0xFFFFFFFFull) throw std::runtime_error( "batch too large: more than 2^32 raw events (split the batch)");
-		IslandParams Q; std::memset( &Q, 0, sizeof(Q));
-		Q.T = P.T; Q.events = P.events; Q.ev_doc = P.ev_doc; Q.nev = nev; Q.ndocs = ndocs; Q.ar_mult = P.ar_mult;
-		uint64_t ntiles = (nev + TsTile - 1) / TsTile;
-		Q.flags = isl_flags.as<uint8_t>( nev);
-		Q.tile_nisl = tile_nisl.as<uint32_t>( ntiles);
-		uint64_t* d_tile_isl_off = tile_isl_off.as<uint64_t>( ntiles + 1);
-		Q.tile_isl_off = d_tile_isl_off;
-		uint64_t* d_aggmax = aggmax.as<uint64_t>( ntiles); uint64_t* d_aggmin = aggmin.as<uint64_t>( ntiles);
-		Q.doc_status = P.status;
-		Q.doc_has_content = doc_has_content.as<uint8_t>( ndocs);
-		Q.doc_elem_begin = doc_elem_begin.as<uint64_t>( (std::size_t)ndocs + 1);
-		Q.lex_off = d_lex_off;
-		SP_CUDA( cudaMemsetAsync( Q.doc_has_content, 0, (std::size_t)ndocs + 1, stream));
-		spanBegin( KIslFlags);
-		k_isl_reduce<<<(unsigned int)ntiles, TsThreads, 0, stream>>>( Q, d_aggmax, d_aggmin);
-		k_tile_carry<OpMax><<<1, 1024, 0, stream>>>( d_aggmax, ntiles, 0, (uint64_t*)0);
-		k_tile_carry<OpMin><<<1, 1024, 0, stream>>>( d_aggmin, ntiles, 1, (uint64_t*)0);
-		k_isl_flags<<<(unsigned int)ntiles, TsThreads, 0, stream>>>( Q, d_aggmax, d_aggmin);
-		exclusiveScan( Q.tile_nisl, ntiles, d_tile_isl_off, scantmp, stream);
-		spanEnd();
-		nisl = readScalar( d_tile_isl_off + ntiles, sizeof(uint64_t));
-		Q.nisl = nisl;
-		Q.isl_start = isl_start.as<uint32_t>( nisl + 1);
-		Q.isl_kept = isl_kept.as<uint32_t>( nisl);
-		uint64_t* d_isl_off = isl_off.as<uint64_t>( nisl + 1);
-		Q.isl_off = d_isl_off;
-		Q.scratch = ar.as<SpMatchEvent>( nev * P.ar_mult + 2);
-		unsigned int igrid = (unsigned int)((nisl + 127) / 128);
-		spanBegin( KIslFlags); k_isl_compact<<<(unsigned int)ntiles, TsThreads, 0, stream>>>( Q); spanEnd();
-		spanBegin( KIslResolve); k_isl_resolve<<<igrid, 128, 0, stream>>>( Q, 0); spanEnd();
-		spanBegin( KScan); exclusiveScan( Q.isl_kept, nisl, d_isl_off, scantmp, stream); spanEnd();
-		nelem = readScalar( d_isl_off + nisl, sizeof(uint64_t));
-		Q.nelem = nelem;
-		Q.elem = elem.as<SpMatchEvent>( nelem);
-		Q.elem_doc = elem_doc.as<uint32_t>( nelem);
-		Q.lexems = lexems.as<sp_lexem>( nelem);
-		spanBegin( KIslResolve); k_isl_resolve<<<igrid, 128, 0, stream>>>( Q, 1); spanEnd();
-		uint64_t* d_scalars = (uint64_t*)scalars.ptr();
-		SP_CUDA( cudaMemsetAsync( d_scalars + 1, 0, sizeof(uint64_t), stream));
-		if (nelem)
-		{
-			uint64_t* d_agg = aggord.as<uint64_t>( (nelem + TsTile - 1) / TsTile);
-			spanBegin( KOrdpos);
-			OrdScanA fa; fa.elem = Q.elem; fa.elem_doc = Q.elem_doc;
-			tileScan( fa, nelem, d_agg, stream);
-			OrdScanB fb; fb.elem = Q.elem; fb.elem_doc = Q.elem_doc; fb.doc_status = Q.doc_status; fb.doc_has_content = Q.doc_has_content;
-			tileScan( fb, nelem, d_agg, stream);
-			OrdScanC fc; fc.elem = Q.elem; fc.elem_doc = Q.elem_doc; fc.doc_elem_begin = Q.doc_elem_begin; fc.lexems = Q.lexems; fc.lex_off = Q.lex_off;
-			tileScan( fc, nelem, d_agg, stream, d_scalars + 1);
-			spanEnd();
-		}
-		k_ord_tail<<<(ndocs + 256) / 256, 256, 0, stream>>>( Q, d_scalars + 1);
-		nlex = readScalar( d_scalars + 1, sizeof(uint64_t));
-	}
-
-	// island pipeline: raw events through HBM (emit, finish), then one of the three second halves
+	// island pipeline: raw events through HBM (emit, finish), then the second half: chunk resolution (default) or the island/slot pipeline
 	void resolveLegacy( SpScanParams& P, uint64_t* d_ev_off, uint64_t* d_doc_ev_begin, uint64_t* d_lex_off)
 	{
 		P.events = events.as<SpRawEvent>( nev);
 		// (not tried again behind a fused scan that gave up: it would give up for the same reason)
-		const bool chunkResolution = hybrid && !sequential && !dense && nchunks && nev && P.T.fwd_cut_n && !fusedGaveUp;
+		const bool chunkResolution = hybrid && nchunks && nev && P.T.fwd_cut_n && !fusedGaveUp;
 		P.head = chunkResolution ? head.as<uint32_t>( nchunks) : 0;
 		SP_CUDA( cudaMemsetAsync( d_doc_ev_begin, 0, ((std::size_t)ndocs + 1) * sizeof(uint64_t), stream));
 		if (ndocs) SP_CUDA( cudaMemcpyAsync( d_doc_ev_begin + ndocs, d_ev_off + nchunks, sizeof(uint64_t), cudaMemcpyDeviceToDevice, stream));
@@ -348,26 +277,7 @@ struct sp_lexer_ctx
 			unsigned int grid = (unsigned int)((nev + LexEventThreads - 1) / LexEventThreads);
 			spanBegin( KFinish); k_lex_finish<<<grid, LexEventThreads, 0, stream>>>( P, nev); spanEnd();
 		}
-		if (sequential)
-		{
-			P.ar = ar.as<SpMatchEvent>( nev * P.ar_mult + 2);
-			if (ndocs)
-			{
-				unsigned int grid = (ndocs + LexDocThreads - 1) / LexDocThreads;
-				spanBegin( KResolve); k_lex_resolve<<<grid, LexDocThreads, 0, stream>>>( P); spanEnd();
-			}
-			spanBegin( KScan); exclusiveScan( P.doc_nlex, ndocs, d_lex_off, scantmp, stream); spanEnd();
-			nlex = readScalar( d_lex_off + ndocs, sizeof(uint64_t));
-			last_path = 0;
-			P.lexems = lexems.as<sp_lexem>( nlex);
-			if (ndocs)
-			{
-				unsigned int grid = (ndocs + LexDocThreads - 1) / LexDocThreads;
-				spanBegin( KWrite); k_lex_write<<<grid, LexDocThreads, 0, stream>>>( P); spanEnd();
-			}
-		}
-		else if (dense) {resolveIslands( P, d_lex_off); last_path = 1;}
-		else if (chunkResolution && resolveFused( P, d_lex_off, true)) {}
+		if (chunkResolution && resolveFused( P, d_lex_off, true)) {}
 		else
 		{
 			if (chunkResolution && nev) k_evdoc_clear<<<(unsigned int)((nev + 255) / 256), 256, 0, stream>>>( P.ev_doc, nev);
@@ -443,7 +353,7 @@ struct sp_lexer_ctx
 		nev = readScalar( d_ev_off + nchunks, sizeof(uint64_t));
 		last_fused = false;
 		const uint64_t fallbacksBefore = fused_fallbacks;
-		if (fused && !sequential && !dense && nchunks && nev && P.T.fwd_cut_n && P.T.npat <= SP_FUSED_MAXPAT && P.T.fwd_max_acc + 1 <= SP_FUSED_BUF) last_fused = resolveFused( P, d_lex_off);
+		if (fused && nchunks && nev && P.T.fwd_cut_n && P.T.npat <= SP_FUSED_MAXPAT && P.T.fwd_max_acc + 1 <= SP_FUSED_BUF) last_fused = resolveFused( P, d_lex_off);
 		fusedGaveUp = !last_fused && fused_fallbacks != fallbacksBefore;
 		if (!last_fused) resolveLegacy( P, d_ev_off, d_doc_ev_begin, d_lex_off);
 		SP_CUDA( cudaGetLastError());
@@ -550,8 +460,6 @@ int64_t sp_lexer_ctx_counter( sp_lexer_ctx* ctx, const char* key)
 		// chunk resolution: count, verify, 3 scan, emit, finish, resolve, fix, 3 scan, docs, write
 		if (ctx->last_path == 4) return 1 + 1 + 2*(int64_t)ctx->rounds + 3 + 1 + 1 + 1 + 1 + 3 + 1 + 1;
 		int64_t first = 1 + 1 + 2*(int64_t)ctx->rounds + 3 + 1 + 1;
-		if (ctx->sequential) return first + 1 + 3 + 1;
-		if (ctx->dense) return first + 8 + 1 + 3 + 1 + 9 + 1;
 		return first + 8 + 2 + 2 + 2;
 	}
 	return -1;

@@ -139,115 +139,6 @@ static __global__ void __launch_bounds__(TsThreads) k_isl_compact( IslandParams 
 	if (blockIdx.x == 0 && threadIdx.x == 0) P.isl_start[ P.nisl] = (uint32_t)P.nev;
 }
 
-static __global__ void __launch_bounds__(128) k_isl_resolve( IslandParams P, int pass)
-{
-	uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (i >= P.nisl) return;
-	uint64_t eb = P.isl_start[ i], ee = P.isl_start[ i+1];
-	uint32_t doc = P.ev_doc[ eb];
-	SpMatchEvent local[ SP_ISLAND_LOCAL];
-	SpMatchEvent* ar = ((ee - eb) * P.ar_mult <= SP_ISLAND_LOCAL) ? local : P.scratch + eb * P.ar_mult;
-	uint32_t n = sp_resolve_island( P.T, P.events, eb, ee, ar, P.doc_status + doc);
-	if (pass == 0) {P.isl_kept[ i] = n; return;}
-	uint64_t out = P.isl_off[ i];
-	bool content = false;
-	for (uint32_t k=0; k<n; ++k)
-	{
-		SpMatchEvent e = ar[ k];
-		uint32_t bind = SP_META_BIND( e.meta);
-		content |= (bind == SP_BIND_CONTENT || bind == SP_BIND_UNIQUE);
-		e.origsize |= bind << 16;	// dense element: origsize | bind << 16 (| SP_SIZE_EMIT later), meta = scan state
-		e.meta = 0;
-		P.elem[ out + k] = e;
-		P.elem_doc[ out + k] = doc;
-	}
-	if (content) P.doc_has_content[ doc] = 1;
-	// first island of a document (and the empty documents in front of it) -> first dense element
-	if (eb == 0 || P.ev_doc[ eb-1] != doc)
-	{
-		uint32_t dprev = eb ? P.ev_doc[ eb-1] + 1 : 0;
-		for (uint32_t d=dprev; d<=doc; ++d) P.doc_elem_begin[ d] = out;
-	}
-	if (i + 1 == P.nisl) for (uint32_t d=doc+1; d<=P.ndocs; ++d) P.doc_elem_begin[ d] = P.nelem;
-}
-
-// ---- scan A: prefix max of the keys of elements that may advance the ordinal position
-struct OrdScanA
-{
-	typedef OpMax Op;
-	SpMatchEvent* elem; const uint32_t* elem_doc;
-	__device__ uint64_t load( uint64_t j) const
-	{
-		SpMatchEvent e = elem[ j];
-		uint32_t doc = elem_doc[ j];
-		bool hasPrev = j > 0 && elem_doc[ j-1] == doc;
-		uint32_t prevBind = hasPrev ? SP_DENSE_BIND( elem[ j-1].origsize) : 0;
-		return sp_ord_key( SP_DENSE_BIND( e.origsize), e.origpos, doc, hasPrev, prevBind);
-	}
-	__device__ void store( uint64_t j, uint64_t excl, uint64_t incl) const
-	{
-		// advance iff the element counts and starts behind everything counted before (in its document)
-		if (incl > excl) elem[ j].meta |= SP_META_INC;
-	}
-};
-// NOTE: the bind of the element in front is read from its origsize word, which scan A never writes; scan B
-// only sets bit 31 of it (SP_SIZE_EMIT) while neighbours read bits 16..23, a benign race.
-
-// ---- scan B: count of advances inside the document -> ordinal position, emit decision
-struct OrdScanB
-{
-	typedef OpSegSum Op;
-	SpMatchEvent* elem; const uint32_t* elem_doc; const uint32_t* doc_status; const uint8_t* doc_has_content;
-	__device__ uint64_t load( uint64_t j) const
-	{
-		return ((uint64_t)elem_doc[ j] << 32) | ((elem[ j].meta & SP_META_INC) ? 1 : 0);
-	}
-	__device__ void store( uint64_t j, uint64_t, uint64_t incl) const
-	{
-		SpMatchEvent e = elem[ j];
-		uint32_t doc = elem_doc[ j];
-		uint32_t bind = SP_DENSE_BIND( e.origsize);
-		bool hasPrev = j > 0 && elem_doc[ j-1] == doc;
-		uint32_t prevBind = hasPrev ? SP_DENSE_BIND( elem[ j-1].origsize) : 0;
-		bool counts = sp_ord_key( bind, e.origpos, doc, hasPrev, prevBind) != 0;
-		uint32_t ordpos;
-		bool emit = sp_ord_decide( bind, counts, (uint32_t)incl, ordpos) && doc_has_content[ doc] && !doc_status[ doc];
-		elem[ j].meta = ordpos;
-		if (emit) elem[ j].origsize = e.origsize | SP_SIZE_EMIT;
-	}
-};
-
-// ---- scan C: output index
-struct OrdScanC
-{
-	typedef OpSum Op;
-	const SpMatchEvent* elem; const uint32_t* elem_doc; const uint64_t* doc_elem_begin; sp_lexem* lexems; uint64_t* lex_off;
-	__device__ uint64_t load( uint64_t j) const {return (elem[ j].origsize & SP_SIZE_EMIT) ? 1 : 0;}
-	__device__ void store( uint64_t j, uint64_t excl, uint64_t) const
-	{
-		SpMatchEvent e = elem[ j];
-		if (e.origsize & SP_SIZE_EMIT)
-		{
-			sp_lexem lx; lx.id = e.id; lx.ordpos = e.meta; lx.origpos = e.origpos; lx.origsize = e.origsize & 0xFFFF;
-			lexems[ excl] = lx;
-		}
-		// first dense element of its document (and of the element-less documents in front): output offset
-		for (uint32_t d=elem_doc[ j];; --d)
-		{
-			if (doc_elem_begin[ d] != j) break;
-			lex_off[ d] = excl;
-			if (d == 0) break;
-		}
-	}
-};
-
-static __global__ void k_ord_tail( IslandParams P, const uint64_t* total)
-{
-	uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
-	if (d <= P.ndocs && P.doc_elem_begin[ d] >= P.nelem) P.lex_off[ d] = *total;
-}
-
-
 // ------------------------------------------------------------------------------------------------
 // Slot pipeline (lexer_device.cuh "slot formulation"): one resolution pass per island, one sum scan over the slots.
 //   k_isl_to_slots  one thread per island: supersede logic, COUNTS/INC flags, slot records; lists the islands whose

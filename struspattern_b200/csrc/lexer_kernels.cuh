@@ -9,10 +9,8 @@
 //                  prefix-summed positions -> events are globally ordered by (document, end offset, definition).
 //   k_lex_finish   one thread per raw event: reverse DFA walk for the leftmost start (HS_FLAG_SOM_LEFTMOST),
 //                  size check, sub expression selection, symbol lookup.
-//   k_lex_resolve  one thread per document: the reference's order dependent supersede logic
-//                  (src/patternLexer.cpp:754-822) over the document's events, then counts the lexems.
-//   k_lex_write    one thread per document: ordinal position assignment (src/patternLexer.cpp:893-945) into the
-//                  prefix-summed output range.
+//   (the per-document form of the second half, spk_resolve_doc / spk_write_doc of lexer_device.cuh, is the definition the
+//   parallel formulations are tested against on the CPU, tests/hostsim; it has no kernel of its own any more)
 #ifndef SP_LEXER_KERNELS_CUH_INCLUDED
 #define SP_LEXER_KERNELS_CUH_INCLUDED
 #include "lexer_device.cuh"
@@ -97,18 +95,6 @@ static __global__ void __launch_bounds__(LexEventThreads) k_lex_finish( SpScanPa
 {
 	uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (i < nev) spk_finish_event( P, i);
-}
-
-static __global__ void __launch_bounds__(LexDocThreads) k_lex_resolve( SpScanParams P)
-{
-	uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
-	if (d < P.ndocs) spk_resolve_doc( P, d);
-}
-
-static __global__ void __launch_bounds__(LexDocThreads) k_lex_write( SpScanParams P)
-{
-	uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
-	if (d < P.ndocs) spk_write_doc( P, d);
 }
 
 // ---- fused segment pipeline (lexer_fused.cuh)

@@ -112,9 +112,9 @@ def test_unique_elements_across_islands_and_all_three_formulations(monkeypatch):
             lx.define_lexem(*d)
         lx.compile()
     ro = o.scan(text, offs, nthreads=8)
-    for env in (None, "SP_LEXER_DENSE", "SP_LEXER_SEQUENTIAL"):
+    for env in (None, "SP_LEXER_HYBRID"):   # default (chunk resolution) and the island/slot pipeline
         if env:
-            monkeypatch.setenv(env, "1")
+            monkeypatch.setenv(env, "0")
         ctx = g.create_context()
         _same(ro, ctx.scan(text, offs))
         ctx.close()
