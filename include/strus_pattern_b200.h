@@ -219,6 +219,33 @@ int64_t sp_matcher_ctx_counter( sp_matcher_ctx* ctx, const char* key);
 /* Fused pipeline: lexems of a finished sp_lexer_scan are fed to the matcher without leaving the device. */
 int sp_matcher_run_lexer_output( sp_matcher_ctx* ctx, sp_lexer_ctx* lexer_ctx);
 
+/* Count pass of the level-2 window evaluator WITHOUT any allocation. No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it). It answers "how many results and items will every document of this batch give"
+ * (what a caller needs to size its own output buffers) with the same kernels as sp_matcher_run (k_eval_prepare,
+ * k_eval_count_join, k_eval_count_full, k_eval_docs and the prefix sums between them), their scratch arrays carved
+ * from one static device array of SP_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit.
+ * The call does not call cudaMalloc / cudaFree or any allocating routine; the rule tables must already be on the
+ * device (sp_matcher_upload or an earlier context). All pointers are DEVICE pointers of the caller:
+ *   in:  tokens[ntokens], tok_offsets[ndocs+1] (as for sp_matcher_run with on_device != 0, origsegs all zero)
+ *   out: doc_results[ndocs], doc_items[ndocs] (= the differences of sp_matcher_fetch's result_offsets / item_offsets),
+ *        doc_stats[ndocs] (= sp_matcher_fetch's stats), doc_flags[ndocs] (1 = the document is order dependent or
+ *        irregular: sp_matcher_run hands it to the state machine; its counts here are 0 and its stats undefined).
+ * Limits (beyond them the call fails with SP_ERR_ARGUMENT and a telling last error, nothing is computed): ntokens <=
+ * SP_NOALLOC_MAX_TOKENS, ndocs <= SP_NOALLOC_MAX_DOCS, rule instances of the batch <= SP_NOALLOC_MAX_RULES, rules that
+ * need the full fold <= SP_NOALLOC_QUEUE; rule sets the evaluator does not cover (sp_matcher_table_info
+ * "eval_capable" == 0) are refused. The outputs are complete when the call returns (it waits for the stream).
+ * Every call on a device shares the one scratch array, which keeps the contents of the last call (the call clears what
+ * has to start at zero): calls that overlap on the GPU (two streams, two host threads) race - serialise them. */
+#define SP_NOALLOC_MAX_TOKENS    262144u
+#define SP_NOALLOC_MAX_DOCS      65536u
+#define SP_NOALLOC_MAX_RULES     (1u << 24)
+#define SP_NOALLOC_QUEUE         262144u
+#define SP_NOALLOC_SCRATCH_BYTES (16u << 20)
+int sp_matcher_count_noalloc( sp_matcher* m, const sp_lexem* tokens_device, const uint64_t* tok_offsets_device, uint32_t ndocs, uint64_t ntokens,
+			      uint32_t* doc_results_device, uint32_t* doc_items_device, sp_matcher_stats* doc_stats_device,
+			      uint32_t* doc_flags_device, void* cuda_stream);
+
 /* Library identification. */
 const char* sp_version(void);
 int sp_device_count(void);

@@ -79,6 +79,7 @@ def lib():
             "sp_matcher_fetch": (C.c_int, [vp, vp, vp, vp, vp, vp, vp]),
             "sp_matcher_run_lexer_output": (C.c_int, [vp, vp]),
             "sp_matcher_fetch_range": (C.c_int, [vp, u32, u32, vp, C.c_uint64, vp, vp, C.c_uint64, vp, vp, vp]),
+            "sp_matcher_count_noalloc": (C.c_int, [vp, vp, vp, u32, C.c_uint64, vp, vp, vp, vp, vp]),
         }
         for table in (sigs, msigs):
             for name, (res, args) in table.items():
@@ -286,6 +287,15 @@ class Matcher:
 
     def create_context(self, stream=None):
         return MatcherContext(self, stream)
+
+    def upload(self):
+        self._ck(self.L.sp_matcher_upload(self.h))
+
+    def count_noalloc(self, tokens_dev, tok_offsets_dev, ndocs, ntokens, doc_results_dev, doc_items_dev, doc_stats_dev, doc_flags_dev, stream=None):
+        """sp_matcher_count_noalloc: all arguments but the sizes are int device pointers of the caller."""
+        self._ck(self.L.sp_matcher_count_noalloc(self.h, C.c_void_p(int(tokens_dev)), C.c_void_p(int(tok_offsets_dev)), int(ndocs), C.c_uint64(int(ntokens)),
+                                                 C.c_void_p(int(doc_results_dev)), C.c_void_p(int(doc_items_dev)), C.c_void_p(int(doc_stats_dev)),
+                                                 C.c_void_p(int(doc_flags_dev)), stream))
 
     def run(self, tokens, tok_offsets, origsegs=None, **_):
         ctx = self.create_context()

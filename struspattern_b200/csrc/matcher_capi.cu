@@ -117,3 +117,130 @@ int64_t sp_matcher_table_info( const sp_matcher* m, const char* key)
 } // extern "C"
 
 #include "matcher_context.inl"
+
+// ---- Count pass of the window evaluator without any allocation (include/strus_pattern_b200.h: sp_matcher_count_noalloc).
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it). The scratch arrays the count pass
+// needs (event slot, work items, document, the three prefix sums and their tile sums, result bits, work queue) are
+// carved from ONE file-scope device array of SP_NOALLOC_SCRATCH_BYTES that every GPU loading this library holds until
+// exit. All calls on a device share it: calls that overlap on the GPU race; everything that must start at zero is
+// cleared at the beginning of every call (the array keeps the contents of the last call).
+static __device__ __align__(256) unsigned char g_noalloc_scratch[ SP_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+enum {NoAllocMaxDevices = 64};
+unsigned char* g_noalloc_base[ NoAllocMaxDevices];	// device address of g_noalloc_scratch per device (0 = not asked yet)
+int g_noalloc_nsm[ NoAllocMaxDevices];
+
+// In host code `g_noalloc_scratch` is only a handle: the device address comes from cudaGetSymbolAddress, once per device,
+// with that device current.
+unsigned char* noallocScratchBase( int dev, int& nsm)
+{
+	if (dev < 0 || dev >= NoAllocMaxDevices) throw std::runtime_error( "device ordinal out of range for the no-alloc entry point");
+	if (!g_noalloc_base[ dev])
+	{
+		void* p = 0;
+		SP_CUDA( cudaGetSymbolAddress( &p, g_noalloc_scratch));
+		int n = 0;
+		SP_CUDA( cudaDeviceGetAttribute( &n, cudaDevAttrMultiProcessorCount, dev));
+		g_noalloc_nsm[ dev] = n;
+		g_noalloc_base[ dev] = static_cast<unsigned char*>( p);
+	}
+	nsm = g_noalloc_nsm[ dev];
+	return g_noalloc_base[ dev];
+}
+
+struct NoAllocCarver
+{
+	unsigned char* base; std::size_t used;
+	explicit NoAllocCarver( unsigned char* base_) :base(base_),used(0){}
+	template <typename T> T* take( std::size_t count)
+	{
+		T* rt = reinterpret_cast<T*>( base + used);
+		used += (count * sizeof(T) + 255) & ~(std::size_t)255;
+		return rt;
+	}
+};
+
+// exclusiveScan (device_util.cuh) with the tile sums in caller provided memory
+void noallocScan( const uint32_t* in, uint64_t n, uint64_t* out, uint64_t* tilesum, cudaStream_t stream)
+{
+	const uint64_t ntiles = (n + ScanTile - 1) / ScanTile;
+	if (!ntiles) {SP_CUDA( cudaMemsetAsync( out, 0, sizeof(uint64_t), stream)); return;}
+	k_scan_tile_sums<<<(unsigned int)ntiles, ScanThreads, 0, stream>>>( in, n, tilesum);
+	k_scan_tile_offsets<<<1, 1024, 0, stream>>>( tilesum, ntiles, out + n);
+	k_scan_write<<<(unsigned int)ntiles, ScanThreads, 0, stream>>>( in, n, tilesum, out);
+	SP_CUDA( cudaGetLastError());
+}
+
+void matcherCountNoAlloc( sp_matcher* m, const sp_lexem* d_tokens, const uint64_t* d_tok_off, uint32_t ndocs, uint64_t ntokens,
+			  uint32_t* d_doc_results, uint32_t* d_doc_items, sp_matcher_stats* d_doc_stats, uint32_t* d_doc_flags, cudaStream_t stream)
+{
+	if (!m->uploaded) throw std::runtime_error( "rule tables are not on the device: call sp_matcher_upload first (the no-alloc entry point does not allocate them)");
+	if (!m->dev.eval_capable) throw std::runtime_error( "the rule set needs the state machine, which works on allocated arenas: no no-alloc count for it");
+	if (ntokens > SP_NOALLOC_MAX_TOKENS) throw std::runtime_error( "batch beyond the limit of the no-alloc entry point: more than SP_NOALLOC_MAX_TOKENS tokens");
+	if (ndocs > SP_NOALLOC_MAX_DOCS) throw std::runtime_error( "batch beyond the limit of the no-alloc entry point: more than SP_NOALLOC_MAX_DOCS documents");
+	if (!ndocs) return;
+	if (!d_tokens || !d_tok_off || !d_doc_results || !d_doc_items || !d_doc_stats || !d_doc_flags) throw std::runtime_error( "null pointer passed to the no-alloc entry point");
+	int dev = -1, nsm = 0;
+	SP_CUDA( cudaGetDevice( &dev));
+	if (dev != m->device) throw std::runtime_error( "matcher tables live on another device than the current one");
+	NoAllocCarver S( noallocScratchBase( dev, nsm));
+
+	EvalParams E; std::memset( &E, 0, sizeof(E));
+	E.T = m->dev; E.tokens = d_tokens; E.origsegs = 0; E.tok_off = d_tok_off; E.ndocs = ndocs; E.ntokens = ntokens;
+	E.tok_slot = S.take<uint32_t>( SP_NOALLOC_MAX_TOKENS); E.tok_work = S.take<uint32_t>( SP_NOALLOC_MAX_TOKENS); E.tok_doc = S.take<uint32_t>( SP_NOALLOC_MAX_TOKENS);
+	uint64_t* d_tok_work_off = S.take<uint64_t>( SP_NOALLOC_MAX_TOKENS + 1);
+	E.tok_nres = S.take<uint32_t>( SP_NOALLOC_MAX_TOKENS); E.tok_nitems = S.take<uint32_t>( SP_NOALLOC_MAX_TOKENS);
+	uint64_t* d_tok_res_off = S.take<uint64_t>( SP_NOALLOC_MAX_TOKENS + 1);
+	uint64_t* d_tok_item_off = S.take<uint64_t>( SP_NOALLOC_MAX_TOKENS + 1);
+	E.tok_work_off = d_tok_work_off; E.tok_res_off = d_tok_res_off; E.tok_item_off = d_tok_item_off;
+	uint64_t* d_tilesum = S.take<uint64_t>( (SP_NOALLOC_MAX_TOKENS + ScanTile - 1) / ScanTile);
+	E.resbits = S.take<uint32_t>( SP_NOALLOC_MAX_RULES / 32 + 2);
+	E.queue = S.take<unsigned long long>( SP_NOALLOC_QUEUE); E.queue_cap = SP_NOALLOC_QUEUE;
+	uint32_t* d_status = S.take<uint32_t>( SP_NOALLOC_MAX_DOCS);
+	uint32_t* d_flag_list = S.take<uint32_t>( SP_NOALLOC_MAX_DOCS);
+	uint64_t* d_scalars = S.take<uint64_t>( 4);		// [0] results [1] items [2] flagged documents [3] queued rules
+	if (S.used > SP_NOALLOC_SCRATCH_BYTES) throw std::logic_error( "scratch layout of the no-alloc entry point exceeds its array");
+	E.queue_count = reinterpret_cast<unsigned long long*>( d_scalars + 3);
+	E.stats = d_doc_stats; E.flags = d_doc_flags;
+
+	// everything that has to start at zero (the array holds what the last call left)
+	SP_CUDA( cudaMemsetAsync( d_doc_flags, 0, (std::size_t)ndocs * sizeof(uint32_t), stream));
+	SP_CUDA( cudaMemsetAsync( d_doc_stats, 0, (std::size_t)ndocs * sizeof(sp_matcher_stats), stream));
+	SP_CUDA( cudaMemsetAsync( d_scalars, 0, 4 * sizeof(uint64_t), stream));
+	uint64_t host[ 4] = {0,0,0,0};
+	if (ntokens)
+	{
+		k_eval_prepare<<<(unsigned int)((ntokens + 255) / 256), 256, 0, stream>>>( E);
+		noallocScan( E.tok_work, ntokens, d_tok_work_off, d_tilesum, stream);
+		SP_CUDA( cudaMemcpyAsync( host, d_tok_work_off + ntokens, sizeof(uint64_t), cudaMemcpyDeviceToHost, stream));
+		SP_CUDA( cudaStreamSynchronize( stream));
+		const uint64_t nwork = host[ 0];
+		if (nwork > SP_NOALLOC_MAX_RULES) throw std::runtime_error( "batch beyond the limit of the no-alloc entry point: more than SP_NOALLOC_MAX_RULES rule instances");
+		SP_CUDA( cudaMemsetAsync( E.resbits, 0, (nwork / 32 + 2) * sizeof(uint32_t), stream));
+		const uint64_t ntiles = (ntokens + EvalTile - 1) / EvalTile;
+		k_eval_count_join<<<(unsigned int)((ntiles + EvalWarpsPerBlock - 1) / EvalWarpsPerBlock), EvalThreads, 0, stream>>>( E);
+		k_eval_count_full<<<(unsigned int)nsm * 8, 128, 0, stream>>>( E);
+		noallocScan( E.tok_nres, ntokens, d_tok_res_off, d_tilesum, stream);
+		noallocScan( E.tok_nitems, ntokens, d_tok_item_off, d_tilesum, stream);
+	}
+	else
+	{
+		SP_CUDA( cudaMemsetAsync( d_tok_res_off, 0, sizeof(uint64_t), stream));
+		SP_CUDA( cudaMemsetAsync( d_tok_item_off, 0, sizeof(uint64_t), stream));
+	}
+	k_eval_docs<<<(ndocs + 255) / 256, 256, 0, stream>>>( E, d_doc_results, d_doc_items, d_status, d_flag_list,
+							     reinterpret_cast<uint32_t*>( d_scalars + 2), reinterpret_cast<unsigned long long*>( d_scalars));
+	SP_CUDA( cudaGetLastError());
+	SP_CUDA( cudaMemcpyAsync( host, d_scalars, 4 * sizeof(uint64_t), cudaMemcpyDeviceToHost, stream));
+	SP_CUDA( cudaStreamSynchronize( stream));
+	if (host[ 3] > SP_NOALLOC_QUEUE) throw std::runtime_error( "batch beyond the limit of the no-alloc entry point: more than SP_NOALLOC_QUEUE rules need the full fold");
+}
+} // namespace
+
+extern "C" int sp_matcher_count_noalloc( sp_matcher* m, const sp_lexem* tokens_device, const uint64_t* tok_offsets_device, uint32_t ndocs, uint64_t ntokens,
+					 uint32_t* doc_results_device, uint32_t* doc_items_device, sp_matcher_stats* doc_stats_device, uint32_t* doc_flags_device, void* cuda_stream)
+{
+	SP_MATCHER_TRY( m, matcherCountNoAlloc( m, tokens_device, tok_offsets_device, ndocs, ntokens, doc_results_device, doc_items_device, doc_stats_device, doc_flags_device, (cudaStream_t)cuda_stream))
+}
