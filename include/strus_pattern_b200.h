@@ -70,11 +70,17 @@ typedef struct sp_result
 	uint32_t item_count;
 } sp_result;
 
-/* One result item = analyzer::PatternMatcherResultItem (src/patternMatcher.cpp:164-190). */
+/* One result item = analyzer::PatternMatcherResultItem (src/patternMatcher.cpp:164-190).
+ * `format`: low half = format handle of the sub expression the item refers to (0 = none: the value of the item is the
+ * piece of the source it spans), high half = number of NESTED records that follow the item: the items of that sub
+ * expression, which the reference hands to the formatter instead of the caller (:172-181). A consumer that lists the
+ * items of a result skips them (i += 1 + SP_ITEM_NESTED(item)); sp_matcher_item_value maps them into the value string. */
+#define SP_ITEM_FORMAT( it)  ((it).format & 0xFFFFu)
+#define SP_ITEM_NESTED( it)  ((it).format >> 16)
 typedef struct sp_item
 {
 	uint32_t variable;    /* variable handle: sp_matcher_variable_name(m, variable) */
-	uint32_t format;
+	uint32_t format;      /* SP_ITEM_FORMAT | SP_ITEM_NESTED << 16 */
 	uint32_t ordpos;
 	uint32_t ordend;
 	uint32_t origseg;
@@ -183,6 +189,20 @@ const char* sp_matcher_pattern_name( const sp_matcher* m, uint32_t handle);    /
 const char* sp_matcher_variable_name( const sp_matcher* m, uint32_t handle);   /* variableMap.key, :170 */
 /* format string of a format handle (sp_result.format / sp_item.format), resultFormatHandles, :560-566 */
 const char* sp_matcher_format_string( const sp_matcher* m, uint32_t handle);
+/* Value strings = PatternMatcherResult::value / PatternMatcherResultItem::value (src/patternMatcher.cpp:253-262, :172-181;
+ * the formatter is strusAnalyzer's PatternResultFormat, restated in csrc/result_format.hpp). `result` and `doc_items`
+ * are records of one document as sp_matcher_fetch delivers them (doc_items = items + item_offsets[d]); `item` points
+ * into such an array (its nested records follow it). Returns the length of the value (the first `capacity` bytes are
+ * written, no terminator: call again with a larger buffer if the length exceeds it), SP_NO_VALUE if the record has no
+ * format string (the reference's value is NULL then), or a negative SP_ERR_*. A result WITH a format string has no
+ * visible items (the reference passes them to the formatter): all its records are material of the value.
+ * The matcher does not see the source text: a span of the source is written into the value as a reference
+ * "\x01" seg "," pos "," endseg "," endpos "\x02" (decimal numbers); sp_resolve_value replaces the references of
+ * segment 0 by the bytes of `source` (same return convention). */
+#define SP_NO_VALUE -100
+int64_t sp_matcher_result_value( const sp_matcher* m, const sp_result* result, const sp_item* doc_items, char* buf, uint64_t capacity);
+int64_t sp_matcher_item_value( const sp_matcher* m, const sp_item* item, char* buf, uint64_t capacity);
+int64_t sp_resolve_value( const char* value, uint64_t value_len, const uint8_t* source, uint64_t source_len, char* buf, uint64_t capacity);
 int64_t sp_matcher_table_info( const sp_matcher* m, const char* key);
 
 sp_matcher_ctx* sp_matcher_ctx_create( sp_matcher* m, void* cuda_stream);      /* :586 */

@@ -37,6 +37,9 @@ struct RefMatcher
 	std::vector<uint64_t> item_offsets;
 	std::vector<sp_matcher_stats> stats;
 	std::vector<uint32_t> status;
+	// value strings (PatternMatcherResult::value / PatternMatcherResultItem::value) parallel to results / items; NULL values have no entry in *_hasvalue
+	std::vector<std::string> result_values, item_values;
+	std::vector<char> result_hasvalue, item_hasvalue;
 
 	RefMatcher() :errorhnd(0),factory(0),inst(0){}
 	~RefMatcher() {delete inst; delete factory; delete errorhnd;}
@@ -61,6 +64,8 @@ struct DocOut
 	std::vector<sp_item> items;
 	std::vector<std::string> resnames;	// parallel to results
 	std::vector<std::string> itemnames;	// parallel to items
+	std::vector<std::string> resvalues, itemvalues;
+	std::vector<char> reshasvalue, itemhasvalue;
 	sp_matcher_stats stats;
 	uint32_t status;
 };
@@ -148,6 +153,7 @@ static void runDocument( const strus::PatternMatcherInstanceInterface* inst, str
 		r.item_begin = (uint32_t)out.items.size(); r.item_count = (uint32_t)ri->items().size();
 		out.results.push_back( r);
 		out.resnames.push_back( ri->name() ? ri->name() : "");
+		out.resvalues.push_back( ri->value() ? ri->value() : ""); out.reshasvalue.push_back( ri->value() ? 1 : 0);
 		std::vector<strus::analyzer::PatternMatcherResultItem>::const_iterator ii = ri->items().begin(), ie = ri->items().end();
 		for (; ii != ie; ++ii)
 		{
@@ -158,6 +164,7 @@ static void runDocument( const strus::PatternMatcherInstanceInterface* inst, str
 			it.endseg = ii->origend().seg(); it.endpos = ii->origend().ofs();
 			out.items.push_back( it);
 			out.itemnames.push_back( ii->name() ? ii->name() : "");
+			out.itemvalues.push_back( ii->value() ? ii->value() : ""); out.itemhasvalue.push_back( ii->value() ? 1 : 0);
 		}
 	}
 }
@@ -182,6 +189,7 @@ int refm_run_batch( void* h, const sp_lexem* tokens, const uint32_t* origsegs, c
 	rm->results.clear(); rm->items.clear();
 	rm->result_offsets.assign( 1, 0); rm->item_offsets.assign( 1, 0);
 	rm->stats.clear(); rm->status.clear();
+	rm->result_values.clear(); rm->item_values.clear(); rm->result_hasvalue.clear(); rm->item_hasvalue.clear();
 	for (uint32_t d=0; d<ndocs; ++d)
 	{
 		DocOut& o = outs[d];
@@ -190,6 +198,10 @@ int refm_run_batch( void* h, const sp_lexem* tokens, const uint32_t* origsegs, c
 			for (std::size_t i=0; i<o.results.size(); ++i) {o.results[i].name = rm->nameIndex( o.resnames[i].c_str()); rm->results.push_back( o.results[i]);}
 			for (std::size_t i=0; i<o.items.size(); ++i) {o.items[i].variable = rm->nameIndex( o.itemnames[i].c_str()); rm->items.push_back( o.items[i]);}
 			rm->result_offsets.push_back( rm->results.size());
+			rm->result_values.insert( rm->result_values.end(), o.resvalues.begin(), o.resvalues.end());
+			rm->result_hasvalue.insert( rm->result_hasvalue.end(), o.reshasvalue.begin(), o.reshasvalue.end());
+			rm->item_values.insert( rm->item_values.end(), o.itemvalues.begin(), o.itemvalues.end());
+			rm->item_hasvalue.insert( rm->item_hasvalue.end(), o.itemhasvalue.begin(), o.itemhasvalue.end());
 		}
 		else
 		{
@@ -214,6 +226,21 @@ int refm_fetch( void* h, sp_result* results, uint64_t* result_offsets, sp_item* 
 	if (status && !rm->status.empty()) std::memcpy( status, rm->status.data(), rm->status.size()*sizeof(uint32_t));
 	return 0;
 }
+// Value string of result / item `idx` (index into the fetched arrays) of the last batch: length (the first `capacity` bytes
+// are written), SP_NO_VALUE if the reference delivered NULL.
+static int64_t valueOut( const std::vector<std::string>& values, const std::vector<char>& has, uint64_t idx, char* buf, uint64_t capacity)
+{
+	if (idx >= values.size()) return SP_ERR_ARGUMENT;
+	if (!has[ idx]) return SP_NO_VALUE;
+	const std::string& v = values[ idx];
+	if (buf && capacity) std::memcpy( buf, v.data(), (std::size_t)(capacity < v.size() ? capacity : v.size()));
+	return (int64_t)v.size();
+}
+int64_t refm_result_value( void* h, uint64_t idx, char* buf, uint64_t capacity)
+	{RefMatcher* rm=(RefMatcher*)h; return valueOut( rm->result_values, rm->result_hasvalue, idx, buf, capacity);}
+int64_t refm_item_value( void* h, uint64_t idx, char* buf, uint64_t capacity)
+	{RefMatcher* rm=(RefMatcher*)h; return valueOut( rm->item_values, rm->item_hasvalue, idx, buf, capacity);}
+
 // Name of a result (sp_result.name) or item (sp_item.variable) index of this oracle's string table.
 const char* refm_name( void* h, uint32_t idx)
 {

@@ -22,6 +22,8 @@ ITEM_DT = np.dtype([(n, "<u4") for n in ("variable", "format", "ordpos", "ordend
 STATS_DT = np.dtype([(n, "<u8") for n in ("nof_programs_installed", "nof_altkey_programs_installed",
                                            "nof_signals_fired", "nof_open_patterns", "nof_events")])
 
+NO_VALUE = -100     # SP_NO_VALUE
+
 BIND_CONTENT, BIND_SUCCESSOR, BIND_PREDECESSOR, BIND_UNIQUE = 0, 1, 2, 3
 OP_SEQUENCE, OP_SEQUENCE_IMM, OP_SEQUENCE_STRUCT, OP_WITHIN, OP_WITHIN_STRUCT, OP_ANY, OP_AND = range(7)
 
@@ -79,6 +81,9 @@ def lib():
             "sp_matcher_fetch": (C.c_int, [vp, vp, vp, vp, vp, vp, vp]),
             "sp_matcher_run_lexer_output": (C.c_int, [vp, vp]),
             "sp_matcher_fetch_range": (C.c_int, [vp, u32, u32, vp, C.c_uint64, vp, vp, C.c_uint64, vp, vp, vp]),
+            "sp_matcher_result_value": (C.c_int64, [vp, vp, vp, vp, C.c_uint64]),
+            "sp_matcher_item_value": (C.c_int64, [vp, vp, vp, C.c_uint64]),
+            "sp_resolve_value": (C.c_int64, [vp, C.c_uint64, vp, C.c_uint64, vp, C.c_uint64]),
             "sp_matcher_count_noalloc": (C.c_int, [vp, vp, vp, u32, C.c_uint64, vp, vp, vp, vp, vp]),
         }
         for table in (sigs, msigs):
@@ -87,6 +92,20 @@ def lib():
                 f.restype, f.argtypes = res, args
         _lib = L
     return _lib
+
+
+def resolve_value(value, source):
+    """sp_resolve_value: the span references of a value string replaced by the bytes of `source` (segment 0)."""
+    if value is None:
+        return None
+    src = np.ascontiguousarray(np.frombuffer(bytes(source), dtype=np.uint8)) if not isinstance(source, np.ndarray) else np.ascontiguousarray(source, dtype=np.uint8)
+    L = lib()
+    n = int(L.sp_resolve_value(value, len(value), _ptr(src), len(src), None, 0))
+    if n < 0:
+        raise PatternError(n, "corrupt value string")
+    buf = C.create_string_buffer(n + 1)
+    L.sp_resolve_value(value, len(value), _ptr(src), len(src), buf, n)
+    return buf.raw[:n]
 
 
 def _ptr(a):
@@ -232,7 +251,68 @@ class LexerContext:
         return self.fetch()
 
 
-class Matcher:
+class ValueStrings:
+    """visible_results for classes that provide _result_value( result_ptr, doc_items_ptr, buf, n) and
+    _item_value( item_ptr, buf, n) with the return convention of sp_matcher_result_value."""
+
+    def _value(self, call):
+        n = int(call(None, 0))
+        if n == NO_VALUE:
+            return None
+        if n < 0:
+            raise PatternError(n, "value string: corrupt item list or unknown format handle")
+        buf = C.create_string_buffer(n + 1)
+        call(buf, n)
+        return buf.raw[:n]
+
+    def visible_results(self, out):
+        """The output of a run (fetch / run) as a caller of the reference's fetchResults sees it (src/patternMatcher.cpp:164-190,
+        248-269): per document the same arrays without the nested records (the items of a result with a format string and of
+        an item that refers to a formatted sub expression are the material of the value string, not items), plus
+        "result_values" / "item_values": bytes, or None where the reference delivers NULL. Span references inside the values
+        are resolved with resolve_value."""
+        item_size = ITEM_DT.itemsize
+        results, items = out["results"].copy(), out["items"]
+        base = items.ctypes.data
+        keep, rvals, ivals = [], [], []
+        io = out["item_offsets"]
+        ro = out["result_offsets"]
+        new_io = [0]
+        fmt = items["format"]
+        for d in range(len(ro) - 1):
+            ib = int(io[d])
+            for ri in range(int(ro[d]), int(ro[d + 1])):
+                r = results[ri]
+                first = len(keep) - new_io[-1]
+                if r["format"]:
+                    rp = C.c_void_p(results.ctypes.data + ri * RESULT_DT.itemsize)
+                    rvals.append(self._value(lambda b, n: self._result_value(rp, C.c_void_p(base + ib * item_size), b, C.c_uint64(n))))
+                else:
+                    rvals.append(None)
+                    k, e = ib + int(r["item_begin"]), ib + int(r["item_begin"]) + int(r["item_count"])
+                    while k < e:
+                        f = int(fmt[k])
+                        keep.append(k)
+                        if f & 0xFFFF:
+                            ip = C.c_void_p(base + k * item_size)
+                            ivals.append(self._value(lambda b, n: self._item_value(ip, b, C.c_uint64(n))))
+                        else:
+                            ivals.append(None)
+                        k += 1 + (f >> 16)
+                results[ri]["item_begin"] = first
+                results[ri]["item_count"] = len(keep) - new_io[-1] - first
+            new_io.append(len(keep))
+        vis = dict(out)
+        vis["results"] = results
+        vis["items"] = items[np.array(keep, dtype=np.int64)] if keep else items[:0]
+        vis["items"]["format"] &= 0xFFFF
+        vis["item_offsets"] = np.array(new_io, dtype=np.uint64)
+        vis["result_values"], vis["item_values"] = rvals, ivals
+        return vis
+
+
+
+class Matcher(ValueStrings):
     """PatternMatcherInstanceInterface over the C ABI; same method names as oracle_util.RefMatcher."""
 
     def __init__(self):
@@ -287,6 +367,12 @@ class Matcher:
 
     def create_context(self, stream=None):
         return MatcherContext(self, stream)
+
+    def _result_value(self, rp, itemsp, buf, n):
+        return self.L.sp_matcher_result_value(self.h, rp, itemsp, buf, n)
+
+    def _item_value(self, ip, buf, n):
+        return self.L.sp_matcher_item_value(self.h, ip, buf, n)
 
     def upload(self):
         self._ck(self.L.sp_matcher_upload(self.h))

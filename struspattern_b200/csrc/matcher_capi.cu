@@ -7,6 +7,7 @@
 #include "matcher_eval_kernels.cuh"
 #include "device_util.cuh"
 #include <vector>
+#include <algorithm>
 #include <string>
 #include <cstring>
 #include <cstdlib>
@@ -91,6 +92,42 @@ int sp_matcher_upload( sp_matcher* m)
 const char* sp_matcher_pattern_name( const sp_matcher* m, uint32_t handle) {return m->prog.patternName( handle);}
 const char* sp_matcher_variable_name( const sp_matcher* m, uint32_t handle) {return m->prog.variableName( handle);}
 const char* sp_matcher_format_string( const sp_matcher* m, uint32_t handle) {return m->prog.formatString( handle);}
+
+static int64_t valueOut( const std::string& val, char* buf, uint64_t capacity)
+{
+	if (buf && capacity) std::memcpy( buf, val.data(), (std::size_t)std::min<uint64_t>( capacity, val.size()));
+	return (int64_t)val.size();
+}
+int64_t sp_matcher_result_value( const sp_matcher* m, const sp_result* result, const sp_item* doc_items, char* buf, uint64_t capacity)
+{
+	try
+	{
+		std::string val;
+		if (!m->prog.resultValue( *result, doc_items, val)) return SP_NO_VALUE;
+		return valueOut( val, buf, capacity);
+	}
+	catch (const std::exception& e) {const_cast<sp_matcher*>( m)->lasterror = e.what(); return SP_ERR_ARGUMENT;}
+}
+int64_t sp_matcher_item_value( const sp_matcher* m, const sp_item* item, char* buf, uint64_t capacity)
+{
+	try
+	{
+		std::string val;
+		if (!m->prog.itemValue( item, val)) return SP_NO_VALUE;
+		return valueOut( val, buf, capacity);
+	}
+	catch (const std::exception& e) {const_cast<sp_matcher*>( m)->lasterror = e.what(); return SP_ERR_ARGUMENT;}
+}
+int64_t sp_resolve_value( const char* value, uint64_t value_len, const uint8_t* source, uint64_t source_len, char* buf, uint64_t capacity)
+{
+	try
+	{
+		std::string val;
+		resolveValue( value, (std::size_t)value_len, source, (std::size_t)source_len, val);
+		return valueOut( val, buf, capacity);
+	}
+	catch (const std::exception&) {return SP_ERR_ARGUMENT;}
+}
 
 int64_t sp_matcher_table_info( const sp_matcher* m, const char* key)
 {

@@ -792,11 +792,15 @@ SP_MHD void sp_mark_covered( const SpMatcherTables& T, SpArena& A, SpDocState& S
 	}
 }
 
-// gatherResultItems without recursion: items of `dataref` in list order, the items of a sub expression (that has
-// no format of its own) directly behind the item that refers to it. out == 0: count only. Returns the item count.
+// gatherResultItems without recursion: items of `dataref` in list order, the items of a sub expression directly behind
+// the item that refers to it. A sub expression without a format of its own joins the list of its parent
+// (src/patternMatcher.cpp:185-188); the items of one WITH a format are what its value string is made of (:172-181): they
+// follow their owner as nested records, their number in the high half of the owner's `format` (SP_ITEM_NESTED in
+// include/strus_pattern_b200.h), so that the host side can map them into the value and hide them from the item list.
+// out == 0: count only. Returns the number of records.
 SP_MHD uint32_t sp_gather_items( const SpArena& A, SpDocState& S, uint32_t dataref, sp_item* out)
 {
-	uint32_t stack[ SP_GATHER_DEPTH]; int depth = 0;
+	uint32_t stack[ SP_GATHER_DEPTH]; uint32_t owner[ SP_GATHER_DEPTH]; int depth = 0;
 	uint32_t n = 0;
 	uint32_t it = A.datarefs[ dataref-1].items;
 	for (;;)
@@ -804,7 +808,14 @@ SP_MHD uint32_t sp_gather_items( const SpArena& A, SpDocState& S, uint32_t datar
 		if (!it)
 		{
 			if (depth == 0) break;
-			it = stack[ --depth];
+			--depth;
+			it = stack[ depth];
+			if (owner[ depth] != 0xFFFFFFFFu)
+			{
+				const uint32_t nested = n - owner[ depth] - 1;
+				if (nested > 0xFFFFu) {sp_fail( S, SP_MST_OVF_DEPTH); return n;}
+				if (out) out[ owner[ depth]].format |= nested << 16;
+			}
 			continue;
 		}
 		const SpItem& rec = A.items[ it-1];
@@ -819,10 +830,11 @@ SP_MHD uint32_t sp_gather_items( const SpArena& A, SpDocState& S, uint32_t datar
 		}
 		++n;
 		uint32_t nx = rec.next;
-		if (rec.data.subdataref && !rec.data.formathandle)
+		if (rec.data.subdataref)
 		{
 			if (depth >= SP_GATHER_DEPTH) {sp_fail( S, SP_MST_OVF_DEPTH); return n;}
-			stack[ depth++] = nx;
+			stack[ depth] = nx; owner[ depth] = rec.data.formathandle ? n - 1 : 0xFFFFFFFFu;
+			++depth;
 			it = A.datarefs[ rec.data.subdataref-1].items;
 		}
 		else it = nx;

@@ -14,6 +14,7 @@
 #define SP_MATCHER_PROGRAM_HPP_INCLUDED
 #include "matcher_tables.h"
 #include "strus_pattern_b200.h"
+#include "result_format.hpp"
 #include <vector>
 #include <string>
 #include <deque>
@@ -46,6 +47,11 @@ public:
 		if (it != m_index.end()) return it->second;
 		m_names.push_back( name);
 		return m_index[ name] = (uint32_t)m_names.size();
+	}
+	uint32_t get( const std::string& name) const
+	{
+		std::unordered_map<std::string,uint32_t>::const_iterator it = m_index.find( name);
+		return it == m_index.end() ? 0 : it->second;
 	}
 	const char* key( uint32_t handle) const {return (handle == 0 || handle > m_names.size()) ? 0 : m_names[ handle-1].c_str();}
 	std::size_t size() const {return m_names.size();}
@@ -184,7 +190,11 @@ public:
 		uint32_t formatHandle = 0;
 		if (!formatstring.empty())
 		{
+			// createResultFormat (src/patternMatcher.cpp:562-565): parsed now, its variables must be known now
+			if (m_formats.size() >= 0xFFFFu) throw std::runtime_error( "too many result format strings (65535 at most)");
+			ResultFormat parsed = parseResultFormat( formatstring, [this]( const std::string& vn) -> uint32_t {return m_variables.get( vn);});
 			m_formats.push_back( formatstring);
+			m_parsedFormats.push_back( parsed);
 			formatHandle = (uint32_t)m_formats.size();
 		}
 		uint32_t program = top.program;
@@ -260,6 +270,20 @@ public:
 	const char* patternName( uint32_t handle) const {return m_patterns.key( handle);}
 	const char* variableName( uint32_t handle) const {return m_variables.key( handle);}
 	const char* formatString( uint32_t handle) const {return (handle == 0 || handle > m_formats.size()) ? 0 : m_formats[ handle-1].c_str();}
+	// PatternMatcherResult::value (src/patternMatcher.cpp:253-262); false: the result has no format string (value NULL)
+	bool resultValue( const sp_result& r, const sp_item* docitems, std::string& out) const
+	{
+		if (!r.format) return false;
+		mapResultFormat( m_parsedFormats, r.format, docitems + r.item_begin, r.item_count, out);
+		return true;
+	}
+	// PatternMatcherResultItem::value (:172-181); the nested records of the item follow it
+	bool itemValue( const sp_item* item, std::string& out) const
+	{
+		if (!SP_ITEM_FORMAT( *item)) return false;
+		mapResultFormat( m_parsedFormats, SP_ITEM_FORMAT( *item), item + 1, SP_ITEM_NESTED( *item), out);
+		return true;
+	}
 	bool exclusive() const {return m_exclusive;}
 	uint32_t maxResultSize() const {return m_maxResultSize;}
 	std::size_t nofPrograms() const {return m_rules.size();}
@@ -398,6 +422,9 @@ private:
 						const SpTriggerDef& def = T.trigger_defs[ P.trig_begin + d];
 						if (def.event == slot.key - 1) {F.sub = def.variable ? 1 : 0; break;}	// the first signal emits
 					}
+					// an item that refers to F carries F's own items as nested records behind it (the value string is made of
+					// them, sp_gather_items): only the state machine writes those
+					if (F.format && F.sub) capable = false;
 					for (uint32_t e = sp_event_slot_hash( F.event) & (nslots-1); T.event_slots[ e].key; e = (e + 1) & (nslots-1))
 					{
 						if (T.event_slots[ e].key == F.event + 1) {F.eslot = e; break;}
@@ -672,6 +699,7 @@ private:
 	std::map<uint32_t,double> m_frequency;
 	NameTable m_patterns, m_variables;
 	std::vector<std::string> m_formats;
+	std::vector<ResultFormat> m_parsedFormats;
 	uint32_t m_expressionEventCnt, m_totalNofPrograms;
 	float m_stopwordOccurrenceFactor, m_weightFactor;
 	uint32_t m_maxRange, m_maxResultSize;

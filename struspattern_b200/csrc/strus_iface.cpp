@@ -22,6 +22,7 @@
 #include <string>
 #include <vector>
 #include <map>
+#include <deque>
 #include <stdexcept>
 #include <limits>
 #include <new>
@@ -255,20 +256,31 @@ public:
 			run();
 			std::vector<strus::analyzer::PatternMatcherResult> rt;
 			rt.reserve( m_results.size());
+			m_values.clear();	// the value strings live in the context, like the reference's PatternResultFormatContext buffer
 			for (const sp_result& r: m_results)
 			{
-				if (r.format) throw CallError( SP_ERR_UNSUPPORTED, "result format strings are not implemented");
 				std::vector<strus::analyzer::PatternMatcherResultItem> items;
-				items.reserve( r.item_count);
-				for (uint32_t k=0; k<r.item_count; ++k)
+				const char* resultValue = 0;
+				if (r.format)
 				{
-					const sp_item& it = m_items[ r.item_begin + k];
-					items.push_back( strus::analyzer::PatternMatcherResultItem(
-						sp_matcher_variable_name( m_matcher, it.variable), 0, (int)it.ordpos, (int)it.ordend,
-						strus::analyzer::Position( (int)it.origseg, (int)it.origpos), strus::analyzer::Position( (int)it.endseg, (int)it.endpos)));
+					// the items are the material of the value (src/patternMatcher.cpp:253-262)
+					resultValue = valueString( sp_matcher_result_value( m_matcher, &r, m_items.data(), 0, 0), &r, 0);
+				}
+				else
+				{
+					items.reserve( r.item_count);
+					for (uint32_t k=0; k<r.item_count; k += 1 + SP_ITEM_NESTED( m_items[ r.item_begin + k]))
+					{
+						const sp_item& it = m_items[ r.item_begin + k];
+						const char* itemValue = 0;
+						if (SP_ITEM_FORMAT( it)) itemValue = valueString( sp_matcher_item_value( m_matcher, &it, 0, 0), 0, &it);	// :172-181
+						items.push_back( strus::analyzer::PatternMatcherResultItem(
+							sp_matcher_variable_name( m_matcher, it.variable), itemValue, (int)it.ordpos, (int)it.ordend,
+							strus::analyzer::Position( (int)it.origseg, (int)it.origpos), strus::analyzer::Position( (int)it.endseg, (int)it.endpos)));
+					}
 				}
 				rt.push_back( strus::analyzer::PatternMatcherResult(
-					sp_matcher_pattern_name( m_matcher, r.name), 0, (int)r.ordpos, (int)r.ordend,
+					sp_matcher_pattern_name( m_matcher, r.name), resultValue, (int)r.ordpos, (int)r.ordend,
 					strus::analyzer::Position( (int)r.origseg, (int)r.origpos), strus::analyzer::Position( (int)r.endseg, (int)r.endpos), items));
 			}
 			return rt;
@@ -293,7 +305,7 @@ public:
 	}
 	virtual void reset()
 	{
-		m_tokens.clear(); m_segs.clear(); m_results.clear(); m_items.clear();
+		m_tokens.clear(); m_segs.clear(); m_results.clear(); m_items.clear(); m_values.clear();
 		std::memset( &m_stats, 0, sizeof(m_stats));
 		m_curPosition = 0; m_dirty = true;
 	}
@@ -314,10 +326,21 @@ private:
 		m_dirty = false;
 		if (status) throw std::runtime_error( "error in pattern matching automaton (rule set inconsistency or limit exceeded)");
 	}
+	// value string of a result (r) or of an item (it) of the length the first call told; kept until the next fetchResults
+	const char* valueString( int64_t len, const sp_result* r, const sp_item* it)
+	{
+		if (len == SP_NO_VALUE) return 0;
+		if (len < 0) throw CallError( (int)len, sp_matcher_last_error( m_matcher));
+		m_values.push_back( std::string( (std::size_t)len, '\0'));
+		std::string& val = m_values.back();
+		if (len) (void)(r ? sp_matcher_result_value( m_matcher, r, m_items.data(), &val[0], (uint64_t)len) : sp_matcher_item_value( m_matcher, it, &val[0], (uint64_t)len));
+		return val.c_str();
+	}
 
 	strus::ErrorBufferInterface* m_errorhnd;
 	sp_matcher* m_matcher;
 	sp_matcher_ctx* m_ctx;
+	std::deque<std::string> m_values;
 	unsigned int m_curPosition;
 	bool m_dirty;
 	std::vector<sp_lexem> m_tokens;

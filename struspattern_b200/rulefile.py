@@ -11,7 +11,9 @@ restated from the published examples (reference doc/webpage/introduction_struspa
     term       := LEXEMNAME ["symbol"]  |  PatternName
 
 Lexem ids are assigned in the order of first appearance (1, 2, ...), symbol ids behind them. Lines starting with '#'
-are comments."""
+are comments. An expression without "| range" gets range argc-1 if it is a sequence_imm (the article's examples omit it
+there), else 0. A format string in square brackets behind the expression is the value of the pattern
+(…htm:143-161; csrc/result_format.hpp)."""
 import re
 
 from .capi import BIND_CONTENT
@@ -148,7 +150,7 @@ def load(text, lexer, matcher, compile_=True):
             raise RuleSyntaxError("identifier expected in expression, found %r" % name)
         if name in OPERATORS and sc2.accept("("):
             argc = 0
-            rng, card = 0, 0
+            rng, card = None, 0
             while True:
                 kind, val, end = sc2.peek()
                 save = sc2.i
@@ -171,6 +173,10 @@ def load(text, lexer, matcher, compile_=True):
                         card = int(sc2.next()[1])
                 sc2.expect(")")
                 break
+            if rng is None:
+                # no range in the source (the article's sequence_imm examples, …htm:140, 156): the arguments of sequence_imm
+                # follow each other at once, so argc-1 positions span them when they are lexems; 0 (one position) otherwise
+                rng = argc - 1 if name == "sequence_imm" else 0
             matcher.push_expression(OPERATORS[name], argc, rng, card)
         elif name in prog.lexem_ids:
             if not sc2.eof() and sc2.peek()[0] == "str":
@@ -217,17 +223,28 @@ def format_tokens(prog, text, lexems):
     return out
 
 
-def format_results(text, out, result_name, item_name, base_offset=0, doc=0, values=None):
-    """the result listing of strusPatternMatch (…htm:232-236): Name [ordpos, origpos]: var [ordpos, origpos, size] 'text' ..."""
+def format_results(text, out, result_name, item_name, base_offset=0, doc=0, resolve=None):
+    """the result listing of strusPatternMatch (…htm:232-236): Name [ordpos, origpos]: var [ordpos, origpos, size] 'text' ...
+    `out` may be the caller's view with value strings (Matcher.visible_results / RefMatcher.run(values=True)): a result
+    with a format string prints its value (span references resolved against `text` by `resolve`, e.g.
+    struspattern_b200.capi.resolve_value) instead of items, an item with a value prints the value instead of its span."""
+    def value_text(v):
+        if resolve is not None:
+            v = resolve(v, text)
+        return bytes(v).decode("utf-8", "replace")
     lines = []
     ro, io = out["result_offsets"], out["item_offsets"]
-    items = out["items"][int(io[doc]):int(io[doc + 1])]
-    for ri, r in enumerate(out["results"][int(ro[doc]):int(ro[doc + 1])]):
+    rvals, ivals = out.get("result_values"), out.get("item_values")
+    ib = int(io[doc])
+    items = out["items"][ib:int(io[doc + 1])]
+    for ri in range(int(ro[doc]), int(ro[doc + 1])):
+        r = out["results"][ri]
         parts = []
-        for it in items[int(r["item_begin"]):int(r["item_begin"]) + int(r["item_count"])]:
+        for k in range(int(r["item_begin"]), int(r["item_begin"]) + int(r["item_count"])):
+            it = items[k]
             b, e = int(it["origpos"]), int(it["endpos"])
-            parts.append("%s [%d, %d, %d] '%s'" % (item_name(it["variable"]), int(it["ordpos"]), b + base_offset, e - b,
-                                                   bytes(text[b:e]).decode("utf-8", "replace")))
-        val = " %s" % values[ri] if values and values[ri] is not None else ""
+            shown = value_text(ivals[ib + k]) if ivals and ivals[ib + k] is not None else bytes(text[b:e]).decode("utf-8", "replace")
+            parts.append("%s [%d, %d, %d] '%s'" % (item_name(it["variable"]), int(it["ordpos"]), b + base_offset, e - b, shown))
+        val = " '%s'" % value_text(rvals[ri]) if rvals and rvals[ri] is not None else ""
         lines.append("%s [%d, %d]:%s %s" % (result_name(r["name"]), int(r["ordpos"]), int(r["origpos"]) + base_offset, val, " ".join(parts)))
     return [ln.rstrip() for ln in lines]

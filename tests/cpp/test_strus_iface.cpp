@@ -141,6 +141,65 @@ static int runMatcherCase( std::istream& in, strus::ErrorBufferInterface* errorh
 	return (int)results.size();
 }
 
+// Result format strings through the strus classes: the money amount example of the article
+// (doc/webpage/introduction_struspattern.htm:148-161): Currency = CURRENCY_CHF ["CHF"]; Currency = CURRENCY_EUR ["EUR"];
+// MoneyAmount = sequence_imm( value=AMOUNT, currency=Currency) ["{currency} {value}"].
+static int runFormatCase( strus::ErrorBufferInterface* errorhnd)
+{
+	enum {AMOUNT=1, CHF=2, EUR=3, WORD=4};
+	strus::local_ptr<strus::PatternMatcherInterface> pt( strus::createPatternMatcher_std( errorhnd));
+	strus::local_ptr<strus::PatternMatcherInstanceInterface> ptinst( pt->createInstance());
+	ptinst->pushTerm( CHF); ptinst->definePattern( "Currency", "CHF", true);
+	ptinst->pushTerm( EUR); ptinst->definePattern( "Currency", "EUR", true);
+	ptinst->pushTerm( AMOUNT); ptinst->attachVariable( "value");
+	ptinst->pushPattern( "Currency"); ptinst->attachVariable( "currency");
+	ptinst->pushExpression( strus::PatternMatcherInstanceInterface::OpSequenceImm, 2, 1, 0);
+	ptinst->definePattern( "MoneyAmount", "{currency} {value}", true);
+	ptinst->pushTerm( AMOUNT); ptinst->attachVariable( "value");
+	ptinst->pushPattern( "Currency"); ptinst->attachVariable( "currency");
+	ptinst->pushExpression( strus::PatternMatcherInstanceInterface::OpSequenceImm, 2, 1, 0);
+	ptinst->definePattern( "PlainAmount", "", true);
+	checkError( errorhnd, "define patterns with format strings");
+	ptinst->pushTerm( AMOUNT);
+	ptinst->definePattern( "Broken", "{nosuchvariable}", true);
+	if (!errorhnd->hasError()) throw std::runtime_error( "a format string with an unknown variable must be refused");
+	(void)errorhnd->fetchError();
+	if (!ptinst->compile()) {checkError( errorhnd, "compile"); throw std::runtime_error( "compile failed");}
+	strus::local_ptr<strus::PatternMatcherContextInterface> mt( ptinst->createContext());
+	// "pay 3'645 Eur or 12 sFr. now"
+	static const unsigned int toks[][3] = {{WORD,0,3},{AMOUNT,4,5},{EUR,10,3},{WORD,14,2},{AMOUNT,17,2},{CHF,20,4},{WORD,25,3}};
+	for (unsigned int i=0; i<7; ++i) mt->putInput( strus::analyzer::PatternLexem( toks[i][0], i+1, strus::analyzer::Position( 0, toks[i][1]), toks[i][2]));
+	std::vector<strus::analyzer::PatternMatcherResult> results = mt->fetchResults();
+	checkError( errorhnd, "fetch results with format strings");
+	std::set<std::string> got;
+	for (const strus::analyzer::PatternMatcherResult& r: results)
+	{
+		std::string key = std::string( r.name()) + "=" + (r.value() ? r.value() : "(null)");
+		if (std::string( r.name()) == "PlainAmount")
+		{
+			// no format string on the result: items visible, the item that refers to Currency carries Currency's value
+			if (r.value() || r.items().size() != 2) throw std::runtime_error( "unexpected items of a result without format string");
+			for (const strus::analyzer::PatternMatcherResultItem& it: r.items())
+			{
+				key += std::string( " ") + it.name() + "=" + (it.value() ? it.value() : "(null)");
+			}
+		}
+		else if (!r.items().empty()) throw std::runtime_error( "a result with a format string must not have items");
+		got.insert( key);
+	}
+	std::set<std::string> expected;
+	expected.insert( "Currency=EUR"); expected.insert( "Currency=CHF");
+	expected.insert( "MoneyAmount=EUR \x01" "0,4,0,9\x02"); expected.insert( "MoneyAmount=CHF \x01" "0,17,0,19\x02");
+	expected.insert( "PlainAmount currency=EUR value=(null)"); expected.insert( "PlainAmount currency=CHF value=(null)");
+	if (got != expected)
+	{
+		std::string msg( "values differ from the expected:");
+		for (const std::string& g: got) msg += " [" + g + "]";
+		throw std::runtime_error( msg);
+	}
+	return (int)results.size();
+}
+
 int main( int argc, const char** argv)
 {
 	if (argc < 2) {std::cerr << "usage: test_strus_iface <casefile> [<module.so>]" << std::endl; return 2;}
@@ -153,6 +212,7 @@ int main( int argc, const char** argv)
 		while (std::getline( in, line))
 		{
 			if (line == "LEXER") {std::cout << "lexer case: " << runLexerCase( in, errorhnd.get()) << " lexems OK" << std::endl; ++ncases;}
+			else if (line == "FORMATS") {std::cout << "format case: " << runFormatCase( errorhnd.get()) << " results OK" << std::endl; ++ncases;}
 			else if (line == "MATCHER") {std::cout << "matcher case: " << runMatcherCase( in, errorhnd.get()) << " results OK" << std::endl; ++ncases;}
 		}
 		if (argc > 2)

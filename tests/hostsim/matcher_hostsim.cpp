@@ -253,6 +253,21 @@ int msim_fetch( void* h, sp_result* results, uint64_t* result_offsets, sp_item* 
 	if (status && !ms->status.empty()) std::memcpy( status, ms->status.data(), ms->status.size()*sizeof(uint32_t));
 	return 0;
 }
+static int64_t valueOut( const std::string& val, char* buf, uint64_t capacity)
+{
+	if (buf && capacity) std::memcpy( buf, val.data(), (std::size_t)(capacity < val.size() ? capacity : val.size()));
+	return (int64_t)val.size();
+}
+int64_t msim_result_value( void* h, const sp_result* result, const sp_item* doc_items, char* buf, uint64_t capacity)
+{
+	try {std::string val; if (!((MatcherSim*)h)->prog.resultValue( *result, doc_items, val)) return SP_NO_VALUE; return valueOut( val, buf, capacity);}
+	catch (const std::exception& e) {((MatcherSim*)h)->lasterror = e.what(); return SP_ERR_ARGUMENT;}
+}
+int64_t msim_item_value( void* h, const sp_item* item, char* buf, uint64_t capacity)
+{
+	try {std::string val; if (!((MatcherSim*)h)->prog.itemValue( item, val)) return SP_NO_VALUE; return valueOut( val, buf, capacity);}
+	catch (const std::exception& e) {((MatcherSim*)h)->lasterror = e.what(); return SP_ERR_ARGUMENT;}
+}
 const char* msim_pattern_name( void* h, uint32_t handle) {const char* s = ((MatcherSim*)h)->prog.patternName( handle); return s ? s : "";}
 const char* msim_variable_name( void* h, uint32_t handle) {const char* s = ((MatcherSim*)h)->prog.variableName( handle); return s ? s : "";}
 int64_t msim_info( void* h, const char* key)

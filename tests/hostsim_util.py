@@ -7,6 +7,7 @@ import subprocess
 import numpy as np
 
 from oracle_util import LEXEM_DT, _ptr
+from struspattern_b200.capi import ValueStrings
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 HS_DIR = os.path.join(ROOT, "tests", "hostsim")
@@ -127,7 +128,7 @@ def build_hostsim_matcher(force=False):
                     "-I", os.path.join(ROOT, "struspattern_b200", "csrc"), "-o", HS_MATCHER_LIB, srcs[0]], check=True)
 
 
-class HostSimMatcher:
+class HostSimMatcher(ValueStrings):
     """The product's rule-graph builder + per-document state machine run on the CPU (tests/hostsim/matcher_hostsim.cpp).
     Same interface as oracle_util.RefMatcher."""
     _lib = None
@@ -143,6 +144,8 @@ class HostSimMatcher:
             for f in ("msim_result_count", "msim_item_count", "msim_retries"):
                 getattr(L, f).restype = C.c_uint64
             L.msim_info.restype = C.c_int64
+            L.msim_result_value.restype = C.c_int64
+            L.msim_item_value.restype = C.c_int64
             cls._lib = L
         return cls._lib
 
@@ -207,6 +210,12 @@ class HostSimMatcher:
         self.L.msim_fetch(self.h, _ptr(out["results"]) if nres else None, _ptr(out["result_offsets"]),
                           _ptr(out["items"]) if nitems else None, _ptr(out["item_offsets"]), _ptr(out["stats"]), _ptr(out["status"]))
         return out
+
+    def _result_value(self, rp, itemsp, buf, n):
+        return self.L.msim_result_value(self.h, rp, itemsp, buf, n)
+
+    def _item_value(self, ip, buf, n):
+        return self.L.msim_item_value(self.h, ip, buf, n)
 
     def result_name(self, idx):
         return self.L.msim_pattern_name(self.h, C.c_uint32(int(idx))).decode()

@@ -45,10 +45,12 @@ class RefMatcher:
             L.refm_name.restype = C.c_char_p
             L.refm_result_count.restype = C.c_uint64
             L.refm_item_count.restype = C.c_uint64
+            L.refm_result_value.restype = C.c_int64
+            L.refm_item_value.restype = C.c_int64
             for f in ("refm_destroy", "refm_last_error", "refm_define_option", "refm_define_term_frequency",
                       "refm_push_term", "refm_push_expression", "refm_push_pattern", "refm_attach_variable",
                       "refm_define_pattern", "refm_compile", "refm_run_batch", "refm_result_count",
-                      "refm_item_count", "refm_fetch", "refm_name"):
+                      "refm_item_count", "refm_fetch", "refm_name", "refm_result_value", "refm_item_value"):
                 getattr(L, f).argtypes = None
             cls._lib = L
         return cls._lib
@@ -90,7 +92,18 @@ class RefMatcher:
     def compile(self):
         self._ck(self.L.refm_compile(self.h))
 
-    def run(self, tokens, tok_offsets, origsegs=None, nthreads=1, with_results=True):
+    def _value(self, fn, idx):
+        n = int(fn(self.h, C.c_uint64(idx), None, C.c_uint64(0)))
+        if n == -100:       # SP_NO_VALUE: the reference delivered NULL
+            return None
+        assert n >= 0
+        buf = C.create_string_buffer(n + 1)
+        fn(self.h, C.c_uint64(idx), buf, C.c_uint64(n))
+        return buf.raw[:n]
+
+    def run(self, tokens, tok_offsets, origsegs=None, nthreads=1, with_results=True, values=False):
+        """values=True adds "result_values" / "item_values": the value strings of PatternMatcherResult /
+        PatternMatcherResultItem as bytes (None where the reference delivers NULL)."""
         tokens = np.ascontiguousarray(tokens, dtype=LEXEM_DT)
         tok_offsets = np.ascontiguousarray(tok_offsets, dtype=np.uint64)
         ndocs = len(tok_offsets) - 1
@@ -111,6 +124,9 @@ class RefMatcher:
         self.L.refm_fetch(self.h, _ptr(out["results"]) if with_results and nres else None, _ptr(out["result_offsets"]),
                           _ptr(out["items"]) if nitems else None, _ptr(out["item_offsets"]), _ptr(out["stats"]),
                           _ptr(out["status"]))
+        if values and with_results:
+            out["result_values"] = [self._value(self.L.refm_result_value, i) for i in range(nres)]
+            out["item_values"] = [self._value(self.L.refm_item_value, i) for i in range(nitems)]
         return out
 
     def name(self, idx):

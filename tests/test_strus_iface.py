@@ -49,6 +49,7 @@ def write_casefile(path):
     for t in simple_document():
         lines.append("d %d %d %d %d" % (t["id"], t["ordpos"], t["origpos"], t["origsize"]))
     lines.append("END")
+    lines.append("FORMATS")
     open(path, "w").write("\n".join(lines) + "\n")
 
 
@@ -66,3 +67,4 @@ def test_interface_program_runs_like_the_reference_tests(tmp_path):
     res = subprocess.run([EXE, casefile, capi.LIB_PATH], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
     assert res.returncode == 0, res.stdout
     assert "lexer case: 36 lexems OK" in res.stdout and "matcher case: 5 results OK" in res.stdout and "module entry point OK" in res.stdout
+    assert "format case: 6 results OK" in res.stdout, res.stdout

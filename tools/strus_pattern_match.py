@@ -43,14 +43,19 @@ def main():
     text = np.frombuffer(b"".join(docs), dtype=np.uint8)
     offs = np.cumsum([0] + [len(d) for d in docs]).astype(np.uint64)
     lo = lexer.scan(text, offs)
-    mo = matcher.run(lo["lexems"], lo["offsets"])
+    if args.oracle:
+        mo, resolve = matcher.run(lo["lexems"], lo["offsets"], values=True), None
+        from struspattern_b200.capi import resolve_value as resolve
+    else:
+        from struspattern_b200.capi import resolve_value as resolve
+        mo = matcher.visible_results(matcher.run(lo["lexems"], lo["offsets"]))
     for d, path in enumerate(args.inputs):
         print("%s:" % path)
         doc = np.frombuffer(docs[d], dtype=np.uint8)
         if args.K:
             for line in rulefile.format_tokens(prog, doc, lo["lexems"][int(lo["offsets"][d]):int(lo["offsets"][d + 1])]):
                 print(line)
-        for line in rulefile.format_results(doc, mo, matcher.result_name, matcher.item_name, base_offset=bases[d], doc=d):
+        for line in rulefile.format_results(doc, mo, matcher.result_name, matcher.item_name, base_offset=bases[d], doc=d, resolve=resolve):
             print(line)
     print("OK done")
 
