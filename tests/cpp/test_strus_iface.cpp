@@ -190,7 +190,7 @@ static int runFormatCase( strus::ErrorBufferInterface* errorhnd)
 	std::set<std::string> expected;
 	expected.insert( "Currency=EUR"); expected.insert( "Currency=CHF");
 	expected.insert( "MoneyAmount=EUR \x01" "0,4,0,9\x02"); expected.insert( "MoneyAmount=CHF \x01" "0,17,0,19\x02");
-	expected.insert( "PlainAmount currency=EUR value=(null)"); expected.insert( "PlainAmount currency=CHF value=(null)");
+	expected.insert( "PlainAmount=(null) currency=EUR value=(null)"); expected.insert( "PlainAmount=(null) currency=CHF value=(null)");
 	if (got != expected)
 	{
 		std::string msg( "values differ from the expected:");
