@@ -52,6 +52,8 @@ struct sp_matcher
 		dev.program_triggers = put( H.program_triggers); dev.event_slots = put( H.event_slots);
 		dev.eval_slots = put( H.eval_slots); dev.eval_follows = put( H.eval_follows); dev.eval_xlist = put( H.eval_xlist); dev.prog_flags = put( H.prog_flags);
 		dev.eval_entries = put( H.eval_entries); dev.eval_vars = put( H.eval_vars);
+		dev.eval_agg = put( H.eval_agg); dev.eval_indlist = put( H.eval_indlist);
+		dev.eval_pairs = put( H.eval_pairs); dev.eval_pairlist = put( H.eval_pairlist);
 		uploaded = true;
 	}
 };

@@ -63,7 +63,7 @@ __device__ __forceinline__ uint32_t evalFindDoc( const uint64_t* __restrict__ to
 	return lo;
 }
 
-__device__ __forceinline__ void evalAddStats( sp_matcher_stats* st, uint32_t installed, uint32_t altkey, uint64_t signals, uint64_t open)
+__device__ __forceinline__ void evalAddStats( sp_matcher_stats* st, uint64_t installed, uint32_t altkey, uint64_t signals, uint64_t open)
 {
 	if (installed) atomicAdd( (unsigned long long*)&st->nof_programs_installed, (unsigned long long)installed);
 	if (altkey) atomicAdd( (unsigned long long*)&st->nof_altkey_programs_installed, (unsigned long long)altkey);
@@ -305,16 +305,23 @@ static __global__ void __launch_bounds__(EvalThreads) k_eval_count_step( EvalPar
 // such as soon as none of the events of its live triggers occurs among the tokens of its window. All rules installed by
 // one token share that window, so the warp builds, once per key token, a small hash table in shared memory: token id ->
 // distance (in ordinal positions) of its first occurrence behind the key token, for the tokens up to EvalJoinRange
-// positions away, plus the number of window tokens per distance. A rule then costs one 32 byte list entry and at most four
-// probes; the rules that can get a signal (and rules with a longer range, and the windows that do not fit the table) are
-// queued in shared memory and followed token by token, 32 at a time (sp_eval_lite_step).
-enum {EvalTile = 8, EvalTileLook = 88, EvalJoinSlots = 128, EvalJoinCap = 64, EvalJoinRange = 15, EvalStepQueue = 96};
+// positions away, plus the number of window tokens per distance and the list of the distinct ids.
+// The quiet rules are never touched: what they add to the counters is summed up per event slot at compile time
+// (matcher_tables.h: SpEvalAgg) and needs the window token counts only. The rules that CAN get a signal are found from the
+// window's side: every distinct id X of the window is looked up with the key token's event slot S in the pair index
+// (SpEvalPair: the entries of S that have a live trigger on X). Those entries are loaded and probed against the table
+// (an entry reached from several ids is taken by the first of its events that is in the window); the ones that get a
+// signal inside their range are queued in shared memory and followed token by token, 32 at a time (sp_eval_lite_step),
+// and their outcome replaces their quiet share of the counters. Entries outside the aggregate (generic ones, a result at
+// the installation, a range beyond the table) and the tokens whose window does not fit the table are handled one by one.
+enum {EvalTile = 8, EvalTileLook = 56, EvalJoinSlots = 128, EvalJoinCap = 64, EvalJoinRange = 15, EvalStepQueue = 64, EvalJoinIds = 32};
 #define SP_JOIN_EMPTY 0xFFFFFFFFFFFFFFFFull
+#define SP_JOINQ_DELTA 0x80000000u	/* queued work item of the aggregate: its outcome is accounted as the difference to its quiet share */
 
-struct EvalLaneAcc		// statistics of the document a lane is in
+struct EvalLaneAcc		// statistics of the document a lane is in (sums modulo 2^64: quiet shares are taken back by subtraction)
 {
-	uint32_t doc, installed;
-	uint64_t signals, open;
+	uint32_t doc;
+	uint64_t installed, signals, open;
 };
 
 __device__ __forceinline__ void evalAccDoc( const EvalParams& P, EvalLaneAcc& acc, uint32_t d)
@@ -324,14 +331,10 @@ __device__ __forceinline__ void evalAccDoc( const EvalParams& P, EvalLaneAcc& ac
 	acc.doc = d; acc.installed = 0; acc.signals = 0; acc.open = 0;
 }
 
-// what an ended rule leaves behind: counters, result count / item count / result bit, or a place in the queue of the full fold
-__device__ __forceinline__ void evalAccount( const EvalParams& P, const SpEvalEntry& en, const SpEvalLite& L, uint64_t item, uint64_t tok, uint64_t te,
-						const SpEvalFollow* F, uint32_t* snres, uint32_t* snitems, EvalLaneAcc& acc)
+// result count / item count / result bit of an ended rule that has a result, or a place in the queue of the full fold
+__device__ __forceinline__ void evalAccountResult( const EvalParams& P, const SpEvalEntry& en, const SpEvalLite& L, uint64_t item, uint64_t tok, uint64_t te,
+							const SpEvalFollow* F, uint32_t* snres, uint32_t* snitems)
 {
-	if (L.flags & SP_LITE_FULL) {evalQueuePush( P, item); return;}
-	acc.installed += 1; acc.signals += L.signals;
-	acc.open += (uint64_t)L.alive_tokens * SP_EVAL_META_NTRIG( en.meta);
-	if (!(L.flags & SP_LITE_RESULT)) return;
 	uint32_t extra = 0;
 	if ((en.meta & SP_EVAL_META_ITEMSFULL) && !sp_eval_lite_follow_items( P.T, P.tokens, tok, te, en, *F, extra))
 	{
@@ -343,17 +346,62 @@ __device__ __forceinline__ void evalAccount( const EvalParams& P, const SpEvalEn
 	atomicOr( P.resbits + (item >> 5), 1u << (item & 31));
 }
 
+// what an ended rule leaves behind: counters, result count / item count / result bit, or a place in the queue of the full fold
+__device__ __forceinline__ void evalAccount( const EvalParams& P, const SpEvalEntry& en, const SpEvalLite& L, uint64_t item, uint64_t tok, uint64_t te,
+						const SpEvalFollow* F, uint32_t* snres, uint32_t* snitems, EvalLaneAcc& acc)
+{
+	if (L.flags & SP_LITE_FULL) {evalQueuePush( P, item); return;}
+	acc.installed += 1; acc.signals += L.signals;
+	acc.open += (uint64_t)L.alive_tokens * SP_EVAL_META_NTRIG( en.meta);
+	if (L.flags & SP_LITE_RESULT) evalAccountResult( P, en, L, item, tok, te, F, snres, snitems);
+}
+
+// the same for an entry of the aggregate (alive behind its installation, no result there) whose quiet share - one program
+// installed, the signals of the installation, its live triggers over the `quiet_alive` tokens of its window - is already
+// in the counters
+__device__ __forceinline__ void evalAccountDelta( const EvalParams& P, const SpEvalEntry& en, const SpEvalLite& L, uint32_t quiet_alive, uint64_t item, uint64_t tok, uint64_t te,
+						     const SpEvalFollow* F, uint32_t* snres, uint32_t* snitems, EvalLaneAcc& acc)
+{
+	const uint64_t ntrig = SP_EVAL_META_NTRIG( en.meta), quiet_signals = SP_EVAL_META_NKEY( en.meta);
+	if (L.flags & SP_LITE_FULL)
+	{
+		// the full fold adds all counters of the rule
+		evalQueuePush( P, item);
+		acc.installed -= 1; acc.signals -= quiet_signals; acc.open -= ntrig * quiet_alive;
+		return;
+	}
+	acc.signals += (uint64_t)L.signals - quiet_signals;
+	acc.open += ntrig * L.alive_tokens - ntrig * quiet_alive;
+	if (L.flags & SP_LITE_RESULT) evalAccountResult( P, en, L, item, tok, te, F, snres, snitems);
+}
+
 __device__ __forceinline__ uint32_t evalJoinHash( uint32_t id) {return (id * 0x9E3779B1u) >> 25;}	// 7 bits: EvalJoinSlots
+
+// number of leading values of the ascending sequence held by the lanes (inclusive prefix sums) that are <= x
+__device__ __forceinline__ uint32_t evalLanesUpTo( uint32_t incl, uint32_t x)
+{
+	uint32_t lo = 0;
+	#pragma unroll
+	for (int step=16; step>0; step>>=1)
+	{
+		const uint32_t v = __shfl_sync( SP_FULL, incl, (lo + step - 1) & 31);
+		if (v <= x) lo += step;
+	}
+	return lo;
+}
 
 static __global__ void __launch_bounds__(EvalThreads, 8) k_eval_count_join( EvalParams P)
 {
 	__shared__ uint32_t s_key[ EvalWarpsPerBlock][ EvalTile][ EvalJoinSlots];		// token id, 0xFFFFFFFF = empty
 	__shared__ uint8_t s_dist[ EvalWarpsPerBlock][ EvalTile][ EvalJoinSlots];		// distance of its first occurrence
 	__shared__ uint8_t s_cnt[ EvalWarpsPerBlock][ EvalTile][ EvalJoinRange + 1];		// window tokens up to a distance
+	__shared__ uint8_t s_wslot[ EvalWarpsPerBlock][ EvalTile][ EvalJoinIds];		// table slots of the distinct ids of a window
+	__shared__ uint32_t s_wn[ EvalWarpsPerBlock][ EvalTile];				// their number (0: no window lookups for this token)
+	__shared__ uint32_t s_slot[ EvalWarpsPerBlock][ EvalTile];				// event slot of a token
 	__shared__ uint32_t s_queue[ EvalWarpsPerBlock][ EvalStepQueue];			// items of the tile to follow token by token
 	__shared__ uint2 s_tok[ EvalWarpsPerBlock][ EvalTile + EvalTileLook];
 	__shared__ uint32_t s_nres[ EvalWarpsPerBlock][ EvalTile], s_nitems[ EvalWarpsPerBlock][ EvalTile];
-	__shared__ uint4 s_info[ EvalWarpsPerBlock][ EvalTile][ 2];	// per token: (first item, work list, program list, direct items), (follow begin, document, position, -)
+	__shared__ uint4 s_info[ EvalWarpsPerBlock][ EvalTile][ 2];	// per token: (first item, work list, program list, direct items), (follow begin, document, position, follow count)
 	__shared__ unsigned long long s_te[ EvalWarpsPerBlock][ EvalTile];
 	const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	uint4 (*sinfo)[ 2] = s_info[ warp];
@@ -361,6 +409,8 @@ static __global__ void __launch_bounds__(EvalThreads, 8) k_eval_count_join( Eval
 	uint32_t (*skey)[ EvalJoinSlots] = s_key[ warp];
 	uint8_t (*sdist)[ EvalJoinSlots] = s_dist[ warp];
 	uint8_t (*scnt)[ EvalJoinRange + 1] = s_cnt[ warp];
+	uint8_t (*swslot)[ EvalJoinIds] = s_wslot[ warp];
+	uint32_t* swn = s_wn[ warp]; uint32_t* sslot = s_slot[ warp];
 	uint32_t* squeue = s_queue[ warp]; uint32_t* snres = s_nres[ warp]; uint32_t* snitems = s_nitems[ warp];
 	uint2* stok = s_tok[ warp];
 
@@ -384,7 +434,7 @@ static __global__ void __launch_bounds__(EvalThreads, 8) k_eval_count_join( Eval
 		}
 	}
 	const unsigned int workmask = __ballot_sync( SP_FULL, my_work != 0);
-	if (lane < EvalTile) {snres[ lane] = 0; snitems[ lane] = 0;}
+	if (lane < EvalTile) {snres[ lane] = 0; snitems[ lane] = 0; swn[ lane] = 0; sslot[ lane] = my_slot;}
 	if (!workmask)
 	{
 		if (lane < ntile) {P.tok_nres[ r0 + lane] = 0; P.tok_nitems[ r0 + lane] = 0;}
@@ -409,7 +459,6 @@ static __global__ void __launch_bounds__(EvalThreads, 8) k_eval_count_join( Eval
 		uint32_t up = __shfl_up_sync( SP_FULL, pre, ofs);
 		if (lane >= (unsigned int)ofs) pre += up;
 	}
-	const uint32_t Wt = __shfl_sync( SP_FULL, pre, EvalTile - 1);
 	pre -= my_work;		// exclusive
 	const uint64_t wbase = __ldg( &P.tok_work_off[ r0]);
 	// ---- hash tables of the windows of the tokens that install something
@@ -422,6 +471,7 @@ static __global__ void __launch_bounds__(EvalThreads, 8) k_eval_count_join( Eval
 		const uint32_t spos = __shfl_sync( SP_FULL, my_pos, t);
 		for (uint32_t h=lane; h<EvalJoinSlots; h+=32) skey[ t][ h] = 0xFFFFFFFFu;
 		uint32_t cnt = 0;	// window tokens of the rounds done
+		uint32_t wn = 0;	// distinct ids of the rounds done
 		if (lane <= EvalJoinRange) scnt[ t][ lane] = 0;
 		__syncwarp();
 		bool more = true;
@@ -439,14 +489,21 @@ static __global__ void __launch_bounds__(EvalThreads, 8) k_eval_count_join( Eval
 			// positions ascend with the lanes and with the rounds: the first occurrence of an id is its lowest lane in the
 			// first round that has it; that lane alone inserts the id, an id that is already there keeps its distance
 			const unsigned int same = __match_any_sync( SP_FULL, in ? tk.x : 0xFFFFFFFFu - lane);
+			bool inserted = false; uint32_t hslot = 0;
 			if (in && (unsigned int)(__ffs( same) - 1) == lane)
 			{
 				for (uint32_t h = evalJoinHash( tk.x);; h = (h + 1) & (EvalJoinSlots - 1))
 				{
 					const uint32_t old = atomicCAS( &skey[ t][ h], 0xFFFFFFFFu, tk.x);
-					if (old == 0xFFFFFFFFu) {sdist[ t][ h] = (uint8_t)(tk.y - spos); break;}
+					if (old == 0xFFFFFFFFu) {sdist[ t][ h] = (uint8_t)(tk.y - spos); inserted = true; hslot = h; break;}
 					if (old == tk.x) break;
 				}
+			}
+			{
+				const unsigned int insmask = __ballot_sync( SP_FULL, inserted);
+				const uint32_t p = wn + __popc( insmask & laneLt( lane));
+				if (inserted && p < EvalJoinIds) swslot[ t][ p] = (uint8_t)hslot;
+				wn += __popc( insmask);
 			}
 			__syncwarp();
 			// window tokens up to a distance: the distances ascend with the lanes, so lane L knows the count for every distance
@@ -461,11 +518,33 @@ static __global__ void __launch_bounds__(EvalThreads, 8) k_eval_count_join( Eval
 			more = inmask == SP_FULL;		// positions ascend: the window ends inside this round otherwise
 			if (more && (round + 1) * 32 >= EvalJoinCap) {bigwindow |= 1u << t; more = false;}
 		}
+		if (wn > EvalJoinIds) bigwindow |= 1u << t;
+		if (lane == 0) swn[ t] = ((bigwindow >> t) & 1u) ? 0u : wn;
 	}
 	__syncwarp();
 
-	// ---- the rules of the tile, 32 per round
 	EvalLaneAcc acc; acc.doc = 0xFFFFFFFFu; acc.installed = 0; acc.signals = 0; acc.open = 0;
+	// ---- the quiet share of the aggregated entries, and the entries to handle one by one (all of them for a window that
+	// does not fit the table)
+	uint32_t my_ic = 0, my_ib = 0;
+	if (lane < ntile && my_work)
+	{
+		const SpEvalAgg* ag = P.T.eval_agg + my_slot;
+		const uint4 head = __ldg( reinterpret_cast<const uint4*>( ag));	// n, signals, ind_begin, ind_count
+		if ((bigwindow >> lane) & 1u) my_ic = my_work;
+		else
+		{
+			my_ic = head.w; my_ib = head.z;
+			uint64_t open = 0;
+			#pragma unroll
+			for (int q=0; q<SP_EVAL_AGG_RANGES/4; ++q)
+			{
+				const uint4 o = __ldg( reinterpret_cast<const uint4*>( ag->open) + q);
+				open += (uint64_t)o.x * scnt[ lane][ 4*q] + (uint64_t)o.y * scnt[ lane][ 4*q+1] + (uint64_t)o.z * scnt[ lane][ 4*q+2] + (uint64_t)o.w * scnt[ lane][ 4*q+3];
+			}
+			acc.doc = my_doc; acc.installed = head.x; acc.signals = head.y; acc.open = open;
+		}
+	}
 	uint32_t nqueue = 0;		// uniform
 	// first items of the tokens, in registers of every lane
 	uint32_t pfx[ EvalTile];
@@ -481,7 +560,7 @@ static __global__ void __launch_bounds__(EvalThreads, 8) k_eval_count_join( Eval
 	auto decode = [&]( uint32_t wl, uint32_t& t, EvalCursor& cur)
 	{
 		// the token of item wl: the last one whose first item is not behind wl (tokens without items share their first item
-		// with the token behind them, and wl < Wt)
+		// with the token behind them, and wl is an item of the tile)
 		uint32_t n = 0;
 		#pragma unroll
 		for (int j=1; j<EvalTile; ++j) n += (wl >= pfx[ j]) ? 1u : 0u;
@@ -496,11 +575,18 @@ static __global__ void __launch_bounds__(EvalThreads, 8) k_eval_count_join( Eval
 			cur.c = it.y; cur.lbegin = it.x;
 		}
 	};
+	auto load_entry = [&]( const EvalCursor& cur, SpEvalEntry& en)
+	{
+		const uint4* ep = reinterpret_cast<const uint4*>( P.T.eval_entries + cur.lbegin + cur.k);
+		const uint4 a = __ldg( ep), b = __ldg( ep + 1);
+		en.ev[0] = a.x; en.ev[1] = a.y; en.ev[2] = a.z; en.ev[3] = a.w; en.codes = b.x; en.value0 = b.y; en.meta = b.z; en.meta2 = b.w;
+	};
 	auto follow_steps = [&]( uint32_t nbatch)
 	{
 		// the first nbatch queued items, one per lane: followed token by token in lock step
 		const bool valid = lane < nbatch;
-		const uint32_t wl = valid ? squeue[ lane] : 0;
+		const uint32_t qv = valid ? squeue[ lane] : 0;
+		const uint32_t wl = qv & ~SP_JOINQ_DELTA;
 		uint32_t t; EvalCursor cur;
 		decode( wl, t, cur);
 		const uint32_t d = sinfo[ t][ 1].y, spos = sinfo[ t][ 1].z;
@@ -512,9 +598,7 @@ static __global__ void __launch_bounds__(EvalThreads, 8) k_eval_count_join( Eval
 		uint64_t k = r0 + t + 1;
 		if (valid)
 		{
-			const uint4* ep = reinterpret_cast<const uint4*>( P.T.eval_entries + cur.lbegin + cur.k);
-			const uint4 a = __ldg( ep), b = __ldg( ep + 1);
-			en.ev[0] = a.x; en.ev[1] = a.y; en.ev[2] = a.z; en.ev[3] = a.w; en.codes = b.x; en.value0 = b.y; en.meta = b.z; en.meta2 = b.w;
+			load_entry( cur, en);
 			sp_eval_lite_init( en, spos, L);
 			expiry = spos + SP_EVAL_META_RANGE( en.meta);
 		}
@@ -538,7 +622,9 @@ static __global__ void __launch_bounds__(EvalThreads, 8) k_eval_count_join( Eval
 		if (valid)
 		{
 			evalAccDoc( P, acc, d);
-			evalAccount( P, en, L, wbase + wl, r0 + t, te, cur.c ? P.T.eval_follows + cur.fb + cur.c - 1 : 0, snres + t, snitems + t, acc);
+			const SpEvalFollow* F = cur.c ? P.T.eval_follows + cur.fb + cur.c - 1 : 0;
+			if (qv & SP_JOINQ_DELTA) evalAccountDelta( P, en, L, scnt[ t][ SP_EVAL_META_RANGE( en.meta)], wbase + wl, r0 + t, te, F, snres + t, snitems + t, acc);
+			else evalAccount( P, en, L, wbase + wl, r0 + t, te, F, snres + t, snitems + t, acc);
 		}
 		__syncwarp();
 		// the rest of the queue moves to the front
@@ -552,78 +638,158 @@ static __global__ void __launch_bounds__(EvalThreads, 8) k_eval_count_join( Eval
 		nqueue = rest;
 		__syncwarp();
 	};
-	// the list entries of a round are loaded one round ahead
-	uint32_t nt = 0; EvalCursor ncur; uint4 na = make_uint4( 0, 0, 0, 0), nb = make_uint4( 0, 0, 0, 0);
-	decode( lane < Wt ? lane : 0, nt, ncur);
-	if (lane < Wt)
+	auto enqueue = [&]( bool tostep, uint32_t value)
 	{
-		const uint4* ep = reinterpret_cast<const uint4*>( P.T.eval_entries + ncur.lbegin);
-		na = __ldg( ep); nb = __ldg( ep + 1);
-	}
-	for (uint32_t base=0; base<Wt; base+=32)
-	{
-		const uint32_t wl = base + lane;
-		const bool valid = wl < Wt;
-		const uint32_t t = nt; const EvalCursor cur = ncur; const uint4 a = na, b = nb;
-		if (base + 32 < Wt)
-		{
-			const uint32_t nwl = base + 32 + lane;
-			decode( nwl < Wt ? nwl : 0, nt, ncur);
-			if (nwl < Wt)
-			{
-				const uint4* ep = reinterpret_cast<const uint4*>( P.T.eval_entries + ncur.lbegin);
-				na = __ldg( ep); nb = __ldg( ep + 1);
-			}
-		}
-		const uint32_t tpos = sinfo[ t][ 1].z, tdoc = sinfo[ t][ 1].y;
-		const uint64_t tte = ste[ t];
-		bool tostep = false;
-		if (valid)
-		{
-			SpEvalEntry en;
-			en.ev[0] = a.x; en.ev[1] = a.y; en.ev[2] = a.z; en.ev[3] = a.w; en.codes = b.x; en.value0 = b.y; en.meta = b.z; en.meta2 = b.w;
-			if (en.meta & SP_EVAL_META_GENERIC) evalQueuePush( P, wbase + wl);
-			else
-			{
-				const uint32_t range = SP_EVAL_META_RANGE( en.meta);
-				bool quiet = true;
-				if (!(en.meta & SP_EVAL_META_DEAD))
-				{
-					if (range > joinrange || ((bigwindow >> t) & 1u)) quiet = false;
-					else
-					{
-						// four probes with the same instruction stream in all lanes (an unused trigger slot probes for 0xFFFFFFFF, which
-						// is the empty mark and never a key); a probe only loops on a collision
-						bool hit = false;
-						#pragma unroll
-						for (int e=0; e<SP_EVAL_NEV; ++e)
-						{
-							const uint32_t ev = en.ev[ e];
-							uint32_t h = evalJoinHash( ev);
-							uint32_t key = skey[ t][ h];
-							while (key != 0xFFFFFFFFu && key != ev) {h = (h + 1) & (EvalJoinSlots - 1); key = skey[ t][ h];}
-							hit |= (key == ev) & (ev != 0xFFFFFFFFu) & (sdist[ t][ h] <= range);
-						}
-						quiet = !hit;
-					}
-				}
-				if (quiet)
-				{
-					SpEvalLite L;
-					sp_eval_lite_init( en, tpos, L);
-					if (L.flags & SP_LITE_ALIVE) L.alive_tokens = scnt[ t][ range];
-					evalAccDoc( P, acc, tdoc);
-					evalAccount( P, en, L, wbase + wl, r0 + t, tte, cur.c ? P.T.eval_follows + cur.fb + cur.c - 1 : 0, snres + t, snitems + t, acc);
-				}
-				else tostep = true;
-			}
-		}
-		// queue the rules that can get a signal
+		// at most 31 items wait in the queue here, so 32 more fit
 		const unsigned int sm = __ballot_sync( SP_FULL, tostep);
-		if (tostep) squeue[ nqueue + __popc( sm & laneLt( lane))] = wl;
+		if (tostep) squeue[ nqueue + __popc( sm & laneLt( lane))] = value;
 		nqueue += __popc( sm);
 		__syncwarp();
-		while (nqueue >= 32) follow_steps( 32);		// full batches; what stays (< 32) waits for the next round (at most 32 more)
+		while (nqueue >= 32) follow_steps( 32);
+	};
+	// ---- entries handled one by one, 32 per round
+	{
+		uint32_t ipre = my_ic;
+		#pragma unroll
+		for (int ofs=1; ofs<EvalTile; ofs<<=1)
+		{
+			uint32_t up = __shfl_up_sync( SP_FULL, ipre, ofs);
+			if (lane >= (unsigned int)ofs) ipre += up;
+		}
+		const uint32_t It = __shfl_sync( SP_FULL, ipre, EvalTile - 1);
+		ipre -= my_ic;		// exclusive
+		for (uint32_t base=0; base<It; base+=32)
+		{
+			const uint32_t il = base + lane;
+			const bool valid = il < It;
+			// the token of the entry: the last one whose first entry is not behind il
+			uint32_t t = 0;
+			#pragma unroll
+			for (int j=1; j<EvalTile; ++j) t += (il >= __shfl_sync( SP_FULL, ipre, j)) ? 1u : 0u;
+			const uint32_t tfirst = __shfl_sync( SP_FULL, ipre, t), tib = __shfl_sync( SP_FULL, my_ib, t);
+			bool tostep = false;
+			uint32_t wl = 0;
+			if (valid)
+			{
+				const bool big = (bigwindow >> t) & 1u;
+				const uint32_t rem = big ? il - tfirst : __ldg( P.T.eval_indlist + tib + (il - tfirst));
+				wl = sinfo[ t][ 0].x + rem;
+				uint32_t t2; EvalCursor cur;
+				decode( wl, t2, cur);
+				SpEvalEntry en;
+				load_entry( cur, en);
+				if (en.meta & SP_EVAL_META_GENERIC) evalQueuePush( P, wbase + wl);
+				else
+				{
+					const uint32_t range = SP_EVAL_META_RANGE( en.meta);
+					bool quiet = true;
+					if (!(en.meta & SP_EVAL_META_DEAD))
+					{
+						if (range > joinrange || big) quiet = false;
+						else
+						{
+							bool hit = false;
+							#pragma unroll
+							for (int e=0; e<SP_EVAL_NEV; ++e)
+							{
+								const uint32_t ev = en.ev[ e];
+								uint32_t h = evalJoinHash( ev);
+								uint32_t key = skey[ t][ h];
+								while (key != 0xFFFFFFFFu && key != ev) {h = (h + 1) & (EvalJoinSlots - 1); key = skey[ t][ h];}
+								hit |= (key == ev) & (ev != 0xFFFFFFFFu) & (sdist[ t][ h] <= range);
+							}
+							quiet = !hit;
+						}
+					}
+					if (quiet)
+					{
+						SpEvalLite L;
+						sp_eval_lite_init( en, sinfo[ t][ 1].z, L);
+						if (L.flags & SP_LITE_ALIVE) L.alive_tokens = scnt[ t][ range];
+						evalAccDoc( P, acc, sinfo[ t][ 1].y);
+						evalAccount( P, en, L, wbase + wl, r0 + t, ste[ t], cur.c ? P.T.eval_follows + cur.fb + cur.c - 1 : 0, snres + t, snitems + t, acc);
+					}
+					else tostep = true;
+				}
+			}
+			enqueue( tostep, wl);
+		}
+	}
+	// ---- the aggregated entries that can get a signal: pair index lookups for the distinct ids of the windows, 32 per round
+	{
+		uint32_t my_wn = lane < EvalTile ? swn[ lane] : 0;
+		uint32_t dpre = my_wn;
+		#pragma unroll
+		for (int ofs=1; ofs<EvalTile; ofs<<=1)
+		{
+			uint32_t up = __shfl_up_sync( SP_FULL, dpre, ofs);
+			if (lane >= (unsigned int)ofs) dpre += up;
+		}
+		const uint32_t Dt = __shfl_sync( SP_FULL, dpre, EvalTile - 1);
+		dpre -= my_wn;		// exclusive
+		const uint32_t pairmask = P.T.eval_pair_mask;
+		for (uint32_t base=0; base<Dt; base+=32)
+		{
+			const uint32_t il = base + lane;
+			uint32_t t = 0;
+			#pragma unroll
+			for (int j=1; j<EvalTile; ++j) t += (il >= __shfl_sync( SP_FULL, dpre, j)) ? 1u : 0u;
+			const uint32_t tfirst = __shfl_sync( SP_FULL, dpre, t);
+			uint32_t cnt = 0, begin = 0, X = 0xFFFFFFFFu;
+			if (il < Dt)
+			{
+				X = skey[ t][ swslot[ t][ il - tfirst]];
+				const uint32_t slot = sslot[ t];
+				for (uint32_t i = sp_eval_pair_hash( slot, X) & pairmask;; i = (i + 1) & pairmask)
+				{
+					const uint4 p = __ldg( reinterpret_cast<const uint4*>( P.T.eval_pairs + i));
+					if (p.x == 0xFFFFFFFFu) break;
+					if (p.x == slot && p.y == X) {begin = p.z; cnt = p.w; break;}
+				}
+			}
+			// the candidates of the round, 32 at a time: lane c takes candidate number c of the concatenated lists
+			uint32_t incl = cnt;
+			#pragma unroll
+			for (int ofs=1; ofs<32; ofs<<=1)
+			{
+				uint32_t up = __shfl_up_sync( SP_FULL, incl, ofs);
+				if (lane >= (unsigned int)ofs) incl += up;
+			}
+			const uint32_t Ct = __shfl_sync( SP_FULL, incl, 31);
+			for (uint32_t cb=0; cb<Ct; cb+=32)
+			{
+				const uint32_t ci = cb + lane;
+				const uint32_t src = evalLanesUpTo( incl, ci);
+				const uint32_t ct = __shfl_sync( SP_FULL, t, src), cbegin = __shfl_sync( SP_FULL, begin, src);
+				const uint32_t cfirst = __shfl_sync( SP_FULL, incl - cnt, src), cX = __shfl_sync( SP_FULL, X, src);
+				bool tostep = false;
+				uint32_t wl = 0;
+				if (ci < Ct)
+				{
+					wl = sinfo[ ct][ 0].x + __ldg( P.T.eval_pairlist + cbegin + (ci - cfirst));
+					uint32_t t2; EvalCursor cur;
+					decode( wl, t2, cur);
+					SpEvalEntry en;
+					load_entry( cur, en);
+					const uint32_t range = SP_EVAL_META_RANGE( en.meta);
+					// the first event of the entry that is in the window owns the entry (it is reached from every one of them)
+					bool hit = false, owned = false; uint32_t owner = 0xFFFFFFFFu;
+					#pragma unroll
+					for (int e=0; e<SP_EVAL_NEV; ++e)
+					{
+						const uint32_t ev = en.ev[ e];
+						uint32_t h = evalJoinHash( ev);
+						uint32_t key = skey[ ct][ h];
+						while (key != 0xFFFFFFFFu && key != ev) {h = (h + 1) & (EvalJoinSlots - 1); key = skey[ ct][ h];}
+						const bool present = (key == ev) & (ev != 0xFFFFFFFFu);
+						if (present && !owned) {owned = true; owner = ev;}
+						hit |= present & (sdist[ ct][ h] <= range);
+					}
+					tostep = hit && owner == cX;
+				}
+				enqueue( tostep, wl | SP_JOINQ_DELTA);
+			}
+		}
 	}
 	while (nqueue) follow_steps( min( nqueue, 32u));
 	// the counters of the lanes: one set of atomics per warp when all lanes are in the same document (the usual case)
@@ -631,10 +797,12 @@ static __global__ void __launch_bounds__(EvalThreads, 8) k_eval_count_join( Eval
 		const uint32_t d0 = __shfl_sync( SP_FULL, my_doc, __ffs( workmask) - 1);
 		if (__all_sync( SP_FULL, acc.doc == d0 || acc.doc == 0xFFFFFFFFu))
 		{
-			const uint32_t inst = __reduce_add_sync( SP_FULL, acc.doc == d0 ? acc.installed : 0u);
-			uint64_t sig = acc.doc == d0 ? acc.signals : 0, open = acc.doc == d0 ? acc.open : 0;
+			uint64_t inst = acc.doc == d0 ? acc.installed : 0, sig = acc.doc == d0 ? acc.signals : 0, open = acc.doc == d0 ? acc.open : 0;
 			#pragma unroll
-			for (int ofs=16; ofs>0; ofs>>=1) {sig += __shfl_xor_sync( SP_FULL, sig, ofs); open += __shfl_xor_sync( SP_FULL, open, ofs);}
+			for (int ofs=16; ofs>0; ofs>>=1)
+			{
+				inst += __shfl_xor_sync( SP_FULL, inst, ofs); sig += __shfl_xor_sync( SP_FULL, sig, ofs); open += __shfl_xor_sync( SP_FULL, open, ofs);
+			}
 			if (lane == 0) evalAddStats( P.stats + d0, inst, 0, sig, open);
 			acc.doc = 0xFFFFFFFFu;
 		}

@@ -73,6 +73,10 @@ struct MatcherTablesHost
 	std::vector<uint32_t> prog_flags;
 	std::vector<SpEvalEntry> eval_entries;
 	std::vector<SpEvalVars> eval_vars;
+	std::vector<SpEvalAgg> eval_agg;	// hash join: quiet outcome per slot, entries handled one by one, pair index
+	std::vector<uint32_t> eval_indlist;
+	std::vector<SpEvalPair> eval_pairs;
+	std::vector<uint32_t> eval_pairlist;
 	SpMatcherTables view;			// pointers are filled by the owner (host or device addresses)
 };
 
@@ -220,6 +224,58 @@ public:
 		rule.formatHandle = formatHandle;
 		m_flattened = false;
 		return formatHandle;
+	}
+	// Pair index and quiet aggregates of the hash join (matcher_tables.h: SpEvalAgg, SpEvalPair)
+	static void buildJoinTables( MatcherTablesHost& T, uint32_t joinrange)
+	{
+		const uint32_t nslots = (uint32_t)T.event_slots.size();
+		SpEvalAgg noagg; std::memset( &noagg, 0, sizeof(noagg));
+		T.eval_agg.assign( nslots, noagg);
+		T.eval_indlist.clear(); T.eval_pairlist.clear();
+		std::map<std::pair<uint32_t,uint32_t>, std::vector<uint32_t> > pairs;
+		for (uint32_t h=0; h<nslots; ++h)
+		{
+			const SpEvalSlot& es = T.eval_slots[ h];
+			SpEvalAgg& agg = T.eval_agg[ h];
+			agg.ind_begin = (uint32_t)T.eval_indlist.size();
+			for (uint32_t rem=0; rem<es.xcount; ++rem)
+			{
+				const SpEvalEntry& en = T.eval_entries[ T.eval_xlist[ es.xbegin + rem].ptidx];
+				const uint32_t range = SP_EVAL_META_RANGE( en.meta);
+				const bool dead = (en.meta & SP_EVAL_META_DEAD) != 0;
+				if ((en.meta & SP_EVAL_META_GENERIC) || (en.meta2 & SP_EVAL_M2_RESULT0) || (!dead && (range > joinrange || range >= SP_EVAL_AGG_RANGES)))
+				{
+					T.eval_indlist.push_back( rem);
+					continue;
+				}
+				agg.n += 1;
+				agg.signals += SP_EVAL_META_NKEY( en.meta);
+				if (dead) continue;
+				agg.open[ range] += SP_EVAL_META_NTRIG( en.meta);
+				std::set<uint32_t> events;
+				for (int e=0; e<SP_EVAL_NEV; ++e) if (en.ev[ e] != 0xFFFFFFFFu) events.insert( en.ev[ e]);
+				for (uint32_t ev: events) pairs[ std::make_pair( h, ev)].push_back( rem);
+			}
+			agg.ind_count = (uint32_t)T.eval_indlist.size() - agg.ind_begin;
+		}
+		uint32_t size = 16;
+		while (size < 2 * pairs.size() + 1) size <<= 1;
+		SpEvalPair nopair; nopair.slot = 0xFFFFFFFFu; nopair.event = 0; nopair.begin = nopair.count = 0;
+		T.eval_pairs.assign( size, nopair);
+		for (std::map<std::pair<uint32_t,uint32_t>, std::vector<uint32_t> >::const_iterator pi = pairs.begin(); pi != pairs.end(); ++pi)
+		{
+			SpEvalPair p; p.slot = pi->first.first; p.event = pi->first.second;
+			p.begin = (uint32_t)T.eval_pairlist.size(); p.count = (uint32_t)pi->second.size();
+			T.eval_pairlist.insert( T.eval_pairlist.end(), pi->second.begin(), pi->second.end());
+			uint32_t i = sp_eval_pair_hash( p.slot, p.event) & (size - 1);
+			while (T.eval_pairs[ i].slot != 0xFFFFFFFFu) i = (i + 1) & (size - 1);
+			T.eval_pairs[ i] = p;
+		}
+		if (T.eval_indlist.empty()) T.eval_indlist.push_back( 0);
+		if (T.eval_pairlist.empty()) T.eval_pairlist.push_back( 0);
+		T.view.eval_agg = T.eval_agg.data(); T.view.eval_indlist = T.eval_indlist.data();
+		T.view.eval_pairs = T.eval_pairs.data(); T.view.eval_pairlist = T.eval_pairlist.data();
+		T.view.eval_pair_mask = size - 1;
 	}
 	// ProgramTable::optimize
 	void compile()
@@ -471,6 +527,7 @@ private:
 			T.eval_slots[ h].xcount = (uint32_t)T.eval_xlist.size() - T.eval_slots[ h].xbegin;
 		}
 		T.view.eval_xlist = T.eval_xlist.data();
+		buildJoinTables( T, joinrange);
 		T.view.eval_slots = T.eval_slots.data(); T.view.eval_follows = T.eval_follows.data(); T.view.prog_flags = T.prog_flags.data();
 		T.view.nfollows = (uint32_t)T.eval_follows.size();
 		T.view.eval_capable = capable ? 1 : 0;

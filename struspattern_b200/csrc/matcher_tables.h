@@ -126,6 +126,31 @@ typedef struct alignas(16) SpEvalVars
 	uint32_t livevar[ SP_EVAL_NEV];
 } SpEvalVars;
 
+/* Pair index of the hash join (k_eval_count_join). More than nine rule instances out of ten never get a signal behind
+ * their installation: none of the events of their live triggers occurs in their window. What such a "quiet" instance
+ * adds to the counters depends on its list entry and on the number of tokens in its window only, so the quiet outcome of
+ * ALL aggregated entries of an event slot is summed up at compile time (SpEvalAgg), and the count pass looks for the
+ * entries that are NOT quiet from the other side: for every distinct token id X in the window of a key token with event
+ * slot S, the pair (S, X) names the aggregated entries of S that have a live trigger on X (SpEvalPair -> eval_pairlist,
+ * positions inside the work list of S). Those alone are loaded, probed and followed; their outcome replaces their quiet
+ * share. Entries that are not aggregated (generic, a result at the installation, a range beyond the join window) are
+ * listed per slot (ind_begin/ind_count -> eval_indlist) and handled one by one. */
+#define SP_EVAL_AGG_RANGES 16
+typedef struct alignas(16) SpEvalAgg
+{
+	uint32_t n;			/* aggregated entries of the slot: programs installed */
+	uint32_t signals;		/* their signals at the installation */
+	uint32_t ind_begin, ind_count;	/* entries handled one by one (eval_indlist range: positions inside the work list) */
+	uint32_t open[ SP_EVAL_AGG_RANGES];	/* [r]: live triggers of the aggregated entries with range r that outlive their installation */
+} SpEvalAgg;
+
+typedef struct alignas(16) SpEvalPair
+{
+	uint32_t slot;			/* event slot of the key token, 0xFFFFFFFF = empty */
+	uint32_t event;			/* token id in the window */
+	uint32_t begin, count;		/* eval_pairlist range */
+} SpEvalPair;
+
 #define SP_PROGFLAG_LISTENS_FOLLOW 1u	/* some trigger definition waits for an event that is not a term event */
 
 typedef struct SpMatcherTables
@@ -149,6 +174,11 @@ typedef struct SpMatcherTables
 	const uint32_t* prog_flags;	/* [nprograms] SP_PROGFLAG_* */
 	const SpEvalEntry* eval_entries;	/* [nprogram_triggers] */
 	const SpEvalVars* eval_vars;	/* [nprogram_triggers] */
+	const SpEvalAgg* eval_agg;	/* [event_mask+1] */
+	const uint32_t* eval_indlist;
+	const SpEvalPair* eval_pairs;	/* [eval_pair_mask+1] open addressing, sp_eval_pair_hash */
+	const uint32_t* eval_pairlist;
+	uint32_t eval_pair_mask;
 	uint32_t nfollows;
 	uint32_t eval_join_range;	/* largest position range of a compiled list entry, at most 15: window of the hash join (k_eval_count_join) */
 	uint32_t eval_capable;		/* 1: the rule set is inside what the window evaluator reproduces exactly (matcher_program.hpp: evalCapable) */
@@ -159,6 +189,11 @@ typedef struct SpMatcherTables
 #else
 #define SP_TAB_HD inline
 #endif
+SP_TAB_HD uint32_t sp_eval_pair_hash( uint32_t slot, uint32_t event)
+{
+	uint32_t h = (slot * 0x85EBCA6Bu) ^ (event * 0x9E3779B1u);
+	return h ^ (h >> 13);
+}
 SP_TAB_HD uint32_t sp_event_slot_hash( uint32_t event)
 {
 	uint32_t h = event * 0x9E3779B1u;
