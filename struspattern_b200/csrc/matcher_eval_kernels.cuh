@@ -324,16 +324,23 @@ struct EvalLaneAcc		// statistics of the document a lane is in (sums modulo 2^64
 	uint64_t installed, signals, open;
 };
 
+// (the rare and the bulky parts of the join kernel are kept out of line: the kernel is bound by instruction fetch, its
+// warps are in different phases most of the time)
+__device__ __noinline__ void evalFlushStats( sp_matcher_stats* st, uint64_t installed, uint64_t signals, uint64_t open)
+{
+	evalAddStats( st, installed, 0, signals, open);
+}
+
 __device__ __forceinline__ void evalAccDoc( const EvalParams& P, EvalLaneAcc& acc, uint32_t d)
 {
 	if (d == acc.doc) return;
-	if (acc.doc != 0xFFFFFFFFu) evalAddStats( P.stats + acc.doc, acc.installed, 0, acc.signals, acc.open);
+	if (acc.doc != 0xFFFFFFFFu) evalFlushStats( P.stats + acc.doc, acc.installed, acc.signals, acc.open);
 	acc.doc = d; acc.installed = 0; acc.signals = 0; acc.open = 0;
 }
 
 // result count / item count / result bit of an ended rule that has a result, or a place in the queue of the full fold
-__device__ __forceinline__ void evalAccountResult( const EvalParams& P, const SpEvalEntry& en, const SpEvalLite& L, uint64_t item, uint64_t tok, uint64_t te,
-							const SpEvalFollow* F, uint32_t* snres, uint32_t* snitems)
+__device__ __noinline__ void evalAccountResult( const EvalParams& P, const SpEvalEntry& en, uint32_t nitems, bool drefemit, uint64_t item, uint64_t tok, uint64_t te,
+						     const SpEvalFollow* F, uint32_t* snres, uint32_t* snitems)
 {
 	uint32_t extra = 0;
 	if ((en.meta & SP_EVAL_META_ITEMSFULL) && !sp_eval_lite_follow_items( P.T, P.tokens, tok, te, en, *F, extra))
@@ -342,8 +349,34 @@ __device__ __forceinline__ void evalAccountResult( const EvalParams& P, const Sp
 		return;
 	}
 	atomicAdd( snres, 1u);
-	if (L.flags & SP_LITE_DREFEMIT) atomicAdd( snitems, L.nitems + extra);
+	if (drefemit) atomicAdd( snitems, nitems + extra);
 	atomicOr( P.resbits + (item >> 5), 1u << (item & 31));
+}
+
+// A batch of rules, one per lane, followed token by token in lock step until the last one has ended (one copy of the
+// state machine of sp_eval_lite_step in the kernel).
+__device__ __noinline__ void evalStepBatch( const SpEvalEntry* enp, SpEvalLite* Lp, uint32_t expiry, uint64_t k, uint64_t te, uint64_t r0, const uint2* stok, const sp_lexem* tokens)
+{
+	const SpEvalEntry en = *enp;
+	SpEvalLite L = *Lp;
+	while (__any_sync( SP_FULL, (L.flags & SP_LITE_ALIVE) != 0))
+	{
+		#pragma unroll 1
+		for (int step=0; step<4; ++step)
+		{
+			if (L.flags & SP_LITE_ALIVE)
+			{
+				if (k < te)
+				{
+					const uint2 tk = (k - r0 < EvalTile + EvalTileLook) ? stok[ k - r0] : __ldg( reinterpret_cast<const uint2*>( tokens + k));
+					sp_eval_lite_step( en, expiry, tk.x, tk.y, L);
+					++k;
+				}
+				else L.flags &= ~SP_LITE_ALIVE;
+			}
+		}
+	}
+	*Lp = L;
 }
 
 // what an ended rule leaves behind: counters, result count / item count / result bit, or a place in the queue of the full fold
@@ -353,7 +386,7 @@ __device__ __forceinline__ void evalAccount( const EvalParams& P, const SpEvalEn
 	if (L.flags & SP_LITE_FULL) {evalQueuePush( P, item); return;}
 	acc.installed += 1; acc.signals += L.signals;
 	acc.open += (uint64_t)L.alive_tokens * SP_EVAL_META_NTRIG( en.meta);
-	if (L.flags & SP_LITE_RESULT) evalAccountResult( P, en, L, item, tok, te, F, snres, snitems);
+	if (L.flags & SP_LITE_RESULT) evalAccountResult( P, en, L.nitems, (L.flags & SP_LITE_DREFEMIT) != 0, item, tok, te, F, snres, snitems);
 }
 
 // the same for an entry of the aggregate (alive behind its installation, no result there) whose quiet share - one program
@@ -372,7 +405,7 @@ __device__ __forceinline__ void evalAccountDelta( const EvalParams& P, const SpE
 	}
 	acc.signals += (uint64_t)L.signals - quiet_signals;
 	acc.open += ntrig * L.alive_tokens - ntrig * quiet_alive;
-	if (L.flags & SP_LITE_RESULT) evalAccountResult( P, en, L, item, tok, te, F, snres, snitems);
+	if (L.flags & SP_LITE_RESULT) evalAccountResult( P, en, L.nitems, (L.flags & SP_LITE_DREFEMIT) != 0, item, tok, te, F, snres, snitems);
 }
 
 __device__ __forceinline__ uint32_t evalJoinHash( uint32_t id) {return (id * 0x9E3779B1u) >> 25;}	// 7 bits: EvalJoinSlots
@@ -390,7 +423,7 @@ __device__ __forceinline__ uint32_t evalLanesUpTo( uint32_t incl, uint32_t x)
 	return lo;
 }
 
-static __global__ void __launch_bounds__(EvalThreads, 8) k_eval_count_join( EvalParams P)
+static __global__ void __launch_bounds__(EvalThreads, 8) k_eval_count_join( const __grid_constant__ EvalParams P)
 {
 	__shared__ uint32_t s_key[ EvalWarpsPerBlock][ EvalTile][ EvalJoinSlots];		// token id, 0xFFFFFFFF = empty
 	__shared__ uint8_t s_dist[ EvalWarpsPerBlock][ EvalTile][ EvalJoinSlots];		// distance of its first occurrence
@@ -602,23 +635,7 @@ static __global__ void __launch_bounds__(EvalThreads, 8) k_eval_count_join( Eval
 			sp_eval_lite_init( en, spos, L);
 			expiry = spos + SP_EVAL_META_RANGE( en.meta);
 		}
-		while (__any_sync( SP_FULL, (L.flags & SP_LITE_ALIVE) != 0))
-		{
-			#pragma unroll
-			for (int step=0; step<4; ++step)
-			{
-				if (L.flags & SP_LITE_ALIVE)
-				{
-					if (k < te)
-					{
-						const uint2 tk = (k - r0 < EvalTile + EvalTileLook) ? stok[ k - r0] : __ldg( reinterpret_cast<const uint2*>( P.tokens + k));
-						sp_eval_lite_step( en, expiry, tk.x, tk.y, L);
-						++k;
-					}
-					else L.flags &= ~SP_LITE_ALIVE;
-				}
-			}
-		}
+		evalStepBatch( &en, &L, expiry, k, te, r0, stok, P.tokens);
 		if (valid)
 		{
 			evalAccDoc( P, acc, d);
