@@ -300,8 +300,12 @@ def run_ours(args, rank, world, local_rank):
     out_status = torch.empty(ndocs, dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)
     errors = []
 
+    trace_e2e = bool(os.environ.get("SP_BENCH_TRACE"))
+    trace_t0 = [0.0]
+
     def e2e_pass(measure_only):
         nxt = [0]
+        trace_t0[0] = time.perf_counter()
         lock = threading.Lock()
 
         def worker(w):
@@ -315,14 +319,21 @@ def run_ours(args, rank, world, local_rank):
                     if k >= len(subs):
                         return
                     b, e = subs[k]
+                    t_a = time.perf_counter()
                     lc.launch(text[int(offs[b]):int(offs[e])], sub_offs[k], on_device=False)
+                    t_b = time.perf_counter()
                     mc.launch_lexer_output(lc)
                     if measure_only:
                         res_begin[k + 1], item_begin[k + 1] = mc.count()
                     else:
                         rb, ib = res_begin[k], item_begin[k]
+                        mc.count()
+                        t_c = time.perf_counter()
                         mc.fetch_into(out_res[rb:res_begin[k + 1] + 1], out_roffs[b + k:e + k + 1], out_items[ib:item_begin[k + 1] + 1],
                                       out_ioffs[b + k:e + k + 1], out_stats[b:e], out_status[b:e])
+                        if trace_e2e:
+                            t_d = time.perf_counter()
+                            sys.stderr.write("[e2e] thread %d sub %d: start %.1f lexer %.1f matcher %.1f fetch %.1f ms\n" % (w, k, (t_a - trace_t0[0]) * 1e3, (t_b - t_a) * 1e3, (t_c - t_b) * 1e3, (t_d - t_c) * 1e3))
             except Exception as exc:  # surfaced after the join
                 errors.append(exc)
 

@@ -52,6 +52,23 @@ private:
 	std::size_t m_cap;
 };
 
+// ---- scalar read back: a few words from device memory into PINNED host memory, written by a kernel (pinned memory
+// is addressable from the device under unified addressing) instead of a copy command: the device-to-host copy engine
+// serves the copies of all streams in the order they were issued, so a 16 byte read back of one context waited behind
+// the gigabyte of results another context was fetching - tens of milliseconds per synchronisation point when several
+// contexts share a device (end-to-end pipeline).
+static __global__ void k_read_back( uint32_t* dst_pinned, const uint32_t* __restrict__ src, uint32_t nwords)
+{
+	if (threadIdx.x < nwords) dst_pinned[ threadIdx.x] = src[ threadIdx.x];
+	__threadfence_system();
+}
+inline void readBackAsync( void* dst_pinned, const void* src_device, std::size_t bytes, cudaStream_t stream)
+{
+	if (bytes % 4 || bytes > 128) throw std::logic_error( "read back of scalars: size not supported");
+	k_read_back<<<1, 32, 0, stream>>>( static_cast<uint32_t*>( dst_pinned), static_cast<const uint32_t*>( src_device), (uint32_t)(bytes / 4));
+	SP_CUDA( cudaGetLastError());
+}
+
 // ---- exclusive prefix sum: out[i] = sum of in[0..i), out[n] = total
 enum {ScanThreads = 256, ScanItems = 8, ScanTile = ScanThreads * ScanItems};
 

@@ -111,7 +111,7 @@ struct sp_lexer_ctx
 	uint64_t readScalar( const void* devptr, std::size_t bytes)
 	{
 		pinned[0] = 0;
-		SP_CUDA( cudaMemcpyAsync( pinned, devptr, bytes, cudaMemcpyDeviceToHost, stream));
+		readBackAsync( pinned, devptr, bytes, stream);
 		SP_CUDA( waitStream());
 		return pinned[0];
 	}
@@ -183,7 +183,7 @@ struct sp_lexer_ctx
 		tileScan( f, nchunks, aggord.as<uint64_t>( (nchunks + TsTile - 1) / TsTile), stream, d_scalars + 1);
 		k_fused_docs<<<(ndocs + 1 + 255) / 256, 256, 0, stream>>>( F, d_scalars + 1);
 		spanEnd();
-		SP_CUDA( cudaMemcpyAsync( pinned, d_scalars + 1, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, stream));
+		readBackAsync( pinned, d_scalars + 1, 2 * sizeof(uint64_t), stream);
 		SP_CUDA( waitStream());
 		if ((uint32_t)pinned[1]) {++fused_fallbacks; return false;}
 		nlex = pinned[0] >> 32;

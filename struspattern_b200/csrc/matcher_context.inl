@@ -69,7 +69,7 @@ struct sp_matcher_ctx
 
 	void readScalars( const void* devptr, std::size_t bytes)
 	{
-		SP_CUDA( cudaMemcpyAsync( pinned, devptr, bytes, cudaMemcpyDeviceToHost, stream));
+		readBackAsync( pinned, devptr, bytes, stream);
 		SP_CUDA( cudaStreamSynchronize( stream));
 	}
 
