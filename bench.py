@@ -266,6 +266,7 @@ def run_ours(args, rank, world, local_rank):
     # ---- parity gate on the timed output: the first documents of the batch against the CPU oracle
     parity = None
     cpu_line = None
+    parity_mo = None
     if rank == 0 and not args.no_parity:
         cpu = CpuPipeline(vocab)
         seconds = args.cpu_seconds if (world == 1 and not args.no_cpu) else 2.0
@@ -274,6 +275,7 @@ def run_ours(args, rank, world, local_rank):
         lo, mo = lctx.fetch_docs(0, nd), mctx.fetch_docs(0, nd)
         n, ntok, tl, tm = parity_check(cpu, text, offs, nd, lo, mo, mt)
         parity = {"results": n, "documents": nd, "tokens": ntok}
+        parity_mo = mo
         if world == 1 and not args.no_cpu:
             cpu_line = {"value": float(offs[nd]) / (tl + tm) / 1e9, "unit": "GB/s", "cores": cpu.nthreads, "kind": "port+reference",
                         "sample": "first %d bytes (%d documents) of the same corpus: level-1 CPU restatement %.2f s + the reference's automaton %.2f s" % (int(offs[nd]), nd, tl, tm),
@@ -292,8 +294,15 @@ def run_ours(args, rank, world, local_rank):
     res_begin, item_begin = [0] * (len(subs) + 1), [0] * (len(subs) + 1)
     streams = [torch.cuda.Stream() for _ in range(args.e2e_threads)]
     pairs = [(lx.create_context(s.cuda_stream), mt.create_context(s.cuda_stream)) for s in streams]
+    from struspattern_b200.capi import ITEM_PACKED_DT, RESULT_PACKED_DT, unpack_results
     out_res = torch.empty((nres + 4096) * RESULT_DT.itemsize, dtype=torch.uint8, pin_memory=True).numpy().view(RESULT_DT)
     out_items = torch.empty((nitems + 4096) * ITEM_DT.itemsize, dtype=torch.uint8, pin_memory=True).numpy().view(ITEM_DT)
+    pk_res = pk_items = None
+    if args.e2e_wire != "records":
+        # second measurement: packed records cross the link (16 / 12 bytes instead of 40 / 32) and stay packed in pinned memory
+        pk_res = torch.empty((nres + 4096) * RESULT_PACKED_DT.itemsize, dtype=torch.uint8, pin_memory=True).numpy().view(RESULT_PACKED_DT)
+        pk_items = torch.empty((nitems + 4096) * ITEM_PACKED_DT.itemsize, dtype=torch.uint8, pin_memory=True).numpy().view(ITEM_PACKED_DT)
+    wire = ["records"]
     out_roffs = torch.empty(ndocs + len(subs) + 1, dtype=torch.int64, pin_memory=True).numpy().view(np.uint64)
     out_ioffs = torch.empty(ndocs + len(subs) + 1, dtype=torch.int64, pin_memory=True).numpy().view(np.uint64)
     out_stats = torch.empty(ndocs * STATS_DT.itemsize, dtype=torch.uint8, pin_memory=True).numpy().view(STATS_DT)
@@ -329,8 +338,12 @@ def run_ours(args, rank, world, local_rank):
                         rb, ib = res_begin[k], item_begin[k]
                         mc.count()
                         t_c = time.perf_counter()
-                        mc.fetch_into(out_res[rb:res_begin[k + 1] + 1], out_roffs[b + k:e + k + 1], out_items[ib:item_begin[k + 1] + 1],
-                                      out_ioffs[b + k:e + k + 1], out_stats[b:e], out_status[b:e])
+                        if wire[0] == "packed":
+                            re_, ie_ = res_begin[k + 1], item_begin[k + 1]
+                            mc.fetch_packed_into(pk_res[rb:re_ + 1], out_roffs[b + k:e + k + 1], pk_items[ib:ie_ + 1], out_ioffs[b + k:e + k + 1], out_stats[b:e], out_status[b:e])
+                        else:
+                            mc.fetch_into(out_res[rb:res_begin[k + 1] + 1], out_roffs[b + k:e + k + 1], out_items[ib:item_begin[k + 1] + 1],
+                                          out_ioffs[b + k:e + k + 1], out_stats[b:e], out_status[b:e])
                         if trace_e2e:
                             t_d = time.perf_counter()
                             sys.stderr.write("[e2e] thread %d sub %d: start %.1f lexer %.1f matcher %.1f fetch %.1f ms\n" % (w, k, (t_a - trace_t0[0]) * 1e3, (t_b - t_a) * 1e3, (t_c - t_b) * 1e3, (t_d - t_c) * 1e3))
@@ -359,7 +372,40 @@ def run_ours(args, rank, world, local_rank):
     e2e_s = time.perf_counter() - t0
     if int(out_status.max(initial=0)) != 0:
         raise RuntimeError("document errors on the synthetic corpus")
+    if parity_mo is not None:
+        # what the end to end path delivered to the host (unpacked, if packed) is the checked output of the device-resident step
+        nr, ni = len(parity_mo["results"]), len(parity_mo["items"])
+        if not ((out_res[:nr] == parity_mo["results"]).all() and (out_items[:ni] == parity_mo["items"]).all()):
+            raise RuntimeError("end to end output differs from the output of the device-resident step")
+        parity["e2e_records_equal"] = nr
     d2h = int(RESULT_DT.itemsize * nres + ITEM_DT.itemsize * nitems + 16 * (ndocs + len(subs)) + (STATS_DT.itemsize + 4) * ndocs)
+    packed_line = None
+    if pk_res is not None:
+        wire[0] = "packed"
+        e2e_pass(False)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            e2e_pass(False)
+        torch.cuda.synchronize()
+        packed_s = time.perf_counter() - t0
+        wire[0] = "records"
+        # untimed: the packed records unpack into the records of the first measurement
+        k_chk = min(len(subs), 2)
+        for k in range(k_chk):
+            b, e = subs[k]
+            rb, re_, ib, ie_ = res_begin[k], res_begin[k + 1], item_begin[k], item_begin[k + 1]
+            chk_res, chk_items = np.zeros(re_ - rb + 1, dtype=RESULT_DT), np.zeros(ie_ - ib + 1, dtype=ITEM_DT)
+            unpack_results(pk_res[rb:re_ + 1], out_roffs[b + k:e + k + 1], pk_items[ib:ie_ + 1], out_ioffs[b + k:e + k + 1], chk_res, chk_items)
+            if not ((chk_res[:re_ - rb] == out_res[rb:re_]).all() and (chk_items[:ie_ - ib] == out_items[ib:ie_]).all()):
+                raise RuntimeError("packed records do not unpack into the records of the full wire format")
+        packed_times = torch.tensor([packed_s * 1000.0], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(packed_times, op=dist.ReduceOp.MAX)
+        packed_line = {"value": float(args.bytes) * world * e2e_steps / (float(packed_times[0]) / 1000.0) / 1e9, "unit": "GB/s",
+                       "d2h_bytes_per_step": int(RESULT_PACKED_DT.itemsize * nres + ITEM_PACKED_DT.itemsize * nitems + 16 * (ndocs + len(subs)) + (STATS_DT.itemsize + 4) * ndocs),
+                       "what": "same pipeline with sp_matcher_fetch_packed: 16 B per result, 12 B per item, left packed in pinned memory (sp_unpack_results restores the records: "
+                               "checked after the timed region on %d sub-batches; unpacking all of them on the host costs more than the link saves)" % k_chk}
 
     times = torch.tensor([ms, e2e_s * 1000.0], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -392,6 +438,7 @@ def run_ours(args, rank, world, local_rank):
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": int(args.bytes + 8 * (ndocs + len(subs))), "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                 "pipeline": "%d host threads x (lexer context + matcher context + stream), sub-batches of %d MiB" % (args.e2e_threads, args.e2e_sub_bytes >> 20),
+                "wire": "sp_result / sp_item records (40 / 32 B) copied to pinned memory", "packed_wire": packed_line,
                 "numa_rank0": numa, "host_cpus": len(os.sched_getaffinity(0))},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -425,7 +472,9 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--e2e-threads", type=int, default=4)
-    ap.add_argument("--e2e-sub-bytes", type=int, default=64 << 20)
+    ap.add_argument("--e2e-sub-bytes", type=int, default=16 << 20)
+    ap.add_argument("--e2e-wire", default="both", choices=["both", "records"],
+                    help="both: a second end-to-end measurement with the packed wire format (reported as e2e.packed_wire)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -232,6 +232,36 @@ int sp_matcher_fetch_range( sp_matcher_ctx* ctx, uint32_t first_doc, uint32_t nd
 			    uint64_t* result_offsets, sp_item* items, uint64_t item_capacity, uint64_t* item_offsets,
 			    sp_matcher_stats* stats, uint32_t* status);
 
+/* Compact wire format for host-bound output (the result and item records are 37 bytes per byte of text on the C3
+ * workload: the device-to-host link bounds the end-to-end rate). The records of the last run are packed on the device
+ * (16 bytes per result, 12 per item instead of 40 and 32), copied, and unpacked on the host by sp_unpack_results into
+ * the same sp_result / sp_item records sp_matcher_fetch delivers. Packable are runs whose records lie in segment 0 (what
+ * the lexer emits), with ordinal spans < 256 (results) / < 16 (items), source spans < 65536 bytes, at most 255 items per
+ * result, pattern handles < 2^18, format handles < 2^14 on results and none on items, variable handles < 4096;
+ * anything else makes sp_matcher_fetch_packed fail with SP_ERR_UNSUPPORTED and the caller uses sp_matcher_fetch.
+ * No counterpart in the reference (its results are C++ objects in host memory). */
+typedef struct sp_result_packed
+{
+	uint32_t name_format;  /* name | format << 18 */
+	uint32_t ordpos;
+	uint32_t origpos;
+	uint32_t lens;         /* (ordend - ordpos) | item_count << 8 | (endpos - origpos) << 16 */
+} sp_result_packed;
+typedef struct sp_item_packed
+{
+	uint32_t var_lens;     /* variable | (ordend - ordpos) << 12 | (endpos - origpos) << 16 */
+	uint32_t ordpos;
+	uint32_t origpos;
+} sp_item_packed;
+/* Like sp_matcher_fetch with packed records: results[nres], result_offsets[ndocs+1], items[nitems],
+ * item_offsets[ndocs+1], stats[ndocs], status[ndocs]; results, items and the offsets are required. */
+int sp_matcher_fetch_packed( sp_matcher_ctx* ctx, sp_result_packed* results, uint64_t* result_offsets,
+			     sp_item_packed* items, uint64_t* item_offsets, sp_matcher_stats* stats, uint32_t* status);
+/* Host side: the documents [0, ndocs) described by result_offsets / item_offsets (as fetched; absolute) unpacked into
+ * out_results[result_offsets[ndocs] - result_offsets[0]] and out_items[item_offsets[ndocs] - item_offsets[0]]. */
+void sp_unpack_results( const sp_result_packed* results, const uint64_t* result_offsets, const sp_item_packed* items,
+			const uint64_t* item_offsets, uint32_t ndocs, sp_result* out_results, sp_item* out_items);
+
 /* Counters of the last run ("results", "items", "tokens", "arena_retries", "pool_retries", "kernel_launches", ...)
  * and tuning knobs ("arena=N", "warps_per_sm=N"); -1 if unknown. */
 int64_t sp_matcher_ctx_counter( sp_matcher_ctx* ctx, const char* key);

@@ -15,6 +15,8 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(PKG, "libstrus_pattern_b200.so")
 
 LEXEM_DT = np.dtype([("id", "<u4"), ("ordpos", "<u4"), ("origpos", "<u4"), ("origsize", "<u4")])
+RESULT_PACKED_DT = np.dtype([(n, "<u4") for n in ("name_format", "ordpos", "origpos", "lens")])
+ITEM_PACKED_DT = np.dtype([(n, "<u4") for n in ("var_lens", "ordpos", "origpos")])
 RESULT_DT = np.dtype([(n, "<u4") for n in ("name", "format", "ordpos", "ordend", "origseg", "origpos",
                                             "endseg", "endpos", "item_begin", "item_count")])
 ITEM_DT = np.dtype([(n, "<u4") for n in ("variable", "format", "ordpos", "ordend", "origseg", "origpos",
@@ -84,6 +86,8 @@ def lib():
             "sp_matcher_result_value": (C.c_int64, [vp, vp, vp, vp, C.c_uint64]),
             "sp_matcher_item_value": (C.c_int64, [vp, vp, vp, C.c_uint64]),
             "sp_resolve_value": (C.c_int64, [vp, C.c_uint64, vp, C.c_uint64, vp, C.c_uint64]),
+            "sp_matcher_fetch_packed": (C.c_int, [vp, vp, vp, vp, vp, vp, vp]),
+            "sp_unpack_results": (None, [vp, vp, vp, vp, u32, vp, vp]),
             "sp_matcher_count_noalloc": (C.c_int, [vp, vp, vp, u32, C.c_uint64, vp, vp, vp, vp, vp]),
         }
         for table in (sigs, msigs):
@@ -466,6 +470,20 @@ class MatcherContext:
         self._ck(self.L.sp_matcher_fetch(self.h, _ptr(results), _ptr(result_offsets), _ptr(items), _ptr(item_offsets), _ptr(stats), _ptr(status)))
         return nres, nitems
 
+    def fetch_packed_into(self, results, result_offsets, items, item_offsets, stats, status):
+        """sp_matcher_fetch_packed into caller provided (e.g. pinned) arrays of RESULT_PACKED_DT / ITEM_PACKED_DT; raises
+        PatternError (code -6) if the run is not packable."""
+        nres, nitems = self.count()
+        if nres > len(results) or nitems > len(items):
+            raise PatternError(-1, "result buffers too small: %d results, %d items" % (nres, nitems))
+        self._ck(self.L.sp_matcher_fetch_packed(self.h, _ptr(results), _ptr(result_offsets), _ptr(items), _ptr(item_offsets), _ptr(stats), _ptr(status)))
+        return nres, nitems
+
     def run(self, tokens, tok_offsets, origsegs=None):
         self.launch(tokens, tok_offsets, origsegs)
         return self.fetch()
+
+
+def unpack_results(results, result_offsets, items, item_offsets, out_results, out_items):
+    """sp_unpack_results (host code): packed records of the documents described by the offsets -> sp_result / sp_item records."""
+    lib().sp_unpack_results(_ptr(results), _ptr(result_offsets), _ptr(items), _ptr(item_offsets), len(result_offsets) - 1, _ptr(out_results), _ptr(out_items))

@@ -58,9 +58,15 @@ struct sp_matcher
 	}
 };
 
+struct UnpackableError :public std::runtime_error
+{
+	UnpackableError() :std::runtime_error( "the records of this run do not fit the packed wire format (segments, long spans, format handles on items): use sp_matcher_fetch"){}
+};
+
 static int matcherFail( std::string& lasterror, const std::exception& e)
 {
 	lasterror = e.what();
+	if (dynamic_cast<const UnpackableError*>( &e)) return SP_ERR_UNSUPPORTED;
 	if (dynamic_cast<const CudaError*>( &e)) return SP_ERR_CUDA;
 	if (dynamic_cast<const std::bad_alloc*>( &e)) return SP_ERR_NOMEM;
 	return SP_ERR_ARGUMENT;

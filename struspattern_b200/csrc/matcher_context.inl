@@ -17,7 +17,8 @@ struct sp_matcher_ctx
 	// device buffers (grow only)
 	DeviceBuffer tokens, origsegs, tok_off, arenas, res_pool, item_pool, scalars, doc_res_begin, doc_res_count, doc_item_begin,
 		     doc_item_count, stats, status, list_a, list_b, res_off, item_off, results, items, scantmp,
-		     tok_nres, tok_nitems, tok_res_off, tok_item_off, flags, flag_list, tok_slot, tok_work, tok_docs, tok_work_off, resbits, queue;
+		     tok_nres, tok_nitems, tok_res_off, tok_item_off, flags, flag_list, tok_slot, tok_work, tok_docs, tok_work_off, resbits, queue,
+		     packed_results, packed_items;
 	uint64_t queue_cap, eval_queued, eval_items;
 	bool count_by_steps;	// SP_EVAL_COUNT=step: the count pass that follows every rule token by token (k_eval_count_step), for A/B runs
 	int mode;			// 0 = automatic (window evaluator if the rule set allows it), 1 = state machine (emission order), 2 = evaluator required
@@ -377,6 +378,62 @@ int sp_matcher_fetch( sp_matcher_ctx* ctx, sp_result* results, uint64_t* result_
 		if (status && nd) SP_CUDA( cudaMemcpyAsync( status, ctx->status.ptr(), nd * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
 		SP_CUDA( cudaStreamSynchronize( st));
 	})
+}
+
+int sp_matcher_fetch_packed( sp_matcher_ctx* ctx, sp_result_packed* results, uint64_t* result_offsets, sp_item_packed* items, uint64_t* item_offsets, sp_matcher_stats* stats, uint32_t* status)
+{
+	SP_MATCHER_TRY( ctx, {
+		if (!ctx->valid) throw std::runtime_error( "no finished run");
+		if (!results || !result_offsets || !items || !item_offsets) throw std::runtime_error( "packed fetch needs buffers for results, items and their offsets");
+		std::size_t nd = ctx->ndocs;
+		cudaStream_t st = ctx->stream;
+		sp_result_packed* d_res = ctx->packed_results.as<sp_result_packed>( ctx->nres);
+		sp_item_packed* d_items = ctx->packed_items.as<sp_item_packed>( ctx->nitems);
+		uint32_t* d_flag = reinterpret_cast<uint32_t*>( ctx->scalars.as<uint64_t>( 32) + 24);
+		SP_CUDA( cudaMemsetAsync( d_flag, 0, sizeof(uint32_t), st));
+		if (ctx->nres) k_pack_results<<<(unsigned int)((ctx->nres + 255) / 256), 256, 0, st>>>( static_cast<const sp_result*>( ctx->results.ptr()), ctx->nres, d_res, d_flag);
+		if (ctx->nitems) k_pack_items<<<(unsigned int)((ctx->nitems + 255) / 256), 256, 0, st>>>( static_cast<const sp_item*>( ctx->items.ptr()), ctx->nitems, d_items, d_flag);
+		SP_CUDA( cudaGetLastError());
+		ctx->readScalars( d_flag, sizeof(uint32_t));
+		if ((uint32_t)ctx->pinned[ 0]) throw UnpackableError();
+		if (ctx->nres) SP_CUDA( cudaMemcpyAsync( results, d_res, ctx->nres * sizeof(sp_result_packed), cudaMemcpyDeviceToHost, st));
+		SP_CUDA( cudaMemcpyAsync( result_offsets, ctx->res_off.ptr(), (nd + 1) * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+		if (ctx->nitems) SP_CUDA( cudaMemcpyAsync( items, d_items, ctx->nitems * sizeof(sp_item_packed), cudaMemcpyDeviceToHost, st));
+		SP_CUDA( cudaMemcpyAsync( item_offsets, ctx->item_off.ptr(), (nd + 1) * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+		if (stats && nd) SP_CUDA( cudaMemcpyAsync( stats, ctx->stats.ptr(), nd * sizeof(sp_matcher_stats), cudaMemcpyDeviceToHost, st));
+		if (status && nd) SP_CUDA( cudaMemcpyAsync( status, ctx->status.ptr(), nd * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+		SP_CUDA( cudaStreamSynchronize( st));
+	})
+}
+
+void sp_unpack_results( const sp_result_packed* results, const uint64_t* result_offsets, const sp_item_packed* items, const uint64_t* item_offsets, uint32_t ndocs,
+			sp_result* out_results, sp_item* out_items)
+{
+	const uint64_t rb = result_offsets[ 0], ib = item_offsets[ 0];
+	for (uint32_t d=0; d<ndocs; ++d)
+	{
+		uint32_t item_begin = 0;
+		for (uint64_t i=result_offsets[ d]-rb, e=result_offsets[ d+1]-rb; i<e; ++i)
+		{
+			const sp_result_packed p = results[ i];
+			sp_result r;
+			r.name = p.name_format & 0x3FFFFu; r.format = p.name_format >> 18;
+			r.ordpos = p.ordpos; r.ordend = p.ordpos + (p.lens & 0xFFu);
+			r.origseg = 0; r.origpos = p.origpos; r.endseg = 0; r.endpos = p.origpos + (p.lens >> 16);
+			r.item_begin = item_begin; r.item_count = (p.lens >> 8) & 0xFFu;
+			item_begin += r.item_count;
+			out_results[ i] = r;
+		}
+	}
+	for (uint64_t i=0, e=item_offsets[ ndocs]-ib; i<e; ++i)
+	{
+		const sp_item_packed p = items[ i];
+		sp_item it;
+		it.variable = p.var_lens & 0xFFFu; it.format = 0;
+		it.ordpos = p.ordpos; it.ordend = p.ordpos + ((p.var_lens >> 12) & 0xFu);
+		it.origseg = 0; it.origpos = p.origpos; it.endseg = 0; it.endpos = p.origpos + (p.var_lens >> 16);
+		out_items[ i] = it;
+	}
 }
 
 int sp_matcher_fetch_range( sp_matcher_ctx* ctx, uint32_t first_doc, uint32_t ndocs, sp_result* results, uint64_t result_capacity, uint64_t* result_offsets,

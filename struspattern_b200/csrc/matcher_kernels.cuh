@@ -214,5 +214,31 @@ static __global__ void __launch_bounds__(256) k_match_compact( MatchParams P, co
 	}
 }
 
+// ---- compact wire format (include/strus_pattern_b200.h: sp_result_packed, sp_item_packed): elementwise, *notpackable is
+// raised by any record that does not fit
+static __global__ void __launch_bounds__(256) k_pack_results( const sp_result* __restrict__ in, uint64_t n, sp_result_packed* __restrict__ out, uint32_t* notpackable)
+{
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const sp_result r = in[ i];
+	const uint32_t ordlen = r.ordend - r.ordpos, origlen = r.endpos - r.origpos;
+	if (r.origseg | r.endseg | (r.name >> 18) | (r.format >> 14) | (ordlen >> 8) | (origlen >> 16) | (r.item_count >> 8)) *notpackable = 1;
+	uint4 o;
+	o.x = r.name | (r.format << 18); o.y = r.ordpos; o.z = r.origpos; o.w = ordlen | (r.item_count << 8) | (origlen << 16);
+	*reinterpret_cast<uint4*>( out + i) = o;
+}
+static __global__ void __launch_bounds__(256) k_pack_items( const sp_item* __restrict__ in, uint64_t n, sp_item_packed* __restrict__ out, uint32_t* notpackable)
+{
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const uint4 a = __ldg( reinterpret_cast<const uint4*>( in + i)), b = __ldg( reinterpret_cast<const uint4*>( in + i) + 1);
+	// a: variable, format, ordpos, ordend; b: origseg, origpos, endseg, endpos
+	const uint32_t ordlen = a.w - a.z, origlen = b.w - b.y;
+	if (b.x | b.z | a.y | (a.x >> 12) | (ordlen >> 4) | (origlen >> 16)) *notpackable = 1;
+	sp_item_packed o;
+	o.var_lens = a.x | (ordlen << 12) | (origlen << 16); o.ordpos = a.z; o.origpos = b.y;
+	out[ i] = o;
+}
+
 } // namespace sp
 #endif
