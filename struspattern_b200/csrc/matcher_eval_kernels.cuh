@@ -879,7 +879,8 @@ static __global__ void __launch_bounds__(128) k_eval_count_full( EvalParams P)
 }
 
 // Write pass: the result bits of a run of tokens, 32 results at a time.
-static __global__ void __launch_bounds__(EvalThreads) k_eval_write( EvalParams P)
+template <int BLOCKS_PER_SM>
+static __global__ void __launch_bounds__(EvalThreads, BLOCKS_PER_SM) k_eval_write( EvalParams P)
 {
 	__shared__ uint32_t s_work[ EvalWarpsPerBlock][ EvalRun + 1];
 	__shared__ uint32_t s_word[ EvalWarpsPerBlock][ 32];
