@@ -265,7 +265,7 @@ void matcherCountNoAlloc( sp_matcher* m, const sp_lexem* d_tokens, const uint64_
 		if (nwork > SP_NOALLOC_MAX_RULES) throw std::runtime_error( "batch beyond the limit of the no-alloc entry point: more than SP_NOALLOC_MAX_RULES rule instances");
 		SP_CUDA( cudaMemsetAsync( E.resbits, 0, (nwork / 32 + 2) * sizeof(uint32_t), stream));
 		const uint64_t ntiles = (ntokens + EvalTile - 1) / EvalTile;
-		k_eval_count_join<<<(unsigned int)((ntiles + EvalWarpsPerBlock - 1) / EvalWarpsPerBlock), EvalThreads, 0, stream>>>( E);
+		k_eval_count_join<8><<<(unsigned int)((ntiles + EvalWarpsPerBlock - 1) / EvalWarpsPerBlock), EvalThreads, 0, stream>>>( E);
 		k_eval_count_full<<<(unsigned int)nsm * 8, 128, 0, stream>>>( E);
 		noallocScan( E.tok_nres, ntokens, d_tok_res_off, d_tilesum, stream);
 		noallocScan( E.tok_nitems, ntokens, d_tok_item_off, d_tilesum, stream);

@@ -20,7 +20,7 @@ struct sp_matcher_ctx
 		     tok_nres, tok_nitems, tok_res_off, tok_item_off, flags, flag_list, tok_slot, tok_work, tok_docs, tok_work_off, resbits, queue,
 		     packed_results, packed_items;
 	uint64_t queue_cap, eval_queued, eval_items;
-	int write_blocks;	// blocks per SM the write pass is compiled for: 4 (128 registers, default; measured 11.4 ms per 64 MiB against 13.8 ms for 3 = 168 registers); SP_EVAL_WRITE_BLOCKS=3|5|6 for A/B runs
+	int write_blocks;	// blocks per SM the write pass is compiled for: 5 (96 registers, default; measured per 64 MiB of C3 text: 3 blocks = 168 registers 13.8 ms, 4 = 128 registers 11.4 ms, 5 = 96 registers 10.2 ms, 6 = 80 registers 10.9 ms); SP_EVAL_WRITE_BLOCKS=3|4|6 for A/B runs
 	bool count_by_steps;	// SP_EVAL_COUNT=step: the count pass that follows every rule token by token (k_eval_count_step), for A/B runs
 	int mode;			// 0 = automatic (window evaluator if the rule set allows it), 1 = state machine (emission order), 2 = evaluator required
 	uint64_t eval_docs, eval_flagged, eval_runs;
@@ -51,7 +51,7 @@ struct sp_matcher_ctx
 		if ((e = std::getenv( "SP_MATCHER_WARPS_PER_SM")) != 0 && std::atoi( e) >= 1) {warps_per_sm = (uint32_t)std::atoi( e); warps_fixed = true;}
 		if (std::getenv( "SP_MATCHER_PROFILE")) profile = true;
 		if ((e = std::getenv( "SP_EVAL_COUNT")) != 0) count_by_steps = !std::strcmp( e, "step");
-		write_blocks = ((e = std::getenv( "SP_EVAL_WRITE_BLOCKS")) != 0 && std::atoi( e) >= 3 && std::atoi( e) <= 6) ? std::atoi( e) : 4;
+		write_blocks = ((e = std::getenv( "SP_EVAL_WRITE_BLOCKS")) != 0 && std::atoi( e) >= 3 && std::atoi( e) <= 6) ? std::atoi( e) : 5;
 		if ((e = std::getenv( "SP_MATCHER_MODE")) != 0) mode = !std::strcmp( e, "statemachine") ? 1 : !std::strcmp( e, "eval") ? 2 : 0;
 		trace = std::getenv( "SP_MATCHER_TRACE") != 0;
 		int dev = 0;
@@ -249,7 +249,9 @@ struct sp_matcher_ctx
 				else
 				{
 					const uint64_t ntiles = (ntokens + EvalTile - 1) / EvalTile;
-					k_eval_count_join<<<(unsigned int)((ntiles + EvalWarpsPerBlock - 1) / EvalWarpsPerBlock), EvalThreads, 0, stream>>>( E);
+					const unsigned int jgrid = (unsigned int)((ntiles + EvalWarpsPerBlock - 1) / EvalWarpsPerBlock);
+					// 8 blocks per SM = 64 registers; builds for 10 / 12 blocks (48 / 40 registers, 0.5 / 0.8 KB of spills) measured slower: 26.4 / 27.7 against 24.7 ms per 64 MiB
+					k_eval_count_join<8><<<jgrid, EvalThreads, 0, stream>>>( E);
 				}
 				k_eval_count_full<<<(unsigned int)nsm * 8, 128, 0, stream>>>( E);
 				if (profile) SP_CUDA( cudaEventRecord( ev_b, stream));
@@ -284,9 +286,9 @@ struct sp_matcher_ctx
 			E.results = results.as<sp_result>( nres); E.items = items.as<sp_item>( nitems);
 			if (profile) SP_CUDA( cudaEventRecord( ev_a, stream));
 			if (write_blocks == 3) k_eval_write<3><<<nblocks, EvalThreads, 0, stream>>>( E);
-			else if (write_blocks == 5) k_eval_write<5><<<nblocks, EvalThreads, 0, stream>>>( E);
+			else if (write_blocks == 4) k_eval_write<4><<<nblocks, EvalThreads, 0, stream>>>( E);
 			else if (write_blocks == 6) k_eval_write<6><<<nblocks, EvalThreads, 0, stream>>>( E);
-			else k_eval_write<4><<<nblocks, EvalThreads, 0, stream>>>( E);
+			else k_eval_write<5><<<nblocks, EvalThreads, 0, stream>>>( E);
 			if (profile) SP_CUDA( cudaEventRecord( ev_b, stream));
 			if (nflagged) k_eval_place<<<(nflagged + 7) / 8, 256, 0, stream>>>( d_flag_list, nflagged, P, d_res_off, d_item_off, E.results, E.items);
 			SP_CUDA( cudaGetLastError());

@@ -314,7 +314,7 @@ static __global__ void __launch_bounds__(EvalThreads) k_eval_count_step( EvalPar
 // signal inside their range are queued in shared memory and followed token by token, 32 at a time (sp_eval_lite_step),
 // and their outcome replaces their quiet share of the counters. Entries outside the aggregate (generic ones, a result at
 // the installation, a range beyond the table) and the tokens whose window does not fit the table are handled one by one.
-enum {EvalTile = 8, EvalTileLook = 56, EvalJoinSlots = 128, EvalJoinCap = 64, EvalJoinRange = 15, EvalStepQueue = 64, EvalJoinIds = 32};
+enum {EvalTile = 8, EvalTileLook = 56, EvalJoinSlots = 64, EvalJoinCap = 64, EvalJoinRange = 15, EvalStepQueue = 64, EvalJoinIds = 32};
 #define SP_JOIN_EMPTY 0xFFFFFFFFFFFFFFFFull
 #define SP_JOINQ_DELTA 0x80000000u	/* queued work item of the aggregate: its outcome is accounted as the difference to its quiet share */
 
@@ -408,7 +408,7 @@ __device__ __forceinline__ void evalAccountDelta( const EvalParams& P, const SpE
 	if (L.flags & SP_LITE_RESULT) evalAccountResult( P, en, L.nitems, (L.flags & SP_LITE_DREFEMIT) != 0, item, tok, te, F, snres, snitems);
 }
 
-__device__ __forceinline__ uint32_t evalJoinHash( uint32_t id) {return (id * 0x9E3779B1u) >> 25;}	// 7 bits: EvalJoinSlots
+__device__ __forceinline__ uint32_t evalJoinHash( uint32_t id) {return (id * 0x9E3779B1u) >> 26;}	// 6 bits: EvalJoinSlots
 
 // number of leading values of the ascending sequence held by the lanes (inclusive prefix sums) that are <= x
 __device__ __forceinline__ uint32_t evalLanesUpTo( uint32_t incl, uint32_t x)
@@ -423,7 +423,8 @@ __device__ __forceinline__ uint32_t evalLanesUpTo( uint32_t incl, uint32_t x)
 	return lo;
 }
 
-static __global__ void __launch_bounds__(EvalThreads, 8) k_eval_count_join( const __grid_constant__ EvalParams P)
+template <int BLOCKS_PER_SM>
+static __global__ void __launch_bounds__(EvalThreads, BLOCKS_PER_SM) k_eval_count_join( const __grid_constant__ EvalParams P)
 {
 	__shared__ uint32_t s_key[ EvalWarpsPerBlock][ EvalTile][ EvalJoinSlots];		// token id, 0xFFFFFFFF = empty
 	__shared__ uint8_t s_dist[ EvalWarpsPerBlock][ EvalTile][ EvalJoinSlots];		// distance of its first occurrence
