@@ -34,7 +34,7 @@ METRIC = "GB/s UTF-8 text lexed+matched at 1/2/4/8 B200 vs same-box hyperscan CP
 SEED = 0x5354525553000003
 NPATTERNS, NSYMBOLS, NPHRASES, PATTERN_SEED = 10000, 5000, 140, 33
 # DRAM traffic of the dominant kernel (dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full launch), per token
-NCU_TRAFFIC = {"k_eval_count": {"bytes_per_token": (488.127744e6 + 147.617280e6) / 11341930, "source": "profiles/r02_eval_v7_count_join_ncu_raw.csv (k_eval_count_join, 32 MiB of this corpus)"}}
+NCU_TRAFFIC = {"k_eval_count": {"bytes_per_token": (490.784768e6 + 179.286e6) / 11344148, "source": "profiles/r02_eval_v11_ncu_raw.csv (k_eval_count_join<8>, 32 MiB of this corpus)"}}
 
 
 def fixed_words():
