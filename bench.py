@@ -298,7 +298,7 @@ def run_ours(args, rank, world, local_rank):
     out_res = torch.empty((nres + 4096) * RESULT_DT.itemsize, dtype=torch.uint8, pin_memory=True).numpy().view(RESULT_DT)
     out_items = torch.empty((nitems + 4096) * ITEM_DT.itemsize, dtype=torch.uint8, pin_memory=True).numpy().view(ITEM_DT)
     pk_res = pk_items = None
-    if args.e2e_wire != "records":
+    if args.e2e_wire != "records" and world == 1:     # (one rank only: every rank would pin another 3.8 GB of host memory)
         # second measurement: packed records cross the link (16 / 12 bytes instead of 40 / 32) and stay packed in pinned memory
         pk_res = torch.empty((nres + 4096) * RESULT_PACKED_DT.itemsize, dtype=torch.uint8, pin_memory=True).numpy().view(RESULT_PACKED_DT)
         pk_items = torch.empty((nitems + 4096) * ITEM_PACKED_DT.itemsize, dtype=torch.uint8, pin_memory=True).numpy().view(ITEM_PACKED_DT)
