@@ -142,3 +142,25 @@ def test_both_count_formulations_give_the_same_output():
     for f in ("results", "items", "result_offsets", "item_offsets", "stats", "status"):
         assert (outs[0][f] == outs[1][f]).all(), f
     MC.compare_outputs(ref, ref.run(toks, offs, nthreads=4), gpu, outs[0], check_order=False)
+
+
+def define_distinct_term_rules(m, seed, nrules, nfeatures):
+    rng = np.random.default_rng(seed)
+    ops = (MC.OP_SEQUENCE, MC.OP_WITHIN, MC.OP_SEQUENCE_IMM)
+    for r in range(nrules):
+        terms = rng.choice(nfeatures, size=int(rng.integers(2, 4)), replace=False) + 1
+        MC.define_term_rule(m, ops[r % 3], terms, int(rng.integers(1, 11)), 0)
+        m.define_pattern("D%u" % r, "", True)
+
+
+def test_crowded_positions_windows_beyond_the_join_table():
+    """Six to seven tokens per ordinal position: the windows of the hash join hold more than 64 tokens or more than 32
+    distinct ids, so their rules are followed one by one (no aggregate, no pair lookups); mixed with windows that fit."""
+    ref, gpu = both(lambda m: define_distinct_term_rules(m, 21, 400, 120), True)
+    crowded, offs1 = MC.random_documents(23, 12, 400, 120, delim_prob=0.0, tokens_per_pos=0.15)
+    sparse, offs2 = MC.random_documents(24, 12, 400, 120, delim_prob=0.0)
+    toks = np.concatenate([crowded, sparse])
+    offs = np.concatenate([offs1, offs2[1:] + offs1[-1]])
+    ctx, go = run_eval(gpu, toks, offs)
+    assert MC.compare_outputs(ref, ref.run(toks, offs, nthreads=4), gpu, go, check_order=False) > 0
+    assert ctx.counter("eval_flagged") <= (len(offs) - 1) // 2
