@@ -472,7 +472,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--e2e-threads", type=int, default=4)
-    ap.add_argument("--e2e-sub-bytes", type=int, default=16 << 20)
+    ap.add_argument("--e2e-sub-bytes", type=int, default=8 << 20)
     ap.add_argument("--e2e-wire", default="both", choices=["both", "records"],
                     help="both: a second end-to-end measurement with the packed wire format (reported as e2e.packed_wire)")
     args = ap.parse_args()
