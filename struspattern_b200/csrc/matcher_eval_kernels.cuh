@@ -359,6 +359,10 @@ __device__ __noinline__ void evalStepBatch( const SpEvalEntry* enp, SpEvalLite* 
 {
 	const SpEvalEntry en = *enp;
 	SpEvalLite L = *Lp;
+	// token numbers relative to the first token of the tile: 32 bit arithmetic in the loop
+	uint32_t kr = (uint32_t)(k - r0);
+	const uint32_t ter = (uint32_t)min( te - r0, (uint64_t)0xFFFFFFFFu);
+	const uint2* tile_tokens = reinterpret_cast<const uint2*>( tokens + r0);	// (id, ordpos) are the first half of a 16 byte record
 	while (__any_sync( SP_FULL, (L.flags & SP_LITE_ALIVE) != 0))
 	{
 		#pragma unroll 1
@@ -366,11 +370,11 @@ __device__ __noinline__ void evalStepBatch( const SpEvalEntry* enp, SpEvalLite* 
 		{
 			if (L.flags & SP_LITE_ALIVE)
 			{
-				if (k < te)
+				if (kr < ter)
 				{
-					const uint2 tk = (k - r0 < EvalTile + EvalTileLook) ? stok[ k - r0] : __ldg( reinterpret_cast<const uint2*>( tokens + k));
+					const uint2 tk = (kr < EvalTile + EvalTileLook) ? stok[ kr] : __ldg( tile_tokens + 2 * (uint64_t)kr);
 					sp_eval_lite_step( en, expiry, tk.x, tk.y, L);
-					++k;
+					++kr;
 				}
 				else L.flags &= ~SP_LITE_ALIVE;
 			}
@@ -685,7 +689,7 @@ static __global__ void __launch_bounds__(EvalThreads, BLOCKS_PER_SM) k_eval_coun
 			#pragma unroll
 			for (int j=1; j<EvalTile; ++j) t += (il >= __shfl_sync( SP_FULL, ipre, j)) ? 1u : 0u;
 			const uint32_t tfirst = __shfl_sync( SP_FULL, ipre, t), tib = __shfl_sync( SP_FULL, my_ib, t);
-			bool tostep = false;
+			bool tostep = false, generic = false;
 			uint32_t wl = 0;
 			if (valid)
 			{
@@ -696,7 +700,7 @@ static __global__ void __launch_bounds__(EvalThreads, BLOCKS_PER_SM) k_eval_coun
 				decode( wl, t2, cur);
 				SpEvalEntry en;
 				load_entry( cur, en);
-				if (en.meta & SP_EVAL_META_GENERIC) evalQueuePush( P, wbase + wl);
+				if (en.meta & SP_EVAL_META_GENERIC) generic = true;
 				else
 				{
 					const uint32_t range = SP_EVAL_META_RANGE( en.meta);
@@ -728,6 +732,19 @@ static __global__ void __launch_bounds__(EvalThreads, BLOCKS_PER_SM) k_eval_coun
 						evalAccount( P, en, L, wbase + wl, r0 + t, ste[ t], cur.c ? P.T.eval_follows + cur.fb + cur.c - 1 : 0, snres + t, snitems + t, acc);
 					}
 					else tostep = true;
+				}
+			}
+			// the entries for the full fold: one addition to the queue counter per round
+			{
+				const unsigned int gm = __ballot_sync( SP_FULL, generic);
+				if (gm)
+				{
+					const int leader = __ffs( gm) - 1;
+					unsigned long long qb = 0;
+					if ((int)lane == leader) qb = atomicAdd( P.queue_count, (unsigned long long)__popc( gm));
+					qb = __shfl_sync( SP_FULL, qb, leader);
+					const unsigned long long q = qb + __popc( gm & laneLt( lane));
+					if (generic && q < P.queue_cap) P.queue[ q] = wbase + wl;
 				}
 			}
 			enqueue( tostep, wl);
