@@ -261,3 +261,46 @@ def test_money_rule_file_gpu():
     mt = Matcher()
     got = money_listing(Lexer(), mt, lambda lo: mt.visible_results(mt.run(lo["lexems"], lo["offsets"])))
     assert sorted(got) == sorted(MONEY_LISTING)
+
+
+def random_format(rng):
+    parts = []
+    for _ in range(int(rng.integers(1, 6))):
+        kind = int(rng.integers(0, 6))
+        if kind == 0:
+            parts.append("{%s}" % "abc"[int(rng.integers(0, 3))])
+        elif kind == 1:
+            parts.append("{ %s |%s}" % ("abc"[int(rng.integers(0, 3))], ("", ", ", "\\}", "|", " - ")[int(rng.integers(0, 5))]))
+        elif kind == 2:
+            parts.append(("\\{", "\\}", "\\\\", "|", " ", "x|y")[int(rng.integers(0, 6))])
+        elif kind == 3:
+            parts.append("{%s|}" % "abc"[int(rng.integers(0, 3))])
+        else:
+            parts.append("".join("lit-.:/"[int(rng.integers(0, 7))] for _ in range(int(rng.integers(1, 5)))))
+    return "".join(parts)
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3, 4])
+def test_random_format_strings_product_and_oracle_formatter_agree(seed):
+    """the two formatters (csrc/result_format.hpp, oracle shim) are written independently: random format strings with
+    escapes, separators (empty, with quoted braces, with '|') and blanks inside the braces give the same values."""
+    rng = np.random.default_rng(seed)
+    formats = [random_format(rng) for _ in range(40)]
+    ref, sim = RefMatcher(), HostSimMatcher(mode=0)
+    for m in (ref, sim):
+        for i, v in enumerate("abc"):
+            m.push_term(i + 1)
+            m.attach_variable(v)
+        m.push_expression(MC.OP_WITHIN, 3, 30, 0)
+        m.define_pattern("KnownVars", "", False)
+        for r, fmt in enumerate(formats):
+            terms = [int(t) for t in np.random.default_rng(seed * 100 + r).integers(1, 9, size=3)]
+            for i, t in enumerate(terms):
+                m.push_term(t)
+                m.attach_variable("abc"[(r + i) % 3] if i < 2 else "a")     # one variable twice: separators show
+            m.push_expression(MC.OP_WITHIN, 3, 6, 0)
+            m.define_pattern("R%d" % r, fmt, True)
+    toks, offs = MC.random_documents(seed + 300, 4, 150, 8, delim_prob=0.0)
+    docs = check(ref, sim, toks, offs, in_order=True)
+    values = [r[1] for d in docs for r in d if r[1] is not None]
+    assert len(values) > 20 and len(set(values)) > 10
