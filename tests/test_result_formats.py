@@ -304,3 +304,19 @@ def test_random_format_strings_product_and_oracle_formatter_agree(seed):
     docs = check(ref, sim, toks, offs, in_order=True)
     values = [r[1] for d in docs for r in d if r[1] is not None]
     assert len(values) > 20 and len(set(values)) > 10
+
+
+@pytest.mark.parametrize("nested", [True, False])
+def test_formats_with_the_exclusive_option(nested):
+    """`exclusive` drops results covered by others (src/patternMatcher.cpp:192-246) before the values are made; the rule set
+    runs on the state machine then."""
+    ref, sim = RefMatcher(), HostSimMatcher(mode=1)
+    for m in (ref, sim):
+        m.define_option("exclusive", 0.0)
+        m.define_option("maxResultSize", 30.0)
+        define_formatted_rules(m, 7, 80, 12, nested=nested)
+        m.compile()
+    assert sim.info("eval_capable") == 0
+    toks, offs = MC.random_documents(91, 6, 200, 12)
+    docs = check(ref, sim, toks, offs, in_order=True)
+    assert any(r[1] is not None for d in docs for r in d)
