@@ -22,7 +22,7 @@ struct sp_lexer_ctx
 	uint64_t nisl, nelem;
 	// last batch
 	uint32_t ndocs;
-	uint64_t total, nchunks, nev, nlex, fixups, rounds;
+	uint64_t total, nchunks, nev, nlex, fixups, rounds, readbacks;	// readbacks: k_read_back launches of the last scan
 	bool valid;
 	uint64_t* pinned;	// [4] host staging for scalar read backs
 	bool blockingSync;	// SP_BLOCKING_SYNC=1 or counter "sync:blocking": host threads sleep in waits instead of spinning (many contexts per host)
@@ -65,7 +65,7 @@ struct sp_lexer_ctx
 	}
 
 	sp_lexer_ctx( const sp_lexer* lx_, cudaStream_t stream_)
-		:lx(lx_),stream(stream_),chunk(512),warmup(96),ndocs(0),total(0),nchunks(0),nev(0),nlex(0),fixups(0),rounds(0),valid(false),pinned(0),blockingSync(false),syncEvent(0),profile(false),nspans(0)
+		:lx(lx_),stream(stream_),chunk(512),warmup(96),ndocs(0),total(0),nchunks(0),nev(0),nlex(0),fixups(0),rounds(0),readbacks(0),valid(false),pinned(0),blockingSync(false),syncEvent(0),profile(false),nspans(0)
 	{
 		std::memset( kernel_ms, 0, sizeof(kernel_ms)); std::memset( kernel_calls, 0, sizeof(kernel_calls));
 		if (std::getenv( "SP_LEXER_PROFILE")) profile = true;
@@ -112,6 +112,7 @@ struct sp_lexer_ctx
 	{
 		pinned[0] = 0;
 		readBackAsync( pinned, devptr, bytes, stream);
+		++readbacks;
 		SP_CUDA( waitStream());
 		return pinned[0];
 	}
@@ -184,6 +185,7 @@ struct sp_lexer_ctx
 		k_fused_docs<<<(ndocs + 1 + 255) / 256, 256, 0, stream>>>( F, d_scalars + 1);
 		spanEnd();
 		readBackAsync( pinned, d_scalars + 1, 2 * sizeof(uint64_t), stream);
+		++readbacks;
 		SP_CUDA( waitStream());
 		if ((uint32_t)pinned[1]) {++fused_fallbacks; return false;}
 		nlex = pinned[0] >> 32;
@@ -300,7 +302,7 @@ struct sp_lexer_ctx
 		ndocs = ndocs_;
 		total = ndocs ? doc_offsets[ ndocs] : 0;
 		nchunks = (total + chunk - 1) / chunk;
-		nev = nlex = fixups = rounds = 0;
+		nev = nlex = fixups = rounds = readbacks = 0;
 
 		SpScanParams P; std::memset( &P, 0, sizeof(P));
 		P.T = lx->dev;
@@ -456,11 +458,12 @@ int64_t sp_lexer_ctx_counter( sp_lexer_ctx* ctx, const char* key)
 	{
 		// count, verify (+2 per repair round), 3 scan, emit, finish; then the chosen second half
 		// fused: count, verify (+2 per repair round), 3 scan, fused, fix, 3 scan, docs, write
-		if (ctx->last_path == 3) return 1 + 1 + 2*(int64_t)ctx->rounds + 3 + 1 + 1 + 3 + 1 + 1;
+		// (+ the scalar read backs, one k_read_back launch each)
+		if (ctx->last_path == 3) return 1 + 1 + 2*(int64_t)ctx->rounds + 3 + 1 + 1 + 3 + 1 + 1 + (int64_t)ctx->readbacks;
 		// chunk resolution: count, verify, 3 scan, emit, finish, resolve, fix, 3 scan, docs, write
-		if (ctx->last_path == 4) return 1 + 1 + 2*(int64_t)ctx->rounds + 3 + 1 + 1 + 1 + 1 + 3 + 1 + 1;
+		if (ctx->last_path == 4) return 1 + 1 + 2*(int64_t)ctx->rounds + 3 + 1 + 1 + 1 + 1 + 3 + 1 + 1 + (int64_t)ctx->readbacks;
 		int64_t first = 1 + 1 + 2*(int64_t)ctx->rounds + 3 + 1 + 1;
-		return first + 8 + 2 + 2 + 2;
+		return first + 8 + 2 + 2 + 2 + (int64_t)ctx->readbacks;
 	}
 	return -1;
 }

@@ -73,6 +73,7 @@ struct sp_matcher_ctx
 	void readScalars( const void* devptr, std::size_t bytes)
 	{
 		readBackAsync( pinned, devptr, bytes, stream);
+		++launches;	// k_read_back
 		SP_CUDA( cudaStreamSynchronize( stream));
 	}
 
